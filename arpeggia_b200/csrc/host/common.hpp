@@ -1,0 +1,55 @@
+// Shared internals of the host side (not part of the ABI).
+#pragma once
+#include <cstdint>
+#include <cstring>
+#include <string>
+
+#include "arpeggia_cuda.h"
+#include "arpeggia_host.h"
+
+namespace arp {
+
+struct Error {
+  int code;
+  std::string msg;
+};
+
+// thread-local message behind arph_last_error() / arp_last_error(NULL)
+std::string& last_error();
+
+inline std::string fixed_field(const char* p, size_t cap) {
+  size_t n = 0;
+  while (n < cap && p[n] != '\0') ++n;
+  return std::string(p, n);
+}
+
+// ---- geometry (geometry.cpp) ----------------------------------------------------------------------
+struct Plane {
+  double c[3];
+  double n[3];
+};
+// center_and_normal, residues.rs:270-298.  pts = 3*n doubles (xyz interleaved). false when n < 3.
+bool fit_plane(const double* pts, int64_t n, Plane& out);
+double plane_point_dist(const Plane& p, const double pt[3]);           // residues.rs:31-35
+double plane_point_angle(const Plane& p, const double pt[3]);          // residues.rs:45-54
+double plane_dihedral(const double n1[3], const double n2[3]);         // residues.rs:65-75
+
+// Exact cosine-domain images of every angle comparison on the path.  The reference compares
+// acos(c).to_degrees() (optionally folded to <= 90) with a constant; acos is monotone, so each comparison
+// is equivalent to comparing c with a boundary double, found here once by bisection with the HOST libm.
+// The device then reproduces the host's decisions bit for bit without evaluating acos.
+struct AngleBounds {
+  // plain angle A(c) = deg(acos(c)), decreasing in c:  A >= T  <=>  c <= ge[T]  (and c >= -1)
+  double a_ge_90, a_ge_130, a_ge_60;
+  // A <= 120  <=>  c >= a_le_120  (and c <= 1)
+  double a_le_120;
+  // folded angle F(c) (residues.rs:49-53):  F <= T  <=>  c >= pos[T] (c in [0,1])  or  c <= neg[T] (c in [-1,0))
+  double f_le_30_pos, f_le_30_neg;
+  double f_le_60_pos, f_le_60_neg;
+  // F < T
+  double f_lt_30_pos, f_lt_30_neg;
+  double f_lt_60_pos, f_lt_60_neg;
+};
+const AngleBounds& angle_bounds();
+
+}  // namespace arp

@@ -1,0 +1,52 @@
+// Packed structure: device SoA + decode dictionaries (the thing behind the opaque arph_packed).
+#pragma once
+#include <set>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "common.hpp"
+
+namespace arp {
+
+struct Packed {
+  // device SoA (arp_structure points into these)
+  std::vector<double> x, y, z, hx, hy, hz, ring_c, ring_n;
+  std::vector<uint32_t> attr, chain_key, res_ordinal, res_id, res_h_begin, ring_attr, ring_chain_key, ring_res_ordinal;
+  std::vector<int32_t> res_cb, res_sg;
+  arp_structure s{};
+
+  // decode side: one ResConf per (residue, conformer) = one ResidueId of the reference (residues.rs:7-21)
+  struct ResConf {
+    int32_t chain, resn, icode, altloc;  // string ids
+    int64_t resi, model_serial;
+    bool has_sc;
+    Plane sc;  // build_sc_plane_positions, complex.rs:486-514
+  };
+  std::vector<ResConf> resconfs;
+  std::vector<uint32_t> atom_rc;     // per atom -> resconfs
+  std::vector<int32_t> atom_name;    // per atom -> strings
+  std::vector<int64_t> atom_serial;  // per atom
+  std::vector<uint32_t> ring_rc;     // per ring -> resconfs
+  int32_t ring_name = -1;            // id of "Ring"
+
+  std::vector<std::string> strings;
+  std::unordered_map<std::string, int32_t> string_ids;
+  std::vector<std::string> warnings;
+
+  int32_t intern(const std::string& s);
+  void finish();
+};
+
+void parse_groups(const std::set<std::string>& all, const std::string& groups, std::set<std::string>& lig, std::set<std::string>& rec);
+void pack_records(const arp_atom_record* recs, int64_t n, const std::string& groups, bool ignore_zero_occupancy, uint32_t flags,
+                  Packed& out);
+
+// rows (structure-local indices) -> sorted table; table.cpp
+struct TableStore;
+arph_table* build_table(const Packed& p, const arp_row* rows, int64_t n_rows);
+
+}  // namespace arp
+
+struct arph_packed;
+const arp::Packed& arph_packed_ref(const arph_packed* p);

@@ -1,0 +1,169 @@
+/*
+ * arpeggia_cuda.h -- C ABI of the B200 (sm_100a) contacts hot path: the drop-in boundary.
+ *
+ * This is what a Rust `arpeggia-cuda-sys` FFI crate (or cffi / ctypes) binds.  It replaces the three
+ * search loops of the reference's `Interactions` trait and everything they call:
+ *
+ *   arp_contacts()  <->  InteractionComplex::get_atomic_contacts   src/contacts/complex.rs:189-299
+ *                        InteractionComplex::get_ring_atom_contacts src/contacts/complex.rs:301-352
+ *                        InteractionComplex::get_ring_ring_contacts src/contacts/complex.rs:354-405
+ *                        (+ should_compare_entities/_residues        src/contacts/complex.rs:76-131,
+ *                           find_vdw_contact/is_disulfide            src/contacts/vdw.rs:19-80,
+ *                           find_ionic_bond/_repulsion               src/contacts/ionic.rs:11-35,
+ *                           find_hydrogen_bond/find_weak_hydrogen_bond src/contacts/hbond.rs:30-110,
+ *                           find_hydrophobic_contact                 src/contacts/hydrophobic.rs:10-24,
+ *                           find_cation_pi / find_pi_pi              src/contacts/aromatic.rs:14-64,
+ *                           pdbtbx create_hierarchy_rtree + rstar locate_within_distance)
+ *
+ * Plain pointers and sizes only; no C++/torch types.  Caller owns inputs (host memory, read-only for the
+ * duration of a call); the library owns outputs until arp_result_free / the next staged call.  Every
+ * function returns an arp_status; arp_last_error() gives the message.  Nothing throws or aborts across
+ * the ABI.  A context is NOT thread-safe: one context per (device, host thread).  There is no CPU
+ * fallback: without a CUDA device every compute entry point fails with ARP_ERR_CUDA.
+ */
+#ifndef ARPEGGIA_CUDA_H
+#define ARPEGGIA_CUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum arp_status {
+  ARP_OK = 0,
+  ARP_ERR_IO = 1,
+  ARP_ERR_BAD_GROUPS = 2,   /* utils.rs:77-80  "Invalid chain groups format! Use '/' for all-to-all comparisons." */
+  ARP_ERR_EMPTY_GROUP = 3,  /* utils.rs:109-112 "Empty chain groups!" */
+  ARP_ERR_NO_RINGS = 4,     /* complex.rs:50    "Error building ring positions" */
+  ARP_ERR_ELEMENT = 5,      /* vdw.rs:24-28 unwrap on element / van_der_waals */
+  ARP_ERR_NARROWING = 6,    /* mod.rs:142-178 u32 / i32 narrowing panics */
+  ARP_ERR_RESIDUE_NAME = 7, /* residues.rs:132 unwrap on Residue::name() */
+  ARP_ERR_ARG = 8,
+  ARP_ERR_CUDA = 9,
+  ARP_ERR_OOM = 10,
+  ARP_ERR_LIMIT = 11        /* > 2^31 atoms, > 2^32 cells, > 256 models, > 2^24 chains */
+} arp_status;
+
+/* Interaction labels: declaration order of `enum Interaction`, src/contacts/structs.rs:6-51. */
+typedef enum arp_label {
+  ARP_StericClash = 0, ARP_CovalentBond, ARP_Disulfide, ARP_VanDerWaalsContact, ARP_IonicBond,
+  ARP_HydrogenBond, ARP_WeakHydrogenBond, ARP_PolarContact, ARP_WeakPolarContact, ARP_IonicRepulsion,
+  ARP_SaltBridge, ARP_PiDisplacedStacking, ARP_PiTStacking, ARP_PiSandwichStacking,
+  ARP_PiParallelInPlaneStacking, ARP_PiTiltedStacking, ARP_PiLStacking, ARP_CationPi,
+  ARP_HydrophobicContact, ARP_N_LABELS
+} arp_label;
+const char* arp_label_name(int label); /* Display of Interaction, structs.rs:151-157 */
+
+/* ---- per-atom attribute word (arp_structure.attr) ------------------------------------------------ */
+#define ARP_ATTR_ELEM_MASK   0x0000000Fu /* element class, see arp_element_class(); 0 = hydrogen */
+#define ARP_ATTR_LIGAND      0x00000010u /* chain is in the ligand set   (utils.rs:71-115) */
+#define ARP_ATTR_RECEPTOR    0x00000020u /* chain is in the receptor set */
+#define ARP_ATTR_POS_CONF    0x00000040u /* is_pos_ionizable(conformer name, atom name)  ionic.rs:83-91 */
+#define ARP_ATTR_NEG_CONF    0x00000080u /* is_neg_ionizable(conformer name, atom name)  ionic.rs:94-99 */
+#define ARP_ATTR_POS_RES     0x00000100u /* is_pos_ionizable(residue name, atom name)    aromatic.rs:18 */
+#define ARP_ATTR_DONOR       0x00000200u /* is_hydrogen_donor    hbond.rs:162-181 */
+#define ARP_ATTR_ACCEPTOR    0x00000400u /* is_hydrogen_acceptor hbond.rs:137-159 */
+#define ARP_ATTR_WEAK_DONOR  0x00000800u /* element C and name != "C"  hbond.rs:204-207 */
+#define ARP_ATTR_HYDROPHOBIC 0x00001000u /* is_hydrophobic(residue name, atom name) hydrophobic.rs:27-45 */
+#define ARP_ATTR_CYS_SG      0x00002000u /* residue CYS, atom SG   vdw.rs:50-53 */
+#define ARP_ATTR_GHOST       0x00004000u /* halo copy owned by another slab/rank: takes part in every test but never
+                                            starts a row (the owner of the `from` atom / ring emits it) */
+
+/* Element class for an upper-case element symbol, or -1 when pdbtbx would have no van der Waals radius
+ * for it (the reference panics, vdw.rs:28).  Class 0 is hydrogen. */
+int arp_element_class(const char* symbol);
+/* covalent-single / van-der-Waals radius of a class (pdbtbx Element::atomic_radius) */
+int arp_element_radii(int element_class, double* covalent_single, double* van_der_waals);
+
+#define ARP_RING_FLAG 0x80000000u /* arp_row.from / .to: bit 31 set = ring index, else atom index */
+
+/* One structure as host SoA.  Atom arrays have n_atoms entries in atoms_with_hierarchy() order. */
+typedef struct arp_structure {
+  int64_t n_atoms, n_residues, n_rings, n_h;
+  const double* x;               /* angstrom, f64 exactly as parsed */
+  const double* y;
+  const double* z;
+  const uint32_t* attr;          /* ARP_ATTR_* */
+  const uint32_t* chain_key;     /* (model index << 24) | lexicographic rank of the chain id  (complex.rs:96,108,129) */
+  const uint32_t* res_ordinal;   /* position of the residue in its chain  (build_residue_index, complex.rs:411-440) */
+  const uint32_t* res_id;        /* index into the residue tables below */
+  const uint32_t* res_h_begin;   /* n_residues+1: CSR into h_* = every hydrogen of the residue (hbond.rs:38-42) */
+  const double* h_x;
+  const double* h_y;
+  const double* h_z;
+  const int32_t* res_cb;         /* n_residues: atom index of the first "CB" / first "SG" of the residue, or -1 */
+  const int32_t* res_sg;         /*             (is_disulfide, vdw.rs:55-74) */
+  const double* ring_center;     /* 3*n_rings, xyz interleaved  (build_ring_positions, complex.rs:442-484) */
+  const double* ring_normal;     /* 3*n_rings */
+  const uint32_t* ring_attr;     /* n_rings: ARP_ATTR_LIGAND / ARP_ATTR_RECEPTOR of the ring's chain */
+  const uint32_t* ring_chain_key;
+  const uint32_t* ring_res_ordinal;
+} arp_structure;
+
+#define ARP_FLAG_EMIT_RADIUS_SCREEN 0x1u /* screen atom pairs at min(dist_cutoff, largest distance at which any
+                                            label can fire) instead of dist_cutoff. Rows are identical;
+                                            pairs_in_cutoff is then not computed (reported as -1). */
+typedef struct arp_params {
+  double vdw_comp;     /* -c / vdw_comp   (cli/contacts.rs:37-39) */
+  double dist_cutoff;  /* -d / dist_cutoff (cli/contacts.rs:41-43) */
+  uint32_t flags;
+  uint32_t reserved_;
+} arp_params;
+
+/* One output row = one ResultEntry (structs.rs:73-85) before string decoding. 16 bytes. */
+typedef struct arp_row {
+  uint32_t from;       /* atom index within the job (batch: global over the concatenated structures) */
+  uint32_t to;
+  uint32_t label;      /* arp_label */
+  float distance;      /* (float) of the f64 distance, round-to-nearest-even == Rust `as f32` (mod.rs:148) */
+} arp_row;
+
+typedef struct arp_result {
+  int64_t n_rows;
+  const arp_row* rows;            /* host memory, UNSORTED (order is not deterministic) */
+  int64_t n_structures;
+  const int64_t* atom_begin;      /* n_structures+1: offsets of each structure's atoms in the job */
+  const int64_t* ring_begin;      /* n_structures+1 */
+  int64_t pairs_screened;         /* distance tests evaluated by the neighbour kernel (unordered candidate pairs) */
+  int64_t pairs_in_cutoff;        /* ordered pairs (from in ligand, non-H; to != from) with d^2 <= rc^2, or -1 */
+  int64_t pairs_classified;       /* ordered pairs that passed should_compare_entities */
+} arp_result;
+
+/* Device-side timings and sizes of the last job (CUDA events on the context's stream). */
+typedef struct arp_stats {
+  int64_t n_atoms, n_rings, n_cells, n_nonempty_cells, n_rows;
+  int64_t kernel_launches;        /* kernels of this library launched by the last run */
+  int32_t pair_kernel_retries;    /* re-runs because the row buffer was too small */
+  int32_t reserved_;
+  float ms_h2d, ms_grid, ms_pairs, ms_rings, ms_d2h, ms_run; /* ms_run = grid + pairs + rings */
+} arp_stats;
+
+typedef struct arp_ctx arp_ctx;
+
+int  arp_ctx_create(arp_ctx** out, int device_ordinal);
+void arp_ctx_destroy(arp_ctx* ctx);
+const char* arp_last_error(const arp_ctx* ctx); /* ctx may be NULL: error of the last failed create */
+void* arp_ctx_stream(arp_ctx* ctx);             /* the cudaStream_t every kernel is launched on (for event timing) */
+
+/* One-shot: host SoA in, host rows out (H2D, all kernels, D2H, stream-synchronised before return). */
+int  arp_contacts(arp_ctx* ctx, const arp_structure* s, const arp_params* p, arp_result** out);
+/* Many independent structures in one job; no pair ever spans two structures. */
+int  arp_contacts_batch(arp_ctx* ctx, const arp_structure* const* s, int64_t n, const arp_params* p, arp_result** out);
+void arp_result_free(arp_ctx* ctx, arp_result* r);
+
+/* Staged form of the same job, for pipelines that keep inputs resident in HBM:
+ * upload once, run any number of times (asynchronous on the stream), download the last run's rows. */
+int  arp_stage_upload(arp_ctx* ctx, const arp_structure* const* s, int64_t n);
+int  arp_stage_run(arp_ctx* ctx, const arp_params* p);
+int  arp_stage_download(arp_ctx* ctx, arp_result** out);
+int  arp_stage_stats(arp_ctx* ctx, arp_stats* out); /* synchronises the stream */
+
+/* Page-locked host memory for callers that want true asynchronous H2D/D2H (optional). */
+int  arp_host_alloc(void** out, int64_t bytes);
+void arp_host_free(void* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

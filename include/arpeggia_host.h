@@ -1,0 +1,101 @@
+/*
+ * arpeggia_host.h -- C ABI of the host side of the contacts path: what sits either side of arp_contacts().
+ *
+ * Mirrors the reference's host functions for this path (same argument meaning and error behaviour):
+ *
+ *   arph_parse_pdb        <->  pdbtbx ReadOptions{only_atomic_coords, Loose}.read()   src/utils.rs:53-57
+ *   arph_pack             <->  load_model residue filter                              src/utils.rs:60
+ *                              optional zero-occupancy filter                         src/python.rs:45-47
+ *                              InteractionComplex::new (parse_groups, build_residue_index,
+ *                              build_ring_positions, build_sc_plane_positions)        src/contacts/complex.rs:36-68, 411-514
+ *   arph_build_table      <->  results_to_df, collect_sc_stats, sc_results_to_df,
+ *                              concat + left join + 10-key sort                      src/contacts/mod.rs:79-214, complex.rs:137-174
+ *   arph_contacts[_file]  <->  get_contacts / arpeggia.contacts()                     src/contacts/mod.rs:61, src/python.rs:31-56
+ *
+ * The atom-record and table layouts are byte-identical to the oracle's (oracle/oracle.h) on purpose, so a
+ * test can hand the same buffers to both; the two code bases share no source.
+ */
+#ifndef ARPEGGIA_HOST_H
+#define ARPEGGIA_HOST_H
+
+#include <stdint.h>
+
+#include "arpeggia_cuda.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* One ATOM/HETATM record as a parser yields it. 96 bytes. */
+typedef struct arp_atom_record {
+  double  x, y, z;
+  double  occupancy;
+  int64_t serial;        /* atom serial number */
+  int64_t resi;          /* residue sequence number */
+  int64_t model;         /* model serial number; 0 when the file has no MODEL record */
+  char    chain[8];      /* NUL padded */
+  char    resn[8];
+  char    name[8];
+  char    element[4];    /* upper-case symbol, "" = unknown */
+  char    altloc[2];
+  char    icode[2];
+  uint8_t hetero;
+  uint8_t pad_[7];
+} arp_atom_record;
+
+/* The 20-column frame of get_contacts (mod.rs:111-136).  String columns are int32 indices into `strings`. */
+typedef struct arph_table {
+  int64_t n_rows;
+  uint32_t* model;
+  uint8_t*  interaction;           /* arp_label; the column value is arp_label_name(code) */
+  float*    distance;
+  int32_t  *from_chain, *from_resn, *from_resi, *from_insertion, *from_altloc, *from_atomn, *from_atomi;
+  int32_t  *to_chain,   *to_resn,   *to_resi,   *to_insertion,   *to_altloc,   *to_atomn,   *to_atomi;
+  float    *sc_centroid_dist, *sc_dihedral, *sc_centroid_angle;
+  uint8_t  *sc_valid;              /* 0 = the three sc_* values are null (left join miss, mod.rs:112-122) */
+  int32_t n_strings;
+  const char* const* strings;
+  int64_t n_atoms;
+  int64_t pairs_in_cutoff;
+  int64_t pairs_classified;
+  double  t_setup_s, t_search_s, t_classify_s, t_rings_s, t_table_s; /* pack, -, device run, -, table */
+} arph_table;
+
+#define ARPH_FLAG_NO_MULTIMODEL_QUIRK 1u /* do NOT reproduce complex.rs:447-449 (planes of every model = last model's) */
+#define ARPH_FLAG_SKIP_LOAD_FILTER    2u /* records are already restricted to the 20 amino acids + HOH */
+
+const char* arph_last_error(void);
+
+/* Fixed-column PDB reader (ATOM / HETATM / MODEL). *out is malloc'd; release with arph_free. */
+int  arph_parse_pdb(const char* path, arp_atom_record** out, int64_t* n);
+void arph_free(void* p);
+
+/* Packed structure: hierarchy + device SoA + the dictionaries needed to decode rows. */
+typedef struct arph_packed arph_packed;
+int  arph_pack(const arp_atom_record* atoms, int64_t n, const char* groups, int ignore_zero_occupancy,
+               uint32_t flags, arph_packed** out);
+const arp_structure* arph_packed_structure(const arph_packed* p);
+int64_t arph_packed_n_warnings(const arph_packed* p);           /* ring residues with < 3 ring atoms (mod.rs:64-68) */
+const char* arph_packed_warning(const arph_packed* p, int64_t i);
+void arph_packed_free(arph_packed* p);
+
+/* rows (structure-local atom / ring indices) -> sorted 20-column table. */
+int  arph_build_table(const arph_packed* p, const arp_row* rows, int64_t n_rows, arph_table** out);
+void arph_table_free(arph_table* t);
+
+/* get_contacts: pack -> arp_contacts -> table. */
+int  arph_contacts(arp_ctx* ctx, const arp_atom_record* atoms, int64_t n, const char* groups, double vdw_comp,
+                   double dist_cutoff, int ignore_zero_occupancy, uint32_t flags, arph_table** out);
+int  arph_contacts_file(arp_ctx* ctx, const char* path, const char* groups, double vdw_comp, double dist_cutoff,
+                        int ignore_zero_occupancy, uint32_t flags, arph_table** out);
+
+/* Plane helpers (residues.rs:31-75, 270-298), exposed for the known-answer tests. */
+int    arph_plane_fit(const double* xyz, int64_t n_points, double center[3], double normal[3]);
+double arph_plane_point_angle(const double center[3], const double normal[3], const double point[3]);
+double arph_plane_dihedral(const double n1[3], const double n2[3]);
+int    arph_parse_groups(const char* chains_csv, const char* groups, char* ligand_out, char* receptor_out, int64_t cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
