@@ -1,0 +1,262 @@
+"""Host-side objects over the C ABI: parsed atom records, packed structures, device contexts, result tables.
+
+Mirrors the reference's host flow for the contacts path (src/python.rs:31-56, src/contacts/mod.rs:61-136):
+load -> (zero-occupancy filter) -> pack -> device search + classification -> 20-column table.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+import numpy as np
+
+from . import _lib
+from ._lib import ATOM_DTYPE, LABELS, ROW_DTYPE, ArpeggiaError, Params, Result, Stats, Structure, Table, check, lib
+
+STRING_COLS = ("chain", "resn", "insertion", "altloc", "atomn")
+COLUMNS = (
+    ["model", "interaction", "distance"]
+    + [f"from_{c}" for c in ("chain", "resn", "resi", "insertion", "altloc", "atomn", "atomi")]
+    + [f"to_{c}" for c in ("chain", "resn", "resi", "insertion", "altloc", "atomn", "atomi")]
+    + ["sc_centroid_dist", "sc_dihedral", "sc_centroid_angle"]
+)
+
+
+def parse_pdb(path) -> np.ndarray:
+    """ATOM/HETATM records of a PDB file as a structured array (ATOM_DTYPE)."""
+    L = lib()
+    p = C.c_void_p()
+    n = C.c_int64()
+    check(L.arph_parse_pdb(os.fspath(path).encode(), C.byref(p), C.byref(n)))
+    try:
+        if n.value == 0:
+            return np.zeros(0, dtype=ATOM_DTYPE)
+        buf = (C.c_char * (n.value * ATOM_DTYPE.itemsize)).from_address(p.value)
+        return np.frombuffer(bytes(buf), dtype=ATOM_DTYPE).copy()
+    finally:
+        L.arph_free(p)
+
+
+def load_atoms(path) -> np.ndarray:
+    """pdbtbx-style dispatch on the file extension (src/utils.rs:51-57)."""
+    ext = os.path.splitext(os.fspath(path))[1].lower()
+    if ext in (".cif", ".mmcif"):
+        from .mmcif import parse_mmcif
+
+        return parse_mmcif(path)
+    return parse_pdb(path)
+
+
+class Packed:
+    """arph_packed: device SoA + decode dictionaries for one structure."""
+
+    def __init__(self, atoms: np.ndarray, groups: str = "/", ignore_zero_occupancy: bool = False, flags: int = 0):
+        L = lib()
+        self._atoms = np.ascontiguousarray(atoms, dtype=ATOM_DTYPE)
+        self._h = C.c_void_p()
+        check(L.arph_pack(self._atoms.ctypes.data, len(self._atoms), groups.encode(), int(ignore_zero_occupancy), flags,
+                          C.byref(self._h)))
+
+    @property
+    def structure(self) -> Structure:
+        return lib().arph_packed_structure(self._h).contents
+
+    @property
+    def structure_ptr(self):
+        return lib().arph_packed_structure(self._h)
+
+    @property
+    def warnings(self) -> list[str]:
+        L = lib()
+        return [L.arph_packed_warning(self._h, i).decode() for i in range(L.arph_packed_n_warnings(self._h))]
+
+    def arrays(self) -> dict:
+        """numpy views of the SoA (valid while this object lives)."""
+        s = self.structure
+        out = {"n_atoms": s.n_atoms, "n_residues": s.n_residues, "n_rings": s.n_rings, "n_h": s.n_h}
+
+        def view(ptr, n, dt):
+            return np.ctypeslib.as_array(ptr, shape=(n,)).view(dt) if n else np.zeros(0, dtype=dt)
+
+        for k in ("x", "y", "z"):
+            out[k] = view(getattr(s, k), s.n_atoms, np.float64)
+        for k in ("attr", "chain_key", "res_ordinal", "res_id"):
+            out[k] = view(getattr(s, k), s.n_atoms, np.uint32)
+        out["res_h_begin"] = view(s.res_h_begin, s.n_residues + 1, np.uint32)
+        for k in ("res_cb", "res_sg"):
+            out[k] = view(getattr(s, k), s.n_residues, np.int32)
+        for k in ("ring_center", "ring_normal"):
+            out[k] = view(getattr(s, k), 3 * s.n_rings, np.float64).reshape(-1, 3)
+        for k in ("ring_attr", "ring_chain_key", "ring_res_ordinal"):
+            out[k] = view(getattr(s, k), s.n_rings, np.uint32)
+        return out
+
+    def build_table(self, rows: np.ndarray) -> dict:
+        L = lib()
+        rows = np.ascontiguousarray(rows, dtype=ROW_DTYPE)
+        tp = C.POINTER(Table)()
+        check(L.arph_build_table(self._h, rows.ctypes.data, len(rows), C.byref(tp)))
+        try:
+            return read_table(tp.contents)
+        finally:
+            L.arph_table_free(tp)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().arph_packed_free(self._h)
+            self._h = None
+
+    __del__ = close
+
+
+def read_table(t: Table) -> dict:
+    """Copy an arph_table into numpy arrays (string columns as object arrays)."""
+    n = t.n_rows
+    strings = np.array([t.strings[i].decode() for i in range(t.n_strings)] + [""], dtype=object)
+
+    def arr(ptr, dt):
+        return np.ctypeslib.as_array(ptr, shape=(n,)).astype(dt, copy=True) if n else np.zeros(0, dtype=dt)
+
+    out = {"n_rows": n, "model": arr(t.model, np.uint32)}
+    code = arr(t.interaction, np.uint8)
+    out["interaction_code"] = code
+    out["interaction"] = np.array(LABELS, dtype=object)[code] if n else np.zeros(0, dtype=object)
+    out["distance"] = arr(t.distance, np.float32)
+    for side in ("from", "to"):
+        for c in ("chain", "resn", "resi", "insertion", "altloc", "atomn", "atomi"):
+            v = arr(getattr(t, f"{side}_{c}"), np.int32)
+            out[f"{side}_{c}"] = strings[v] if c in STRING_COLS else v
+    out["sc_valid"] = arr(t.sc_valid, np.uint8).astype(bool)
+    for c in ("sc_centroid_dist", "sc_dihedral", "sc_centroid_angle"):
+        out[c] = arr(getattr(t, c), np.float32)
+    for c in ("n_atoms", "pairs_in_cutoff", "pairs_classified", "t_setup_s", "t_classify_s", "t_table_s"):
+        out[c] = getattr(t, c)
+    return out
+
+
+class Context:
+    """arp_ctx: one per (device, host thread).  Creating it without a CUDA device raises ArpeggiaError."""
+
+    def __init__(self, device: int = 0):
+        L = lib()
+        self._h = C.c_void_p()
+        check(L.arp_ctx_create(C.byref(self._h), device))
+        self.device = device
+
+    @property
+    def stream(self) -> int:
+        """cudaStream_t (as int) every kernel of this context is launched on."""
+        return lib().arp_ctx_stream(self._h) or 0
+
+    # ---- one-shot ---------------------------------------------------------------------------------
+    def contacts_rows(self, structures, vdw_comp=0.1, dist_cutoff=6.5, flags=0) -> dict:
+        """arp_contacts / arp_contacts_batch on Packed structures (or raw Structure pointers) -> raw rows."""
+        L = lib()
+        if isinstance(structures, Packed):
+            structures = [structures]
+        ptrs = (C.POINTER(Structure) * len(structures))(*[s.structure_ptr if isinstance(s, Packed) else s for s in structures])
+        prm = Params(vdw_comp, dist_cutoff, flags, 0)
+        rp = C.POINTER(Result)()
+        check(L.arp_contacts_batch(self._h, ptrs, len(structures), C.byref(prm), C.byref(rp)), self._h)
+        try:
+            return _read_result(rp.contents)
+        finally:
+            L.arp_result_free(self._h, rp)
+
+    def contacts_table(self, atoms: np.ndarray, groups="/", vdw_comp=0.1, dist_cutoff=6.5, ignore_zero_occupancy=False,
+                       flags=0) -> dict:
+        """arph_contacts: get_contacts on atom records -> sorted 20-column table (dict of numpy arrays)."""
+        L = lib()
+        atoms = np.ascontiguousarray(atoms, dtype=ATOM_DTYPE)
+        tp = C.POINTER(Table)()
+        check(L.arph_contacts(self._h, atoms.ctypes.data, len(atoms), groups.encode(), vdw_comp, dist_cutoff,
+                              int(ignore_zero_occupancy), flags, C.byref(tp)))
+        try:
+            return read_table(tp.contents)
+        finally:
+            L.arph_table_free(tp)
+
+    # ---- staged -------------------------------------------------------------------------------------
+    def upload(self, structures):
+        if isinstance(structures, Packed):
+            structures = [structures]
+        self._keep = structures  # host arrays must stay alive during the call only, but keep refs anyway
+        ptrs = (C.POINTER(Structure) * len(structures))(*[s.structure_ptr if isinstance(s, Packed) else s for s in structures])
+        check(lib().arp_stage_upload(self._h, ptrs, len(structures)), self._h)
+
+    def run(self, vdw_comp=0.1, dist_cutoff=6.5, flags=0):
+        prm = Params(vdw_comp, dist_cutoff, flags, 0)
+        check(lib().arp_stage_run(self._h, C.byref(prm)), self._h)
+
+    def download(self) -> dict:
+        L = lib()
+        rp = C.POINTER(Result)()
+        check(L.arp_stage_download(self._h, C.byref(rp)), self._h)
+        try:
+            return _read_result(rp.contents)
+        finally:
+            L.arp_result_free(self._h, rp)
+
+    def stats(self) -> dict:
+        st = Stats()
+        check(lib().arp_stage_stats(self._h, C.byref(st)), self._h)
+        return {k: getattr(st, k) for k, _ in Stats._fields_ if k != "reserved_"}
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().arp_ctx_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+
+def _read_result(r: Result) -> dict:
+    n = r.n_rows
+    if n:
+        buf = (C.c_char * (n * ROW_DTYPE.itemsize)).from_address(r.rows)
+        rows = np.frombuffer(buf, dtype=ROW_DTYPE).copy()
+    else:
+        rows = np.zeros(0, dtype=ROW_DTYPE)
+    ns = r.n_structures
+    return {
+        "rows": rows,
+        "atom_begin": np.ctypeslib.as_array(r.atom_begin, shape=(ns + 1,)).copy(),
+        "ring_begin": np.ctypeslib.as_array(r.ring_begin, shape=(ns + 1,)).copy(),
+        "pairs_screened": r.pairs_screened,
+        "pairs_in_cutoff": r.pairs_in_cutoff,
+        "pairs_classified": r.pairs_classified,
+    }
+
+
+def split_rows(result: dict) -> list[np.ndarray]:
+    """Rows of a batch job -> one array per structure with structure-local atom / ring indices."""
+    rows, ab, rb = result["rows"], result["atom_begin"], result["ring_begin"]
+    is_ring_f = (rows["from"] & _lib.RING_FLAG) != 0
+    idx_f = (rows["from"] & ~np.uint32(_lib.RING_FLAG)).astype(np.int64)
+    s = np.where(is_ring_f, np.searchsorted(rb, idx_f, side="right") - 1, np.searchsorted(ab, idx_f, side="right") - 1)
+    out = []
+    order = np.argsort(s, kind="stable")
+    bounds = np.searchsorted(s[order], np.arange(len(ab)))
+    for k in range(len(ab) - 1):
+        part = rows[order[bounds[k]:bounds[k + 1]]].copy()
+        for col in ("from", "to"):
+            ring = (part[col] & _lib.RING_FLAG) != 0
+            v = (part[col] & ~np.uint32(_lib.RING_FLAG)).astype(np.int64)
+            v = np.where(ring, v - rb[k], v - ab[k]).astype(np.uint32)
+            part[col] = np.where(ring, v | np.uint32(_lib.RING_FLAG), v)
+        out.append(part)
+    return out
+
+
+_default = threading.local()
+
+
+def default_context(device: int = 0) -> Context:
+    """Per-thread cached context for the convenience API."""
+    cache = getattr(_default, "ctx", None)
+    if cache is None:
+        cache = _default.ctx = {}
+    if device not in cache:
+        cache[device] = Context(device)
+    return cache[device]

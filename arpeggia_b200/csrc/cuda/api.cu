@@ -1,0 +1,257 @@
+// C ABI of the device path (include/arpeggia_cuda.h): context, staged upload / run / download, one-shot calls.
+// sm_100a only; every kernel of the job is launched on the context's own stream.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <type_traits>
+#include <vector>
+
+#include "../host/common.hpp"
+#include "grid_kernels.cuh"
+#include "pair_kernel.cuh"
+#include "ring_kernels.cuh"
+
+using namespace arpd;
+
+namespace {
+
+struct CudaFail {
+  int code;
+  std::string msg;
+};
+
+#define CK(call)                                                                                         \
+  do {                                                                                                   \
+    cudaError_t e_ = (call);                                                                             \
+    if (e_ != cudaSuccess)                                                                               \
+      throw CudaFail{e_ == cudaErrorMemoryAllocation ? ARP_ERR_OOM : ARP_ERR_CUDA,                       \
+                     std::string(#call) + ": " + cudaGetErrorString(e_)};                                \
+  } while (0)
+
+// grow-only device / pinned-host buffers
+template <class T>
+struct DBuf {
+  T* p = nullptr;
+  size_t cap = 0;
+  void need(size_t n) {
+    if (n <= cap) return;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    const size_t want = n + n / 8 + 64;
+    CK(cudaMalloc((void**)&p, want * sizeof(T)));
+    cap = want;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+template <class T>
+struct HBuf {
+  T* p = nullptr;
+  size_t cap = 0;
+  void need(size_t n) {
+    if (n <= cap) return;
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+    const size_t want = n + n / 8 + 64;
+    CK(cudaMallocHost((void**)&p, want * sizeof(T)));
+    cap = want;
+  }
+  void release() {
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+
+}  // namespace
+
+struct arp_ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  std::string err;
+
+  // job inputs in HBM (original order)
+  int64_t n_struct = 0, n_atoms = 0, n_res = 0, n_rings = 0, n_h = 0;
+  DBuf<double> x, y, z, hx, hy, hz, ring_c, ring_n;
+  DBuf<uint32_t> attr, chain_key, res_ordinal, res_id, res_h_begin, ring_attr, ring_chain_key, ring_res_ordinal;
+  DBuf<int32_t> res_cb, res_sg;
+  DBuf<uint32_t> atom_struct, ring_struct;
+  DBuf<StructDesc> descs;
+  std::vector<StructDesc> h_descs;
+  std::vector<int64_t> atom_begin, ring_begin;
+
+  // cell lists and sorted records
+  DBuf<unsigned long long> bbox;
+  DBuf<uint32_t> cell_of, rank_of, cell_start, tile_sums, perm, res_sorted;
+  DBuf<uint32_t> rcell_of, rrank_of, rcell_start, rperm;
+  DBuf<RecA> recA;
+  DBuf<RecB> recB;
+  DBuf<uint2> items;
+  DBuf<Counters> ctr;
+  DBuf<arp_row> rows;
+  uint64_t row_cap = 0;
+  int64_t n_cells = 0, n_rcells = 0;
+
+  // host staging
+  HBuf<unsigned long long> h_bbox;
+  HBuf<Counters> h_ctr;
+  HBuf<unsigned char> stage;  // concatenation buffer for batch uploads
+  HBuf<arp_row> h_rows;       // result rows (library-owned, reused by the next download)
+
+  // bookkeeping of the last run
+  bool have_job = false, have_run = false;
+  arp_params last_params{};
+  DevParams dp{};
+  cudaEvent_t ev[8] = {};
+  int64_t launches = 0;
+  int retries = 0;
+  float ms_h2d = 0.f, ms_d2h = 0.f;
+};
+
+namespace {
+
+int fail(arp_ctx* c, int code, const std::string& msg) {
+  if (c) c->err = msg;
+  arp::last_error() = msg;
+  return code;
+}
+
+template <class F>
+int guarded(arp_ctx* c, F&& f) {
+  try {
+    f();
+    return ARP_OK;
+  } catch (const CudaFail& e) {
+    return fail(c, e.code, e.msg);
+  } catch (const arp::Error& e) {
+    return fail(c, e.code, e.msg);
+  } catch (const std::exception& e) {
+    return fail(c, ARP_ERR_OOM, e.what());
+  }
+}
+
+// Concatenate one array of every structure into device memory.  `adjust(s)` is added to every element of
+// structure s (index arrays that point into the concatenated job).  n == 1: straight from the caller's memory.
+template <class T, class GetPtr, class GetLen>
+void upload_concat(arp_ctx* c, DBuf<T>& dst, const arp_structure* const* s, int64_t n, GetPtr ptr, GetLen len, size_t extra_tail,
+                   const std::vector<int64_t>* adjust, bool skip_negative) {
+  size_t total = extra_tail;
+  for (int64_t k = 0; k < n; ++k) total += (size_t)len(s[k]);
+  dst.need(std::max<size_t>(total, 1));
+  if (total == 0) return;
+  if (n == 1 && !adjust) {
+    if (len(s[0])) CK(cudaMemcpyAsync(dst.p, ptr(s[0]), (size_t)len(s[0]) * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+    return;
+  }
+  // the staging buffer is reused by the next array: wait until the previous copy has left it
+  CK(cudaStreamSynchronize(c->stream));
+  c->stage.need(total * sizeof(T));
+  T* h = reinterpret_cast<T*>(c->stage.p);
+  size_t off = 0;
+  for (int64_t k = 0; k < n; ++k) {
+    const size_t m = (size_t)len(s[k]);
+    const T* src = ptr(s[k]);
+    if (adjust && (*adjust)[k] != 0) {
+      const T add = (T)(*adjust)[k];
+      for (size_t i = 0; i < m; ++i) h[off + i] = (skip_negative && (int64_t)src[i] < 0 && std::is_signed<T>::value) ? src[i] : (T)(src[i] + add);
+    } else if (m) {
+      std::memcpy(h + off, src, m * sizeof(T));
+    }
+    off += m;
+  }
+  CK(cudaMemcpyAsync(dst.p, h, off * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+}
+
+void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
+  CK(cudaSetDevice(c->device));
+  if (n < 1) throw arp::Error{ARP_ERR_ARG, "a job needs at least one structure"};
+  c->have_job = c->have_run = false;
+  c->atom_begin.assign(n + 1, 0);
+  c->ring_begin.assign(n + 1, 0);
+  std::vector<int64_t> res_begin(n + 1, 0), h_begin(n + 1, 0);
+  for (int64_t k = 0; k < n; ++k) {
+    if (!s[k]) throw arp::Error{ARP_ERR_ARG, "null structure"};
+    c->atom_begin[k + 1] = c->atom_begin[k] + s[k]->n_atoms;
+    c->ring_begin[k + 1] = c->ring_begin[k] + s[k]->n_rings;
+    res_begin[k + 1] = res_begin[k] + s[k]->n_residues;
+    h_begin[k + 1] = h_begin[k] + s[k]->n_h;
+  }
+  c->n_struct = n;
+  c->n_atoms = c->atom_begin[n];
+  c->n_rings = c->ring_begin[n];
+  c->n_res = res_begin[n];
+  c->n_h = h_begin[n];
+  if (c->n_atoms >= ((int64_t)1 << 31) || c->n_rings >= ((int64_t)1 << 31) || c->n_h >= ((int64_t)1 << 32))
+    throw arp::Error{ARP_ERR_LIMIT, "job exceeds 2^31 atoms / rings"};
+
+  CK(cudaEventRecord(c->ev[0], c->stream));
+  auto nat = [](const arp_structure* t) { return t->n_atoms; };
+  auto nrs = [](const arp_structure* t) { return t->n_residues; };
+  auto nrg = [](const arp_structure* t) { return t->n_rings; };
+  auto nrg3 = [](const arp_structure* t) { return 3 * t->n_rings; };
+  auto nh = [](const arp_structure* t) { return t->n_h; };
+#define UP(buf, field, lenf) upload_concat(c, c->buf, s, n, [](const arp_structure* t) { return t->field; }, lenf, 0, nullptr, false)
+  UP(x, x, nat);
+  UP(y, y, nat);
+  UP(z, z, nat);
+  UP(attr, attr, nat);
+  UP(chain_key, chain_key, nat);
+  UP(res_ordinal, res_ordinal, nat);
+  UP(hx, h_x, nh);
+  UP(hy, h_y, nh);
+  UP(hz, h_z, nh);
+  UP(ring_c, ring_center, nrg3);
+  UP(ring_n, ring_normal, nrg3);
+  UP(ring_attr, ring_attr, nrg);
+  UP(ring_chain_key, ring_chain_key, nrg);
+  UP(ring_res_ordinal, ring_res_ordinal, nrg);
+#undef UP
+  std::vector<int64_t> res_adj(res_begin.begin(), res_begin.end() - 1), atom_adj(c->atom_begin.begin(), c->atom_begin.end() - 1),
+      h_adj(h_begin.begin(), h_begin.end() - 1);
+  const bool multi = n > 1;
+  upload_concat(c, c->res_id, s, n, [](const arp_structure* t) { return t->res_id; }, nat, 0, multi ? &res_adj : nullptr, false);
+  upload_concat(c, c->res_cb, s, n, [](const arp_structure* t) { return t->res_cb; }, nrs, 0, multi ? &atom_adj : nullptr, true);
+  upload_concat(c, c->res_sg, s, n, [](const arp_structure* t) { return t->res_sg; }, nrs, 0, multi ? &atom_adj : nullptr, true);
+  // res_h_begin: n_res + 1 entries; each structure contributes its first n_residues offsets, the tail closes the CSR
+  upload_concat(c, c->res_h_begin, s, n, [](const arp_structure* t) { return t->res_h_begin; }, nrs, 1, multi ? &h_adj : nullptr, false);
+  {
+    const uint32_t tail = (uint32_t)c->n_h;
+    CK(cudaStreamSynchronize(c->stream));
+    c->stage.need(64);
+    std::memcpy(c->stage.p, &tail, 4);
+    CK(cudaMemcpyAsync(c->res_h_begin.p + c->n_res, c->stage.p, 4, cudaMemcpyHostToDevice, c->stream));
+  }
+  // structure descriptors (grids are filled in by the run, they depend on the cutoff)
+  c->h_descs.assign(n, StructDesc{});
+  for (int64_t k = 0; k < n; ++k) {
+    c->h_descs[k].atom_begin = (uint32_t)c->atom_begin[k];
+    c->h_descs[k].atom_end = (uint32_t)c->atom_begin[k + 1];
+    c->h_descs[k].ring_begin = (uint32_t)c->ring_begin[k];
+    c->h_descs[k].ring_end = (uint32_t)c->ring_begin[k + 1];
+  }
+  c->descs.need(n);
+  CK(cudaStreamSynchronize(c->stream));
+  CK(cudaMemcpyAsync(c->descs.p, c->h_descs.data(), n * sizeof(StructDesc), cudaMemcpyHostToDevice, c->stream));
+  if (multi) {
+    c->atom_struct.need(std::max<int64_t>(c->n_atoms, 1));
+    c->ring_struct.need(std::max<int64_t>(c->n_rings, 1));
+    k_fill_struct<<<(unsigned)n, 256, 0, c->stream>>>(c->descs.p, c->atom_struct.p, c->ring_struct.p);
+    CK(cudaGetLastError());
+  }
+  CK(cudaEventRecord(c->ev[1], c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  CK(cudaEventElapsedTime(&c->ms_h2d, c->ev[0], c->ev[1]));
+  c->have_job = true;
+}
+
+}  // namespace
+
+#include "api_run.inc"

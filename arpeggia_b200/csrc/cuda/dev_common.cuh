@@ -1,0 +1,127 @@
+// Device-side data layout shared by the kernels and the C-ABI glue (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "arpeggia_cuda.h"
+
+namespace arpd {
+
+// Per structure of a job: atom grid (edge = screening radius) and ring-centroid grid (edge = 6.0 A).
+struct StructDesc {
+  double ox, oy, oz;       // grid origin = bounding-box minimum of the structure's atoms
+  int nx, ny, nz;          // atom grid
+  int rnx, rny, rnz;       // ring-centroid grid
+  uint32_t cell_base;      // first cell id of this structure in the job-wide cell arrays
+  uint32_t rcell_base;
+  uint32_t atom_begin, atom_end;
+  uint32_t ring_begin, ring_end;
+};
+
+// Sorted (by cell) atom records.
+// RecA: what the screen reads: origin-relative f32 position + attribute word.  16 B -> one LDG.128 / LDS.128.
+// RecB: what the exact test reads: f64 position + chain key + residue ordinal.  32 B = one sector.
+struct __align__(16) RecA {
+  float x, y, z;
+  uint32_t attr;
+};
+struct __align__(32) RecB {
+  double x, y, z;
+  uint32_t chain_key;
+  uint32_t res_ordinal;
+};
+
+// Cosine-domain images of the angle comparisons (host-computed, see host/geometry.cpp).
+struct DevAngles {
+  double a_ge_90, a_ge_130, a_ge_60, a_le_120;
+  double f_le_30_pos, f_le_30_neg, f_le_60_pos, f_le_60_neg;
+  double f_lt_30_pos, f_lt_30_neg, f_lt_60_pos, f_lt_60_neg;
+};
+
+// Everything a kernel needs that is not a pointer; passed by value (constant bank).
+struct DevParams {
+  double rc2;            // dist_cutoff * dist_cutoff                      (complex.rs:191)
+  double comp;           // vdw_comp
+  double cov[16];        // covalent-single radius per element class       (vdw.rs:24-27)
+  double vdw[16];        // van der Waals radius per element class         (vdw.rs:28)
+  double emit_d2_max;    // no label can fire beyond this squared distance (conservative)
+  double inv_edge;       // 1 / atom-grid cell edge
+  double inv_redge;      // 1 / ring-grid cell edge
+  float rc2_screen;      // f32 pre-screen threshold = r_screen^2 + guard
+  uint32_t flags;        // ARP_FLAG_*
+  int count_in_cutoff;   // 1: screening radius == dist_cutoff, pairs_in_cutoff is counted
+  int n_struct;
+  DevAngles ang;
+};
+
+// job-wide counters, one cache line each to keep the atomics apart
+struct Counters {
+  unsigned long long rows;        uint64_t pad0[15];
+  unsigned long long screened;    uint64_t pad1[15];
+  unsigned long long in_cutoff;   uint64_t pad2[15];
+  unsigned long long classified;  uint64_t pad3[15];
+  unsigned int work;              uint32_t padw[31];   // work-item cursor of the persistent pair kernel
+  unsigned int n_items;           uint32_t padi[31];   // non-empty cells
+  unsigned int error;             uint32_t pade[31];   // 1 = CYS residue without CB / SG (vdw.rs:58 unwrap)
+};
+
+struct PairArgs {
+  const RecA* recA;
+  const RecB* recB;
+  const uint32_t* perm;        // sorted slot -> job-global atom index
+  const uint32_t* res_sorted;  // sorted slot -> job-global residue id
+  const uint32_t* cell_start;  // n_cells + 1
+  const uint2* items;          // non-empty cells: (cell id, structure)
+  const StructDesc* descs;
+  // original-order arrays (gathers for disulfide / hydrogen lists)
+  const double* x;
+  const double* y;
+  const double* z;
+  const int32_t* res_cb;
+  const int32_t* res_sg;
+  const uint32_t* res_h_begin;
+  const double* hx;
+  const double* hy;
+  const double* hz;
+  arp_row* rows;
+  unsigned long long row_cap;
+  Counters* ctr;
+};
+
+struct RingArgs {
+  const double* center;        // 3 * n_rings
+  const double* normal;
+  const uint32_t* attr;
+  const uint32_t* chain_key;
+  const uint32_t* res_ordinal;
+  const uint32_t* ring_struct;  // nullptr when the job has one structure
+  uint32_t n_rings;
+  // ring-centroid cell list
+  const uint32_t* rcell_start;
+  const uint32_t* rperm;        // sorted slot -> ring index
+  // atom cell list
+  const RecA* recA;
+  const RecB* recB;
+  const uint32_t* perm;
+  const uint32_t* cell_start;
+  const StructDesc* descs;
+  arp_row* rows;
+  unsigned long long row_cap;
+  Counters* ctr;
+};
+
+// ---- exact FP64 helpers: every operation individually rounded (no FMA contraction), the order the reference uses ----
+__device__ __forceinline__ double dsub(double a, double b) { return __dsub_rn(a, b); }
+__device__ __forceinline__ double dadd(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ double dmul(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double dot3(double ax, double ay, double az, double bx, double by, double bz) {
+  return dadd(dadd(dmul(ax, bx), dmul(ay, by)), dmul(az, bz));
+}
+__device__ __forceinline__ double norm3(double ax, double ay, double az) { return __dsqrt_rn(dot3(ax, ay, az, ax, ay, az)); }
+
+// folded angle <= 30 / <= 60 / < 30 / < 60 in the cosine domain; |c| > 1 and NaN give false like acos -> NaN
+__device__ __forceinline__ bool fold_pred(double c, double pos, double neg) {
+  return (c >= pos && c <= 1.0) || (c <= neg && c >= -1.0);
+}
+
+}  // namespace arpd

@@ -1,0 +1,229 @@
+// Cell-list build for sm_100a: bounding boxes -> cell id + in-cell rank (one atomic per atom) -> exclusive scan
+// of the cell counts -> scatter into cell-sorted records.  This is a single-digit radix (counting) sort with
+// radix = number of cells: two passes over the atoms and one scan over the cells, no key/value ping-pong.
+// Replaces pdbtbx create_hierarchy_rtree (rstar bulk load), src/contacts/complex.rs:190 and :302.
+#pragma once
+#include "dev_common.cuh"
+
+namespace arpd {
+
+// ---- order-preserving u64 encoding of doubles, for atomicMin / atomicMax --------------------------------
+__device__ __forceinline__ unsigned long long enc_f64(double d) {
+  unsigned long long b = (unsigned long long)__double_as_longlong(d);
+  return (b & 0x8000000000000000ull) ? ~b : (b | 0x8000000000000000ull);
+}
+static inline double dec_f64_host(unsigned long long e) {
+  unsigned long long b = (e & 0x8000000000000000ull) ? (e & 0x7fffffffffffffffull) : ~e;
+  double d;
+  memcpy(&d, &b, 8);
+  return d;
+}
+
+// bbox[s*6 + 0..2] = min xyz (encoded), [3..5] = max xyz (encoded)
+__global__ void k_bbox_init(unsigned long long* bbox, int n_struct) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_struct * 6) bbox[i] = (i % 6) < 3 ? ~0ull : 0ull;
+}
+
+// one CTA per structure of the job writes the structure id of its atoms / rings (batch jobs only)
+__global__ void k_fill_struct(const StructDesc* __restrict__ descs, uint32_t* __restrict__ atom_struct,
+                              uint32_t* __restrict__ ring_struct) {
+  const StructDesc d = descs[blockIdx.x];
+  for (uint32_t a = d.atom_begin + threadIdx.x; a < d.atom_end; a += blockDim.x) atom_struct[a] = blockIdx.x;
+  for (uint32_t r = d.ring_begin + threadIdx.x; r < d.ring_end; r += blockDim.x) ring_struct[r] = blockIdx.x;
+}
+
+// Bounding boxes.  Each CTA reads BBOX_PER_CTA consecutive atoms (coalesced), reduces the atoms of the first
+// structure it sees in registers / shuffles and sends the few others straight to the atomics.
+constexpr int BBOX_THREADS = 256;
+constexpr int BBOX_PER_THREAD = 8;
+__global__ void __launch_bounds__(BBOX_THREADS)
+k_bbox(const double* __restrict__ x, const double* __restrict__ y, const double* __restrict__ z, uint32_t n,
+       const uint32_t* __restrict__ atom_struct, unsigned long long* __restrict__ bbox) {
+  const uint32_t base = blockIdx.x * (BBOX_THREADS * BBOX_PER_THREAD);
+  if (base >= n) return;
+  const uint32_t s0 = atom_struct ? atom_struct[base] : 0u;
+  double lo[3] = {1e308, 1e308, 1e308}, hi[3] = {-1e308, -1e308, -1e308};
+#pragma unroll
+  for (int k = 0; k < BBOX_PER_THREAD; ++k) {
+    const uint32_t a = base + k * BBOX_THREADS + threadIdx.x;
+    if (a >= n) break;
+    const double p[3] = {x[a], y[a], z[a]};
+    const uint32_t s = atom_struct ? atom_struct[a] : 0u;
+    if (s == s0) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        lo[c] = fmin(lo[c], p[c]);
+        hi[c] = fmax(hi[c], p[c]);
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        atomicMin(&bbox[s * 6 + c], enc_f64(p[c]));
+        atomicMax(&bbox[s * 6 + 3 + c], enc_f64(p[c]));
+      }
+    }
+  }
+  __shared__ double red[6][BBOX_THREADS / 32];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    double a = lo[c], b = hi[c];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      a = fmin(a, __shfl_xor_sync(0xffffffffu, a, o));
+      b = fmax(b, __shfl_xor_sync(0xffffffffu, b, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+      red[c][threadIdx.x >> 5] = a;
+      red[3 + c][threadIdx.x >> 5] = b;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < 6) {
+    double v = red[threadIdx.x][0];
+    for (int w = 1; w < BBOX_THREADS / 32; ++w) v = threadIdx.x < 3 ? fmin(v, red[threadIdx.x][w]) : fmax(v, red[threadIdx.x][w]);
+    if (threadIdx.x < 3) {
+      if (v < 1e307) atomicMin(&bbox[s0 * 6 + threadIdx.x], enc_f64(v));
+    } else {
+      if (v > -1e307) atomicMax(&bbox[s0 * 6 + threadIdx.x], enc_f64(v));
+    }
+  }
+}
+
+// cell coordinate along one axis, clamped into the grid
+__device__ __forceinline__ int cell_coord(double p, double origin, double inv_edge, int dim) {
+  int c = (int)floor((p - origin) * inv_edge);
+  return min(max(c, 0), dim - 1);
+}
+
+// Pass 1 of the counting sort: cell id of every point and its arrival rank inside the cell.
+// `ring_grid` selects which of the two grids of StructDesc is addressed; points are read with a stride so that
+// both the SoA atom arrays (stride 1) and the interleaved ring centres (stride 3) fit.
+__global__ void __launch_bounds__(256)
+k_cell_assign(const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz, int stride, uint32_t n,
+              const uint32_t* __restrict__ point_struct, const StructDesc* __restrict__ descs, double inv_edge, int ring_grid,
+              uint32_t* __restrict__ cell_of, uint32_t* __restrict__ rank_of, uint32_t* __restrict__ cell_count) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const StructDesc& d = descs[point_struct ? point_struct[i] : 0u];
+  const int nx = ring_grid ? d.rnx : d.nx, ny = ring_grid ? d.rny : d.ny, nz = ring_grid ? d.rnz : d.nz;
+  const int ix = cell_coord(px[(size_t)i * stride], d.ox, inv_edge, nx);
+  const int iy = cell_coord(py[(size_t)i * stride], d.oy, inv_edge, ny);
+  const int iz = cell_coord(pz[(size_t)i * stride], d.oz, inv_edge, nz);
+  const uint32_t c = (ring_grid ? d.rcell_base : d.cell_base) + (uint32_t)((iz * ny + iy) * nx + ix);
+  cell_of[i] = c;
+  rank_of[i] = atomicAdd(&cell_count[c], 1u);
+}
+
+// ---- exclusive scan of the cell counts (in place), three small kernels --------------------------------
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_PER_THREAD = 8;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_PER_THREAD;
+
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* total) {
+  __shared__ uint32_t wsum[SCAN_THREADS / 32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  uint32_t inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) wsum[w] = inc;
+  __syncthreads();
+  if (w == 0) {
+    uint32_t s = lane < SCAN_THREADS / 32 ? wsum[lane] : 0u;
+#pragma unroll
+    for (int o = 1; o < SCAN_THREADS / 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, s, o);
+      if (lane >= o) s += t;
+    }
+    if (lane < SCAN_THREADS / 32) wsum[lane] = s;
+  }
+  __syncthreads();
+  const uint32_t before = w ? wsum[w - 1] : 0u;
+  *total = wsum[SCAN_THREADS / 32 - 1];
+  __syncthreads();
+  return before + inc - v;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_tiles(uint32_t* __restrict__ data, uint32_t n, uint32_t* __restrict__ tile_sums) {
+  const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_PER_THREAD;
+  uint32_t v[SCAN_PER_THREAD], sum = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_PER_THREAD; ++k) {
+    v[k] = base + k < n ? data[base + k] : 0u;
+    sum += v[k];
+  }
+  uint32_t total;
+  uint32_t run = block_exclusive_scan(sum, &total);
+#pragma unroll
+  for (int k = 0; k < SCAN_PER_THREAD; ++k) {
+    if (base + k < n) data[base + k] = run;
+    run += v[k];
+  }
+  if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_sums(uint32_t* __restrict__ tile_sums, uint32_t n_tiles) {
+  uint32_t carry = 0;
+  for (uint32_t base = 0; base < n_tiles; base += SCAN_THREADS) {
+    const uint32_t i = base + threadIdx.x;
+    const uint32_t v = i < n_tiles ? tile_sums[i] : 0u;
+    uint32_t total;
+    const uint32_t ex = block_exclusive_scan(v, &total);
+    if (i < n_tiles) tile_sums[i] = carry + ex;
+    carry += total;
+  }
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_add(uint32_t* __restrict__ data, uint32_t n, const uint32_t* __restrict__ tile_sums) {
+  const uint32_t off = tile_sums[blockIdx.x];
+  const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_PER_THREAD;
+#pragma unroll
+  for (int k = 0; k < SCAN_PER_THREAD; ++k)
+    if (base + k < n) data[base + k] += off;
+}
+
+// Pass 2 of the counting sort: write the cell-sorted records.  The atom that arrived first in a cell also
+// publishes the cell as a work item of the pair kernel.
+__global__ void __launch_bounds__(256)
+k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, const double* __restrict__ z,
+                const uint32_t* __restrict__ attr, const uint32_t* __restrict__ chain_key, const uint32_t* __restrict__ res_ordinal,
+                const uint32_t* __restrict__ res_id, const uint32_t* __restrict__ atom_struct, const StructDesc* __restrict__ descs,
+                const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of, const uint32_t* __restrict__ cell_start,
+                uint32_t n, RecA* __restrict__ recA, RecB* __restrict__ recB, uint32_t* __restrict__ perm,
+                uint32_t* __restrict__ res_sorted, uint2* __restrict__ items, Counters* __restrict__ ctr) {
+  const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= n) return;
+  const uint32_t s = atom_struct ? atom_struct[a] : 0u;
+  const StructDesc& d = descs[s];
+  const uint32_t c = cell_of[a], r = rank_of[a];
+  const uint32_t slot = cell_start[c] + r;
+  const double px = x[a], py = y[a], pz = z[a];
+  RecA ra;
+  ra.x = (float)(px - d.ox);
+  ra.y = (float)(py - d.oy);
+  ra.z = (float)(pz - d.oz);
+  ra.attr = attr[a];
+  recA[slot] = ra;
+  RecB rb;
+  rb.x = px;
+  rb.y = py;
+  rb.z = pz;
+  rb.chain_key = chain_key[a];
+  rb.res_ordinal = res_ordinal[a];
+  recB[slot] = rb;
+  perm[slot] = a;
+  res_sorted[slot] = res_id[a];
+  if (r == 0) items[atomicAdd(&ctr->n_items, 1u)] = make_uint2(c, s);
+}
+
+__global__ void __launch_bounds__(256)
+k_scatter_rings(const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of, const uint32_t* __restrict__ rcell_start,
+                uint32_t n, uint32_t* __restrict__ rperm) {
+  const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < n) rperm[rcell_start[cell_of[r]] + rank_of[r]] = r;
+}
+
+}  // namespace arpd

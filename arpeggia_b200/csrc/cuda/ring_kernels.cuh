@@ -1,0 +1,95 @@
+// Ring kernels (sm_100a): cation-pi (ring centroid vs atom grid) and pi-pi (ring-centroid grid).
+//   k_ring_atom  <->  get_ring_atom_contacts + find_cation_pi   src/contacts/complex.rs:301-352, aromatic.rs:14-29
+//   k_ring_ring  <->  get_ring_ring_contacts + find_pi_pi       src/contacts/complex.rs:354-405, aromatic.rs:33-64
+// The reference's ring-ring loop is O(R^2) over all ring pairs; find_pi_pi rejects centroid distances above
+// 6.0 A first, so a centroid grid with edge >= 6.0 visits exactly the pairs that can produce a row.
+#pragma once
+#include "classify.cuh"
+
+namespace arpd {
+
+__device__ __forceinline__ void push_row(arp_row* rows, unsigned long long cap, Counters* ctr, uint32_t from, uint32_t to, uint32_t label,
+                                         double dist) {
+  const unsigned long long w = atomicAdd(&ctr->rows, 1ull);
+  if (w < cap) rows[w] = arp_row{from, to, label, __double2float_rn(dist)};
+}
+
+// one warp per ring; lanes sweep the atoms of the 27 cells around the ring centroid (9 contiguous runs)
+__global__ void __launch_bounds__(256) k_ring_atom(const RingArgs R, const DevParams P) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  for (uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < R.n_rings; r += warps) {
+    const uint32_t wr = R.attr[r];
+    if (wr & ARP_ATTR_GHOST) continue;
+    const StructDesc& D = R.descs[R.ring_struct ? R.ring_struct[r] : 0u];
+    const double cx = R.center[3 * r], cy = R.center[3 * r + 1], cz = R.center[3 * r + 2];
+    const double nx_ = R.normal[3 * r], ny_ = R.normal[3 * r + 1], nz_ = R.normal[3 * r + 2];
+    const uint32_t kr = R.chain_key[r], orr = R.res_ordinal[r];
+    const int ix = min(max((int)floor((cx - D.ox) * P.inv_edge), 0), D.nx - 1);
+    const int iy = min(max((int)floor((cy - D.oy) * P.inv_edge), 0), D.ny - 1);
+    const int iz = min(max((int)floor((cz - D.oz) * P.inv_edge), 0), D.nz - 1);
+    const double nn = norm3(nx_, ny_, nz_);
+    for (int k = 0; k < 9; ++k) {
+      const int y = iy + k % 3 - 1, z = iz + k / 3 - 1;
+      if (y < 0 || y >= D.ny || z < 0 || z >= D.nz) continue;
+      const uint32_t row = D.cell_base + (uint32_t)((z * D.ny + y) * D.nx);
+      const uint32_t sb = R.cell_start[row + max(ix - 1, 0)], se = R.cell_start[row + min(ix + 1, D.nx - 1) + 1];
+      for (uint32_t t = sb + lane; t < se; t += 32) {
+        const uint32_t wy = R.recA[t].attr;
+        if (!(wy & ARP_ATTR_POS_RES)) continue;  // aromatic.rs:18: only cations can give a row
+        const RecB b = R.recB[t];
+        const double vx = dsub(b.x, cx), vy = dsub(b.y, cy), vz = dsub(b.z, cz);
+        const double d2 = dot3(vx, vy, vz, vx, vy, vz);
+        if (!(d2 <= P.rc2)) continue;  // tree.locate_within_distance(center, rc^2), complex.rs:310-313
+        if (!ring_atom_filter(wr, kr, orr, wy, b.chain_key, b.res_ordinal)) continue;
+        const double dist = __dsqrt_rn(d2);  // ring.point_dist
+        if (!(dist <= 4.5)) continue;
+        const double c = __ddiv_rn(dot3(nx_, ny_, nz_, vx, vy, vz), dmul(nn, dist));
+        if (!fold_pred(c, P.ang.f_le_30_pos, P.ang.f_le_30_neg)) continue;  // theta <= 30
+        push_row(R.rows, R.row_cap, R.ctr, r | ARP_RING_FLAG, R.perm[t], ARP_CationPi, dist);
+      }
+    }
+  }
+}
+
+// one thread per ring r1; 27 cells of the ring-centroid grid
+__global__ void __launch_bounds__(128) k_ring_ring(const RingArgs R, const DevParams P) {
+  const uint32_t r1 = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r1 >= R.n_rings) return;
+  const uint32_t w1 = R.attr[r1];
+  if (!(w1 & ARP_ATTR_LIGAND) || (w1 & ARP_ATTR_GHOST)) return;  // complex.rs:363
+  const StructDesc& D = R.descs[R.ring_struct ? R.ring_struct[r1] : 0u];
+  const double c1[3] = {R.center[3 * r1], R.center[3 * r1 + 1], R.center[3 * r1 + 2]};
+  const double n1[3] = {R.normal[3 * r1], R.normal[3 * r1 + 1], R.normal[3 * r1 + 2]};
+  const uint32_t k1 = R.chain_key[r1], o1 = R.res_ordinal[r1];
+  const int ix = min(max((int)floor((c1[0] - D.ox) * P.inv_redge), 0), D.rnx - 1);
+  const int iy = min(max((int)floor((c1[1] - D.oy) * P.inv_redge), 0), D.rny - 1);
+  const int iz = min(max((int)floor((c1[2] - D.oz) * P.inv_redge), 0), D.rnz - 1);
+  for (int k = 0; k < 9; ++k) {
+    const int y = iy + k % 3 - 1, z = iz + k / 3 - 1;
+    if (y < 0 || y >= D.rny || z < 0 || z >= D.rnz) continue;
+    const uint32_t row = D.rcell_base + (uint32_t)((z * D.rny + y) * D.rnx);
+    const uint32_t sb = R.rcell_start[row + max(ix - 1, 0)], se = R.rcell_start[row + min(ix + 1, D.rnx - 1) + 1];
+    for (uint32_t t = sb; t < se; ++t) {
+      const uint32_t r2 = R.rperm[t];
+      const uint32_t w2 = R.attr[r2];
+      if (!(w2 & ARP_ATTR_RECEPTOR)) continue;  // complex.rs:364
+      const uint32_t k2 = R.chain_key[r2], o2 = R.res_ordinal[r2];
+      // should_compare_residues(k1, k2, true), complex.rs:94-131
+      if ((k1 ^ k2) >> 24) continue;
+      if (k1 == k2) {
+        if (!((o2 > 1u) && (o1 < o2 - 1u))) continue;
+      } else {
+        const bool both = (w1 & w2 & ARP_ATTR_LIGAND) && (w1 & w2 & ARP_ATTR_RECEPTOR);
+        if (both && k1 > k2) continue;
+      }
+      const double c2[3] = {R.center[3 * r2], R.center[3 * r2 + 1], R.center[3 * r2 + 2]};
+      const double n2[3] = {R.normal[3 * r2], R.normal[3 * r2 + 1], R.normal[3 * r2 + 2]};
+      double dist;
+      const int label = find_pi_pi(P, c1, n1, c2, n2, &dist);
+      if (label >= 0) push_row(R.rows, R.row_cap, R.ctr, r1 | ARP_RING_FLAG, r2 | ARP_RING_FLAG, (uint32_t)label, dist);
+    }
+  }
+}
+
+}  // namespace arpd

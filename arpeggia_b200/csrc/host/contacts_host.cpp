@@ -1,0 +1,61 @@
+// arph_contacts / arph_contacts_file: the host mirror of get_contacts (src/contacts/mod.rs:61-136) and of
+// arpeggia.contacts() (src/python.rs:31-56): load -> filters -> pack -> arp_contacts (device) -> table.
+#include <chrono>
+
+#include "packed.hpp"
+
+namespace {
+double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+}  // namespace
+
+extern "C" {
+
+int arph_contacts(arp_ctx* ctx, const arp_atom_record* atoms, int64_t n, const char* groups, double vdw_comp, double dist_cutoff,
+                  int ignore_zero_occupancy, uint32_t flags, arph_table** out) {
+  *out = nullptr;
+  if (!ctx) {
+    arp::last_error() = "arph_contacts needs a device context (there is no CPU fallback)";
+    return ARP_ERR_CUDA;
+  }
+  const double t0 = now_s();
+  arph_packed* pk = nullptr;
+  int rc = arph_pack(atoms, n, groups, ignore_zero_occupancy, flags, &pk);
+  if (rc != ARP_OK) return rc;
+  const double t1 = now_s();
+  arp_params prm{};
+  prm.vdw_comp = vdw_comp;
+  prm.dist_cutoff = dist_cutoff;
+  prm.flags = 0;
+  arp_result* res = nullptr;
+  rc = arp_contacts(ctx, arph_packed_structure(pk), &prm, &res);
+  if (rc != ARP_OK) {
+    arp::last_error() = arp_last_error(ctx);
+    arph_packed_free(pk);
+    return rc;
+  }
+  const double t2 = now_s();
+  rc = arph_build_table(pk, res->rows, res->n_rows, out);
+  if (rc == ARP_OK) {
+    (*out)->pairs_in_cutoff = res->pairs_in_cutoff;
+    (*out)->pairs_classified = res->pairs_classified;
+    (*out)->t_setup_s = t1 - t0;
+    (*out)->t_classify_s = t2 - t1;
+    (*out)->t_table_s = now_s() - t2;
+  }
+  arp_result_free(ctx, res);
+  arph_packed_free(pk);
+  return rc;
+}
+
+int arph_contacts_file(arp_ctx* ctx, const char* path, const char* groups, double vdw_comp, double dist_cutoff,
+                       int ignore_zero_occupancy, uint32_t flags, arph_table** out) {
+  *out = nullptr;
+  arp_atom_record* recs = nullptr;
+  int64_t n = 0;
+  int rc = arph_parse_pdb(path, &recs, &n);
+  if (rc != ARP_OK) return rc;
+  rc = arph_contacts(ctx, recs, n, groups, vdw_comp, dist_cutoff, ignore_zero_occupancy, flags, out);
+  arph_free(recs);
+  return rc;
+}
+}

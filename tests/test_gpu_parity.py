@@ -1,0 +1,85 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle on the same inputs.  Needs a B200."""
+import numpy as np
+import pytest
+
+import arpeggia_b200 as A
+from oracle import oracle as O
+from tests.util import assert_tables_equal
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    return A.Context(0)
+
+
+@pytest.fixture(scope="module")
+def ubq(ubq_path):
+    return A.parse_pdb(ubq_path)
+
+
+@pytest.fixture(scope="module")
+def bft(bft_path):
+    return A.parse_pdb(bft_path)
+
+
+def test_config1_1ubq_golden_532(ctx, ubq):
+    got = ctx.contacts_table(ubq, "/", 0.1, 6.5)
+    assert got["n_rows"] == 532  # python/tests/test_arpeggia.py:35
+    want = O.contacts(ubq.view(O.ATOM_DTYPE), "/", 0.1, 6.5)
+    assert_tables_equal(got, want, "1ubq")
+    assert got["pairs_in_cutoff"] == want["pairs_in_cutoff"] == 29028
+    assert got["pairs_classified"] == want["pairs_classified"] == 9128
+
+
+def test_config2_6bft_bit_exact(ctx, bft):
+    got = ctx.contacts_table(bft, "/", 0.1, 6.5)
+    want = O.contacts(bft.view(O.ATOM_DTYPE), "/", 0.1, 6.5)
+    assert_tables_equal(got, want, "6bft")
+    assert got["n_rows"] == 7236
+    assert got["pairs_in_cutoff"] == want["pairs_in_cutoff"] and got["pairs_classified"] == want["pairs_classified"]
+
+
+@pytest.mark.parametrize("groups", ["A,B/G", "H,L/", "/C,G", "A,B,H/B,H,L", "A/A"])
+def test_group_selection(ctx, bft, groups):
+    got = ctx.contacts_table(bft, groups, 0.1, 6.5)
+    want = O.contacts(bft.view(O.ATOM_DTYPE), groups, 0.1, 6.5)
+    assert_tables_equal(got, want, groups)
+
+
+@pytest.mark.parametrize("vdw_comp,rc", [(0.1, 4.0), (0.3, 5.0), (0.0, 3.0), (0.1, 9.0), (1.0, 6.5), (0.1, 12.5)])
+def test_parameters(ctx, bft, vdw_comp, rc):
+    got = ctx.contacts_table(bft, "/", vdw_comp, rc)
+    want = O.contacts(bft.view(O.ATOM_DTYPE), "/", vdw_comp, rc)
+    assert_tables_equal(got, want, f"comp={vdw_comp} rc={rc}")
+    assert got["pairs_in_cutoff"] == want["pairs_in_cutoff"]
+
+
+def test_emit_radius_screen_gives_identical_rows(ctx, bft):
+    p = A.Packed(bft)
+    a = ctx.contacts_rows(p, 0.1, 6.5, flags=0)
+    b = ctx.contacts_rows(p, 0.1, 6.5, flags=1)
+    ra, rb = np.sort(a["rows"], order=["from", "to", "label"]), np.sort(b["rows"], order=["from", "to", "label"])
+    assert np.array_equal(ra, rb)
+    assert b["pairs_in_cutoff"] == -1 and b["pairs_screened"] < a["pairs_screened"]
+
+
+def test_errors_match_reference_panics(ctx, bft):
+    with pytest.raises(A.ArpeggiaError, match="Invalid chain groups format"):
+        ctx.contacts_table(bft, "A,B", 0.1, 6.5)
+    with pytest.raises(A.ArpeggiaError, match="Empty chain groups!"):
+        ctx.contacts_table(bft, "A,B,C,G,H,L/", 0.1, 6.5)
+    gly = bft[np.isin(bft["resn"], [b"GLY", b"ALA"])]
+    with pytest.raises(A.ArpeggiaError, match="Error building ring positions"):
+        ctx.contacts_table(gly, "/", 0.1, 6.5)
+
+
+def test_python_dropin_surface(ubq_path):
+    df = A.contacts(ubq_path, groups="/", vdw_comp=0.1, dist_cutoff=6.5)
+    n = df.height if hasattr(df, "height") else df.num_rows
+    assert n == 532
+    cols = list(df.columns) if not hasattr(df, "column_names") else df.column_names
+    assert cols == A.COLUMNS and len(cols) == 20
+    df2 = A.contacts(ubq_path, ignore_zero_occupancy=True)
+    assert (df2.height if hasattr(df2, "height") else df2.num_rows) == 532
