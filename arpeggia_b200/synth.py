@@ -1,0 +1,69 @@
+"""Synthetic protein-density workloads (BASELINE.json configs 3-5).  No RNG except the seeded jitter.
+
+All generators work on atom records (ATOM_DTYPE), i.e. on what a parser yields, so the same arrays feed the
+product and the oracle.  Coordinates stay on the PDB 0.001 A lattice: shifts are applied in integer
+milli-angstrom and converted back with one correctly rounded division, exactly like parsing the decimal text.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from ._lib import ATOM_DTYPE
+
+# 6bft bounding box is 180.254 x 86.988 x 111.932 A; the pitch leaves a ~3 A gap so neighbouring copies touch
+PITCH_6BFT = (183.300, 90.000, 114.900)
+# shrunk pitch: copies interpenetrate until the mean occupancy of occupied 6.5 A cells is >= 14 atoms
+PITCH_6BFT_DENSE = (91.650, 60.000, 57.450)
+
+
+def _milli(v: np.ndarray) -> np.ndarray:
+    return np.rint(v * 1000.0).astype(np.int64)
+
+
+def tile(atoms: np.ndarray, nx: int, ny: int, nz: int, pitch=PITCH_6BFT, serial_stride: int | None = None) -> np.ndarray:
+    """nx*ny*nz translated copies of `atoms`; copy (i,j,k) is shifted by (i,j,k)*pitch and its chains are
+    renamed "<id><5-digit copy number>" so every chain id stays unique (model 0)."""
+    atoms = np.ascontiguousarray(atoms, dtype=ATOM_DTYPE)
+    n = len(atoms)
+    copies = nx * ny * nz
+    if serial_stride is None:
+        serial_stride = int(atoms["serial"].max()) + 1
+    out = np.empty(n * copies, dtype=ATOM_DTYPE)
+    mx, my, mz = _milli(atoms["x"]), _milli(atoms["y"]), _milli(atoms["z"])
+    px, py, pz = (int(round(p * 1000)) for p in pitch)
+    chains = np.unique(atoms["chain"])
+    c = 0
+    for k in range(nz):
+        for j in range(ny):
+            for i in range(nx):
+                blk = out[c * n:(c + 1) * n]
+                blk[:] = atoms
+                blk["x"] = (mx + i * px) / 1000.0
+                blk["y"] = (my + j * py) / 1000.0
+                blk["z"] = (mz + k * pz) / 1000.0
+                blk["serial"] = atoms["serial"] + c * serial_stride
+                if copies > 1:
+                    for ch in chains:
+                        blk["chain"][atoms["chain"] == ch] = ch + b"%05d" % c
+                c += 1
+    return out
+
+
+def assembly_1m(base: np.ndarray, dense: bool = False) -> np.ndarray:
+    """Config 3: 6bft tiled 5x5x5 = 1 022 500 atoms (dense=True: overlapping copies, interior density)."""
+    return tile(base, 5, 5, 5, PITCH_6BFT_DENSE if dense else PITCH_6BFT)
+
+
+def assembly_100m(base: np.ndarray) -> np.ndarray:
+    """Config 5: 6bft tiled 16x32x24 = 100 515 840 atoms."""
+    return tile(base, 16, 32, 24, PITCH_6BFT)
+
+
+def jittered_complex(base: np.ndarray, k: int, chains=(b"A", b"B", b"C", b"G"), amplitude_milli: int = 50) -> np.ndarray:
+    """Config 4, complex k: chains A,B,C,G of 6bft with a per-coordinate jitter uniform in [-0.050, +0.050] A on
+    the 0.001 A lattice, PCG64 stream seeded 20260000 + k."""
+    sub = np.ascontiguousarray(base[np.isin(base["chain"], list(chains))], dtype=ATOM_DTYPE).copy()
+    rng = np.random.Generator(np.random.PCG64(20260000 + k))
+    for ax in ("x", "y", "z"):
+        sub[ax] = (_milli(sub[ax]) + rng.integers(-amplitude_milli, amplitude_milli + 1, size=len(sub))) / 1000.0
+    return sub

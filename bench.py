@@ -1,0 +1,285 @@
+#!/usr/bin/env python
+"""bench.py -- contacts hot path on B200 (driver contract; see the task prompt and DESIGN.md "Measurement").
+
+A "step" = one pass of the hot path (cell-list build + neighbour/classify kernel + ring kernels) over the
+synthetic 1 022 500-atom protein-density assembly of BASELINE.json configs[2] (6bft tiled 5x5x5), inputs already
+resident in HBM.  With N > 1 ranks every rank owns one such assembly (sharding by structure, no collective on
+the data path): weak scaling.  Metric: atom pairs screened per second = ordered atom pairs within dist_cutoff
+(what the reference's R*-tree query returns and its classification loop consumes), a property of the workload
+and therefore identical for every implementation; contacts/s, candidate tests/s and atoms/s ride along.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            # our arm (GPU)
+  python bench.py --impl reference [...]                         # the CPU restatement of the reference
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "atom_pairs_screened_per_s"
+UNIT = "pairs/s"
+WORKLOAD = "6bft tiled 5x5x5 = 1,022,500 atoms (BASELINE.json configs[2]), groups '/', dist_cutoff 6.5, vdw_comp 0.1"
+
+
+def build_workload(dense: bool = False):
+    import arpeggia_b200 as A
+    from arpeggia_b200 import synth
+
+    base = A.parse_pdb(ROOT / "tests" / "data" / "6bft.pdb")
+    return synth.assembly_1m(base, dense=dense)
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([f.strip() for f in out.split(",")])
+            except Exception:
+                pass
+            self._stop_evt.wait(0.1)
+
+    def summary(self):
+        self._stop_evt.set()
+        self.join(timeout=6)
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(r[3 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_reference(atoms, sample_copies: int, threads: int):
+    """The CPU restatement of the reference (oracle/, "port"): hot-path seconds on a bounded sample."""
+    from oracle import oracle as O
+
+    n_per = len(atoms) // 125
+    sample = atoms[: n_per * sample_copies]
+    r = O.contacts(sample.view(O.ATOM_DTYPE), "/", 0.1, 6.5, flags=O.FLAG_NO_TABLE | O.FLAG_SKIP_LOAD_FILTER, num_threads=threads)
+    hot = r["t_search_s"] + r["t_classify_s"] + r["t_rings_s"]
+    return {"pairs": r["pairs_in_cutoff"], "rows": r["n_rows"], "atoms": r["n_atoms"], "hot_s": hot,
+            "sample": f"first {sample_copies} of the 125 6bft copies = {len(sample):,} atoms; neighbour search + classification + ring loops "
+                      f"(hierarchy build and table excluded)"}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    atoms = build_workload()
+    threads = os.cpu_count() or 1
+    copies = 25  # ~1/5 of the workload: about 1-4 s per step on 8+ cores
+    for _ in range(max(args.warmup, 0) and 1):
+        cpu_reference(atoms, copies, threads)
+    t_tot, pairs, rows = 0.0, 0, 0
+    for _ in range(args.steps):
+        r = cpu_reference(atoms, copies, threads)
+        t_tot += r["hot_s"]
+        pairs += r["pairs"]
+        rows += r["rows"]
+    value = pairs / t_tot
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * t_tot / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "note": "CPU restatement (oracle/) of the reference's Rust path; the Rust crate cannot be built here"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": r["sample"]},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "contacts_per_s": rows / t_tot, "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def pinned_structure(A, packed):
+    """Copy the packed SoA into page-locked memory (arp_host_alloc) and return (Structure, keepalive, bytes)."""
+    from arpeggia_b200 import _lib
+
+    L = _lib.lib()
+    src = packed.structure
+    dst = _lib.Structure()
+    keep, total = [], 0
+    for name, ctype in _lib.Structure._fields_:
+        v = getattr(src, name)
+        if name.startswith("n_"):
+            setattr(dst, name, v)
+    sizes = {"x": 8, "y": 8, "z": 8, "attr": 4, "chain_key": 4, "res_ordinal": 4, "res_id": 4}
+    n, nr, ng, nh = src.n_atoms, src.n_residues, src.n_rings, src.n_h
+    lens = {**{k: n * s for k, s in sizes.items()}, "res_h_begin": 4 * (nr + 1), "h_x": 8 * nh, "h_y": 8 * nh, "h_z": 8 * nh,
+            "res_cb": 4 * nr, "res_sg": 4 * nr, "ring_center": 24 * ng, "ring_normal": 24 * ng, "ring_attr": 4 * ng,
+            "ring_chain_key": 4 * ng, "ring_res_ordinal": 4 * ng}
+    for name, nbytes in lens.items():
+        p = C.c_void_p()
+        _lib.check(L.arp_host_alloc(C.byref(p), max(nbytes, 1)))
+        keep.append(p)
+        if nbytes:
+            C.memmove(p, C.cast(getattr(src, name), C.c_void_p), nbytes)
+        setattr(dst, name, C.cast(p, dict(_lib.Structure._fields_)[name]))
+        total += nbytes
+    return dst, keep, total
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--dense", action="store_true", help="overlapping copies (protein-interior density) instead of config 3")
+    ap.add_argument("--flags", type=int, default=0, help="arp_params.flags (1 = emit-radius screen)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        return run_reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+
+    import arpeggia_b200 as A
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    atoms = build_workload(args.dense)
+    packed = A.Packed(atoms, "/", flags=2)
+    ctx = A.Context(local)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=local)
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=f"cuda:{local}")  # > 126 MB of L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput ---------------------------------------------------------------------
+    ctx.upload(packed)
+    for _ in range(args.warmup):
+        ctx.run(0.1, 6.5, args.flags)
+    res = ctx.download()
+    st0 = ctx.stats()
+    n_atoms, n_rows = st0["n_atoms"], st0["n_rows"]
+    pairs = res["pairs_in_cutoff"] if res["pairs_in_cutoff"] >= 0 else None
+    if pairs is None:  # emit-radius screen does not count them: take the workload constant from a plain run
+        ctx.run(0.1, 6.5, 0)
+        pairs = ctx.download()["pairs_in_cutoff"]
+        ctx.run(0.1, 6.5, args.flags)
+        ctx.download()
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    t_step = t_pairs = t_grid = t_rings = 0.0
+    with torch.cuda.stream(stream):
+        for _ in range(args.steps):
+            flush.zero_()  # evict L2 between timed steps
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            ctx.run(0.1, 6.5, args.flags)
+            e1.record(stream)
+            e1.synchronize()
+            t_step += e0.elapsed_time(e1)
+            s = ctx.stats()
+            t_pairs += s["ms_pairs"]
+            t_grid += s["ms_grid"]
+            t_rings += s["ms_rings"]
+    barrier()
+    clocks = sampler.summary()
+    ms_step = t_step / args.steps
+    times = torch.tensor([ms_step], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    ms_max = float(times.item())
+    value = world * pairs / (ms_max * 1e-3)
+
+    # ---- end to end through the C ABI with pinned HOST buffers (H2D + kernels + D2H inside the timed region) ------
+    hs, keep, h2d_bytes = pinned_structure(A, packed)
+    for _ in range(2):
+        r = ctx.contacts_rows([C.pointer(hs)], 0.1, 6.5, args.flags)
+    barrier()
+    t0 = time.perf_counter()
+    e2e_steps = max(3, min(args.steps, 10))
+    for _ in range(e2e_steps):
+        r = ctx.contacts_rows([C.pointer(hs)], 0.1, 6.5, args.flags)
+    torch.cuda.synchronize()
+    e2e_ms = 1e3 * (time.perf_counter() - t0) / e2e_steps
+    e2e_t = torch.tensor([e2e_ms], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_value = world * pairs / (float(e2e_t.item()) * 1e-3)
+    d2h_bytes = int(len(r["rows"]) * 16)
+    st = ctx.stats()
+
+    if rank == 0:
+        peaks = {}
+        pk = ROOT / "MEASURED_PEAKS.json"
+        if pk.exists():
+            peaks = json.loads(pk.read_text())
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        ms_pairs = t_pairs / args.steps
+        alg_bytes = 32 * n_atoms + 8 * st["n_cells"] + 16 * n_rows  # B_alg = 32 N + 8 C + 16 R
+        achieved = alg_bytes / (ms_pairs * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_max, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD + (" [dense pitch]" if args.dense else ""), "per_gpu": "one assembly per rank (sharded by structure)",
+                       "l2": "512 MiB buffer written between timed steps (L2 flushed)", "flags": args.flags,
+                       "atoms": n_atoms, "cells": st["n_cells"], "nonempty_cells": st["n_nonempty_cells"], "rows": n_rows,
+                       "pairs_within_cutoff": pairs, "candidate_tests": res["pairs_screened"]},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "kernel": "k_pairs", "kernel_ms": ms_pairs, "algorithmic_bytes": alg_bytes,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
+                    "ms_per_step": float(e2e_t.item()), "ms_h2d": st["ms_h2d"], "ms_run": st["ms_run"], "ms_d2h": st["ms_d2h"],
+                    "api": "arp_contacts (C ABI, pinned host SoA in, host rows out)"},
+            "gpu_launches": int(st0["kernel_launches"]) * args.steps,
+            "clocks": clocks,
+            "contacts_per_s": world * n_rows / (ms_max * 1e-3),
+            "candidate_tests_per_s": world * res["pairs_screened"] / (ms_max * 1e-3),
+            "atoms_per_s": world * n_atoms / (ms_max * 1e-3),
+            "stage_ms": {"grid": t_grid / args.steps, "pairs": ms_pairs, "rings": t_rings / args.steps},
+        }
+        if not args.no_cpu and world == 1:
+            threads = os.cpu_count() or 1
+            c = cpu_reference(atoms, 25, threads)
+            line["cpu_baseline"] = {"value": c["pairs"] / c["hot_s"], "unit": UNIT, "cores": threads, "kind": "port",
+                                    "sample": c["sample"], "seconds": c["hot_s"]}
+        else:
+            line["cpu_baseline"] = None
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

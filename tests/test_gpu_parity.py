@@ -83,3 +83,40 @@ def test_python_dropin_surface(ubq_path):
     assert cols == A.COLUMNS and len(cols) == 20
     df2 = A.contacts(ubq_path, ignore_zero_occupancy=True)
     assert (df2.height if hasattr(df2, "height") else df2.num_rows) == 532
+
+
+def test_config3_1m_atoms_bit_exact(ctx, bft):
+    """BASELINE config 3 at full size: 6bft tiled 5x5x5 = 1 022 500 atoms, table identical to the oracle's."""
+    from arpeggia_b200 import synth
+
+    atoms = synth.assembly_1m(bft)
+    assert len(atoms) == 1022500
+    got = ctx.contacts_table(atoms, "/", 0.1, 6.5, flags=2)
+    want = O.contacts(atoms.view(O.ATOM_DTYPE), "/", 0.1, 6.5, flags=O.FLAG_SKIP_LOAD_FILTER, num_threads=0)
+    assert_tables_equal(got, want, "1M")
+    assert got["pairs_in_cutoff"] == want["pairs_in_cutoff"] and got["pairs_classified"] == want["pairs_classified"]
+
+
+def test_dense_overlapping_copies_clashes(ctx, bft):
+    """Interpenetrating copies: steric clashes, crowded cells (> 32 atoms), row-buffer growth."""
+    from arpeggia_b200 import synth
+
+    atoms = synth.tile(bft, 2, 2, 2, pitch=(20.0, 15.0, 10.0))
+    got = ctx.contacts_table(atoms, "/", 0.1, 6.5, flags=2)
+    want = O.contacts(atoms.view(O.ATOM_DTYPE), "/", 0.1, 6.5, flags=O.FLAG_SKIP_LOAD_FILTER, num_threads=0)
+    assert_tables_equal(got, want, "dense")
+    assert (got["interaction"] == "StericClash").sum() > 1000
+
+
+def test_batch_equals_singles(ctx, bft):
+    """arp_contacts_batch: rows of every structure equal the rows of a single-structure call."""
+    from arpeggia_b200 import synth
+
+    packs = [A.Packed(synth.jittered_complex(bft, k), "/", flags=2) for k in range(5)] + [A.Packed(bft)]
+    res = ctx.contacts_rows(packs, 0.1, 6.5)
+    parts = A.split_rows(res)
+    assert len(parts) == len(packs)
+    for p, part in zip(packs, parts):
+        single = ctx.contacts_rows(p, 0.1, 6.5)["rows"]
+        key = ["from", "to", "label"]
+        assert np.array_equal(np.sort(part, order=key), np.sort(single, order=key))
