@@ -28,6 +28,7 @@ assert ATOM_DTYPE.itemsize == 96
 ROW_DTYPE = np.dtype([("from", "<u4"), ("to", "<u4"), ("label", "<u4"), ("distance", "<f4")])
 RING_FLAG = 0x80000000
 FLAG_EMIT_RADIUS_SCREEN = 1
+FLAG_COUNT_CLASSIFIED = 2
 HOST_FLAG_NO_MULTIMODEL_QUIRK = 1
 HOST_FLAG_SKIP_LOAD_FILTER = 2
 

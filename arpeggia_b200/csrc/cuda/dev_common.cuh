@@ -47,7 +47,10 @@ struct DevParams {
   double emit_d2_max;    // no label can fire beyond this squared distance (conservative)
   double inv_edge;       // 1 / atom-grid cell edge
   double inv_redge;      // 1 / ring-grid cell edge
-  float rc2_screen;      // f32 pre-screen threshold = r_screen^2 + guard
+  float thr_hit;         // f32 screen: d2 <= thr_hit  -> may be within the screening radius   (r_screen^2 + g)
+  float thr_cert;        //             d2 <= thr_cert -> certainly within dist_cutoff          (rc^2 - g)
+  float thr_near;        //             d2 <= thr_near -> may be within the emit radius         (r_emit^2 + g)
+  int count_classified;  // 1: every in-cutoff pair goes through the exact filter (pairs_classified is counted)
   uint32_t flags;        // ARP_FLAG_*
   int count_in_cutoff;   // 1: screening radius == dist_cutoff, pairs_in_cutoff is counted
   int n_struct;

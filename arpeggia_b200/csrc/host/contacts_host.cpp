@@ -25,7 +25,7 @@ int arph_contacts(arp_ctx* ctx, const arp_atom_record* atoms, int64_t n, const c
   arp_params prm{};
   prm.vdw_comp = vdw_comp;
   prm.dist_cutoff = dist_cutoff;
-  prm.flags = 0;
+  prm.flags = ARP_FLAG_COUNT_CLASSIFIED;  // the table reports both workload counters
   arp_result* res = nullptr;
   rc = arp_contacts(ctx, arph_packed_structure(pk), &prm, &res);
   if (rc != ARP_OK) {

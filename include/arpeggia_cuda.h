@@ -104,6 +104,9 @@ typedef struct arp_structure {
 #define ARP_FLAG_EMIT_RADIUS_SCREEN 0x1u /* screen atom pairs at min(dist_cutoff, largest distance at which any
                                             label can fire) instead of dist_cutoff. Rows are identical;
                                             pairs_in_cutoff is then not computed (reported as -1). */
+#define ARP_FLAG_COUNT_CLASSIFIED    0x2u /* also count pairs_classified: every pair within dist_cutoff is sent through
+                                            the exact filter, not only those close enough to produce a row (slower;
+                                            without it pairs_classified is reported as -1). Rows are identical. */
 typedef struct arp_params {
   double vdw_comp;     /* -c / vdw_comp   (cli/contacts.rs:37-39) */
   double dist_cutoff;  /* -d / dist_cutoff (cli/contacts.rs:41-43) */
@@ -127,7 +130,7 @@ typedef struct arp_result {
   const int64_t* ring_begin;      /* n_structures+1 */
   int64_t pairs_screened;         /* distance tests evaluated by the neighbour kernel (unordered candidate pairs) */
   int64_t pairs_in_cutoff;        /* ordered pairs (from in ligand, non-H; to != from) with d^2 <= rc^2, or -1 */
-  int64_t pairs_classified;       /* ordered pairs that passed should_compare_entities */
+  int64_t pairs_classified;       /* ordered pairs that passed should_compare_entities, or -1 (see flags) */
 } arp_result;
 
 /* Device-side timings and sizes of the last job (CUDA events on the context's stream). */

@@ -56,13 +56,18 @@ def test_parameters(ctx, bft, vdw_comp, rc):
     assert got["pairs_in_cutoff"] == want["pairs_in_cutoff"]
 
 
-def test_emit_radius_screen_gives_identical_rows(ctx, bft):
+def test_screen_modes_give_identical_rows(ctx, bft):
+    """flags only change which counters are produced, never the rows."""
     p = A.Packed(bft)
-    a = ctx.contacts_rows(p, 0.1, 6.5, flags=0)
-    b = ctx.contacts_rows(p, 0.1, 6.5, flags=1)
-    ra, rb = np.sort(a["rows"], order=["from", "to", "label"]), np.sort(b["rows"], order=["from", "to", "label"])
-    assert np.array_equal(ra, rb)
-    assert b["pairs_in_cutoff"] == -1 and b["pairs_screened"] < a["pairs_screened"]
+    key = ["from", "to", "label"]
+    full = ctx.contacts_rows(p, 0.1, 6.5, flags=2)   # every in-cutoff pair through the exact filter
+    dflt = ctx.contacts_rows(p, 0.1, 6.5, flags=0)   # default: exact stage only where a row is possible
+    tight = ctx.contacts_rows(p, 0.1, 6.5, flags=1)  # screen at the emit radius
+    assert np.array_equal(np.sort(full["rows"], order=key), np.sort(dflt["rows"], order=key))
+    assert np.array_equal(np.sort(full["rows"], order=key), np.sort(tight["rows"], order=key))
+    assert full["pairs_in_cutoff"] == dflt["pairs_in_cutoff"] == 396474
+    assert full["pairs_classified"] == 124047 and dflt["pairs_classified"] == -1
+    assert tight["pairs_in_cutoff"] == -1 and tight["pairs_screened"] < dflt["pairs_screened"]
 
 
 def test_errors_match_reference_panics(ctx, bft):
