@@ -71,13 +71,14 @@ class Packed:
         L = lib()
         return [L.arph_packed_warning(self._h, i).decode() for i in range(L.arph_packed_n_warnings(self._h))]
 
-    def arrays(self) -> dict:
-        """numpy views of the SoA (valid while this object lives)."""
+    def arrays(self, copy: bool = True) -> dict:
+        """The SoA as numpy arrays (copy=False: views that are only valid while this object lives)."""
         s = self.structure
         out = {"n_atoms": s.n_atoms, "n_residues": s.n_residues, "n_rings": s.n_rings, "n_h": s.n_h}
 
         def view(ptr, n, dt):
-            return np.ctypeslib.as_array(ptr, shape=(n,)).view(dt) if n else np.zeros(0, dtype=dt)
+            v = np.ctypeslib.as_array(ptr, shape=(n,)).view(dt) if n else np.zeros(0, dtype=dt)
+            return v.copy() if copy else v
 
         for k in ("x", "y", "z"):
             out[k] = view(getattr(s, k), s.n_atoms, np.float64)

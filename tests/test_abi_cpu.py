@@ -1,0 +1,64 @@
+"""The C-ABI library loads without a GPU, exports every symbol include/*.h declares, and fails loudly
+(no CPU fallback) when a compute entry point is called without a CUDA device."""
+import ctypes as C
+import re
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import arpeggia_b200 as A
+from arpeggia_b200 import _lib
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def declared_functions():
+    names = set()
+    for h in (ROOT / "include").glob("*.h"):
+        text = re.sub(r"/\*.*?\*/", "", h.read_text(), flags=re.S)
+        for m in re.finditer(r"\b(arph?_[a-z0-9_]+)\s*\(", text):
+            names.add(m.group(1))
+    return names
+
+
+def test_every_declared_symbol_is_exported_and_bound():
+    L = _lib.lib()
+    decl = declared_functions()
+    assert len(decl) >= 30
+    for name in decl:
+        assert hasattr(L, name), f"{name} is declared in include/ but not exported by the library"
+    assert decl == set(_lib.SIGNATURES), decl ^ set(_lib.SIGNATURES)
+
+
+def test_struct_sizes_match_the_headers():
+    assert C.sizeof(_lib.Params) == 24 and _lib.ROW_DTYPE.itemsize == 16 and _lib.ATOM_DTYPE.itemsize == 96
+    assert C.sizeof(_lib.Structure) == 4 * 8 + 18 * 8
+    assert C.sizeof(_lib.Result) == 8 * 8
+
+
+def test_labels_and_elements():
+    L = _lib.lib()
+    assert [L.arp_label_name(i).decode() for i in range(19)] == _lib.LABELS
+    assert L.arp_element_class(b"H") == 0 and L.arp_element_class(b"XX") == -1
+    cov, vdw = C.c_double(), C.c_double()
+    for sym, (c, v) in {"C": (0.75, 1.77), "N": (0.71, 1.66), "O": (0.63, 1.50), "S": (1.03, 1.89), "H": (0.32, 1.20)}.items():
+        assert L.arp_element_radii(L.arp_element_class(sym.encode()), C.byref(cov), C.byref(vdw)) == 0
+        assert (cov.value, vdw.value) == (c, v)
+
+
+def test_no_cpu_fallback():
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(A.ArpeggiaError, match="no CUDA device") as e:
+        A.Context(0)
+    assert e.value.code == 9  # ARP_ERR_CUDA
+    with pytest.raises(A.ArpeggiaError):
+        A.contacts(str(ROOT / "tests" / "data" / "1ubq.pdb"))
+    L = _lib.lib()
+    tp = C.POINTER(_lib.Table)()
+    atoms = A.parse_pdb(ROOT / "tests" / "data" / "1ubq.pdb")
+    rc = L.arph_contacts(None, atoms.ctypes.data, len(atoms), b"/", 0.1, 6.5, 0, 0, C.byref(tp))
+    assert rc == 9 and b"no CPU fallback" in L.arph_last_error()

@@ -1,0 +1,160 @@
+"""Host side of the product (parser, packer, plane fit, table builder) against the oracle.  CPU only."""
+import collections
+
+import numpy as np
+import pytest
+
+import arpeggia_b200 as A
+from arpeggia_b200 import _lib
+from oracle import oracle as O
+from tests.util import assert_tables_equal
+
+
+@pytest.fixture(scope="module")
+def ubq(ubq_path):
+    return A.parse_pdb(ubq_path)
+
+
+@pytest.fixture(scope="module")
+def bft(bft_path):
+    return A.parse_pdb(bft_path)
+
+
+def test_parsers_agree(ubq_path, bft_path):
+    for p in (ubq_path, bft_path):
+        a, b = A.parse_pdb(p), O.parse_pdb(p)
+        assert a.tobytes() == b.tobytes()
+    assert len(A.parse_pdb(ubq_path)) == 660 and len(A.parse_pdb(bft_path)) == 8180
+
+
+def test_g5_g6_g7_through_the_product_host_code(ubq):
+    import ctypes as C
+    L = _lib.lib()
+    ring = ubq[(ubq["resi"] == 4) & np.isin(ubq["name"], [b"CG", b"CD1", b"CD2", b"CE1", b"CE2", b"CZ"])]
+    pts = np.ascontiguousarray(np.stack([ring["x"], ring["y"], ring["z"]], 1))
+    c, n = np.zeros(3), np.zeros(3)
+    assert L.arph_plane_fit(pts.ctypes.data, 6, c.ctypes.data, n.ctypes.data) == 0
+    np.testing.assert_allclose(c, [24.96883333, 34.687, 6.16233333], rtol=1e-6)  # residues.rs:355-362
+    ref = np.array([0.53253994, -0.82736044, -0.17853828])
+    np.testing.assert_allclose(n * np.sign(n @ ref), ref, rtol=1e-6)
+    oc, on = O.plane_fit(pts)  # same recipe in both code bases -> same bits
+    assert np.array_equal(oc, c) and np.array_equal(on, n)
+    o, z, pt, x = np.zeros(3), np.array([0.0, 0.0, 1.0]), np.array([0.0, 1.0, 1.0]), np.array([1.0, 0.0, 0.0])
+    ang = lambda cc, nn, p: L.arph_plane_point_angle(cc.ctypes.data, nn.ctypes.data, p.ctypes.data)
+    assert abs(ang(o, z, pt) - 45.0) < 1e-6 and abs(ang(pt, x, o) - 90.0) < 1e-6  # residues.rs:306-332
+    assert L.arph_plane_dihedral(z.ctypes.data, (-z).ctypes.data) < 1e-6
+    lig, rec = C.create_string_buffer(64), C.create_string_buffer(64)
+    cases = {"A,B/C,D": ("A,B", "C,D"), "A/C,D": ("A", "C,D"), "/C,D": ("A,B", "C,D"), "C/": ("C", "A,B,D"), "/": ("A,B,C,D", "A,B,C,D")}
+    for g, (l, r) in cases.items():  # utils.rs:174-209
+        assert L.arph_parse_groups(b"A,B,C,D", g.encode(), lig, rec, 64) == 0
+        assert (lig.value.decode(), rec.value.decode()) == (l, r)
+    assert L.arph_parse_groups(b"A,B,C,D", b"A,B", lig, rec, 64) == 2
+    assert b"Invalid chain groups format! Use '/' for all-to-all comparisons." in L.arph_last_error()
+    assert L.arph_parse_groups(b"A,B,C,D", b"A,B,C,D/", lig, rec, 64) == 3 and b"Empty chain groups!" in L.arph_last_error()
+
+
+def test_packer_1ubq(ubq):
+    p = A.Packed(ubq)
+    a = p.arrays()
+    assert (a["n_atoms"], a["n_residues"], a["n_rings"], a["n_h"]) == (660, 134, 4, 0)
+    # chains.rs:21-40: 76 residues then 58 waters in the same chain -> ordinals 0..133, waters last
+    assert a["res_ordinal"].max() == 133 and (np.diff(a["res_ordinal"].astype(int)) >= 0).all()
+    hoh = ubq["resn"] == b"HOH"
+    assert a["res_ordinal"][hoh].min() == 76
+    attr = a["attr"]
+    el = attr & 0xF
+    assert collections.Counter(el.tolist()) == collections.Counter(
+        {b"C": 1, b"N": 2, b"O": 3, b"S": 4}[e] for e in ubq["element"])
+    assert ((attr & 0x30) == 0x30).all()  # "/" -> every chain is ligand and receptor
+    name, resn = ubq["name"], ubq["resn"]
+    flag = lambda bit: (attr & bit) != 0
+    assert np.array_equal(flag(0x200), (name == b"N") | ((resn == b"ARG") & np.isin(name, [b"NE", b"NH1", b"NH2"]))
+                          | ((resn == b"ASN") & (name == b"ND2")) | ((resn == b"GLN") & (name == b"NE2"))
+                          | ((resn == b"HIS") & np.isin(name, [b"ND1", b"NE2"])) | ((resn == b"LYS") & (name == b"NZ"))
+                          | ((resn == b"SER") & (name == b"OG")) | ((resn == b"THR") & (name == b"OG1"))
+                          | ((resn == b"TRP") & (name == b"NE1")) | ((resn == b"TYR") & (name == b"OH")) | ((resn == b"CYS") & (name == b"SG")))
+    assert not flag(0x400)[hoh].any()  # water O is no acceptor (hbond.rs:139-142)
+    assert flag(0x400)[(name == b"O") & ~hoh].all()
+    assert np.array_equal(flag(0x800), (ubq["element"] == b"C") & (name != b"C"))
+    assert flag(0x1000)[(name == b"CB") & (resn != b"SER")].all() and not flag(0x1000)[(name == b"CB") & (resn == b"SER")].any()
+    assert np.array_equal(flag(0x40), flag(0x100))  # conformer name == residue name in standard files
+    # ring planes equal the oracle's, bit for bit
+    for k, resi in enumerate([4, 45, 59, 68]):  # PHE4 PHE45 TYR59 HIS68
+        n, c, nrm = O.residue_plane(ubq.view(O.ATOM_DTYPE), "A", resi, "ring")
+        assert np.array_equal(a["ring_center"][k], c) and np.array_equal(a["ring_normal"][k], nrm)
+
+
+def test_packer_groups_and_errors(bft):
+    a = A.Packed(bft, "A,B/G").arrays()
+    chains = bft["chain"]
+    assert np.array_equal((a["attr"] & 0x10) != 0, np.isin(chains, [b"A", b"B"]))
+    assert np.array_equal((a["attr"] & 0x20) != 0, chains == b"G")
+    ranks = {c: i for i, c in enumerate(sorted(set(chains.tolist())))}  # complex.rs:129 string order
+    assert np.array_equal(a["chain_key"], np.array([ranks[c] for c in chains.tolist()], dtype=np.uint32))
+    cys = A.Packed(bft).arrays()
+    sg = np.nonzero((bft["resn"] == b"CYS") & (bft["name"] == b"SG"))[0]
+    assert np.array_equal(np.sort(cys["res_sg"][cys["res_sg"] >= 0]), sg) and ((cys["attr"][sg] & 0x2000) != 0).all()
+    with pytest.raises(A.ArpeggiaError, match="Invalid chain groups format") as e:
+        A.Packed(bft, "A,B")
+    assert e.value.code == 2
+    with pytest.raises(A.ArpeggiaError, match="Empty chain groups!"):
+        A.Packed(bft, "A,B,C,G,H,L/")
+    with pytest.raises(A.ArpeggiaError, match="Error building ring positions"):
+        A.Packed(bft[np.isin(bft["resn"], [b"GLY", b"ALA", b"LEU"])])
+    bad = bft.copy()
+    bad["element"][5] = b"XX"
+    with pytest.raises(A.ArpeggiaError, match="van der Waals"):
+        A.Packed(bad)
+    w = A.Packed(bft).warnings  # HIS A230 has no side chain: warning, not an error (mod.rs:64-68)
+    assert len(w) == 1 and "230" in w[0]
+
+
+def rows_from_oracle_table(atoms, packed, t):
+    """Invert the oracle's table into device rows (atom / ring indices) to drive arph_build_table alone."""
+    a = packed.arrays()
+    serial_to_idx = {int(s): i for i, s in enumerate(atoms["serial"])}
+    chains_sorted = sorted(set(atoms["chain"].tolist()))
+    ring_idx = {}
+    res_seq = {}
+    for r in atoms:  # ordinal -> resi per chain (fixtures have no insertion codes)
+        key = r["chain"]
+        seq = res_seq.setdefault(key, [])
+        if not seq or seq[-1] != int(r["resi"]):
+            seq.append(int(r["resi"]))
+    for k in range(a["n_rings"]):
+        ch = chains_sorted[int(a["ring_chain_key"][k]) & 0xFFFFFF]
+        ring_idx[(ch.decode(), res_seq[ch][int(a["ring_res_ordinal"][k])])] = k
+    rows = np.zeros(t["n_rows"], dtype=_lib.ROW_DTYPE)
+    for side in ("from", "to"):
+        isring = t[f"{side}_atomn"] == "Ring"
+        idx = np.array([ring_idx[(c, int(r))] | _lib.RING_FLAG if g else serial_to_idx[int(s)]
+                        for c, r, s, g in zip(t[f"{side}_chain"], t[f"{side}_resi"], t[f"{side}_atomi"], isring)], dtype=np.uint32)
+        rows[side] = idx
+    rows["label"] = t["interaction_code"]
+    rows["distance"] = t["distance"]
+    return rows
+
+
+@pytest.mark.parametrize("which", ["ubq", "bft"])
+def test_table_builder_equals_oracle(which, ubq, bft):
+    atoms = {"ubq": ubq, "bft": bft}[which]
+    want = O.contacts(atoms.view(O.ATOM_DTYPE))
+    p = A.Packed(atoms)
+    rows = rows_from_oracle_table(atoms, p, want)
+    rng = np.random.default_rng(7)
+    got = p.build_table(rows[rng.permutation(len(rows))])  # device rows arrive in arbitrary order
+    assert_tables_equal(got, want, which)
+    at = A.to_arrow(got)
+    assert at.column_names == A.COLUMNS and at.num_rows == want["n_rows"]
+    import pyarrow as pa
+    assert at.schema.field("model").type == pa.uint32() and at.schema.field("distance").type == pa.float32()
+    assert at.schema.field("from_resi").type == pa.int32() and at.schema.field("interaction").type == pa.large_string()
+    assert at["sc_dihedral"].null_count == int((~want["sc_valid"]).sum())
+
+
+def test_table_builder_rejects_bad_rows(ubq):
+    p = A.Packed(ubq)
+    rows = np.zeros(1, dtype=_lib.ROW_DTYPE)
+    rows["from"] = 100000
+    with pytest.raises(A.ArpeggiaError, match="outside the structure"):
+        p.build_table(rows)
