@@ -85,6 +85,8 @@ class Packed:
         for k in ("attr", "chain_key", "res_ordinal", "res_id"):
             out[k] = view(getattr(s, k), s.n_atoms, np.uint32)
         out["res_h_begin"] = view(s.res_h_begin, s.n_residues + 1, np.uint32)
+        for k in ("h_x", "h_y", "h_z"):
+            out[k] = view(getattr(s, k), s.n_h, np.float64)
         for k in ("res_cb", "res_sg"):
             out[k] = view(getattr(s, k), s.n_residues, np.int32)
         for k in ("ring_center", "ring_normal"):

@@ -148,7 +148,7 @@ void upload_concat(arp_ctx* c, DBuf<T>& dst, const arp_structure* const* s, int6
   dst.need(std::max<size_t>(total, 1));
   if (total == 0) return;
   if (n == 1 && !adjust) {
-    if (len(s[0])) CK(cudaMemcpyAsync(dst.p, ptr(s[0]), (size_t)len(s[0]) * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+    if (len(s[0])) CK(cudaMemcpyAsync(dst.p, ptr(s[0]), (size_t)len(s[0]) * sizeof(T), cudaMemcpyDefault, c->stream));
     return;
   }
   // the staging buffer is reused by the next array: wait until the previous copy has left it
@@ -167,7 +167,7 @@ void upload_concat(arp_ctx* c, DBuf<T>& dst, const arp_structure* const* s, int6
     }
     off += m;
   }
-  CK(cudaMemcpyAsync(dst.p, h, off * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(dst.p, h, off * sizeof(T), cudaMemcpyDefault, c->stream));
 }
 
 void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
@@ -227,7 +227,7 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
     CK(cudaStreamSynchronize(c->stream));
     c->stage.need(64);
     std::memcpy(c->stage.p, &tail, 4);
-    CK(cudaMemcpyAsync(c->res_h_begin.p + c->n_res, c->stage.p, 4, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->res_h_begin.p + c->n_res, c->stage.p, 4, cudaMemcpyDefault, c->stream));
   }
   // structure descriptors (grids are filled in by the run, they depend on the cutoff)
   c->h_descs.assign(n, StructDesc{});
@@ -239,7 +239,7 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
   }
   c->descs.need(n);
   CK(cudaStreamSynchronize(c->stream));
-  CK(cudaMemcpyAsync(c->descs.p, c->h_descs.data(), n * sizeof(StructDesc), cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(c->descs.p, c->h_descs.data(), n * sizeof(StructDesc), cudaMemcpyDefault, c->stream));
   if (multi) {
     c->atom_struct.need(std::max<int64_t>(c->n_atoms, 1));
     c->ring_struct.need(std::max<int64_t>(c->n_rings, 1));

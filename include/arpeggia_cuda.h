@@ -78,7 +78,10 @@ int arp_element_radii(int element_class, double* covalent_single, double* van_de
 
 #define ARP_RING_FLAG 0x80000000u /* arp_row.from / .to: bit 31 set = ring index, else atom index */
 
-/* One structure as host SoA.  Atom arrays have n_atoms entries in atoms_with_hierarchy() order. */
+/* One structure as SoA.  Atom arrays have n_atoms entries in atoms_with_hierarchy() order.  The pointers may be
+ * host memory (pageable or page-locked) or device memory of the context's GPU (unified addressing decides the
+ * copy direction), so buffers that were produced on the GPU -- e.g. a slab plus its NCCL-exchanged halo -- are
+ * consumed in place. */
 typedef struct arp_structure {
   int64_t n_atoms, n_residues, n_rings, n_h;
   const double* x;               /* angstrom, f64 exactly as parsed */

@@ -125,3 +125,23 @@ def test_batch_equals_singles(ctx, bft):
         single = ctx.contacts_rows(p, 0.1, 6.5)["rows"]
         key = ["from", "to", "label"]
         assert np.array_equal(np.sort(part, order=key), np.sort(single, order=key))
+
+
+EDGE_CASES = ["protonated", "salt_bridges", "altloc", "altloc_protonated", "insertion", "two_models", "zero_occupancy", "ties"]
+
+
+@pytest.mark.parametrize("case", EDGE_CASES)
+def test_edge_cases_equal_oracle(ctx, ubq, case):
+    """Behaviour no reference fixture pins (hydrogens, altlocs, icodes, models, occupancy, ties): GPU == oracle."""
+    from tests import fixtures as F
+
+    atoms = F.all_cases(ubq.view(O.ATOM_DTYPE))[case]
+    zero = case == "zero_occupancy"
+    got = ctx.contacts_table(atoms.view(A.ATOM_DTYPE), "/", 0.1, 6.5, ignore_zero_occupancy=zero)
+    want = O.contacts(atoms, "/", 0.1, 6.5, ignore_zero_occupancy=zero)
+    assert_tables_equal(got, want, case)
+    assert got["pairs_in_cutoff"] == want["pairs_in_cutoff"] and got["pairs_classified"] == want["pairs_classified"]
+    if case == "two_models":  # and without reproducing complex.rs:447-449
+        got = ctx.contacts_table(atoms.view(A.ATOM_DTYPE), "/", 0.1, 6.5, flags=1)
+        want = O.contacts(atoms, "/", 0.1, 6.5, flags=O.FLAG_NO_MULTIMODEL_QUIRK)
+        assert_tables_equal(got, want, case + " (no quirk)")
