@@ -363,13 +363,13 @@ void pack_records(const arp_atom_record* recs, int64_t n, const std::string& gro
   for (size_t mi = 0; mi < models.size(); ++mi) {
     const ModelT& M = models[mi];
     for (auto& Cn : M.chains) {
-      const std::string& chain_str = P.strings[Cn.id];
+      const std::string chain_str = P.strings[Cn.id];  // by value: intern() below may reallocate P.strings
       const uint32_t group_bits = (ligand.count(chain_str) ? ARP_ATTR_LIGAND : 0u) | (receptor.count(chain_str) ? ARP_ATTR_RECEPTOR : 0u);
       const uint32_t ckey = ((uint32_t)mi << 24) | chain_rank[Cn.id];
       for (size_t ordinal = 0; ordinal < Cn.residues.size(); ++ordinal) {
         const ResT& R = Cn.residues[ordinal];
         const int32_t resn_id = uniform_name(R);
-        const std::string& resn = P.strings[resn_id];
+        const std::string resn = P.strings[resn_id];
         const uint32_t rid = (uint32_t)P.res_cb.size();
         P.res_cb.push_back(-1);
         P.res_sg.push_back(-1);
@@ -415,8 +415,6 @@ void pack_records(const arp_atom_record* recs, int64_t n, const std::string& gro
             P.warnings.push_back("Failed to calculate ring position for chain " + chain_str + " residue " + resn + " " +
                                  std::to_string(R.resi) + P.strings[R.icode]);
           }
-          const std::string& conf_name = P.strings[c.name];
-          (void)conf_name;
           for (int64_t k : c.recs) {
             const arp_atom_record& a = recs[k];
             if (std::memcmp(last_name, a.name, 8) != 0 || last_name_id < 0) {
