@@ -94,7 +94,7 @@ struct arp_ctx {
   DBuf<uint32_t> rcell_of, rrank_of, rcell_start, rperm;
   DBuf<RecA> recA;
   DBuf<RecB> recB;
-  DBuf<uint2> items;
+  DBuf<uint4> items;
   DBuf<Counters> ctr;
   DBuf<arp_row> rows;
   uint64_t row_cap = 0;

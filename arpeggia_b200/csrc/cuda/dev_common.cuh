@@ -74,7 +74,7 @@ struct PairArgs {
   const uint32_t* perm;        // sorted slot -> job-global atom index
   const uint32_t* res_sorted;  // sorted slot -> job-global residue id
   const uint32_t* cell_start;  // n_cells + 1
-  const uint2* items;          // non-empty cells: (cell id, structure)
+  const uint4* items;          // non-empty cells: (cell id, structure, ix | iy << 21 | iz << 42)
   const StructDesc* descs;
   // original-order arrays (gathers for disulfide / hydrogen lists)
   const double* x;

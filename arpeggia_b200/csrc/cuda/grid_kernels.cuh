@@ -193,7 +193,7 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
                 const uint32_t* __restrict__ res_id, const uint32_t* __restrict__ atom_struct, const StructDesc* __restrict__ descs,
                 const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of, const uint32_t* __restrict__ cell_start,
                 uint32_t n, RecA* __restrict__ recA, RecB* __restrict__ recB, uint32_t* __restrict__ perm,
-                uint32_t* __restrict__ res_sorted, uint2* __restrict__ items, Counters* __restrict__ ctr) {
+                uint32_t* __restrict__ res_sorted, uint4* __restrict__ items, Counters* __restrict__ ctr) {
   const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
   if (a >= n) return;
   const uint32_t s = atom_struct ? atom_struct[a] : 0u;
@@ -216,7 +216,13 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
   recB[slot] = rb;
   perm[slot] = a;
   res_sorted[slot] = res_id[a];
-  if (r == 0) items[atomicAdd(&ctr->n_items, 1u)] = make_uint2(c, s);
+  if (r == 0) {  // first arrival publishes the cell as a work item, with its grid coordinates
+    const uint32_t local = c - d.cell_base;
+    const unsigned long long ix = local % (uint32_t)d.nx, iy = (local / (uint32_t)d.nx) % (uint32_t)d.ny,
+                             iz = local / ((uint32_t)d.nx * (uint32_t)d.ny);
+    const unsigned long long key = ix | (iy << 21) | (iz << 42);
+    items[atomicAdd(&ctr->n_items, 1u)] = make_uint4(c, s, (uint32_t)key, (uint32_t)(key >> 32));
+  }
 }
 
 __global__ void __launch_bounds__(256)

@@ -26,8 +26,7 @@ namespace arpd {
 constexpr int PAIR_WARPS = 8;
 constexpr int PAIR_THREADS = PAIR_WARPS * 32;
 constexpr int FROM_CHUNK = 32;                 // from-atoms per pass (bits of the hit mask)
-constexpr int SUB_BITS = 8;                    // mask bits compacted per queue append
-constexpr int Q1_CAP = 32 + 32 * SUB_BITS;     // carry-over + worst case of one append
+constexpr int Q1_CAP = 32 + 4 * 32;            // carry-over (< 32) + four ballots
 constexpr int Q2_CAP = 32 + 64;                // carry-over + two orientations of one exact batch
 constexpr uint32_t Q_FLAG = 0x80000000u;       // queue 1: pair still has to be counted; queue 2: orientation b -> a
 
