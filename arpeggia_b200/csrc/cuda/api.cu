@@ -94,7 +94,7 @@ struct arp_ctx {
   DBuf<uint32_t> rcell_of, rrank_of, rcell_start, rperm;
   DBuf<RecA> recA;
   DBuf<RecB> recB;
-  DBuf<uint4> items;
+  DBuf<Item> items;
   DBuf<Counters> ctr;
   DBuf<arp_row> rows;
   uint64_t row_cap = 0;
@@ -189,8 +189,8 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
   c->n_rings = c->ring_begin[n];
   c->n_res = res_begin[n];
   c->n_h = h_begin[n];
-  if (c->n_atoms >= ((int64_t)1 << 31) || c->n_rings >= ((int64_t)1 << 31) || c->n_h >= ((int64_t)1 << 32))
-    throw arp::Error{ARP_ERR_LIMIT, "job exceeds 2^31 atoms / rings"};
+  if (c->n_atoms >= ((int64_t)1 << 30) || c->n_rings >= ((int64_t)1 << 31) || c->n_h >= ((int64_t)1 << 32))
+    throw arp::Error{ARP_ERR_LIMIT, "job exceeds 2^30 atoms / 2^31 rings"};
 
   CK(cudaEventRecord(c->ev[0], c->stream));
   auto nat = [](const arp_structure* t) { return t->n_atoms; };

@@ -31,6 +31,19 @@ struct __align__(32) RecB {
   uint32_t res_ordinal;
 };
 
+// Work item of the pair kernel: one non-empty cell and its half shell (the cell plus its 13 forward neighbours),
+// which in the x-fastest cell order are 5 contiguous runs of cell-sorted atoms.  The candidates of the item are the
+// concatenation of the runs; run 0 starts at the own cell, so the first n_own candidates are the cell's own atoms.
+// Candidate e lives in sorted slot  e + cb  (e < off[0])  or  e + delta[r]  (off[r] <= e < off[r+1]).
+// 64 bytes: a warp reads one item with a single coalesced load (word k in lane k).
+struct __align__(16) Item {
+  uint32_t cb, n_own, total, sid;   // own cell: first slot, atoms; candidates in the half shell; structure
+  uint32_t off[4];                  // first candidate index of runs 1..4
+  uint32_t delta[4];                // run r+1: first slot - off[r]
+  float cx, cy, cz;                 // cell centre relative to the structure origin (f32 local frame of the screen)
+  uint32_t pad;
+};
+
 // Cosine-domain images of the angle comparisons (host-computed, see host/geometry.cpp).
 struct DevAngles {
   double a_ge_90, a_ge_130, a_ge_60, a_le_120;
@@ -47,9 +60,15 @@ struct DevParams {
   double emit_d2_max;    // no label can fire beyond this squared distance (conservative)
   double inv_edge;       // 1 / atom-grid cell edge
   double inv_redge;      // 1 / ring-grid cell edge
-  float thr_hit;         // f32 screen: d2 <= thr_hit  -> may be within the screening radius   (r_screen^2 + g)
-  float thr_cert;        //             d2 <= thr_cert -> certainly within dist_cutoff          (rc^2 - g)
-  float thr_near;        //             d2 <= thr_near -> may be within the emit radius         (r_emit^2 + g)
+  float thr_hit;         // f32 re-test: d2 <= thr_hit  -> may be within the screening radius  (r_screen^2 + g)
+  float thr_cert;        //              d2 <= thr_cert -> certainly within dist_cutoff         (rc^2 - g)
+  float thr_near;        //              d2 <= thr_near -> may be within the emit radius        (r_emit^2 + g)
+  float scr_hit;         // the same three thresholds for the dot-product screen (wider guard band gA >= g)
+  float scr_cert;
+  float scr_near;
+  float guard;           // g (added to the per-pair label limits)
+  float polar_d2;        // largest squared distance of an H-bond / polar label: 4.0^2 with hydrogens in the job, else 3.5^2
+  float edge;            // atom-grid cell edge
   int count_classified;  // 1: every in-cutoff pair goes through the exact filter (pairs_classified is counted)
   uint32_t flags;        // ARP_FLAG_*
   int count_in_cutoff;   // 1: screening radius == dist_cutoff, pairs_in_cutoff is counted
@@ -74,7 +93,7 @@ struct PairArgs {
   const uint32_t* perm;        // sorted slot -> job-global atom index
   const uint32_t* res_sorted;  // sorted slot -> job-global residue id
   const uint32_t* cell_start;  // n_cells + 1
-  const uint4* items;          // non-empty cells: (cell id, structure, ix | iy << 21 | iz << 42)
+  const Item* items;           // non-empty cells
   const StructDesc* descs;
   // original-order arrays (gathers for disulfide / hydrogen lists)
   const double* x;

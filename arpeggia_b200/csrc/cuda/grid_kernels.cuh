@@ -192,8 +192,8 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
                 const uint32_t* __restrict__ attr, const uint32_t* __restrict__ chain_key, const uint32_t* __restrict__ res_ordinal,
                 const uint32_t* __restrict__ res_id, const uint32_t* __restrict__ atom_struct, const StructDesc* __restrict__ descs,
                 const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of, const uint32_t* __restrict__ cell_start,
-                uint32_t n, RecA* __restrict__ recA, RecB* __restrict__ recB, uint32_t* __restrict__ perm,
-                uint32_t* __restrict__ res_sorted, uint4* __restrict__ items, Counters* __restrict__ ctr) {
+                uint32_t n, double edge, RecA* __restrict__ recA, RecB* __restrict__ recB, uint32_t* __restrict__ perm,
+                uint32_t* __restrict__ res_sorted, Item* __restrict__ items, Counters* __restrict__ ctr) {
   const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
   if (a >= n) return;
   const uint32_t s = atom_struct ? atom_struct[a] : 0u;
@@ -216,12 +216,36 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
   recB[slot] = rb;
   perm[slot] = a;
   res_sorted[slot] = res_id[a];
-  if (r == 0) {  // first arrival publishes the cell as a work item, with its grid coordinates
+  if (r == 0) {  // first arrival publishes the cell as a work item: its half shell as 5 runs of sorted slots
     const uint32_t local = c - d.cell_base;
-    const unsigned long long ix = local % (uint32_t)d.nx, iy = (local / (uint32_t)d.nx) % (uint32_t)d.ny,
-                             iz = local / ((uint32_t)d.nx * (uint32_t)d.ny);
-    const unsigned long long key = ix | (iy << 21) | (iz << 42);
-    items[atomicAdd(&ctr->n_items, 1u)] = make_uint4(c, s, (uint32_t)key, (uint32_t)(key >> 32));
+    const int nx = d.nx, ny = d.ny, nz = d.nz;
+    const int ix = (int)(local % (uint32_t)nx), iy = (int)((local / (uint32_t)nx) % (uint32_t)ny), iz = (int)(local / ((uint32_t)nx * (uint32_t)ny));
+    Item it;
+    it.cb = cell_start[c];
+    it.n_own = cell_start[c + 1] - it.cb;
+    it.sid = s;
+    // run 0: own cell and its +x neighbour; runs 1..4: rows (dy, dz) = (+1,0) (-1,+1) (0,+1) (+1,+1), x from ix-1 to ix+1
+    uint32_t acc = cell_start[c + (ix + 1 < nx ? 2 : 1)] - it.cb;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int dy = (k == 0) ? 1 : (k - 2), dz = (k == 0) ? 0 : 1;
+      const int y = iy + dy, z = iz + dz;
+      uint32_t b = 0, e = 0;
+      if (y >= 0 && y < ny && z < nz) {
+        const uint32_t row = d.cell_base + (uint32_t)((z * ny + y) * nx);
+        b = cell_start[row + (uint32_t)max(ix - 1, 0)];
+        e = cell_start[row + (uint32_t)min(ix + 1, nx - 1) + 1u];
+      }
+      it.off[k] = acc;
+      it.delta[k] = b - acc;
+      acc += e - b;
+    }
+    it.total = acc;
+    it.cx = (float)(((double)ix + 0.5) * edge);
+    it.cy = (float)(((double)iy + 0.5) * edge);
+    it.cz = (float)(((double)iz + 0.5) * edge);
+    it.pad = 0;
+    items[atomicAdd(&ctr->n_items, 1u)] = it;
   }
 }
 

@@ -1,39 +1,66 @@
 // k_pairs: neighbour search + classification + compaction for atom-atom contacts (sm_100a).
 // Replaces get_atomic_contacts, src/contacts/complex.rs:189-299.
 //
-// Work decomposition: one warp per non-empty cell ("from" cell), persistent CTAs pulling cells from an atomic
-// cursor.  A warp visits the half shell of its cell -- the cell itself plus the 13 forward neighbours, which
-// in the x-fastest cell order are 5 contiguous runs of sorted atoms -- so every unordered atom pair is screened
-// once; both orientations are then filtered and classified.  Lanes own CANDIDATE atoms (coalesced 16-byte
-// RecA loads, next batch prefetched into registers); the from-cell's atoms sit in shared memory and are
-// broadcast to all lanes.
+// Work decomposition.  One warp per non-empty cell ("from" cell), persistent CTAs pulling work items (Item,
+// dev_common.cuh) from an atomic cursor.  A warp sweeps the HALF SHELL of its cell -- the cell itself plus its 13
+// forward neighbours, 5 contiguous runs of cell-sorted atoms -- so every unordered atom pair is screened once; the
+// orientation of the row is decided later by the pair filter (at most one orientation of a pair can pass
+// should_compare_entities, complex.rs:76-131).
 //
-// Three-stage funnel, each stage running with (nearly) all lanes busy:
-//   1. screen   f32 squared distance against three thresholds (rigorous guard band g, see api_run.inc):
-//               hit  = d2 <= rc^2 + g          may be within the cutoff
-//               cert = d2 <= rc^2 - g          certainly within the cutoff: counted here, no FP64 needed
-//               near = d2 <= r_emit^2 + g      may be close enough for some label to fire
-//               Only near pairs and the ambiguous shell (hit & !cert) go on; they are compacted by a warp
-//               prefix sum into a shared-memory queue.
-//   2. exact    (32 queued pairs at a time) FP64 d^2 exactly as the reference computes it, inclusive cutoff,
-//               pair filter for both orientations; survivors are queued again.
-//   3. classify (32 survivors at a time) sqrt, label ladder, rows out through one atomicAdd per batch.
+// Stage A, the screen (all the volume: ~116 tests per atom at protein density).  Lanes own CANDIDATES: 4 per lane,
+// held in registers in a cell-local f32 frame (cx, cy, cz, h = -|c|^2/2); the cell's own atoms are broadcast from
+// shared memory one after the other as (fx, fy, fz, k).  With s = f.c + h the test d^2 <= T is s >= |f|^2/2 - T/2,
+// i.e. three FMAs and compares against per-from-atom constants -- no subtraction, no square, no branch:
+//     inside  = T_near < d^2 <= T_cert   certainly within dist_cutoff and too far for any label: COUNTED here
+//     push    = d^2 <= T_hit and not inside   (close enough for a label, or too close to the cutoff to call in f32)
+// `inside` pairs add a packed weight to a per-lane counter, `push` pairs set bit i of a per-lane mask.  The guard
+// band gA (api_run.inc) makes both decisions rigorous against the exact FP64 distances.
+//
+// Stage B (what survives: ~8 pairs per atom).  The masks are expanded through a warp prefix sum into a per-warp
+// shared-memory queue of (from slot, candidate slot) and handled 32 at a time with all lanes busy:
+//   B1  f32 re-test on the stored positions, in-cutoff counting, per-pair label limit (no label of
+//       complex.rs:217-296 can fire beyond max(vdW sum + comp, 4.5 | 4.0 | 3.5 by flags)), pair filter.
+//   B2  exact FP64 d^2 in the reference's operation order, inclusive cutoff (rstar), sqrt, label ladder, rows out
+//       through a warp prefix sum and ONE atomicAdd per 32 pairs.
+//
+// Latency.  A warp always has three items in flight: cursor of item k+3 (atomic), record of item k+2 (one
+// coalesced 64-byte load), candidates of item k+1 (four 16-byte loads per lane, issued before item k is computed).
 #pragma once
 #include "classify.cuh"
 
 namespace arpd {
 
-constexpr int PAIR_WARPS = 8;
+constexpr int PAIR_WARPS = 4;
 constexpr int PAIR_THREADS = PAIR_WARPS * 32;
-constexpr int FROM_CHUNK = 32;                 // from-atoms per pass (bits of the hit mask)
-constexpr int Q1_CAP = 32 + 4 * 32;            // carry-over (< 32) + four ballots
-constexpr int Q2_CAP = 32 + 64;                // carry-over + two orientations of one exact batch
-constexpr uint32_t Q_FLAG = 0x80000000u;       // queue 1: pair still has to be counted; queue 2: orientation b -> a
+#ifndef PAIR_MIN_BLOCKS
+#define PAIR_MIN_BLOCKS 5
+#endif
+constexpr int SLOTS = 4;                 // candidates per lane per chunk
+constexpr int CHUNK = 32 * SLOTS;        // candidates per chunk
+constexpr int FROM_PASS = 32;            // from-atoms per pass (bits of a mask)
+constexpr int Q1_CAP = 256;              // screened pairs waiting for B1
+constexpr int Q2_CAP = 64;               // filtered pairs waiting for B2 (carry-over < 32 + one batch)
+constexpr uint32_t SLOT_MASK = 0x3fffffffu;
+constexpr uint32_t QF_A = 0x80000000u;   // q2.x: in-cutoff still undecided (count in B2)   q2.y: row runs candidate -> from
+constexpr uint32_t QF_B = 0x40000000u;   // q2.x: the pair filter passed                     q2.y: a label may fire
+
+// One from-atom as the screen reads it (two LDS.128 broadcasts).
+struct __align__(16) FromRec {
+  float x, y, z, k_hit;      // cell-local position; s >= k_hit <=> d^2 <= T_hit
+  float k_cert, k_near;      // s >= k_cert <=> d^2 <= T_cert; s < k_near <=> d^2 > T_near
+  uint32_t w;                // (eligible as `from` ? 1 << 16 : 0) | 1
+  uint32_t pad;
+};
 
 struct PairSmem {
-  RecA from[PAIR_WARPS][FROM_CHUNK];
+  FromRec from[PAIR_WARPS][FROM_PASS];
   uint2 q1[PAIR_WARPS][Q1_CAP];
   uint2 q2[PAIR_WARPS][Q2_CAP];
+  float lim2[256];           // per element-class pair: (max(cov sum, vdW sum) + comp)^2, rounded up
+};
+
+struct PairCounts {
+  unsigned long long n_in, n_cls;
 };
 
 __device__ __forceinline__ uint32_t warp_inclusive_sum(uint32_t v, int lane) {
@@ -45,21 +72,36 @@ __device__ __forceinline__ uint32_t warp_inclusive_sum(uint32_t v, int lane) {
   return v;
 }
 
-// Stage 3: up to 32 (from, to) survivors, one per lane.
-__device__ __forceinline__ void classify_batch(const PairArgs& G, const DevParams& P, const uint2* q, int count, int lane) {
+// atoms that can start a row / are counted as `from`: in the ligand set, not hydrogen, not a ghost (complex.rs:200-202)
+__device__ __forceinline__ uint32_t eligible(uint32_t w) {
+  return ((w & ARP_ATTR_LIGAND) && (w & ARP_ATTR_ELEM_MASK) && !(w & ARP_ATTR_GHOST)) ? 1u : 0u;
+}
+
+// ---- B2: up to 32 filtered pairs, one per lane: exact distance, counters, label ladder, rows ----------------------
+__device__ __forceinline__ void exact_batch(const PairArgs& G, const DevParams& P, const uint2* q, int count, int lane, PairCounts& K) {
   uint32_t m = 0, sp = 0, sq = 0;
   double dist = 0.0;
   if (lane < count) {
     const uint2 e = q[lane];
-    // orientation flag: the row runs from e.y to e.x
-    sp = (e.x & Q_FLAG) ? e.y : (e.x & ~Q_FLAG);
-    sq = (e.x & Q_FLAG) ? (e.x & ~Q_FLAG) : e.y;
-    const RecB p = G.recB[sp], r = G.recB[sq];
-    const uint32_t wp = G.recA[sp].attr, wr = G.recA[sq].attr;
-    // pdbtbx Atom::distance: sqrt((dx*dx + dy*dy) + dz*dz), every op rounded once
-    const double dx = dsub(r.x, p.x), dy = dsub(r.y, p.y), dz = dsub(r.z, p.z);
-    dist = __dsqrt_rn(dadd(dadd(dmul(dx, dx), dmul(dy, dy)), dmul(dz, dz)));
-    m = classify_pair(G, P, p, wp, sp, r, wr, sq, dist);
+    const uint32_t sa = e.x & SLOT_MASK, sb = e.y & SLOT_MASK;
+    const RecB a = G.recB[sa], b = G.recB[sb];
+    const uint32_t wa = G.recA[sa].attr, wb = G.recA[sb].attr;
+    // rstar distance_2 / pdbtbx Atom::distance: ((dx*dx + dy*dy) + dz*dz), every operation rounded once
+    const double dx = dsub(b.x, a.x), dy = dsub(b.y, a.y), dz = dsub(b.z, a.z);
+    const double d2 = dadd(dadd(dmul(dx, dx), dmul(dy, dy)), dmul(dz, dz));
+    if (d2 <= P.rc2) {  // locate_within_distance is inclusive
+      if (e.x & QF_A) {
+        K.n_in += eligible(wa) + eligible(wb);
+        if (P.count_classified && (e.x & QF_B)) K.n_cls += 1u;
+      }
+      if ((e.x & QF_B) && (e.y & QF_B) && d2 <= P.emit_d2_max) {
+        dist = __dsqrt_rn(d2);
+        const bool swap = (e.y & QF_A) != 0u;
+        sp = swap ? sb : sa;
+        sq = swap ? sa : sb;
+        m = swap ? classify_pair(G, P, b, wb, sb, a, wa, sa, dist) : classify_pair(G, P, a, wa, sa, b, wb, sb, dist);
+      }
+    }
   }
   const uint32_t mine = __popc(m);
   if (!__any_sync(0xffffffffu, mine != 0u)) return;
@@ -81,47 +123,329 @@ __device__ __forceinline__ void classify_batch(const PairArgs& G, const DevParam
   }
 }
 
-// Stage 2: up to 32 candidate pairs, one per lane: exact cutoff test, counters, pair filter; survivors -> q2.
-__device__ __forceinline__ void exact_batch(const PairArgs& G, const DevParams& P, const uint2* q, int count, int lane, uint2* q2,
-                                            int& q2len, unsigned long long& n_in_cutoff, unsigned long long& n_classified) {
-  bool f_ab = false, f_ba = false;
-  uint32_t sa = 0, sb = 0;
+// largest squared distance (f32, guard included) at which any label of complex.rs:217-296 can fire for this pair
+__device__ __forceinline__ float label_limit2(const DevParams& P, const float* lim2, uint32_t wa, uint32_t wb) {
+  float l = lim2[((wa & ARP_ATTR_ELEM_MASK) << 4) | (wb & ARP_ATTR_ELEM_MASK)];  // clash / covalent / vdW ladder
+  const uint32_t both = wa & wb;
+  // ionic bond (opposite charges) and ionic repulsion (like charges): <= 4.0
+  const bool charged = ((wa & (ARP_ATTR_POS_CONF | ARP_ATTR_NEG_CONF)) && (wb & (ARP_ATTR_POS_CONF | ARP_ATTR_NEG_CONF)));
+  if (charged) l = fmaxf(l, 16.0f + P.guard);
+  // (weak) hydrogen bond / polar contact: an acceptor on one side, a (weak) donor on the other
+  const bool polar = ((wa & ARP_ATTR_ACCEPTOR) && (wb & (ARP_ATTR_DONOR | ARP_ATTR_WEAK_DONOR))) ||
+                     ((wb & ARP_ATTR_ACCEPTOR) && (wa & (ARP_ATTR_DONOR | ARP_ATTR_WEAK_DONOR)));
+  if (polar) l = fmaxf(l, P.polar_d2);
+  if (both & ARP_ATTR_HYDROPHOBIC) l = fmaxf(l, 20.25f + P.guard);
+  return l;
+}
+
+// ---- B1: up to 32 screened pairs, one per lane: f32 re-test, counting, label limit, pair filter; survivors -> q2 ----
+__device__ __forceinline__ void filter_batch(const PairArgs& G, const DevParams& P, const float* lim2, const uint2* q, int count, int lane,
+                                             uint2* q2, int& q2len, uint32_t& n_in32, PairCounts& K) {
+  bool go = false;
+  uint2 out = make_uint2(0u, 0u);
   if (lane < count) {
     const uint2 e = q[lane];
-    sa = e.x;
-    sb = e.y & ~Q_FLAG;
-    const RecB a = G.recB[sa], b = G.recB[sb];
-    const uint32_t wa = G.recA[sa].attr, wb = G.recA[sb].attr;
-    // rstar distance_2: ((dx*dx + dy*dy) + dz*dz); locate_within_distance is inclusive
-    const double dx = dsub(b.x, a.x), dy = dsub(b.y, a.y), dz = dsub(b.z, a.z);
-    const double d2 = dadd(dadd(dmul(dx, dx), dmul(dy, dy)), dmul(dz, dz));
-    if (d2 <= P.rc2) {
-      if (e.y & Q_FLAG) {  // not yet counted by the screen
-        n_in_cutoff += ((wa & ARP_ATTR_LIGAND) && (wa & ARP_ATTR_ELEM_MASK) && !(wa & ARP_ATTR_GHOST)) ? 1u : 0u;
-        n_in_cutoff += ((wb & ARP_ATTR_LIGAND) && (wb & ARP_ATTR_ELEM_MASK) && !(wb & ARP_ATTR_GHOST)) ? 1u : 0u;
+    const RecA a = G.recA[e.x], b = G.recA[e.y];
+    const float dx = b.x - a.x, dy = b.y - a.y, dz = b.z - a.z;
+    const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+    if (d2 <= P.thr_hit) {
+      const bool counting = P.count_in_cutoff != 0;
+      const bool cert = d2 <= P.thr_cert;
+      if (counting && cert) n_in32 += eligible(a.attr) + eligible(b.attr);
+      const bool amb = counting && !cert;  // the exact stage decides and counts
+      const bool pot = d2 <= P.thr_near && d2 <= label_limit2(P, lim2, a.attr, b.attr);
+      if (amb || pot || P.count_classified) {
+        const uint2 ka = *reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(G.recB + e.x) + 24);
+        const uint2 kb = *reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(G.recB + e.y) + 24);
+        const bool f_ab = pair_filter(a.attr, ka.x, ka.y, b.attr, kb.x, kb.y);
+        const bool f_ba = pair_filter(b.attr, kb.x, kb.y, a.attr, ka.x, ka.y);
+        const bool valid = f_ab || f_ba;
+        if (P.count_classified && cert) K.n_cls += (f_ab ? 1u : 0u) + (f_ba ? 1u : 0u);
+        go = amb || (pot && valid);
+        out.x = e.x | (amb ? QF_A : 0u) | (valid ? QF_B : 0u);
+        out.y = e.y | ((f_ba && !f_ab) ? QF_A : 0u) | (pot ? QF_B : 0u);
       }
-      f_ab = pair_filter(wa, a.chain_key, a.res_ordinal, wb, b.chain_key, b.res_ordinal);
-      f_ba = pair_filter(wb, b.chain_key, b.res_ordinal, wa, a.chain_key, a.res_ordinal);
-      n_classified += (f_ab ? 1u : 0u) + (f_ba ? 1u : 0u);
-      if (!(d2 <= P.emit_d2_max)) f_ab = f_ba = false;  // no label can fire beyond the emit radius
     }
   }
-  const uint32_t mine = (f_ab ? 1u : 0u) + (f_ba ? 1u : 0u);
-  if (__any_sync(0xffffffffu, mine != 0u)) {
-    const uint32_t inc = warp_inclusive_sum(mine, lane);
-    int pos = q2len + (int)(inc - mine);
-    if (f_ab) q2[pos++] = make_uint2(sa, sb);
-    if (f_ba) q2[pos++] = make_uint2(sa | Q_FLAG, sb);
-    q2len += (int)__shfl_sync(0xffffffffu, inc, 31);
+  const uint32_t bal = __ballot_sync(0xffffffffu, go);
+  if (bal) {
+    if (go) q2[q2len + __popc(bal & ((1u << lane) - 1u))] = out;
+    q2len += __popc(bal);
     __syncwarp();
-    while (q2len >= 32) {
-      classify_batch(G, P, q2 + (q2len - 32), 32, lane);
+    if (q2len >= 32) {
+      exact_batch(G, P, q2 + (q2len - 32), 32, lane, K);
       q2len -= 32;
       __syncwarp();
     }
   }
 }
 
-}  // namespace arpd
+// ---- stage A ----------------------------------------------------------------------------------------------------
+struct Cand {
+  float x[SLOTS], y[SLOTS], z[SLOTS], h[SLOTS];
+  uint32_t t[SLOTS];  // sorted slot of the candidate | eligible << 31
+};
 
-#include "pair_kernel_main.cuh"
+// The screen: every from-atom of the pass against the 4 candidates of this lane.
+// lim[u] = number of leading from-atoms candidate u may pair with (own-cell candidates pair only with the atoms that
+// precede them, everything else with all of them).  TRI = 0: no own-cell atom among the candidates, 1: only in slot 0,
+// 2: anywhere.
+template <int TRI>
+__device__ __forceinline__ void screen_pass(const FromRec* sf, int nf, const Cand& C, const uint32_t (&lim)[SLOTS], uint32_t (&mask)[SLOTS],
+                                            uint32_t (&cnt)[SLOTS]) {
+#pragma unroll 2
+  for (int i = 0; i < nf; ++i) {
+    const float4 f = *reinterpret_cast<const float4*>(&sf[i]);
+    const float4 g = *(reinterpret_cast<const float4*>(&sf[i]) + 1);
+    const uint32_t w = __float_as_uint(g.z);
+    const uint32_t bit = 1u << i;
+#pragma unroll
+    for (int u = 0; u < SLOTS; ++u) {
+      const float s = fmaf(f.x, C.x[u], fmaf(f.y, C.y[u], fmaf(f.z, C.z[u], C.h[u])));
+      // inside = tri && s >= k_cert && s < k_near;  push = tri && s >= k_hit && !inside; predicated add / or
+      // (written in PTX: the compiler otherwise turns both updates into SEL + ALU pairs)
+      if (TRI == 2 || (TRI == 1 && u == 0)) {
+        asm("{\n\t.reg .pred pt, pi, pp;\n\t"
+            "setp.lt.u32 pt, %8, %9;\n\t"
+            "setp.ge.and.f32 pi, %2, %3, pt;\n\t"
+            "setp.lt.and.f32 pi, %2, %4, pi;\n\t"
+            "setp.ge.and.f32 pp, %2, %5, pt;\n\t"
+            "and.pred pp, pp, !pi;\n\t"
+            "@pi add.u32 %0, %0, %6;\n\t"
+            "@pp or.b32 %1, %1, %7;\n\t}"
+            : "+r"(cnt[u]), "+r"(mask[u])
+            : "f"(s), "f"(g.x), "f"(g.y), "f"(f.w), "r"(w), "r"(bit), "r"((uint32_t)i), "r"(lim[u]));
+      } else {
+        asm("{\n\t.reg .pred pi, pp;\n\t"
+            "setp.ge.f32 pi, %2, %3;\n\t"
+            "setp.lt.and.f32 pi, %2, %4, pi;\n\t"
+            "setp.ge.and.f32 pp, %2, %5, !pi;\n\t"
+            "@pi add.u32 %0, %0, %6;\n\t"
+            "@pp or.b32 %1, %1, %7;\n\t}"
+            : "+r"(cnt[u]), "+r"(mask[u])
+            : "f"(s), "f"(g.x), "f"(g.y), "f"(f.w), "r"(w), "r"(bit));
+      }
+    }
+  }
+}
+
+// drain full batches of q1 through B1 (and, behind it, B2)
+__device__ __forceinline__ void drain_q1(const PairArgs& G, const DevParams& P, const float* lim2, uint2* q1, int& q1len, uint2* q2,
+                                         int& q2len, int lane, uint32_t& n_in32, PairCounts& K) {
+  while (q1len >= 32) {
+    filter_batch(G, P, lim2, q1 + (q1len - 32), 32, lane, q2, q2len, n_in32, K);
+    q1len -= 32;
+    __syncwarp();
+  }
+}
+
+// masks -> q1.  Entries are (from slot, candidate slot); bounded queue: when it fills up it is drained and the
+// remaining bits are expanded in another round.
+__device__ __forceinline__ void expand_masks(const PairArgs& G, const DevParams& P, const float* lim2, uint32_t (&mask)[SLOTS],
+                                             const Cand& C, uint32_t from_slot0, uint2* q1, int& q1len, uint2* q2, int& q2len, int lane,
+                                             uint32_t& n_in32, PairCounts& K) {
+  uint32_t mine = 0;
+#pragma unroll
+  for (int u = 0; u < SLOTS; ++u) mine += __popc(mask[u]);
+  while (__any_sync(0xffffffffu, mine != 0u)) {
+    const uint32_t inc = warp_inclusive_sum(mine, lane);
+    const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+    uint32_t pos = (uint32_t)q1len + (inc - mine);
+#pragma unroll
+    for (int u = 0; u < SLOTS; ++u) {
+      const uint32_t t = C.t[u] & SLOT_MASK;
+      while (mask[u] && pos < (uint32_t)Q1_CAP) {
+        const uint32_t i = __ffs(mask[u]) - 1;
+        mask[u] &= mask[u] - 1;
+        q1[pos++] = make_uint2(from_slot0 + i, t);
+        --mine;
+      }
+    }
+    q1len = min(q1len + (int)total, Q1_CAP);
+    __syncwarp();
+    drain_q1(G, P, lim2, q1, q1len, q2, q2len, lane, n_in32, K);
+  }
+}
+
+// candidate e of the item -> sorted slot
+__device__ __forceinline__ uint32_t cand_slot(uint32_t e, uint32_t cb, const uint32_t (&off)[4], const uint32_t (&delta)[4]) {
+  uint32_t d = cb;
+  d = e >= off[0] ? delta[0] : d;
+  d = e >= off[1] ? delta[1] : d;
+  d = e >= off[2] ? delta[2] : d;
+  d = e >= off[3] ? delta[3] : d;
+  return e + d;
+}
+
+struct RawChunk {
+  uint4 r[SLOTS];      // RecA bits; attr = 0xffffffff marks "no candidate"
+  uint32_t t[SLOTS];
+};
+
+// issue the loads of candidates [chunk0, chunk0 + CHUNK) of the item whose record is spread over the lanes (word)
+__device__ __forceinline__ void load_chunk(const PairArgs& G, uint32_t word, uint32_t chunk0, int lane, RawChunk& R) {
+  const uint32_t cb = __shfl_sync(0xffffffffu, word, 0), total = __shfl_sync(0xffffffffu, word, 2);
+  uint32_t off[4], delta[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    off[k] = __shfl_sync(0xffffffffu, word, 4 + k);
+    delta[k] = __shfl_sync(0xffffffffu, word, 8 + k);
+  }
+#pragma unroll
+  for (int u = 0; u < SLOTS; ++u) {
+    const uint32_t e = chunk0 + 32u * u + lane;
+    R.t[u] = cand_slot(e, cb, off, delta);
+    R.r[u] = make_uint4(0u, 0u, 0u, 0xffffffffu);
+    if (e < total) R.r[u] = *reinterpret_cast<const uint4*>(G.recA + R.t[u]);
+  }
+}
+
+__device__ __forceinline__ uint32_t fetch_cursor(const PairArgs& G, int lane) {
+  uint32_t w = 0;
+  if (lane == 0) w = atomicAdd(&G.ctr->work, 1u);
+  return __shfl_sync(0xffffffffu, w, 0);
+}
+// word `lane` of item w (lanes 16..31 and out-of-range items read nothing); total = 0 marks the end
+__device__ __forceinline__ uint32_t fetch_item(const PairArgs& G, uint32_t w, uint32_t n_items, int lane) {
+  uint32_t v = 0;
+  if (w < n_items && lane < 16) v = reinterpret_cast<const uint32_t*>(G.items + w)[lane];
+  return v;
+}
+
+__global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_pairs(const PairArgs G, const DevParams P) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  PairSmem& S = *reinterpret_cast<PairSmem*>(smem_raw);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  // per element-class pair: no vdW-ladder label beyond (max(cov sum, vdW sum) + comp)^2 (vdw.rs:33-41)
+  for (int k = threadIdx.x; k < 256; k += PAIR_THREADS) {
+    const int ea = k >> 4, eb = k & 15;
+    const double r = fmax(P.cov[ea] + P.cov[eb], P.vdw[ea] + P.vdw[eb]) + fabs(P.comp);
+    const double r2 = r > 0.0 ? r * r * (1.0 + 1e-9) : 0.0;
+    S.lim2[k] = __double2float_ru(r2) + P.guard;
+  }
+  __syncthreads();
+  FromRec* sfrom = S.from[wid];
+  uint2* q1 = S.q1[wid];
+  uint2* q2 = S.q2[wid];
+  const float* lim2 = S.lim2;
+  int q1len = 0, q2len = 0;
+  uint32_t n_in32 = 0;  // pairs counted in f32 (screen and B1), per lane; flushed into 64 bits per item
+  PairCounts K{0ull, 0ull};
+  unsigned long long n_screened = 0, n_in = 0;
+  const uint32_t n_items = G.ctr->n_items;
+  const float half_hit = 0.5f * P.scr_hit, half_cert = 0.5f * P.scr_cert, half_near = 0.5f * P.scr_near;
+
+  // ---- pipeline prologue ------------------------------------------------------------------------------------------
+  uint32_t w_next = fetch_cursor(G, lane);
+  uint32_t word = fetch_item(G, w_next, n_items, lane);      // current item
+  w_next = fetch_cursor(G, lane);
+  uint32_t word_n = fetch_item(G, w_next, n_items, lane);    // next item
+  w_next = fetch_cursor(G, lane);                            // cursor of the item after that
+  uint32_t chunk0 = 0;
+  RawChunk raw;
+  load_chunk(G, word, 0, lane, raw);
+
+  while (__shfl_sync(0xffffffffu, word, 2) != 0u) {
+    const uint32_t cb = __shfl_sync(0xffffffffu, word, 0), n_own = __shfl_sync(0xffffffffu, word, 1),
+                   total = __shfl_sync(0xffffffffu, word, 2);
+    const float ccx = __uint_as_float(__shfl_sync(0xffffffffu, word, 12)), ccy = __uint_as_float(__shfl_sync(0xffffffffu, word, 13)),
+                ccz = __uint_as_float(__shfl_sync(0xffffffffu, word, 14));
+    // ---- this chunk's candidates: registers, cell-local frame ----------------------------------------------------------
+    Cand C;
+    uint4 own_raw = raw.r[0];  // chunk 0: lane < n_own holds own atom `lane`
+#pragma unroll
+    for (int u = 0; u < SLOTS; ++u) {
+      const bool ok = raw.r[u].w != 0xffffffffu;
+      const float x = __uint_as_float(raw.r[u].x) - ccx, y = __uint_as_float(raw.r[u].y) - ccy, z = __uint_as_float(raw.r[u].z) - ccz;
+      C.x[u] = ok ? x : 0.f;
+      C.y[u] = ok ? y : 0.f;
+      C.z[u] = ok ? z : 0.f;
+      C.h[u] = ok ? -0.5f * fmaf(z, z, fmaf(y, y, x * x)) : -1.0e30f;
+      C.t[u] = raw.t[u] | (ok ? (eligible(raw.r[u].w) << 31) : 0u);
+    }
+    // ---- prefetch: the next chunk of this item, or chunk 0 of the next item -------------------------------------------
+    const bool more = chunk0 + CHUNK < total;
+    uint32_t word_nn = word_n, w_nn = w_next;
+    if (more) {
+      load_chunk(G, word, chunk0 + CHUNK, lane, raw);
+    } else {
+      load_chunk(G, word_n, 0, lane, raw);
+      word_nn = fetch_item(G, w_next, n_items, lane);
+      w_nn = fetch_cursor(G, lane);
+    }
+    if (chunk0 == 0 && lane == 0)
+      n_screened += (unsigned long long)n_own * (total - n_own) + (unsigned long long)n_own * (n_own - 1) / 2;
+
+    // ---- from-atoms in passes of 32 (one pass for every realistic cell) ------------------------------------------------
+    for (uint32_t fbo = 0; fbo < n_own; fbo += FROM_PASS) {
+      const int nf = (int)min((uint32_t)FROM_PASS, n_own - fbo);
+      __syncwarp();
+      if (lane < nf && (chunk0 == 0 || n_own > (uint32_t)FROM_PASS)) {  // a single pass stays staged for the later chunks
+        uint4 fr = own_raw;
+        if (chunk0 != 0 || fbo != 0) fr = *reinterpret_cast<const uint4*>(G.recA + cb + fbo + lane);
+        FromRec f;
+        f.x = __uint_as_float(fr.x) - ccx;
+        f.y = __uint_as_float(fr.y) - ccy;
+        f.z = __uint_as_float(fr.z) - ccz;
+        const float hf = 0.5f * fmaf(f.z, f.z, fmaf(f.y, f.y, f.x * f.x));
+        f.k_hit = hf - half_hit;
+        f.k_cert = hf - half_cert;
+        f.k_near = hf - half_near;
+        f.w = (eligible(fr.w) << 16) | 1u;
+        f.pad = 0u;
+        sfrom[lane] = f;
+      }
+      __syncwarp();
+      uint32_t lim[SLOTS], mask[SLOTS], cnt[SLOTS];
+#pragma unroll
+      for (int u = 0; u < SLOTS; ++u) {
+        const uint32_t e = chunk0 + 32u * u + lane;
+        lim[u] = e < n_own ? (e > fbo ? e - fbo : 0u) : 0xffffffffu;
+        mask[u] = cnt[u] = 0u;
+      }
+      if (chunk0 >= n_own)
+        screen_pass<0>(sfrom, nf, C, lim, mask, cnt);
+      else if (chunk0 + 32u >= n_own)
+        screen_pass<1>(sfrom, nf, C, lim, mask, cnt);
+      else
+        screen_pass<2>(sfrom, nf, C, lim, mask, cnt);
+      if (P.count_in_cutoff) {
+#pragma unroll
+        for (int u = 0; u < SLOTS; ++u) n_in32 += (cnt[u] >> 16) + (cnt[u] & 0xffffu) * (C.t[u] >> 31);
+      }
+      expand_masks(G, P, lim2, mask, C, cb + fbo, q1, q1len, q2, q2len, lane, n_in32, K);
+    }
+    n_in += n_in32;
+    n_in32 = 0;
+
+    // ---- advance ------------------------------------------------------------------------------------------------------
+    if (more) {
+      chunk0 += CHUNK;
+    } else {
+      chunk0 = 0;
+      word = word_n;
+      word_n = word_nn;
+      w_next = w_nn;
+    }
+  }
+  // ---- tails of the queues ------------------------------------------------------------------------------------------
+  if (q1len > 0) filter_batch(G, P, lim2, q1, q1len, lane, q2, q2len, n_in32, K);
+  __syncwarp();
+  if (q2len > 0) exact_batch(G, P, q2, q2len, lane, K);
+  n_in += n_in32;
+  n_in += K.n_in;
+  unsigned long long n_cls = K.n_cls;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    n_screened += __shfl_xor_sync(0xffffffffu, n_screened, o);
+    n_in += __shfl_xor_sync(0xffffffffu, n_in, o);
+    n_cls += __shfl_xor_sync(0xffffffffu, n_cls, o);
+  }
+  if (lane == 0) {
+    atomicAdd(&G.ctr->screened, n_screened);
+    atomicAdd(&G.ctr->in_cutoff, n_in);
+    atomicAdd(&G.ctr->classified, n_cls);
+  }
+}
+
+}  // namespace arpd
