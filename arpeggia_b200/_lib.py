@@ -6,13 +6,15 @@ fallback of any kind: a missing library raises ImportError, a missing GPU makes 
 from __future__ import annotations
 
 import ctypes as C
+import os
 import subprocess
 from pathlib import Path
 
 import numpy as np
 
 _PKG = Path(__file__).resolve().parent
-LIB_PATH = _PKG / "_build" / "libarpeggia_b200.so"
+# ARPEGGIA_B200_LIB: kernel-tuning builds of the same library (scratch/variants.sh); never a different implementation
+LIB_PATH = Path(os.environ.get("ARPEGGIA_B200_LIB") or (_PKG / "_build" / "libarpeggia_b200.so"))
 
 # byte-identical to arp_atom_record (include/arpeggia_host.h)
 ATOM_DTYPE = np.dtype(

@@ -27,6 +27,25 @@ __device__ __forceinline__ bool pair_filter(uint32_t wp, uint32_t kp, uint32_t o
   return !(both && kp > kq);                                                              // complex.rs:124-129
 }
 
+// Both orientations of an unordered pair at once: 0 = neither passes, 1 = a -> b, 2 = b -> a.  At most one orientation
+// can pass: within a chain the row runs from the earlier residue to the later one (complex.rs:112-113); across chains
+// either only one side satisfies ligand -> receptor, or both do and the string-order dedupe keeps one (complex.rs:124-129).
+__device__ __forceinline__ int pair_direction(uint32_t wa, uint32_t ka, uint32_t oa, uint32_t wb, uint32_t kb, uint32_t ob) {
+  if ((wa & ARP_ATTR_ELEM_MASK) == 0u || (wb & ARP_ATTR_ELEM_MASK) == 0u) return 0;  // hydrogens, complex.rs:83-87
+  if ((ka ^ kb) >> 24) return 0;                                                      // different models, complex.rs:96
+  const bool ab = (wa & ARP_ATTR_LIGAND) && (wb & ARP_ATTR_RECEPTOR) && !(wa & ARP_ATTR_GHOST);
+  const bool ba = (wb & ARP_ATTR_LIGAND) && (wa & ARP_ATTR_RECEPTOR) && !(wb & ARP_ATTR_GHOST);
+  if (ka == kb) {
+    if (ab && ob > 1u && oa < ob - 1u) return 1;
+    if (ba && oa > 1u && ob < oa - 1u) return 2;
+    return 0;
+  }
+  const bool both = (wa & wb & ARP_ATTR_LIGAND) && (wa & wb & ARP_ATTR_RECEPTOR);
+  if (ab && !(both && ka > kb)) return 1;
+  if (ba && !(both && kb > ka)) return 2;
+  return 0;
+}
+
 // complex.rs:94-131 with symmetric = false (ring -> atom), ring r, atom y
 __device__ __forceinline__ bool ring_atom_filter(uint32_t wr, uint32_t kr, uint32_t orr, uint32_t wy, uint32_t ky, uint32_t oy) {
   if (wr & ARP_ATTR_GHOST) return false;
@@ -102,12 +121,19 @@ __device__ __forceinline__ uint32_t classify_pair(const PairArgs& G, const DevPa
   // ionic.rs:11-22
   const bool ion_pair = ((wa & ARP_ATTR_POS_CONF) && (wb & ARP_ATTR_NEG_CONF)) || ((wb & ARP_ATTR_POS_CONF) && (wa & ARP_ATTR_NEG_CONF));
   const bool ionic = ion_pair && dist <= 4.0;
-  // hbond.rs:30-66 with is_donor_acceptor_pair (entity1 is tried as the donor first)
-  int hb = 0;
-  if ((wa & ARP_ATTR_DONOR) && (wb & ARP_ATTR_ACCEPTOR))
-    hb = hbond_body(G, P, a.x, a.y, a.z, b.x, b.y, b.z, G.res_sorted[sa], eb, dist, P.ang.a_ge_90);
-  else if ((wb & ARP_ATTR_DONOR) && (wa & ARP_ATTR_ACCEPTOR))
-    hb = hbond_body(G, P, b.x, b.y, b.z, a.x, a.y, a.z, G.res_sorted[sb], ea, dist, P.ang.a_ge_90);
+  // hbond.rs:30-66 (k = 0, donors) and hbond.rs:74-110 (k = 1, weak donors), both with is_donor_acceptor_pair: entity1 is
+  // tried as the donor first.  One rolled loop = one instance of hbond_body (instruction-cache footprint).
+  int hb = 0, wk = 0;
+#pragma unroll 1
+  for (int k = 0; k < 2; ++k) {
+    const uint32_t dflag = k ? ARP_ATTR_WEAK_DONOR : ARP_ATTR_DONOR;
+    const bool fa = (wa & dflag) && (wb & ARP_ATTR_ACCEPTOR);
+    const bool fb = !fa && (wb & dflag) && (wa & ARP_ATTR_ACCEPTOR);
+    if (!(fa || fb)) continue;
+    const int r = hbond_body(G, P, fa ? a.x : b.x, fa ? a.y : b.y, fa ? a.z : b.z, fa ? b.x : a.x, fa ? b.y : a.y, fa ? b.z : a.z,
+                             G.res_sorted[fa ? sa : sb], fa ? eb : ea, dist, k ? P.ang.a_ge_130 : P.ang.a_ge_90);
+    if (k) wk = r; else hb = r;
+  }
   // complex.rs:240-251
   if (ionic)
     m |= (hb == 2) ? LBIT(ARP_SaltBridge) : LBIT(ARP_IonicBond);
@@ -115,12 +141,6 @@ __device__ __forceinline__ uint32_t classify_pair(const PairArgs& G, const DevPa
     m |= LBIT(ARP_HydrogenBond);
   else if (hb == 1)
     m |= LBIT(ARP_PolarContact);
-  // hbond.rs:74-110
-  int wk = 0;
-  if ((wa & ARP_ATTR_WEAK_DONOR) && (wb & ARP_ATTR_ACCEPTOR))
-    wk = hbond_body(G, P, a.x, a.y, a.z, b.x, b.y, b.z, G.res_sorted[sa], eb, dist, P.ang.a_ge_130);
-  else if ((wb & ARP_ATTR_WEAK_DONOR) && (wa & ARP_ATTR_ACCEPTOR))
-    wk = hbond_body(G, P, b.x, b.y, b.z, a.x, a.y, a.z, G.res_sorted[sb], ea, dist, P.ang.a_ge_130);
   if (wk == 2) m |= LBIT(ARP_WeakHydrogenBond);
   if (wk == 1) m |= LBIT(ARP_WeakPolarContact);
   // ionic.rs:25-35

@@ -67,6 +67,7 @@ struct DevParams {
   float scr_cert;
   float scr_near;
   float guard;           // g (added to the per-pair label limits)
+  float guard_a;         // gA (added to the per-atom label limits of the screen)
   float polar_d2;        // largest squared distance of an H-bond / polar label: 4.0^2 with hydrogens in the job, else 3.5^2
   float edge;            // atom-grid cell edge
   int count_classified;  // 1: every in-cutoff pair goes through the exact filter (pairs_classified is counted)

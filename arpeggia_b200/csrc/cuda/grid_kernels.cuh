@@ -205,7 +205,9 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
   ra.x = (float)(px - d.ox);
   ra.y = (float)(py - d.oy);
   ra.z = (float)(pz - d.oz);
-  ra.attr = attr[a];
+  // bit 31 of the sorted attribute word (internal): the atom may start a row / counts as `from` (complex.rs:200-202)
+  const uint32_t w = attr[a] & 0x7fffffffu;
+  ra.attr = w | (((w & ARP_ATTR_LIGAND) && (w & ARP_ATTR_ELEM_MASK) && !(w & ARP_ATTR_GHOST)) ? 0x80000000u : 0u);
   recA[slot] = ra;
   RecB rb;
   rb.x = px;

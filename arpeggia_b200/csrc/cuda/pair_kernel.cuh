@@ -7,7 +7,7 @@
 // orientation of the row is decided later by the pair filter (at most one orientation of a pair can pass
 // should_compare_entities, complex.rs:76-131).
 //
-// Stage A, the screen (all the volume: ~116 tests per atom at protein density).  Lanes own CANDIDATES: 4 per lane,
+// Stage A, the screen (all the volume: ~116 tests per atom at protein density).  Lanes own CANDIDATES: up to 6 per lane,
 // held in registers in a cell-local f32 frame (cx, cy, cz, h = -|c|^2/2); the cell's own atoms are broadcast from
 // shared memory one after the other as (fx, fy, fz, k).  With s = f.c + h the test d^2 <= T is s >= |f|^2/2 - T/2,
 // i.e. three FMAs and compares against per-from-atom constants -- no subtraction, no square, no branch:
@@ -24,7 +24,8 @@
 //       through a warp prefix sum and ONE atomicAdd per 32 pairs.
 //
 // Latency.  A warp always has three items in flight: cursor of item k+3 (atomic), record of item k+2 (one
-// coalesced 64-byte load), candidates of item k+1 (four 16-byte loads per lane, issued before item k is computed).
+// coalesced 64-byte load), candidates of item k+1 (cp.async into the warp's double-buffered shared-memory stage, issued
+// before item k is computed; no registers are held while the copies fly).
 #pragma once
 #include "classify.cuh"
 
@@ -33,9 +34,9 @@ namespace arpd {
 constexpr int PAIR_WARPS = 4;
 constexpr int PAIR_THREADS = PAIR_WARPS * 32;
 #ifndef PAIR_MIN_BLOCKS
-#define PAIR_MIN_BLOCKS 5
+#define PAIR_MIN_BLOCKS 4
 #endif
-constexpr int SLOTS = 4;                 // candidates per lane per chunk
+constexpr int SLOTS = 6;                 // candidates per lane per chunk
 constexpr int CHUNK = 32 * SLOTS;        // candidates per chunk
 constexpr int FROM_PASS = 32;            // from-atoms per pass (bits of a mask)
 constexpr int Q1_CAP = 256;              // screened pairs waiting for B1
@@ -53,10 +54,14 @@ struct __align__(16) FromRec {
 };
 
 struct PairSmem {
+  uint4 buf[PAIR_WARPS][2][CHUNK];      // staged candidate records (RecA bits), double buffered
+  uint32_t tbuf[PAIR_WARPS][2][CHUNK];  // their sorted slots
   FromRec from[PAIR_WARPS][FROM_PASS];
   uint2 q1[PAIR_WARPS][Q1_CAP];
   uint2 q2[PAIR_WARPS][Q2_CAP];
-  float lim2[256];           // per element-class pair: (max(cov sum, vdW sum) + comp)^2, rounded up
+  unsigned long long acc[PAIR_WARPS][4];
+  float lim2[256];           // per element-class pair: (max(cov sum, vdW sum) + |comp|)^2 + g, rounded up
+  float lim1[16];            // per element class: largest entry of its row
 };
 
 struct PairCounts {
@@ -72,10 +77,9 @@ __device__ __forceinline__ uint32_t warp_inclusive_sum(uint32_t v, int lane) {
   return v;
 }
 
-// atoms that can start a row / are counted as `from`: in the ligand set, not hydrogen, not a ghost (complex.rs:200-202)
-__device__ __forceinline__ uint32_t eligible(uint32_t w) {
-  return ((w & ARP_ATTR_LIGAND) && (w & ARP_ATTR_ELEM_MASK) && !(w & ARP_ATTR_GHOST)) ? 1u : 0u;
-}
+// atoms that can start a row / are counted as `from`: in the ligand set, not hydrogen, not a ghost (complex.rs:200-202);
+// k_scatter_atoms caches the predicate in bit 31 of the sorted attribute word
+__device__ __forceinline__ uint32_t eligible(uint32_t w) { return w >> 31; }
 
 // ---- B2: up to 32 filtered pairs, one per lane: exact distance, counters, label ladder, rows ----------------------
 __device__ __forceinline__ void exact_batch(const PairArgs& G, const DevParams& P, const uint2* q, int count, int lane, PairCounts& K) {
@@ -99,7 +103,13 @@ __device__ __forceinline__ void exact_batch(const PairArgs& G, const DevParams& 
         const bool swap = (e.y & QF_A) != 0u;
         sp = swap ? sb : sa;
         sq = swap ? sa : sb;
-        m = swap ? classify_pair(G, P, b, wb, sb, a, wa, sa, dist) : classify_pair(G, P, a, wa, sa, b, wb, sb, dist);
+        // one instance of the ladder (instruction-cache footprint): operands selected, not two inlined calls
+        RecB p, r;
+        p.x = swap ? b.x : a.x, p.y = swap ? b.y : a.y, p.z = swap ? b.z : a.z;
+        r.x = swap ? a.x : b.x, r.y = swap ? a.y : b.y, r.z = swap ? a.z : b.z;
+        p.chain_key = r.chain_key = 0u;      // classify_pair reads positions only
+        p.res_ordinal = r.res_ordinal = 0u;
+        m = classify_pair(G, P, p, swap ? wb : wa, sp, r, swap ? wa : wb, sq, dist);
       }
     }
   }
@@ -139,13 +149,17 @@ __device__ __forceinline__ float label_limit2(const DevParams& P, const float* l
 }
 
 // ---- B1: up to 32 screened pairs, one per lane: f32 re-test, counting, label limit, pair filter; survivors -> q2 ----
+// flush_q2: this is the last batch of the kernel, q2 is emptied completely behind it.
 __device__ __forceinline__ void filter_batch(const PairArgs& G, const DevParams& P, const float* lim2, const uint2* q, int count, int lane,
-                                             uint2* q2, int& q2len, uint32_t& n_in32, PairCounts& K) {
+                                             uint2* q2, int& q2len, uint32_t& n_in32, PairCounts& K, bool flush_q2) {
   bool go = false;
   uint2 out = make_uint2(0u, 0u);
   if (lane < count) {
     const uint2 e = q[lane];
     const RecA a = G.recA[e.x], b = G.recA[e.y];
+    // chain key + residue ordinal of both atoms, requested together with the positions (one latency, not two)
+    const uint2 ka = *reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(G.recB + e.x) + 24);
+    const uint2 kb = *reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(G.recB + e.y) + 24);
     const float dx = b.x - a.x, dy = b.y - a.y, dz = b.z - a.z;
     const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
     if (d2 <= P.thr_hit) {
@@ -155,28 +169,24 @@ __device__ __forceinline__ void filter_batch(const PairArgs& G, const DevParams&
       const bool amb = counting && !cert;  // the exact stage decides and counts
       const bool pot = d2 <= P.thr_near && d2 <= label_limit2(P, lim2, a.attr, b.attr);
       if (amb || pot || P.count_classified) {
-        const uint2 ka = *reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(G.recB + e.x) + 24);
-        const uint2 kb = *reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(G.recB + e.y) + 24);
-        const bool f_ab = pair_filter(a.attr, ka.x, ka.y, b.attr, kb.x, kb.y);
-        const bool f_ba = pair_filter(b.attr, kb.x, kb.y, a.attr, ka.x, ka.y);
-        const bool valid = f_ab || f_ba;
-        if (P.count_classified && cert) K.n_cls += (f_ab ? 1u : 0u) + (f_ba ? 1u : 0u);
+        const int dir = pair_direction(a.attr, ka.x, ka.y, b.attr, kb.x, kb.y);
+        const bool valid = dir != 0;
+        if (P.count_classified && cert) K.n_cls += valid ? 1u : 0u;
         go = amb || (pot && valid);
         out.x = e.x | (amb ? QF_A : 0u) | (valid ? QF_B : 0u);
-        out.y = e.y | ((f_ba && !f_ab) ? QF_A : 0u) | (pot ? QF_B : 0u);
+        out.y = e.y | (dir == 2 ? QF_A : 0u) | (pot ? QF_B : 0u);
       }
     }
   }
   const uint32_t bal = __ballot_sync(0xffffffffu, go);
-  if (bal) {
-    if (go) q2[q2len + __popc(bal & ((1u << lane) - 1u))] = out;
-    q2len += __popc(bal);
+  if (go) q2[q2len + __popc(bal & ((1u << lane) - 1u))] = out;
+  q2len += __popc(bal);
+  __syncwarp();
+  while (q2len >= 32 || (flush_q2 && q2len > 0)) {  // the only call site of exact_batch
+    const int m = min(q2len, 32);
+    exact_batch(G, P, q2 + (q2len - m), m, lane, K);
+    q2len -= m;
     __syncwarp();
-    if (q2len >= 32) {
-      exact_batch(G, P, q2 + (q2len - 32), 32, lane, K);
-      q2len -= 32;
-      __syncwarp();
-    }
   }
 }
 
@@ -186,11 +196,11 @@ struct Cand {
   uint32_t t[SLOTS];  // sorted slot of the candidate | eligible << 31
 };
 
-// The screen: every from-atom of the pass against the 4 candidates of this lane.
+// The screen: every from-atom of the pass against the NS candidates of this lane.
 // lim[u] = number of leading from-atoms candidate u may pair with (own-cell candidates pair only with the atoms that
 // precede them, everything else with all of them).  TRI = 0: no own-cell atom among the candidates, 1: only in slot 0,
-// 2: anywhere.
-template <int TRI>
+// 2: anywhere.  NS = slots of the chunk that hold candidates (the last chunk of an item is rarely full).
+template <int TRI, int NS>
 __device__ __forceinline__ void screen_pass(const FromRec* sf, int nf, const Cand& C, const uint32_t (&lim)[SLOTS], uint32_t (&mask)[SLOTS],
                                             uint32_t (&cnt)[SLOTS]) {
 #pragma unroll 2
@@ -200,7 +210,7 @@ __device__ __forceinline__ void screen_pass(const FromRec* sf, int nf, const Can
     const uint32_t w = __float_as_uint(g.z);
     const uint32_t bit = 1u << i;
 #pragma unroll
-    for (int u = 0; u < SLOTS; ++u) {
+    for (int u = 0; u < NS; ++u) {
       const float s = fmaf(f.x, C.x[u], fmaf(f.y, C.y[u], fmaf(f.z, C.z[u], C.h[u])));
       // inside = tri && s >= k_cert && s < k_near;  push = tri && s >= k_hit && !inside; predicated add / or
       // (written in PTX: the compiler otherwise turns both updates into SEL + ALU pairs)
@@ -229,12 +239,14 @@ __device__ __forceinline__ void screen_pass(const FromRec* sf, int nf, const Can
   }
 }
 
-// drain full batches of q1 through B1 (and, behind it, B2)
+// drain full batches of q1 through B1 (and, behind it, B2); flush: everything, partial batches included (end of kernel)
 __device__ __forceinline__ void drain_q1(const PairArgs& G, const DevParams& P, const float* lim2, uint2* q1, int& q1len, uint2* q2,
-                                         int& q2len, int lane, uint32_t& n_in32, PairCounts& K) {
-  while (q1len >= 32) {
-    filter_batch(G, P, lim2, q1 + (q1len - 32), 32, lane, q2, q2len, n_in32, K);
-    q1len -= 32;
+                                         int& q2len, int lane, uint32_t& n_in32, PairCounts& K, bool flush) {
+  while (true) {  // the only call site of filter_batch
+    const int n = q1len >= 32 ? 32 : (flush ? q1len : 0);
+    if (n == 0 && !(flush && q2len > 0)) break;
+    filter_batch(G, P, lim2, q1 + (q1len - n), n, lane, q2, q2len, n_in32, K, flush && q1len == n);
+    q1len -= n;
     __syncwarp();
   }
 }
@@ -243,11 +255,11 @@ __device__ __forceinline__ void drain_q1(const PairArgs& G, const DevParams& P, 
 // remaining bits are expanded in another round.
 __device__ __forceinline__ void expand_masks(const PairArgs& G, const DevParams& P, const float* lim2, uint32_t (&mask)[SLOTS],
                                              const Cand& C, uint32_t from_slot0, uint2* q1, int& q1len, uint2* q2, int& q2len, int lane,
-                                             uint32_t& n_in32, PairCounts& K) {
+                                             uint32_t& n_in32, PairCounts& K, bool flush) {
   uint32_t mine = 0;
 #pragma unroll
   for (int u = 0; u < SLOTS; ++u) mine += __popc(mask[u]);
-  while (__any_sync(0xffffffffu, mine != 0u)) {
+  while (__any_sync(0xffffffffu, mine != 0u) || flush) {
     const uint32_t inc = warp_inclusive_sum(mine, lane);
     const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
     uint32_t pos = (uint32_t)q1len + (inc - mine);
@@ -263,7 +275,8 @@ __device__ __forceinline__ void expand_masks(const PairArgs& G, const DevParams&
     }
     q1len = min(q1len + (int)total, Q1_CAP);
     __syncwarp();
-    drain_q1(G, P, lim2, q1, q1len, q2, q2len, lane, n_in32, K);
+    drain_q1(G, P, lim2, q1, q1len, q2, q2len, lane, n_in32, K, flush);  // the only call site
+    if (flush) break;
   }
 }
 
@@ -277,13 +290,16 @@ __device__ __forceinline__ uint32_t cand_slot(uint32_t e, uint32_t cb, const uin
   return e + d;
 }
 
-struct RawChunk {
-  uint4 r[SLOTS];      // RecA bits; attr = 0xffffffff marks "no candidate"
-  uint32_t t[SLOTS];
-};
+// ---- asynchronous staging of the next unit's candidates (cp.async: no registers are held while the copy is in flight) ----
+__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-// issue the loads of candidates [chunk0, chunk0 + CHUNK) of the item whose record is spread over the lanes (word)
-__device__ __forceinline__ void load_chunk(const PairArgs& G, uint32_t word, uint32_t chunk0, int lane, RawChunk& R) {
+// candidates [chunk0, chunk0 + CHUNK) of the item whose record is spread over the lanes (word): records -> buf, slots -> tbuf.
+// Lane l stages (and later reads) entries l, l + 32, ...: no cross-lane dependency.
+__device__ __forceinline__ void stage_chunk(const PairArgs& G, uint32_t word, uint32_t chunk0, int lane, uint4* buf, uint32_t* tbuf) {
   const uint32_t cb = __shfl_sync(0xffffffffu, word, 0), total = __shfl_sync(0xffffffffu, word, 2);
   uint32_t off[4], delta[4];
 #pragma unroll
@@ -294,16 +310,23 @@ __device__ __forceinline__ void load_chunk(const PairArgs& G, uint32_t word, uin
 #pragma unroll
   for (int u = 0; u < SLOTS; ++u) {
     const uint32_t e = chunk0 + 32u * u + lane;
-    R.t[u] = cand_slot(e, cb, off, delta);
-    R.r[u] = make_uint4(0u, 0u, 0u, 0xffffffffu);
-    if (e < total) R.r[u] = *reinterpret_cast<const uint4*>(G.recA + R.t[u]);
+    if (chunk0 + 32u * u < total) {  // warp-uniform: slots beyond the item are never read
+      const uint32_t t = cand_slot(e, cb, off, delta);
+      tbuf[32 * u + lane] = t;
+      if (e < total)
+        cp_async16(buf + 32 * u + lane, G.recA + t);
+      else
+        buf[32 * u + lane] = make_uint4(0x5d5e0b6bu, 0x5d5e0b6bu, 0x5d5e0b6bu, 0u);  // "no candidate": a point 1e18 A away
+    }
   }
+  cp_async_commit();
 }
 
-__device__ __forceinline__ uint32_t fetch_cursor(const PairArgs& G, int lane) {
+// lane 0 draws the next item index; the value is broadcast only when it is needed (one iteration later)
+__device__ __forceinline__ uint32_t draw_cursor(const PairArgs& G, int lane) {
   uint32_t w = 0;
   if (lane == 0) w = atomicAdd(&G.ctr->work, 1u);
-  return __shfl_sync(0xffffffffu, w, 0);
+  return w;
 }
 // word `lane` of item w (lanes 16..31 and out-of-range items read nothing); total = 0 marks the end
 __device__ __forceinline__ uint32_t fetch_item(const PairArgs& G, uint32_t w, uint32_t n_items, int lane) {
@@ -312,11 +335,20 @@ __device__ __forceinline__ uint32_t fetch_item(const PairArgs& G, uint32_t w, ui
   return v;
 }
 
+// largest squared distance at which a label can fire for this atom with ANY partner (guard included)
+__device__ __forceinline__ float atom_limit2(const DevParams& P, const float* lim1, uint32_t w) {
+  float l = lim1[w & ARP_ATTR_ELEM_MASK];
+  if (w & (ARP_ATTR_POS_CONF | ARP_ATTR_NEG_CONF)) l = fmaxf(l, 16.0f + P.guard);
+  if (w & (ARP_ATTR_DONOR | ARP_ATTR_WEAK_DONOR | ARP_ATTR_ACCEPTOR)) l = fmaxf(l, P.polar_d2);
+  if (w & ARP_ATTR_HYDROPHOBIC) l = fmaxf(l, 20.25f + P.guard);
+  return l;
+}
+
 __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_pairs(const PairArgs G, const DevParams P) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   PairSmem& S = *reinterpret_cast<PairSmem*>(smem_raw);
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  // per element-class pair: no vdW-ladder label beyond (max(cov sum, vdW sum) + comp)^2 (vdw.rs:33-41)
+  // per element-class pair: no clash / covalent / vdW label beyond (max(cov sum, vdW sum) + |comp|)^2 (vdw.rs:33-41)
   for (int k = threadIdx.x; k < 256; k += PAIR_THREADS) {
     const int ea = k >> 4, eb = k & 15;
     const double r = fmax(P.cov[ea] + P.cov[eb], P.vdw[ea] + P.vdw[eb]) + fabs(P.comp);
@@ -324,61 +356,82 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_pairs(const P
     S.lim2[k] = __double2float_ru(r2) + P.guard;
   }
   __syncthreads();
+  if (threadIdx.x < 16) {  // per element class: the largest of its row
+    float m = 0.f;
+    for (int eb = 0; eb < 16; ++eb) m = fmaxf(m, S.lim2[threadIdx.x * 16 + eb]);
+    S.lim1[threadIdx.x] = m;
+  }
+  if (lane < 4) S.acc[wid][lane] = 0ull;
+  __syncthreads();
   FromRec* sfrom = S.from[wid];
   uint2* q1 = S.q1[wid];
   uint2* q2 = S.q2[wid];
+  unsigned long long* acc = S.acc[wid];  // [0] candidate tests, lane 0 only
   const float* lim2 = S.lim2;
   int q1len = 0, q2len = 0;
   uint32_t n_in32 = 0;  // pairs counted in f32 (screen and B1), per lane; flushed into 64 bits per item
   PairCounts K{0ull, 0ull};
-  unsigned long long n_screened = 0, n_in = 0;
+  unsigned long long n_in = 0;
   const uint32_t n_items = G.ctr->n_items;
-  const float half_hit = 0.5f * P.scr_hit, half_cert = 0.5f * P.scr_cert, half_near = 0.5f * P.scr_near;
+  const float half_hit = 0.5f * P.scr_hit, half_cert = 0.5f * P.scr_cert;
+  const float guard_a = P.guard_a;
 
   // ---- pipeline prologue ------------------------------------------------------------------------------------------
-  uint32_t w_next = fetch_cursor(G, lane);
-  uint32_t word = fetch_item(G, w_next, n_items, lane);      // current item
-  w_next = fetch_cursor(G, lane);
-  uint32_t word_n = fetch_item(G, w_next, n_items, lane);    // next item
-  w_next = fetch_cursor(G, lane);                            // cursor of the item after that
+  uint32_t word = fetch_item(G, __shfl_sync(0xffffffffu, draw_cursor(G, lane), 0), n_items, lane);    // current item
+  uint32_t word_n = fetch_item(G, __shfl_sync(0xffffffffu, draw_cursor(G, lane), 0), n_items, lane);  // next item
+  uint32_t w_raw = draw_cursor(G, lane);                                                              // the one after
   uint32_t chunk0 = 0;
-  RawChunk raw;
-  load_chunk(G, word, 0, lane, raw);
+  int pb = 0;
+  stage_chunk(G, word, 0, lane, S.buf[wid][0], S.tbuf[wid][0]);
 
-  while (__shfl_sync(0xffffffffu, word, 2) != 0u) {
+  // The last trip of the loop has no item (live = false): it only flushes the queues, through the same (single)
+  // instance of the stage-B code as every other trip.
+  while (true) {
     const uint32_t cb = __shfl_sync(0xffffffffu, word, 0), n_own = __shfl_sync(0xffffffffu, word, 1),
                    total = __shfl_sync(0xffffffffu, word, 2);
+    const bool live = total != 0u;
     const float ccx = __uint_as_float(__shfl_sync(0xffffffffu, word, 12)), ccy = __uint_as_float(__shfl_sync(0xffffffffu, word, 13)),
                 ccz = __uint_as_float(__shfl_sync(0xffffffffu, word, 14));
-    // ---- this chunk's candidates: registers, cell-local frame ----------------------------------------------------------
+    const int ns = live ? (int)min((uint32_t)SLOTS, (total - chunk0 + 31u) >> 5) : 0;
+    // ---- this chunk's candidates: shared memory -> registers, cell-local frame --------------------------------------
+    cp_async_wait_all();
+    const uint4* buf = S.buf[wid][pb];
+    const uint32_t* tbuf = S.tbuf[wid][pb];
     Cand C;
-    uint4 own_raw = raw.r[0];  // chunk 0: lane < n_own holds own atom `lane`
+    const uint4 own_raw = buf[lane];  // chunk 0: lane < n_own holds own atom `lane`
 #pragma unroll
     for (int u = 0; u < SLOTS; ++u) {
-      const bool ok = raw.r[u].w != 0xffffffffu;
-      const float x = __uint_as_float(raw.r[u].x) - ccx, y = __uint_as_float(raw.r[u].y) - ccy, z = __uint_as_float(raw.r[u].z) - ccz;
-      C.x[u] = ok ? x : 0.f;
-      C.y[u] = ok ? y : 0.f;
-      C.z[u] = ok ? z : 0.f;
-      C.h[u] = ok ? -0.5f * fmaf(z, z, fmaf(y, y, x * x)) : -1.0e30f;
-      C.t[u] = raw.t[u] | (ok ? (eligible(raw.r[u].w) << 31) : 0u);
+      if (u < ns) {
+        const uint4 r = buf[32 * u + lane];
+        const float x = __uint_as_float(r.x) - ccx, y = __uint_as_float(r.y) - ccy, z = __uint_as_float(r.z) - ccz;
+        C.x[u] = x;
+        C.y[u] = y;
+        C.z[u] = z;
+        C.h[u] = -0.5f * fmaf(z, z, fmaf(y, y, x * x));  // "no candidate": h = -1.5e36 fails every test
+        C.t[u] = tbuf[32 * u + lane] | (r.w & 0x80000000u);
+      } else {
+        C.x[u] = C.y[u] = C.z[u] = 0.f;
+        C.h[u] = -1.0e30f;
+        C.t[u] = 0u;
+      }
     }
-    // ---- prefetch: the next chunk of this item, or chunk 0 of the next item -------------------------------------------
-    const bool more = chunk0 + CHUNK < total;
-    uint32_t word_nn = word_n, w_nn = w_next;
-    if (more) {
-      load_chunk(G, word, chunk0 + CHUNK, lane, raw);
+    // ---- stage the next unit: the next chunk of this item, or chunk 0 of the next item ------------------------------
+    const bool more = live && chunk0 + CHUNK < total;
+    uint32_t word_nn = word_n, w_raw_n = w_raw;
+    if (!live) {
+    } else if (more) {
+      stage_chunk(G, word, chunk0 + CHUNK, lane, S.buf[wid][pb ^ 1], S.tbuf[wid][pb ^ 1]);
     } else {
-      load_chunk(G, word_n, 0, lane, raw);
-      word_nn = fetch_item(G, w_next, n_items, lane);
-      w_nn = fetch_cursor(G, lane);
+      stage_chunk(G, word_n, 0, lane, S.buf[wid][pb ^ 1], S.tbuf[wid][pb ^ 1]);
+      word_nn = fetch_item(G, __shfl_sync(0xffffffffu, w_raw, 0), n_items, lane);
+      w_raw_n = draw_cursor(G, lane);
     }
-    if (chunk0 == 0 && lane == 0)
-      n_screened += (unsigned long long)n_own * (total - n_own) + (unsigned long long)n_own * (n_own - 1) / 2;
+    if (live && chunk0 == 0 && lane == 0)
+      acc[0] += (unsigned long long)n_own * (total - n_own) + (unsigned long long)n_own * (n_own - 1) / 2;
 
     // ---- from-atoms in passes of 32 (one pass for every realistic cell) ------------------------------------------------
-    for (uint32_t fbo = 0; fbo < n_own; fbo += FROM_PASS) {
-      const int nf = (int)min((uint32_t)FROM_PASS, n_own - fbo);
+    for (uint32_t fbo = 0; fbo < (live ? n_own : 1u); fbo += FROM_PASS) {
+      const int nf = live ? (int)min((uint32_t)FROM_PASS, n_own - fbo) : 0;
       __syncwarp();
       if (lane < nf && (chunk0 == 0 || n_own > (uint32_t)FROM_PASS)) {  // a single pass stays staged for the later chunks
         uint4 fr = own_raw;
@@ -388,10 +441,12 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_pairs(const P
         f.y = __uint_as_float(fr.y) - ccy;
         f.z = __uint_as_float(fr.z) - ccz;
         const float hf = 0.5f * fmaf(f.z, f.z, fmaf(f.y, f.y, f.x * f.x));
+        // no label can fire for this atom beyond its own limit: a per-atom T_near (conservative; B1 applies the pair limit)
+        const float t_near = fminf(P.scr_near, atom_limit2(P, S.lim1, fr.w) + guard_a);
         f.k_hit = hf - half_hit;
         f.k_cert = hf - half_cert;
-        f.k_near = hf - half_near;
-        f.w = (eligible(fr.w) << 16) | 1u;
+        f.k_near = hf - 0.5f * (P.count_classified ? P.scr_near : t_near);
+        f.w = ((fr.w >> 31) << 16) | 1u;
         f.pad = 0u;
         sfrom[lane] = f;
       }
@@ -403,46 +458,47 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_pairs(const P
         lim[u] = e < n_own ? (e > fbo ? e - fbo : 0u) : 0xffffffffu;
         mask[u] = cnt[u] = 0u;
       }
-      if (chunk0 >= n_own)
-        screen_pass<0>(sfrom, nf, C, lim, mask, cnt);
-      else if (chunk0 + 32u >= n_own)
-        screen_pass<1>(sfrom, nf, C, lim, mask, cnt);
-      else
-        screen_pass<2>(sfrom, nf, C, lim, mask, cnt);
+      const int tri = chunk0 >= n_own ? 0 : (chunk0 + 32u >= n_own ? 1 : 2);
+      // own-cell atoms beyond slot 0 (more than 32 atoms in a cell) are rare: one variant, all slots
+      switch (live ? (tri == 2 ? 2 * SLOTS : tri * SLOTS + ns - 1) : -1) {
+#define SCREEN_CASE(T, N) \
+  case (T) * SLOTS + (N) - 1: screen_pass<T, N>(sfrom, nf, C, lim, mask, cnt); break;
+#define SCREEN_ROW(T) SCREEN_CASE(T, 1) SCREEN_CASE(T, 2) SCREEN_CASE(T, 3) SCREEN_CASE(T, 4) SCREEN_CASE(T, 5) SCREEN_CASE(T, 6)
+        SCREEN_ROW(0) SCREEN_ROW(1)
+        case 2 * SLOTS: screen_pass<2, SLOTS>(sfrom, nf, C, lim, mask, cnt); break;
+#undef SCREEN_ROW
+#undef SCREEN_CASE
+      }
       if (P.count_in_cutoff) {
 #pragma unroll
         for (int u = 0; u < SLOTS; ++u) n_in32 += (cnt[u] >> 16) + (cnt[u] & 0xffffu) * (C.t[u] >> 31);
       }
-      expand_masks(G, P, lim2, mask, C, cb + fbo, q1, q1len, q2, q2len, lane, n_in32, K);
+      expand_masks(G, P, lim2, mask, C, cb + fbo, q1, q1len, q2, q2len, lane, n_in32, K, !live);
     }
     n_in += n_in32;
     n_in32 = 0;
+    if (!live) break;
 
     // ---- advance ------------------------------------------------------------------------------------------------------
+    pb ^= 1;
     if (more) {
       chunk0 += CHUNK;
     } else {
       chunk0 = 0;
       word = word_n;
       word_n = word_nn;
-      w_next = w_nn;
+      w_raw = w_raw_n;
     }
   }
-  // ---- tails of the queues ------------------------------------------------------------------------------------------
-  if (q1len > 0) filter_batch(G, P, lim2, q1, q1len, lane, q2, q2len, n_in32, K);
-  __syncwarp();
-  if (q2len > 0) exact_batch(G, P, q2, q2len, lane, K);
-  n_in += n_in32;
   n_in += K.n_in;
   unsigned long long n_cls = K.n_cls;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
-    n_screened += __shfl_xor_sync(0xffffffffu, n_screened, o);
     n_in += __shfl_xor_sync(0xffffffffu, n_in, o);
     n_cls += __shfl_xor_sync(0xffffffffu, n_cls, o);
   }
   if (lane == 0) {
-    atomicAdd(&G.ctr->screened, n_screened);
+    atomicAdd(&G.ctr->screened, acc[0]);
     atomicAdd(&G.ctr->in_cutoff, n_in);
     atomicAdd(&G.ctr->classified, n_cls);
   }
