@@ -75,6 +75,7 @@ struct HBuf {
 struct arp_ctx {
   int device = 0;
   int sm_count = 148;
+  int occ_screen = 1, occ_filter = 1, occ_exact = 1;  // resident CTAs per SM (grids are sized to one full wave)
   cudaStream_t stream = nullptr;
   std::string err;
 
@@ -90,7 +91,7 @@ struct arp_ctx {
 
   // cell lists and sorted records
   DBuf<unsigned long long> bbox;
-  DBuf<uint32_t> cell_of, rank_of, cell_start, tile_sums, perm, res_sorted;
+  DBuf<uint32_t> cell_of, rank_of, cell_start, tile_sums;
   DBuf<uint32_t> rcell_of, rrank_of, rcell_start, rperm;
   DBuf<RecA> recA;
   DBuf<RecB> recB;
@@ -98,6 +99,8 @@ struct arp_ctx {
   DBuf<Counters> ctr;
   DBuf<arp_row> rows;
   uint64_t row_cap = 0;
+  DBuf<uint2> pairq, pairq2;  // pairs between k_screen -> k_filter -> k_exact
+  uint64_t pairq_cap = 0, pairq2_cap = 0;
   int64_t n_cells = 0, n_rcells = 0;
 
   // host staging

@@ -113,7 +113,7 @@ __device__ __forceinline__ uint32_t classify_pair(const PairArgs& G, const DevPa
   uint32_t m = 0;
   if (dist < dsub(sum_cov, P.comp)) return LBIT(ARP_StericClash);  // complex.rs:233-235: a clash suppresses the rest
   if (dist < dadd(sum_cov, P.comp)) {
-    const bool ss = (wa & wb & ARP_ATTR_CYS_SG) && is_disulfide(G, P, G.res_sorted[sa], G.res_sorted[sb]);
+    const bool ss = (wa & wb & ARP_ATTR_CYS_SG) && is_disulfide(G, P, G.recA[sa].res_id, G.recA[sb].res_id);
     m |= ss ? LBIT(ARP_Disulfide) : LBIT(ARP_CovalentBond);
   } else if (dist < dadd(sum_vdw, P.comp)) {
     m |= LBIT(ARP_VanDerWaalsContact);
@@ -131,7 +131,7 @@ __device__ __forceinline__ uint32_t classify_pair(const PairArgs& G, const DevPa
     const bool fb = !fa && (wb & dflag) && (wa & ARP_ATTR_ACCEPTOR);
     if (!(fa || fb)) continue;
     const int r = hbond_body(G, P, fa ? a.x : b.x, fa ? a.y : b.y, fa ? a.z : b.z, fa ? b.x : a.x, fa ? b.y : a.y, fa ? b.z : a.z,
-                             G.res_sorted[fa ? sa : sb], fa ? eb : ea, dist, k ? P.ang.a_ge_130 : P.ang.a_ge_90);
+                             G.recA[fa ? sa : sb].res_id, fa ? eb : ea, dist, k ? P.ang.a_ge_130 : P.ang.a_ge_90);
     if (k) wk = r; else hb = r;
   }
   // complex.rs:240-251

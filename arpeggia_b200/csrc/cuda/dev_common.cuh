@@ -18,12 +18,17 @@ struct StructDesc {
   uint32_t ring_begin, ring_end;
 };
 
-// Sorted (by cell) atom records.
-// RecA: what the screen reads: origin-relative f32 position + attribute word.  16 B -> one LDG.128 / LDS.128.
-// RecB: what the exact test reads: f64 position + chain key + residue ordinal.  32 B = one sector.
-struct __align__(16) RecA {
+// Sorted (by cell) atom records, 32 bytes = one sector each.
+// RecA: everything the f32 stages need about an atom.  The screen reads the first 16 bytes (origin-relative f32 position +
+//       attribute word: one 16-byte cp.async per candidate), the pair filter reads the whole sector in one gather.
+// RecB: what the exact stage reads: f64 position (+ chain key and residue ordinal for the ring kernels).
+struct __align__(32) RecA {
   float x, y, z;
-  uint32_t attr;
+  uint32_t attr;         // ARP_ATTR_* | bit 31: may start a row (k_scatter_atoms)
+  uint32_t chain_key;
+  uint32_t res_ordinal;
+  uint32_t res_id;       // job-global residue id (H lists, CB / SG slots)
+  uint32_t perm;         // job-global atom index in input order (output rows)
 };
 struct __align__(32) RecB {
   double x, y, z;
@@ -86,13 +91,13 @@ struct Counters {
   unsigned int work;              uint32_t padw[31];   // work-item cursor of the persistent pair kernel
   unsigned int n_items;           uint32_t padi[31];   // non-empty cells
   unsigned int error;             uint32_t pade[31];   // 1 = CYS residue without CB / SG (vdw.rs:58 unwrap)
+  unsigned long long q_len;       uint64_t padq[15];   // pairs pushed by k_screen (may exceed the queue's capacity)
+  unsigned long long q2_len;      uint64_t padr[15];   // pairs pushed by k_filter (likewise)
 };
 
 struct PairArgs {
   const RecA* recA;
   const RecB* recB;
-  const uint32_t* perm;        // sorted slot -> job-global atom index
-  const uint32_t* res_sorted;  // sorted slot -> job-global residue id
   const uint32_t* cell_start;  // n_cells + 1
   const Item* items;           // non-empty cells
   const StructDesc* descs;
@@ -106,6 +111,10 @@ struct PairArgs {
   const double* hx;
   const double* hy;
   const double* hz;
+  uint2* pairq;                // k_screen -> k_filter: (from slot, candidate slot)
+  unsigned long long pairq_cap;
+  uint2* pairq2;               // k_filter -> k_exact: the same with flags in the top bits
+  unsigned long long pairq2_cap;
   arp_row* rows;
   unsigned long long row_cap;
   Counters* ctr;
@@ -125,7 +134,6 @@ struct RingArgs {
   // atom cell list
   const RecA* recA;
   const RecB* recB;
-  const uint32_t* perm;
   const uint32_t* cell_start;
   const StructDesc* descs;
   arp_row* rows;

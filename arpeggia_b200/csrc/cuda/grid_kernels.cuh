@@ -192,8 +192,8 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
                 const uint32_t* __restrict__ attr, const uint32_t* __restrict__ chain_key, const uint32_t* __restrict__ res_ordinal,
                 const uint32_t* __restrict__ res_id, const uint32_t* __restrict__ atom_struct, const StructDesc* __restrict__ descs,
                 const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of, const uint32_t* __restrict__ cell_start,
-                uint32_t n, double edge, RecA* __restrict__ recA, RecB* __restrict__ recB, uint32_t* __restrict__ perm,
-                uint32_t* __restrict__ res_sorted, Item* __restrict__ items, Counters* __restrict__ ctr) {
+                uint32_t n, double edge, RecA* __restrict__ recA, RecB* __restrict__ recB, Item* __restrict__ items,
+                Counters* __restrict__ ctr) {
   const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
   if (a >= n) return;
   const uint32_t s = atom_struct ? atom_struct[a] : 0u;
@@ -208,16 +208,18 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
   // bit 31 of the sorted attribute word (internal): the atom may start a row / counts as `from` (complex.rs:200-202)
   const uint32_t w = attr[a] & 0x7fffffffu;
   ra.attr = w | (((w & ARP_ATTR_LIGAND) && (w & ARP_ATTR_ELEM_MASK) && !(w & ARP_ATTR_GHOST)) ? 0x80000000u : 0u);
+  ra.chain_key = chain_key[a];
+  ra.res_ordinal = res_ordinal[a];
+  ra.res_id = res_id[a];
+  ra.perm = a;
   recA[slot] = ra;
   RecB rb;
   rb.x = px;
   rb.y = py;
   rb.z = pz;
-  rb.chain_key = chain_key[a];
-  rb.res_ordinal = res_ordinal[a];
+  rb.chain_key = ra.chain_key;
+  rb.res_ordinal = ra.res_ordinal;
   recB[slot] = rb;
-  perm[slot] = a;
-  res_sorted[slot] = res_id[a];
   if (r == 0) {  // first arrival publishes the cell as a work item: its half shell as 5 runs of sorted slots
     const uint32_t local = c - d.cell_base;
     const int nx = d.nx, ny = d.ny, nz = d.nz;

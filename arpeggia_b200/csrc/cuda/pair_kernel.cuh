@@ -1,31 +1,34 @@
-// k_pairs: neighbour search + classification + compaction for atom-atom contacts (sm_100a).
+// Neighbour search + classification + compaction for atom-atom contacts (sm_100a), three kernels.
 // Replaces get_atomic_contacts, src/contacts/complex.rs:189-299.
 //
-// Work decomposition.  One warp per non-empty cell ("from" cell), persistent CTAs pulling work items (Item,
-// dev_common.cuh) from an atomic cursor.  A warp sweeps the HALF SHELL of its cell -- the cell itself plus its 13
-// forward neighbours, 5 contiguous runs of cell-sorted atoms -- so every unordered atom pair is screened once; the
-// orientation of the row is decided later by the pair filter (at most one orientation of a pair can pass
-// should_compare_entities, complex.rs:76-131).
+// k_screen (stage A: all the volume, ~116 distance tests per atom at protein density).
+//   One warp per non-empty cell ("from" cell), persistent CTAs pulling work items (Item, dev_common.cuh) from an
+//   atomic cursor.  A warp sweeps the HALF SHELL of its cell -- the cell itself plus its 13 forward neighbours,
+//   5 contiguous runs of cell-sorted atoms -- so every unordered atom pair is screened once.  Lanes own CANDIDATES:
+//   up to 6 per lane, held in registers in a cell-local f32 frame (cx, cy, cz, h = -|c|^2/2); the cell's own atoms
+//   are broadcast from shared memory one after the other as (fx, fy, fz, k).  With s = f.c + h the test d^2 <= T
+//   is s >= |f|^2/2 - T/2: three FMAs and compares against per-from-atom constants, no subtraction, no branch:
+//       inside = T_near < d^2 <= T_cert   certainly within dist_cutoff and too far for any label: COUNTED here
+//       push   = d^2 <= T_hit and not inside   (close enough for a label, or too close to the cutoff to call in f32)
+//   `inside` pairs add a packed weight to a per-lane counter, `push` pairs set bit i of a per-lane mask; the masks
+//   are expanded through a warp prefix sum into the job's PAIR QUEUE in HBM as (from slot, candidate slot), one
+//   atomicAdd per warp and pass.  The guard band gA (api_run.inc) makes both decisions rigorous against the exact
+//   FP64 distances.  T_near is per from-atom: no label can fire for an atom beyond its own largest limit.
+//   Latency: a warp always has three items in flight -- cursor of item k+3 (atomic), record of item k+2 (one
+//   coalesced 64-byte load), candidates of item k+1 (cp.async into a double-buffered shared-memory stage).
 //
-// Stage A, the screen (all the volume: ~116 tests per atom at protein density).  Lanes own CANDIDATES: up to 6 per lane,
-// held in registers in a cell-local f32 frame (cx, cy, cz, h = -|c|^2/2); the cell's own atoms are broadcast from
-// shared memory one after the other as (fx, fy, fz, k).  With s = f.c + h the test d^2 <= T is s >= |f|^2/2 - T/2,
-// i.e. three FMAs and compares against per-from-atom constants -- no subtraction, no square, no branch:
-//     inside  = T_near < d^2 <= T_cert   certainly within dist_cutoff and too far for any label: COUNTED here
-//     push    = d^2 <= T_hit and not inside   (close enough for a label, or too close to the cutoff to call in f32)
-// `inside` pairs add a packed weight to a per-lane counter, `push` pairs set bit i of a per-lane mask.  The guard
-// band gA (api_run.inc) makes both decisions rigorous against the exact FP64 distances.
+// k_filter (stage B1: what survives the screen, ~6 pairs per atom).  Grid-stride over the pair queue, one pair per lane:
+//   f32 re-test on the stored positions, in-cutoff counting, per-pair label limit (no label of complex.rs:217-296 can
+//   fire beyond max(vdW sum + comp, 4.5 | 4.0 | 3.5 by flags)), pair filter (at most one orientation of a pair can pass
+//   should_compare_entities, complex.rs:76-131).  About one pair in nine goes on to the second queue.
+// k_exact (stage B2, ~0.7 pairs per atom).  Exact FP64 d^2 in the reference's operation order, inclusive cutoff (rstar),
+//   sqrt, label ladder, rows out through a warp prefix sum and ONE atomicAdd per 32 pairs.
 //
-// Stage B (what survives: ~8 pairs per atom).  The masks are expanded through a warp prefix sum into a per-warp
-// shared-memory queue of (from slot, candidate slot) and handled 32 at a time with all lanes busy:
-//   B1  f32 re-test on the stored positions, in-cutoff counting, per-pair label limit (no label of
-//       complex.rs:217-296 can fire beyond max(vdW sum + comp, 4.5 | 4.0 | 3.5 by flags)), pair filter.
-//   B2  exact FP64 d^2 in the reference's operation order, inclusive cutoff (rstar), sqrt, label ladder, rows out
-//       through a warp prefix sum and ONE atomicAdd per 32 pairs.
-//
-// Latency.  A warp always has three items in flight: cursor of item k+3 (atomic), record of item k+2 (one
-// coalesced 64-byte load), candidates of item k+1 (cp.async into the warp's double-buffered shared-memory stage, issued
-// before item k is computed; no registers are held while the copies fly).
+// Why three kernels: fused into one persistent kernel the stages made a 70-160 KB instruction footprint with every
+// warp in a different place; ncu showed 27-36 % of the stall samples as "no instruction" (the L1.5 I-cache is 32 KB)
+// and the stage-B gathers stalled behind the screen's registers.  Split, each kernel is a tight loop, k_screen keeps no
+// stage-B state, k_filter runs at full occupancy to hide its gathers and k_exact carries the heavy FP64 ladder for the few
+// pairs that need it.  The price is the queues' trip through HBM: 8 bytes written and read per surviving pair.
 #pragma once
 #include "classify.cuh"
 
@@ -34,13 +37,13 @@ namespace arpd {
 constexpr int PAIR_WARPS = 4;
 constexpr int PAIR_THREADS = PAIR_WARPS * 32;
 #ifndef PAIR_MIN_BLOCKS
-#define PAIR_MIN_BLOCKS 4
+#define PAIR_MIN_BLOCKS 5
 #endif
 constexpr int SLOTS = 6;                 // candidates per lane per chunk
 constexpr int CHUNK = 32 * SLOTS;        // candidates per chunk
 constexpr int FROM_PASS = 32;            // from-atoms per pass (bits of a mask)
-constexpr int Q1_CAP = 256;              // screened pairs waiting for B1
-constexpr int Q2_CAP = 64;               // filtered pairs waiting for B2 (carry-over < 32 + one batch)
+constexpr int CLS_WARPS = 8;
+constexpr int CLS_THREADS = CLS_WARPS * 32;
 constexpr uint32_t SLOT_MASK = 0x3fffffffu;
 constexpr uint32_t QF_A = 0x80000000u;   // q2.x: in-cutoff still undecided (count in B2)   q2.y: row runs candidate -> from
 constexpr uint32_t QF_B = 0x40000000u;   // q2.x: the pair filter passed                     q2.y: a label may fire
@@ -53,15 +56,11 @@ struct __align__(16) FromRec {
   uint32_t pad;
 };
 
-struct PairSmem {
+struct ScreenSmem {
   uint4 buf[PAIR_WARPS][2][CHUNK];      // staged candidate records (RecA bits), double buffered
   uint32_t tbuf[PAIR_WARPS][2][CHUNK];  // their sorted slots
   FromRec from[PAIR_WARPS][FROM_PASS];
-  uint2 q1[PAIR_WARPS][Q1_CAP];
-  uint2 q2[PAIR_WARPS][Q2_CAP];
-  unsigned long long acc[PAIR_WARPS][4];
-  float lim2[256];           // per element-class pair: (max(cov sum, vdW sum) + |comp|)^2 + g, rounded up
-  float lim1[16];            // per element class: largest entry of its row
+  float lim1[16];                       // per element class: largest (max(cov sum, vdW sum) + |comp|)^2 + g over partners
 };
 
 struct PairCounts {
@@ -80,6 +79,13 @@ __device__ __forceinline__ uint32_t warp_inclusive_sum(uint32_t v, int lane) {
 // atoms that can start a row / are counted as `from`: in the ligand set, not hydrogen, not a ghost (complex.rs:200-202);
 // k_scatter_atoms caches the predicate in bit 31 of the sorted attribute word
 __device__ __forceinline__ uint32_t eligible(uint32_t w) { return w >> 31; }
+
+// per element-class pair: no clash / covalent / vdW label beyond (max(cov sum, vdW sum) + |comp|)^2 (vdw.rs:33-41)
+__device__ __forceinline__ float class_pair_limit2(const DevParams& P, int ea, int eb) {
+  const double r = fmax(P.cov[ea] + P.cov[eb], P.vdw[ea] + P.vdw[eb]) + fabs(P.comp);
+  const double r2 = r > 0.0 ? r * r * (1.0 + 1e-9) : 0.0;
+  return __double2float_ru(r2) + P.guard;
+}
 
 // ---- B2: up to 32 filtered pairs, one per lane: exact distance, counters, label ladder, rows ----------------------
 __device__ __forceinline__ void exact_batch(const PairArgs& G, const DevParams& P, const uint2* q, int count, int lane, PairCounts& K) {
@@ -122,7 +128,7 @@ __device__ __forceinline__ void exact_batch(const PairArgs& G, const DevParams& 
   base = __shfl_sync(0xffffffffu, base, 31);
   unsigned long long w = base + (inc - mine);
   if (mine) {
-    const uint32_t ip = G.perm[sp], iq = G.perm[sq];
+    const uint32_t ip = G.recA[sp].perm, iq = G.recA[sq].perm;
     const float fd = __double2float_rn(dist);  // Rust `as f32`, mod.rs:148
     while (m) {
       const uint32_t l = __ffs(m) - 1;
@@ -148,45 +154,103 @@ __device__ __forceinline__ float label_limit2(const DevParams& P, const float* l
   return l;
 }
 
-// ---- B1: up to 32 screened pairs, one per lane: f32 re-test, counting, label limit, pair filter; survivors -> q2 ----
-// flush_q2: this is the last batch of the kernel, q2 is emptied completely behind it.
-__device__ __forceinline__ void filter_batch(const PairArgs& G, const DevParams& P, const float* lim2, const uint2* q, int count, int lane,
-                                             uint2* q2, int& q2len, uint32_t& n_in32, PairCounts& K, bool flush_q2) {
-  bool go = false;
-  uint2 out = make_uint2(0u, 0u);
-  if (lane < count) {
-    const uint2 e = q[lane];
-    const RecA a = G.recA[e.x], b = G.recA[e.y];
-    // chain key + residue ordinal of both atoms, requested together with the positions (one latency, not two)
-    const uint2 ka = *reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(G.recB + e.x) + 24);
-    const uint2 kb = *reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(G.recB + e.y) + 24);
-    const float dx = b.x - a.x, dy = b.y - a.y, dz = b.z - a.z;
-    const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-    if (d2 <= P.thr_hit) {
-      const bool counting = P.count_in_cutoff != 0;
-      const bool cert = d2 <= P.thr_cert;
-      if (counting && cert) n_in32 += eligible(a.attr) + eligible(b.attr);
-      const bool amb = counting && !cert;  // the exact stage decides and counts
-      const bool pot = d2 <= P.thr_near && d2 <= label_limit2(P, lim2, a.attr, b.attr);
-      if (amb || pot || P.count_classified) {
-        const int dir = pair_direction(a.attr, ka.x, ka.y, b.attr, kb.x, kb.y);
-        const bool valid = dir != 0;
-        if (P.count_classified && cert) K.n_cls += valid ? 1u : 0u;
-        go = amb || (pot && valid);
-        out.x = e.x | (amb ? QF_A : 0u) | (valid ? QF_B : 0u);
-        out.y = e.y | (dir == 2 ? QF_A : 0u) | (pot ? QF_B : 0u);
+// ---- k_filter (B1) ----------------------------------------------------------------------------------------------
+// Grid-stride over the pair queue, one pair per lane: f32 re-test on the stored positions, in-cutoff counting, per-pair
+// label limit, pair filter.  One 32-byte gather per atom brings everything.  Survivors (about one in nine) are collected
+// per warp in shared memory and go to the second queue 32 at a time.
+__global__ void __launch_bounds__(CLS_THREADS, 4) k_filter(const PairArgs G, const DevParams P) {
+  __shared__ float lim2[256];  // per element-class pair: (max(cov sum, vdW sum) + |comp|)^2 + g, rounded up
+  __shared__ uint2 keep[CLS_WARPS][64];  // survivors waiting for a full 32-entry flush (carry-over < 32 + one trip)
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  for (int k = threadIdx.x; k < 256; k += CLS_THREADS) lim2[k] = class_pair_limit2(P, k >> 4, k & 15);
+  __syncthreads();
+  uint2* sq = keep[wid];
+  int sqlen = 0;
+  uint32_t n_in32 = 0, n_cls32 = 0;
+  const unsigned long long n_pairs = min(G.ctr->q_len, G.pairq_cap);
+  const unsigned long long stride = (unsigned long long)gridDim.x * CLS_WARPS * 32ull;
+  const bool counting = P.count_in_cutoff != 0;
+  unsigned long long base = ((unsigned long long)blockIdx.x * CLS_WARPS + wid) * 32ull;
+  // The only dependent memory round trip of a trip is the gather: the queue entry is read one trip ahead and the
+  // output atomic is paid once per 32 survivors.
+  uint2 e_next = make_uint2(0u, 0u);
+  if (base + lane < n_pairs) e_next = G.pairq[base + lane];
+  for (; base < n_pairs; base += stride) {
+    const uint2 e = e_next;
+    const bool have = base + lane < n_pairs;
+    if (base + stride + lane < n_pairs) e_next = G.pairq[base + stride + lane];
+    bool go = false;
+    uint2 out = make_uint2(0u, 0u);
+    if (have) {
+      const uint4* pa = reinterpret_cast<const uint4*>(G.recA + e.x);
+      const uint4* pb = reinterpret_cast<const uint4*>(G.recA + e.y);
+      const uint4 a0 = pa[0], a1 = pa[1], b0 = pb[0], b1 = pb[1];  // position + attr | chain key, ordinal, ...
+      const float dx = __uint_as_float(b0.x) - __uint_as_float(a0.x), dy = __uint_as_float(b0.y) - __uint_as_float(a0.y),
+                  dz = __uint_as_float(b0.z) - __uint_as_float(a0.z);
+      const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+      if (d2 <= P.thr_hit) {
+        const bool cert = d2 <= P.thr_cert;
+        if (counting && cert) n_in32 += eligible(a0.w) + eligible(b0.w);
+        const bool amb = counting && !cert;  // the exact stage decides and counts
+        const bool pot = d2 <= P.thr_near && d2 <= label_limit2(P, lim2, a0.w, b0.w);
+        if (amb || pot || P.count_classified) {
+          const int dir = pair_direction(a0.w, a1.x, a1.y, b0.w, b1.x, b1.y);
+          const bool valid = dir != 0;
+          if (P.count_classified && cert) n_cls32 += valid ? 1u : 0u;
+          go = amb || (pot && valid);
+          out.x = e.x | (amb ? QF_A : 0u) | (valid ? QF_B : 0u);
+          out.y = e.y | (dir == 2 ? QF_A : 0u) | (pot ? QF_B : 0u);
+        }
       }
     }
-  }
-  const uint32_t bal = __ballot_sync(0xffffffffu, go);
-  if (go) q2[q2len + __popc(bal & ((1u << lane) - 1u))] = out;
-  q2len += __popc(bal);
-  __syncwarp();
-  while (q2len >= 32 || (flush_q2 && q2len > 0)) {  // the only call site of exact_batch
-    const int m = min(q2len, 32);
-    exact_batch(G, P, q2 + (q2len - m), m, lane, K);
-    q2len -= m;
+    const uint32_t bal = __ballot_sync(0xffffffffu, go);
+    if (go) sq[sqlen + __popc(bal & ((1u << lane) - 1u))] = out;
+    sqlen += __popc(bal);
     __syncwarp();
+    if (sqlen >= 32) {
+      unsigned long long w = 0;
+      if (lane == 0) w = atomicAdd(&G.ctr->q2_len, 32ull);
+      w = __shfl_sync(0xffffffffu, w, 0) + lane;
+      sqlen -= 32;
+      if (w < G.pairq2_cap) G.pairq2[w] = sq[sqlen + lane];
+      __syncwarp();
+    }
+  }
+  if (sqlen > 0) {
+    unsigned long long w = 0;
+    if (lane == 0) w = atomicAdd(&G.ctr->q2_len, (unsigned long long)sqlen);
+    w = __shfl_sync(0xffffffffu, w, 0) + lane;
+    if (lane < sqlen && w < G.pairq2_cap) G.pairq2[w] = sq[lane];
+  }
+  unsigned long long n_in = n_in32, n_cls = n_cls32;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    n_in += __shfl_xor_sync(0xffffffffu, n_in, o);
+    n_cls += __shfl_xor_sync(0xffffffffu, n_cls, o);
+  }
+  if (lane == 0) {
+    if (n_in) atomicAdd(&G.ctr->in_cutoff, n_in);
+    if (n_cls) atomicAdd(&G.ctr->classified, n_cls);
+  }
+}
+
+// ---- k_exact (B2) -----------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(CLS_THREADS, 4) k_exact(const PairArgs G, const DevParams P) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  PairCounts K{0ull, 0ull};
+  const unsigned long long n_pairs = min(G.ctr->q2_len, G.pairq2_cap);
+  const unsigned long long stride = (unsigned long long)gridDim.x * CLS_WARPS * 32ull;
+  for (unsigned long long base = ((unsigned long long)blockIdx.x * CLS_WARPS + wid) * 32ull; base < n_pairs; base += stride)
+    exact_batch(G, P, G.pairq2 + base, (int)min(32ull, n_pairs - base), lane, K);
+  unsigned long long n_in = K.n_in, n_cls = K.n_cls;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    n_in += __shfl_xor_sync(0xffffffffu, n_in, o);
+    n_cls += __shfl_xor_sync(0xffffffffu, n_cls, o);
+  }
+  if (lane == 0) {
+    if (n_in) atomicAdd(&G.ctr->in_cutoff, n_in);
+    if (n_cls) atomicAdd(&G.ctr->classified, n_cls);
   }
 }
 
@@ -198,15 +262,20 @@ struct Cand {
 
 // The screen: every from-atom of the pass against the NS candidates of this lane.
 // lim[u] = number of leading from-atoms candidate u may pair with (own-cell candidates pair only with the atoms that
-// precede them, everything else with all of them).  TRI = 0: no own-cell atom among the candidates, 1: only in slot 0,
-// 2: anywhere.  NS = slots of the chunk that hold candidates (the last chunk of an item is rarely full).
-template <int TRI, int NS>
+// precede them, everything else with all of them).  ALL = false: only slot 0 can hold own-cell atoms (cells of at most
+// 32 atoms, chunk 0), the other slots skip the comparison.  NS = slots of the chunk that hold candidates (the last
+// chunk of an item is rarely full).  Rolled loop, next from-atom prefetched by hand: the instruction footprint of all
+// variants together stays below 8 KB.
+template <bool ALL, int NS>
 __device__ __forceinline__ void screen_pass(const FromRec* sf, int nf, const Cand& C, const uint32_t (&lim)[SLOTS], uint32_t (&mask)[SLOTS],
                                             uint32_t (&cnt)[SLOTS]) {
-#pragma unroll 2
+  float4 f = *reinterpret_cast<const float4*>(&sf[0]);
+  float4 g = *(reinterpret_cast<const float4*>(&sf[0]) + 1);
+#pragma unroll 1
   for (int i = 0; i < nf; ++i) {
-    const float4 f = *reinterpret_cast<const float4*>(&sf[i]);
-    const float4 g = *(reinterpret_cast<const float4*>(&sf[i]) + 1);
+    const int nx = min(i + 1, FROM_PASS - 1);
+    const float4 fn = *reinterpret_cast<const float4*>(&sf[nx]);
+    const float4 gn = *(reinterpret_cast<const float4*>(&sf[nx]) + 1);
     const uint32_t w = __float_as_uint(g.z);
     const uint32_t bit = 1u << i;
 #pragma unroll
@@ -214,7 +283,7 @@ __device__ __forceinline__ void screen_pass(const FromRec* sf, int nf, const Can
       const float s = fmaf(f.x, C.x[u], fmaf(f.y, C.y[u], fmaf(f.z, C.z[u], C.h[u])));
       // inside = tri && s >= k_cert && s < k_near;  push = tri && s >= k_hit && !inside; predicated add / or
       // (written in PTX: the compiler otherwise turns both updates into SEL + ALU pairs)
-      if (TRI == 2 || (TRI == 1 && u == 0)) {
+      if (ALL || u == 0) {
         asm("{\n\t.reg .pred pt, pi, pp;\n\t"
             "setp.lt.u32 pt, %8, %9;\n\t"
             "setp.ge.and.f32 pi, %2, %3, pt;\n\t"
@@ -236,58 +305,33 @@ __device__ __forceinline__ void screen_pass(const FromRec* sf, int nf, const Can
             : "f"(s), "f"(g.x), "f"(g.y), "f"(f.w), "r"(w), "r"(bit));
       }
     }
+    f = fn;
+    g = gn;
   }
 }
 
-// drain full batches of q1 through B1 (and, behind it, B2); flush: everything, partial batches included (end of kernel)
-__device__ __forceinline__ void drain_q1(const PairArgs& G, const DevParams& P, const float* lim2, uint2* q1, int& q1len, uint2* q2,
-                                         int& q2len, int lane, uint32_t& n_in32, PairCounts& K, bool flush) {
-  while (true) {  // the only call site of filter_batch
-    const int n = q1len >= 32 ? 32 : (flush ? q1len : 0);
-    if (n == 0 && !(flush && q2len > 0)) break;
-    filter_batch(G, P, lim2, q1 + (q1len - n), n, lane, q2, q2len, n_in32, K, flush && q1len == n);
-    q1len -= n;
-    __syncwarp();
-  }
-}
-
-// masks -> q1.  Entries are (from slot, candidate slot); bounded queue: when it fills up it is drained and the
-// remaining bits are expanded in another round.
-__device__ __forceinline__ void expand_masks(const PairArgs& G, const DevParams& P, const float* lim2, uint32_t (&mask)[SLOTS],
-                                             const Cand& C, uint32_t from_slot0, uint2* q1, int& q1len, uint2* q2, int& q2len, int lane,
-                                             uint32_t& n_in32, PairCounts& K, bool flush) {
+// masks -> pair queue in HBM.  Entries are (from slot, candidate slot); one atomicAdd per warp reserves the range.
+// Writes beyond the capacity are dropped; the counter keeps counting, the host grows the queue and re-runs the job.
+__device__ __forceinline__ void expand_masks(const PairArgs& G, uint32_t (&mask)[SLOTS], const Cand& C, uint32_t from_slot0, int lane) {
   uint32_t mine = 0;
 #pragma unroll
   for (int u = 0; u < SLOTS; ++u) mine += __popc(mask[u]);
-  while (__any_sync(0xffffffffu, mine != 0u) || flush) {
-    const uint32_t inc = warp_inclusive_sum(mine, lane);
-    const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
-    uint32_t pos = (uint32_t)q1len + (inc - mine);
+  if (!__any_sync(0xffffffffu, mine != 0u)) return;
+  const uint32_t inc = warp_inclusive_sum(mine, lane);
+  unsigned long long base = 0;
+  if (lane == 31) base = atomicAdd(&G.ctr->q_len, (unsigned long long)inc);
+  base = __shfl_sync(0xffffffffu, base, 31);
+  unsigned long long pos = base + (inc - mine);
 #pragma unroll
-    for (int u = 0; u < SLOTS; ++u) {
-      const uint32_t t = C.t[u] & SLOT_MASK;
-      while (mask[u] && pos < (uint32_t)Q1_CAP) {
-        const uint32_t i = __ffs(mask[u]) - 1;
-        mask[u] &= mask[u] - 1;
-        q1[pos++] = make_uint2(from_slot0 + i, t);
-        --mine;
-      }
+  for (int u = 0; u < SLOTS; ++u) {
+    const uint32_t t = C.t[u] & SLOT_MASK;
+    while (mask[u]) {
+      const uint32_t i = __ffs(mask[u]) - 1;
+      mask[u] &= mask[u] - 1;
+      if (pos < G.pairq_cap) G.pairq[pos] = make_uint2(from_slot0 + i, t);
+      ++pos;
     }
-    q1len = min(q1len + (int)total, Q1_CAP);
-    __syncwarp();
-    drain_q1(G, P, lim2, q1, q1len, q2, q2len, lane, n_in32, K, flush);  // the only call site
-    if (flush) break;
   }
-}
-
-// candidate e of the item -> sorted slot
-__device__ __forceinline__ uint32_t cand_slot(uint32_t e, uint32_t cb, const uint32_t (&off)[4], const uint32_t (&delta)[4]) {
-  uint32_t d = cb;
-  d = e >= off[0] ? delta[0] : d;
-  d = e >= off[1] ? delta[1] : d;
-  d = e >= off[2] ? delta[2] : d;
-  d = e >= off[3] ? delta[3] : d;
-  return e + d;
 }
 
 // ---- asynchronous staging of the next unit's candidates (cp.async: no registers are held while the copy is in flight) ----
@@ -298,7 +342,8 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 // candidates [chunk0, chunk0 + CHUNK) of the item whose record is spread over the lanes (word): records -> buf, slots -> tbuf.
-// Lane l stages (and later reads) entries l, l + 32, ...: no cross-lane dependency.
+// Lane l stages (and later reads) entries l, l + 32, ...: no cross-lane dependency.  Candidate e lives in sorted slot
+// e + cb (run 0) or e + delta[r] (run r + 1, from candidate off[r] on).
 __device__ __forceinline__ void stage_chunk(const PairArgs& G, uint32_t word, uint32_t chunk0, int lane, uint4* buf, uint32_t* tbuf) {
   const uint32_t cb = __shfl_sync(0xffffffffu, word, 0), total = __shfl_sync(0xffffffffu, word, 2);
   uint32_t off[4], delta[4];
@@ -307,17 +352,20 @@ __device__ __forceinline__ void stage_chunk(const PairArgs& G, uint32_t word, ui
     off[k] = __shfl_sync(0xffffffffu, word, 4 + k);
     delta[k] = __shfl_sync(0xffffffffu, word, 8 + k);
   }
-#pragma unroll
-  for (int u = 0; u < SLOTS; ++u) {
-    const uint32_t e = chunk0 + 32u * u + lane;
-    if (chunk0 + 32u * u < total) {  // warp-uniform: slots beyond the item are never read
-      const uint32_t t = cand_slot(e, cb, off, delta);
-      tbuf[32 * u + lane] = t;
-      if (e < total)
-        cp_async16(buf + 32 * u + lane, G.recA + t);
-      else
-        buf[32 * u + lane] = make_uint4(0x5d5e0b6bu, 0x5d5e0b6bu, 0x5d5e0b6bu, 0u);  // "no candidate": a point 1e18 A away
-    }
+#pragma unroll 1
+  for (uint32_t e0 = chunk0; e0 < min(total, chunk0 + (uint32_t)CHUNK); e0 += 32u) {  // slots beyond the item are never read
+    const uint32_t e = e0 + lane;
+    uint32_t d = cb;
+    d = e >= off[0] ? delta[0] : d;
+    d = e >= off[1] ? delta[1] : d;
+    d = e >= off[2] ? delta[2] : d;
+    d = e >= off[3] ? delta[3] : d;
+    const uint32_t t = e + d;
+    tbuf[e - chunk0] = t;
+    if (e < total)
+      cp_async16(buf + (e - chunk0), G.recA + t);  // first half of the record: position + attr
+    else
+      buf[e - chunk0] = make_uint4(0x5d5e0b6bu, 0x5d5e0b6bu, 0x5d5e0b6bu, 0u);  // "no candidate": a point 1e18 A away
   }
   cp_async_commit();
 }
@@ -344,37 +392,21 @@ __device__ __forceinline__ float atom_limit2(const DevParams& P, const float* li
   return l;
 }
 
-__global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_pairs(const PairArgs G, const DevParams P) {
+// ---- k_screen --------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_screen(const PairArgs G, const DevParams P) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  PairSmem& S = *reinterpret_cast<PairSmem*>(smem_raw);
+  ScreenSmem& S = *reinterpret_cast<ScreenSmem*>(smem_raw);
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  // per element-class pair: no clash / covalent / vdW label beyond (max(cov sum, vdW sum) + |comp|)^2 (vdw.rs:33-41)
-  for (int k = threadIdx.x; k < 256; k += PAIR_THREADS) {
-    const int ea = k >> 4, eb = k & 15;
-    const double r = fmax(P.cov[ea] + P.cov[eb], P.vdw[ea] + P.vdw[eb]) + fabs(P.comp);
-    const double r2 = r > 0.0 ? r * r * (1.0 + 1e-9) : 0.0;
-    S.lim2[k] = __double2float_ru(r2) + P.guard;
-  }
-  __syncthreads();
-  if (threadIdx.x < 16) {  // per element class: the largest of its row
+  if (threadIdx.x < 16) {  // per element class: the largest limit over all partner classes
     float m = 0.f;
-    for (int eb = 0; eb < 16; ++eb) m = fmaxf(m, S.lim2[threadIdx.x * 16 + eb]);
+    for (int eb = 0; eb < 16; ++eb) m = fmaxf(m, class_pair_limit2(P, threadIdx.x, eb));
     S.lim1[threadIdx.x] = m;
   }
-  if (lane < 4) S.acc[wid][lane] = 0ull;
   __syncthreads();
   FromRec* sfrom = S.from[wid];
-  uint2* q1 = S.q1[wid];
-  uint2* q2 = S.q2[wid];
-  unsigned long long* acc = S.acc[wid];  // [0] candidate tests, lane 0 only
-  const float* lim2 = S.lim2;
-  int q1len = 0, q2len = 0;
-  uint32_t n_in32 = 0;  // pairs counted in f32 (screen and B1), per lane; flushed into 64 bits per item
-  PairCounts K{0ull, 0ull};
-  unsigned long long n_in = 0;
+  unsigned long long n_in = 0, n_tests = 0;  // n_tests: lane 0 only
   const uint32_t n_items = G.ctr->n_items;
   const float half_hit = 0.5f * P.scr_hit, half_cert = 0.5f * P.scr_cert;
-  const float guard_a = P.guard_a;
 
   // ---- pipeline prologue ------------------------------------------------------------------------------------------
   uint32_t word = fetch_item(G, __shfl_sync(0xffffffffu, draw_cursor(G, lane), 0), n_items, lane);    // current item
@@ -384,15 +416,12 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_pairs(const P
   int pb = 0;
   stage_chunk(G, word, 0, lane, S.buf[wid][0], S.tbuf[wid][0]);
 
-  // The last trip of the loop has no item (live = false): it only flushes the queues, through the same (single)
-  // instance of the stage-B code as every other trip.
-  while (true) {
+  while (__shfl_sync(0xffffffffu, word, 2) != 0u) {
     const uint32_t cb = __shfl_sync(0xffffffffu, word, 0), n_own = __shfl_sync(0xffffffffu, word, 1),
                    total = __shfl_sync(0xffffffffu, word, 2);
-    const bool live = total != 0u;
     const float ccx = __uint_as_float(__shfl_sync(0xffffffffu, word, 12)), ccy = __uint_as_float(__shfl_sync(0xffffffffu, word, 13)),
                 ccz = __uint_as_float(__shfl_sync(0xffffffffu, word, 14));
-    const int ns = live ? (int)min((uint32_t)SLOTS, (total - chunk0 + 31u) >> 5) : 0;
+    const int ns = (int)min((uint32_t)SLOTS, (total - chunk0 + 31u) >> 5);
     // ---- this chunk's candidates: shared memory -> registers, cell-local frame --------------------------------------
     cp_async_wait_all();
     const uint4* buf = S.buf[wid][pb];
@@ -416,22 +445,21 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_pairs(const P
       }
     }
     // ---- stage the next unit: the next chunk of this item, or chunk 0 of the next item ------------------------------
-    const bool more = live && chunk0 + CHUNK < total;
+    const bool more = chunk0 + CHUNK < total;
     uint32_t word_nn = word_n, w_raw_n = w_raw;
-    if (!live) {
-    } else if (more) {
+    if (more) {
       stage_chunk(G, word, chunk0 + CHUNK, lane, S.buf[wid][pb ^ 1], S.tbuf[wid][pb ^ 1]);
     } else {
       stage_chunk(G, word_n, 0, lane, S.buf[wid][pb ^ 1], S.tbuf[wid][pb ^ 1]);
       word_nn = fetch_item(G, __shfl_sync(0xffffffffu, w_raw, 0), n_items, lane);
       w_raw_n = draw_cursor(G, lane);
     }
-    if (live && chunk0 == 0 && lane == 0)
-      acc[0] += (unsigned long long)n_own * (total - n_own) + (unsigned long long)n_own * (n_own - 1) / 2;
+    // distance tests this item stands for: own-cell pairs once, every other candidate against every own atom
+    if (chunk0 == 0) n_tests += (unsigned long long)n_own * (total - n_own) + (unsigned long long)n_own * (n_own - 1) / 2;
 
     // ---- from-atoms in passes of 32 (one pass for every realistic cell) ------------------------------------------------
-    for (uint32_t fbo = 0; fbo < (live ? n_own : 1u); fbo += FROM_PASS) {
-      const int nf = live ? (int)min((uint32_t)FROM_PASS, n_own - fbo) : 0;
+    for (uint32_t fbo = 0; fbo < n_own; fbo += FROM_PASS) {
+      const int nf = (int)min((uint32_t)FROM_PASS, n_own - fbo);
       __syncwarp();
       if (lane < nf && (chunk0 == 0 || n_own > (uint32_t)FROM_PASS)) {  // a single pass stays staged for the later chunks
         uint4 fr = own_raw;
@@ -442,10 +470,10 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_pairs(const P
         f.z = __uint_as_float(fr.z) - ccz;
         const float hf = 0.5f * fmaf(f.z, f.z, fmaf(f.y, f.y, f.x * f.x));
         // no label can fire for this atom beyond its own limit: a per-atom T_near (conservative; B1 applies the pair limit)
-        const float t_near = fminf(P.scr_near, atom_limit2(P, S.lim1, fr.w) + guard_a);
+        const float t_near = P.count_classified ? P.scr_near : fminf(P.scr_near, atom_limit2(P, S.lim1, fr.w) + P.guard_a);
         f.k_hit = hf - half_hit;
         f.k_cert = hf - half_cert;
-        f.k_near = hf - 0.5f * (P.count_classified ? P.scr_near : t_near);
+        f.k_near = hf - 0.5f * t_near;
         f.w = ((fr.w >> 31) << 16) | 1u;
         f.pad = 0u;
         sfrom[lane] = f;
@@ -458,26 +486,24 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_pairs(const P
         lim[u] = e < n_own ? (e > fbo ? e - fbo : 0u) : 0xffffffffu;
         mask[u] = cnt[u] = 0u;
       }
-      const int tri = chunk0 >= n_own ? 0 : (chunk0 + 32u >= n_own ? 1 : 2);
       // own-cell atoms beyond slot 0 (more than 32 atoms in a cell) are rare: one variant, all slots
-      switch (live ? (tri == 2 ? 2 * SLOTS : tri * SLOTS + ns - 1) : -1) {
-#define SCREEN_CASE(T, N) \
-  case (T) * SLOTS + (N) - 1: screen_pass<T, N>(sfrom, nf, C, lim, mask, cnt); break;
-#define SCREEN_ROW(T) SCREEN_CASE(T, 1) SCREEN_CASE(T, 2) SCREEN_CASE(T, 3) SCREEN_CASE(T, 4) SCREEN_CASE(T, 5) SCREEN_CASE(T, 6)
-        SCREEN_ROW(0) SCREEN_ROW(1)
-        case 2 * SLOTS: screen_pass<2, SLOTS>(sfrom, nf, C, lim, mask, cnt); break;
-#undef SCREEN_ROW
-#undef SCREEN_CASE
+      switch ((chunk0 < n_own && chunk0 + 32u < n_own) ? 0 : ns) {
+        case 0: screen_pass<true, SLOTS>(sfrom, nf, C, lim, mask, cnt); break;
+        case 1: screen_pass<false, 1>(sfrom, nf, C, lim, mask, cnt); break;
+        case 2: screen_pass<false, 2>(sfrom, nf, C, lim, mask, cnt); break;
+        case 3: screen_pass<false, 3>(sfrom, nf, C, lim, mask, cnt); break;
+        case 4: screen_pass<false, 4>(sfrom, nf, C, lim, mask, cnt); break;
+        case 5: screen_pass<false, 5>(sfrom, nf, C, lim, mask, cnt); break;
+        default: screen_pass<false, 6>(sfrom, nf, C, lim, mask, cnt); break;
       }
       if (P.count_in_cutoff) {
+        uint32_t c = 0;
 #pragma unroll
-        for (int u = 0; u < SLOTS; ++u) n_in32 += (cnt[u] >> 16) + (cnt[u] & 0xffffu) * (C.t[u] >> 31);
+        for (int u = 0; u < SLOTS; ++u) c += (cnt[u] >> 16) + (cnt[u] & 0xffffu) * (C.t[u] >> 31);
+        n_in += c;
       }
-      expand_masks(G, P, lim2, mask, C, cb + fbo, q1, q1len, q2, q2len, lane, n_in32, K, !live);
+      expand_masks(G, mask, C, cb + fbo, lane);
     }
-    n_in += n_in32;
-    n_in32 = 0;
-    if (!live) break;
 
     // ---- advance ------------------------------------------------------------------------------------------------------
     pb ^= 1;
@@ -490,17 +516,12 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_pairs(const P
       w_raw = w_raw_n;
     }
   }
-  n_in += K.n_in;
-  unsigned long long n_cls = K.n_cls;
+  cp_async_wait_all();
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    n_in += __shfl_xor_sync(0xffffffffu, n_in, o);
-    n_cls += __shfl_xor_sync(0xffffffffu, n_cls, o);
-  }
+  for (int o = 16; o > 0; o >>= 1) n_in += __shfl_xor_sync(0xffffffffu, n_in, o);
   if (lane == 0) {
-    atomicAdd(&G.ctr->screened, acc[0]);
-    atomicAdd(&G.ctr->in_cutoff, n_in);
-    atomicAdd(&G.ctr->classified, n_cls);
+    atomicAdd(&G.ctr->screened, n_tests);
+    if (n_in) atomicAdd(&G.ctr->in_cutoff, n_in);
   }
 }
 

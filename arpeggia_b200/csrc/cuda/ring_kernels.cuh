@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(256) k_ring_atom(const RingArgs R, const DevPa
         if (!(dist <= 4.5)) continue;
         const double c = __ddiv_rn(dot3(nx_, ny_, nz_, vx, vy, vz), dmul(nn, dist));
         if (!fold_pred(c, P.ang.f_le_30_pos, P.ang.f_le_30_neg)) continue;  // theta <= 30
-        push_row(R.rows, R.row_cap, R.ctr, r | ARP_RING_FLAG, R.perm[t], ARP_CationPi, dist);
+        push_row(R.rows, R.row_cap, R.ctr, r | ARP_RING_FLAG, R.recA[t].perm, ARP_CationPi, dist);
       }
     }
   }
