@@ -14,7 +14,46 @@ __device__ __forceinline__ void push_row(arp_row* rows, unsigned long long cap, 
   if (w < cap) rows[w] = arp_row{from, to, label, __double2float_rn(dist)};
 }
 
-// one warp per ring; lanes sweep the atoms of the 27 cells around the ring centroid (9 contiguous runs)
+// The 27 cells around a point are 9 rows (y, z) of up to 3 x-adjacent cells = 9 contiguous runs of sorted slots.
+// Lane k < 9 fetches the bounds of run k (all nine in one memory round trip); the warp then walks the concatenation of
+// the runs, one entry per lane.  Returns this lane's run (begin, length) and the exclusive prefix / total over the runs.
+struct Runs9 {
+  uint32_t begin, len, off, total;
+};
+__device__ __forceinline__ Runs9 fetch_runs9(const uint32_t* __restrict__ cell_start, uint32_t cell_base, int nx, int ny, int nz, int ix,
+                                             int iy, int iz, int lane) {
+  Runs9 r{0u, 0u, 0u, 0u};
+  if (lane < 9) {
+    const int y = iy + lane % 3 - 1, z = iz + lane / 3 - 1;
+    if (y >= 0 && y < ny && z >= 0 && z < nz) {
+      const uint32_t row = cell_base + (uint32_t)((z * ny + y) * nx);
+      r.begin = cell_start[row + (uint32_t)max(ix - 1, 0)];
+      r.len = cell_start[row + (uint32_t)min(ix + 1, nx - 1) + 1u] - r.begin;
+    }
+  }
+  uint32_t inc = r.len;
+#pragma unroll
+  for (int o = 1; o < 16; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  r.off = inc - r.len;
+  r.total = __shfl_sync(0xffffffffu, inc, 8);
+  return r;
+}
+// entry j of the concatenation -> sorted slot (every lane asks for its own j)
+__device__ __forceinline__ uint32_t runs9_slot(const Runs9& r, uint32_t j) {
+  uint32_t slot = 0;
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    const uint32_t off = __shfl_sync(0xffffffffu, r.off, k), len = __shfl_sync(0xffffffffu, r.len, k),
+                   begin = __shfl_sync(0xffffffffu, r.begin, k);
+    if (j >= off && j < off + len) slot = begin + (j - off);
+  }
+  return slot;
+}
+
+// one warp per ring; lanes sweep the atoms of the 27 cells around the ring centroid
 __global__ void __launch_bounds__(256) k_ring_atom(const RingArgs R, const DevParams P) {
   const int lane = threadIdx.x & 31;
   const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
@@ -29,48 +68,46 @@ __global__ void __launch_bounds__(256) k_ring_atom(const RingArgs R, const DevPa
     const int iy = min(max((int)floor((cy - D.oy) * P.inv_edge), 0), D.ny - 1);
     const int iz = min(max((int)floor((cz - D.oz) * P.inv_edge), 0), D.nz - 1);
     const double nn = norm3(nx_, ny_, nz_);
-    for (int k = 0; k < 9; ++k) {
-      const int y = iy + k % 3 - 1, z = iz + k / 3 - 1;
-      if (y < 0 || y >= D.ny || z < 0 || z >= D.nz) continue;
-      const uint32_t row = D.cell_base + (uint32_t)((z * D.ny + y) * D.nx);
-      const uint32_t sb = R.cell_start[row + max(ix - 1, 0)], se = R.cell_start[row + min(ix + 1, D.nx - 1) + 1];
-      for (uint32_t t = sb + lane; t < se; t += 32) {
-        const uint32_t wy = R.recA[t].attr;
-        if (!(wy & ARP_ATTR_POS_RES)) continue;  // aromatic.rs:18: only cations can give a row
-        const RecB b = R.recB[t];
-        const double vx = dsub(b.x, cx), vy = dsub(b.y, cy), vz = dsub(b.z, cz);
-        const double d2 = dot3(vx, vy, vz, vx, vy, vz);
-        if (!(d2 <= P.rc2)) continue;  // tree.locate_within_distance(center, rc^2), complex.rs:310-313
-        if (!ring_atom_filter(wr, kr, orr, wy, b.chain_key, b.res_ordinal)) continue;
-        const double dist = __dsqrt_rn(d2);  // ring.point_dist
-        if (!(dist <= 4.5)) continue;
-        const double c = __ddiv_rn(dot3(nx_, ny_, nz_, vx, vy, vz), dmul(nn, dist));
-        if (!fold_pred(c, P.ang.f_le_30_pos, P.ang.f_le_30_neg)) continue;  // theta <= 30
-        push_row(R.rows, R.row_cap, R.ctr, r | ARP_RING_FLAG, R.recA[t].perm, ARP_CationPi, dist);
-      }
+    const Runs9 runs = fetch_runs9(R.cell_start, D.cell_base, D.nx, D.ny, D.nz, ix, iy, iz, lane);
+    for (uint32_t j0 = 0; j0 < runs.total; j0 += 32) {
+      const uint32_t j = j0 + lane;
+      const uint32_t t = runs9_slot(runs, j);
+      if (j >= runs.total) continue;
+      const uint32_t wy = R.recA[t].attr;
+      if (!(wy & ARP_ATTR_POS_RES)) continue;  // aromatic.rs:18: only cations can give a row
+      const RecB b = R.recB[t];
+      const double vx = dsub(b.x, cx), vy = dsub(b.y, cy), vz = dsub(b.z, cz);
+      const double d2 = dot3(vx, vy, vz, vx, vy, vz);
+      if (!(d2 <= P.rc2)) continue;  // tree.locate_within_distance(center, rc^2), complex.rs:310-313
+      if (!ring_atom_filter(wr, kr, orr, wy, b.chain_key, b.res_ordinal)) continue;
+      const double dist = __dsqrt_rn(d2);  // ring.point_dist
+      if (!(dist <= 4.5)) continue;
+      const double c = __ddiv_rn(dot3(nx_, ny_, nz_, vx, vy, vz), dmul(nn, dist));
+      if (!fold_pred(c, P.ang.f_le_30_pos, P.ang.f_le_30_neg)) continue;  // theta <= 30
+      push_row(R.rows, R.row_cap, R.ctr, r | ARP_RING_FLAG, R.recA[t].perm, ARP_CationPi, dist);
     }
   }
 }
 
-// one thread per ring r1; 27 cells of the ring-centroid grid
-__global__ void __launch_bounds__(128) k_ring_ring(const RingArgs R, const DevParams P) {
-  const uint32_t r1 = blockIdx.x * blockDim.x + threadIdx.x;
-  if (r1 >= R.n_rings) return;
-  const uint32_t w1 = R.attr[r1];
-  if (!(w1 & ARP_ATTR_LIGAND) || (w1 & ARP_ATTR_GHOST)) return;  // complex.rs:363
-  const StructDesc& D = R.descs[R.ring_struct ? R.ring_struct[r1] : 0u];
-  const double c1[3] = {R.center[3 * r1], R.center[3 * r1 + 1], R.center[3 * r1 + 2]};
-  const double n1[3] = {R.normal[3 * r1], R.normal[3 * r1 + 1], R.normal[3 * r1 + 2]};
-  const uint32_t k1 = R.chain_key[r1], o1 = R.res_ordinal[r1];
-  const int ix = min(max((int)floor((c1[0] - D.ox) * P.inv_redge), 0), D.rnx - 1);
-  const int iy = min(max((int)floor((c1[1] - D.oy) * P.inv_redge), 0), D.rny - 1);
-  const int iz = min(max((int)floor((c1[2] - D.oz) * P.inv_redge), 0), D.rnz - 1);
-  for (int k = 0; k < 9; ++k) {
-    const int y = iy + k % 3 - 1, z = iz + k / 3 - 1;
-    if (y < 0 || y >= D.rny || z < 0 || z >= D.rnz) continue;
-    const uint32_t row = D.rcell_base + (uint32_t)((z * D.rny + y) * D.rnx);
-    const uint32_t sb = R.rcell_start[row + max(ix - 1, 0)], se = R.rcell_start[row + min(ix + 1, D.rnx - 1) + 1];
-    for (uint32_t t = sb; t < se; ++t) {
+// one warp per ring r1; lanes take the rings of the 27 cells of the ring-centroid grid around it
+__global__ void __launch_bounds__(256) k_ring_ring(const RingArgs R, const DevParams P) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  for (uint32_t r1 = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r1 < R.n_rings; r1 += warps) {
+    const uint32_t w1 = R.attr[r1];
+    if (!(w1 & ARP_ATTR_LIGAND) || (w1 & ARP_ATTR_GHOST)) continue;  // complex.rs:363
+    const StructDesc& D = R.descs[R.ring_struct ? R.ring_struct[r1] : 0u];
+    const double c1[3] = {R.center[3 * r1], R.center[3 * r1 + 1], R.center[3 * r1 + 2]};
+    const double n1[3] = {R.normal[3 * r1], R.normal[3 * r1 + 1], R.normal[3 * r1 + 2]};
+    const uint32_t k1 = R.chain_key[r1], o1 = R.res_ordinal[r1];
+    const int ix = min(max((int)floor((c1[0] - D.ox) * P.inv_redge), 0), D.rnx - 1);
+    const int iy = min(max((int)floor((c1[1] - D.oy) * P.inv_redge), 0), D.rny - 1);
+    const int iz = min(max((int)floor((c1[2] - D.oz) * P.inv_redge), 0), D.rnz - 1);
+    const Runs9 runs = fetch_runs9(R.rcell_start, D.rcell_base, D.rnx, D.rny, D.rnz, ix, iy, iz, lane);
+    for (uint32_t j0 = 0; j0 < runs.total; j0 += 32) {
+      const uint32_t j = j0 + lane;
+      const uint32_t t = runs9_slot(runs, j);
+      if (j >= runs.total) continue;
       const uint32_t r2 = R.rperm[t];
       const uint32_t w2 = R.attr[r2];
       if (!(w2 & ARP_ATTR_RECEPTOR)) continue;  // complex.rs:364
