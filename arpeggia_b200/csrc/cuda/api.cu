@@ -77,6 +77,7 @@ struct arp_ctx {
   int sm_count = 148;
   int occ_screen = 1, occ_filter = 1, occ_exact = 1;  // resident CTAs per SM (grids are sized to one full wave)
   cudaStream_t stream = nullptr;
+  cudaStream_t side = nullptr;  // k_rings runs here, concurrently with the pair kernels (forked / joined with events)
   std::string err;
 
   // job inputs in HBM (original order)
@@ -88,11 +89,14 @@ struct arp_ctx {
   DBuf<StructDesc> descs;
   std::vector<StructDesc> h_descs;
   std::vector<int64_t> atom_begin, ring_begin;
+  std::vector<double> hint_lo, hint_hi;  // callers' bounding boxes (arp_structure.bbox_*), 3 per structure
+  bool have_hint = false;                // every structure of the job came with one
+  bool ignore_hint = false;              // a hint turned out wrong: the job is re-run with the computed boxes
 
   // cell lists and sorted records
   DBuf<unsigned long long> bbox;
   DBuf<uint32_t> cell_of, rank_of, cell_start, tile_sums;
-  DBuf<uint32_t> rcell_of, rrank_of, rcell_start, rperm;
+  DBuf<uint32_t> rcell_of, rrank_of, rcell_start, rperm, cations;
   DBuf<RecA> recA;
   DBuf<RecB> recB;
   DBuf<Item> items;
@@ -113,7 +117,7 @@ struct arp_ctx {
   bool have_job = false, have_run = false;
   arp_params last_params{};
   DevParams dp{};
-  cudaEvent_t ev[8] = {};
+  cudaEvent_t ev[10] = {};
   int64_t launches = 0;
   int retries = 0;
   float ms_h2d = 0.f, ms_d2h = 0.f;
@@ -186,6 +190,19 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
     c->ring_begin[k + 1] = c->ring_begin[k] + s[k]->n_rings;
     res_begin[k + 1] = res_begin[k] + s[k]->n_residues;
     h_begin[k + 1] = h_begin[k] + s[k]->n_h;
+  }
+  c->hint_lo.assign(3 * n, 0.0);
+  c->hint_hi.assign(3 * n, 0.0);
+  c->have_hint = true;
+  c->ignore_hint = false;
+  for (int64_t k = 0; k < n; ++k) {
+    if (s[k]->n_atoms > 0 && !s[k]->has_bbox) c->have_hint = false;
+    for (int a = 0; a < 3; ++a) {
+      c->hint_lo[3 * k + a] = s[k]->has_bbox ? s[k]->bbox_min[a] : 0.0;
+      c->hint_hi[3 * k + a] = s[k]->has_bbox ? s[k]->bbox_max[a] : 0.0;
+      if (s[k]->has_bbox && !(std::isfinite(s[k]->bbox_min[a]) && std::isfinite(s[k]->bbox_max[a]) && s[k]->bbox_min[a] <= s[k]->bbox_max[a]))
+        c->have_hint = false;
+    }
   }
   c->n_struct = n;
   c->n_atoms = c->atom_begin[n];

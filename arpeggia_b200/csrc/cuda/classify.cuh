@@ -63,7 +63,7 @@ __device__ __forceinline__ bool ring_atom_filter(uint32_t wr, uint32_t kr, uint3
 __device__ __forceinline__ bool is_disulfide(const PairArgs& G, const DevParams& P, uint32_t ra, uint32_t rb) {
   const int cb1 = G.res_cb[ra], s1 = G.res_sg[ra], cb2 = G.res_cb[rb], s2 = G.res_sg[rb];
   if (cb1 < 0 || cb2 < 0 || s1 < 0 || s2 < 0) {  // `.find(..).unwrap()` panics in the reference
-    atomicExch(&G.ctr->error, 1u);
+    atomicOr(&G.ctr->error, 1u);
     return false;
   }
   // pdbtbx Atom::dihedral(cb1; s1, s2, cb2): angle between the normals of (cb1,s1,s2) and (s1,s2,cb2)

@@ -90,6 +90,7 @@ struct Counters {
   unsigned long long classified;  uint64_t pad3[15];
   unsigned int work;              uint32_t padw[31];   // work-item cursor of the persistent pair kernel
   unsigned int n_items;           uint32_t padi[31];   // non-empty cells
+  unsigned int n_cations;         uint32_t padc[31];   // atoms that can take part in a cation-pi contact (aromatic.rs:18)
   unsigned int error;             uint32_t pade[31];   // 1 = CYS residue without CB / SG (vdw.rs:58 unwrap)
   unsigned long long q_len;       uint64_t padq[15];   // pairs pushed by k_screen (may exceed the queue's capacity)
   unsigned long long q2_len;      uint64_t padr[15];   // pairs pushed by k_filter (likewise)
@@ -131,10 +132,11 @@ struct RingArgs {
   // ring-centroid cell list
   const uint32_t* rcell_start;
   const uint32_t* rperm;        // sorted slot -> ring index
-  // atom cell list
+  // cation list: sorted slots of the atoms with ARP_ATTR_POS_RES (k_scatter_atoms)
+  const uint32_t* cations;
+  const uint32_t* atom_struct;  // input-order atom -> structure; nullptr when the job has one structure
   const RecA* recA;
   const RecB* recB;
-  const uint32_t* cell_start;
   const StructDesc* descs;
   arp_row* rows;
   unsigned long long row_cap;

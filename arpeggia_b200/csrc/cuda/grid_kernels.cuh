@@ -102,14 +102,22 @@ __device__ __forceinline__ int cell_coord(double p, double origin, double inv_ed
 __global__ void __launch_bounds__(256)
 k_cell_assign(const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz, int stride, uint32_t n,
               const uint32_t* __restrict__ point_struct, const StructDesc* __restrict__ descs, double inv_edge, int ring_grid,
-              uint32_t* __restrict__ cell_of, uint32_t* __restrict__ rank_of, uint32_t* __restrict__ cell_count) {
+              uint32_t* __restrict__ cell_of, uint32_t* __restrict__ rank_of, uint32_t* __restrict__ cell_count,
+              unsigned int* __restrict__ box_error) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const StructDesc& d = descs[point_struct ? point_struct[i] : 0u];
   const int nx = ring_grid ? d.rnx : d.nx, ny = ring_grid ? d.rny : d.ny, nz = ring_grid ? d.rnz : d.nz;
-  const int ix = cell_coord(px[(size_t)i * stride], d.ox, inv_edge, nx);
-  const int iy = cell_coord(py[(size_t)i * stride], d.oy, inv_edge, ny);
-  const int iz = cell_coord(pz[(size_t)i * stride], d.oz, inv_edge, nz);
+  const double x = px[(size_t)i * stride], y = py[(size_t)i * stride], z = pz[(size_t)i * stride];
+  if (box_error) {
+    // the grid was laid out from the caller's bounding-box hint: an atom outside it (or a NaN) voids the layout
+    const double tx = (x - d.ox) * inv_edge, ty = (y - d.oy) * inv_edge, tz = (z - d.oz) * inv_edge;
+    const double eps = 1e-6;
+    if (!(tx > -eps && tx < nx + eps && ty > -eps && ty < ny + eps && tz > -eps && tz < nz + eps)) atomicOr(box_error, 2u);
+  }
+  const int ix = cell_coord(x, d.ox, inv_edge, nx);
+  const int iy = cell_coord(y, d.oy, inv_edge, ny);
+  const int iz = cell_coord(z, d.oz, inv_edge, nz);
   const uint32_t c = (ring_grid ? d.rcell_base : d.cell_base) + (uint32_t)((iz * ny + iy) * nx + ix);
   cell_of[i] = c;
   rank_of[i] = atomicAdd(&cell_count[c], 1u);
@@ -193,7 +201,7 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
                 const uint32_t* __restrict__ res_id, const uint32_t* __restrict__ atom_struct, const StructDesc* __restrict__ descs,
                 const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of, const uint32_t* __restrict__ cell_start,
                 uint32_t n, double edge, RecA* __restrict__ recA, RecB* __restrict__ recB, Item* __restrict__ items,
-                Counters* __restrict__ ctr) {
+                uint32_t* __restrict__ cations, Counters* __restrict__ ctr) {
   const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
   if (a >= n) return;
   const uint32_t s = atom_struct ? atom_struct[a] : 0u;
@@ -220,6 +228,8 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
   rb.chain_key = ra.chain_key;
   rb.res_ordinal = ra.res_ordinal;
   recB[slot] = rb;
+  // the few atoms that can make a cation-pi contact (aromatic.rs:18) are listed for the ring kernel
+  if (w & ARP_ATTR_POS_RES) cations[atomicAdd(&ctr->n_cations, 1u)] = slot;
   if (r == 0) {  // first arrival publishes the cell as a work item: its half shell as 5 runs of sorted slots
     const uint32_t local = c - d.cell_base;
     const int nx = d.nx, ny = d.ny, nz = d.nz;

@@ -62,6 +62,7 @@ struct ScreenSmem {
   uint4 buf[PAIR_WARPS][2][CHUNK];      // staged candidate records (RecA bits), double buffered
   uint32_t tbuf[PAIR_WARPS][2][CHUNK];  // their sorted slots
   FromRec from[PAIR_WARPS][FROM_PASS + 1];
+  unsigned int* cursor[32];             // &ctr->work, one copy per lane (see draw_cursor)
   float lim1[16];                       // per element class: largest (max(cov sum, vdW sum) + |comp|)^2 + g over partners
 };
 
@@ -397,10 +398,13 @@ __device__ __forceinline__ void stage_chunk(const PairArgs& G, uint32_t word, ui
   cp_async_commit();
 }
 
-// lane 0 draws the next item index; the value is broadcast only when it is needed (one iteration later)
-__device__ __forceinline__ uint32_t draw_cursor(const PairArgs& G, int lane) {
+// lane 0 draws the next item index; the value is broadcast only when it is needed (one iteration later).
+// `cursor` is this lane's copy of &ctr->work read from shared memory: with an address it can prove warp-uniform, ptxas
+// rewrites the atomic into its warp-aggregated form, whose result shuffle right behind the atomic stalled the warp for
+// the whole round trip (12 % of the stall samples).
+__device__ __forceinline__ uint32_t draw_cursor(unsigned int* cursor, int lane) {
   uint32_t w = 0;
-  if (lane == 0) w = atomicAdd(&G.ctr->work, 1u);
+  if (lane == 0) w = atomicAdd(cursor, 1u);
   return w;
 }
 // word `lane` of item w (lanes 16..31 and out-of-range items read nothing); total = 0 marks the end
@@ -429,7 +433,9 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_screen(const 
     for (int eb = 0; eb < 16; ++eb) m = fmaxf(m, class_pair_limit2(P, threadIdx.x, eb));
     S.lim1[threadIdx.x] = m;
   }
+  if (threadIdx.x < 32) S.cursor[threadIdx.x] = &G.ctr->work;
   __syncthreads();
+  unsigned int* const cursor = S.cursor[lane];
   FromRec* sfrom = S.from[wid];
   unsigned long long n_in = 0, n_tests = 0;
   QWindow Q{0ull, 0ull};
@@ -437,9 +443,9 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_screen(const 
   const float half_hit = 0.5f * P.scr_hit, half_cert = 0.5f * P.scr_cert;
 
   // ---- pipeline prologue ------------------------------------------------------------------------------------------
-  uint32_t word = fetch_item(G, __shfl_sync(0xffffffffu, draw_cursor(G, lane), 0), n_items, lane);    // current item
-  uint32_t word_n = fetch_item(G, __shfl_sync(0xffffffffu, draw_cursor(G, lane), 0), n_items, lane);  // next item
-  uint32_t w_raw = draw_cursor(G, lane);                                                              // the one after
+  uint32_t word = fetch_item(G, __shfl_sync(0xffffffffu, draw_cursor(cursor, lane), 0), n_items, lane);    // current item
+  uint32_t word_n = fetch_item(G, __shfl_sync(0xffffffffu, draw_cursor(cursor, lane), 0), n_items, lane);  // next item
+  uint32_t w_raw = draw_cursor(cursor, lane);                                                              // the one after
   uint32_t chunk0 = 0;
   int pb = 0;
   stage_chunk(G, word, 0, lane, S.buf[wid][0], S.tbuf[wid][0]);
@@ -480,7 +486,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_screen(const 
     } else {
       stage_chunk(G, word_n, 0, lane, S.buf[wid][pb ^ 1], S.tbuf[wid][pb ^ 1]);
       word_nn = fetch_item(G, __shfl_sync(0xffffffffu, w_raw, 0), n_items, lane);
-      w_raw_n = draw_cursor(G, lane);
+      w_raw_n = draw_cursor(cursor, lane);
     }
     // distance tests this item stands for: own-cell pairs once, every other candidate against every own atom
     if (chunk0 == 0) n_tests += (unsigned long long)n_own * (total - n_own) + (unsigned long long)n_own * (n_own - 1) / 2;

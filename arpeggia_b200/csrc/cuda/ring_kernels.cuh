@@ -1,6 +1,6 @@
-// Ring kernels (sm_100a): cation-pi (ring centroid vs atom grid) and pi-pi (ring-centroid grid).
-//   k_ring_atom  <->  get_ring_atom_contacts + find_cation_pi   src/contacts/complex.rs:301-352, aromatic.rs:14-29
-//   k_ring_ring  <->  get_ring_ring_contacts + find_pi_pi       src/contacts/complex.rs:354-405, aromatic.rs:33-64
+// Ring kernel (sm_100a): cation-pi and pi-pi contacts, both against the ring-centroid grid.
+//   k_rings  <->  get_ring_atom_contacts + find_cation_pi   src/contacts/complex.rs:301-352, aromatic.rs:14-29
+//                 get_ring_ring_contacts + find_pi_pi       src/contacts/complex.rs:354-405, aromatic.rs:33-64
 // The reference's ring-ring loop is O(R^2) over all ring pairs; find_pi_pi rejects centroid distances above
 // 6.0 A first, so a centroid grid with edge >= 6.0 visits exactly the pairs that can produce a row.
 #pragma once
@@ -53,53 +53,38 @@ __device__ __forceinline__ uint32_t runs9_slot(const Runs9& r, uint32_t j) {
   return slot;
 }
 
-// one warp per ring; lanes sweep the atoms of the 27 cells around the ring centroid
-__global__ void __launch_bounds__(256) k_ring_atom(const RingArgs R, const DevParams P) {
+// k_rings: one warp per QUERY -- a ring (pi-pi, complex.rs:354-405) or a cation (cation-pi, complex.rs:301-352) -- against
+// the rings of the 27 ring-grid cells around it.  The reference searches the atoms around every ring centroid; only
+// atoms that are positively ionizable by residue name can give a row (aromatic.rs:18) and a row needs
+// dist <= 4.5 < ring-grid edge, so walking the few cations and looking for rings around them visits exactly the pairs
+// that can produce a row -- about 20x fewer tests than sweeping all atoms around all rings.
+__global__ void __launch_bounds__(256) k_rings(const RingArgs R, const DevParams P) {
   const int lane = threadIdx.x & 31;
   const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
-  for (uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < R.n_rings; r += warps) {
-    const uint32_t wr = R.attr[r];
-    if (wr & ARP_ATTR_GHOST) continue;
-    const StructDesc& D = R.descs[R.ring_struct ? R.ring_struct[r] : 0u];
-    const double cx = R.center[3 * r], cy = R.center[3 * r + 1], cz = R.center[3 * r + 2];
-    const double nx_ = R.normal[3 * r], ny_ = R.normal[3 * r + 1], nz_ = R.normal[3 * r + 2];
-    const uint32_t kr = R.chain_key[r], orr = R.res_ordinal[r];
-    const int ix = min(max((int)floor((cx - D.ox) * P.inv_edge), 0), D.nx - 1);
-    const int iy = min(max((int)floor((cy - D.oy) * P.inv_edge), 0), D.ny - 1);
-    const int iz = min(max((int)floor((cz - D.oz) * P.inv_edge), 0), D.nz - 1);
-    const double nn = norm3(nx_, ny_, nz_);
-    const Runs9 runs = fetch_runs9(R.cell_start, D.cell_base, D.nx, D.ny, D.nz, ix, iy, iz, lane);
-    for (uint32_t j0 = 0; j0 < runs.total; j0 += 32) {
-      const uint32_t j = j0 + lane;
-      const uint32_t t = runs9_slot(runs, j);
-      if (j >= runs.total) continue;
-      const uint32_t wy = R.recA[t].attr;
-      if (!(wy & ARP_ATTR_POS_RES)) continue;  // aromatic.rs:18: only cations can give a row
+  const uint32_t n_queries = R.n_rings + R.ctr->n_cations;
+  for (uint32_t q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; q < n_queries; q += warps) {
+    const bool is_ring = q < R.n_rings;
+    // query position, attributes, structure
+    double c1[3], n1[3] = {0.0, 0.0, 0.0};
+    uint32_t w1, k1, o1, sid, id1;
+    if (is_ring) {
+      id1 = q;
+      w1 = R.attr[q];
+      if (!(w1 & ARP_ATTR_LIGAND) || (w1 & ARP_ATTR_GHOST)) continue;  // complex.rs:363
+      c1[0] = R.center[3 * q], c1[1] = R.center[3 * q + 1], c1[2] = R.center[3 * q + 2];
+      n1[0] = R.normal[3 * q], n1[1] = R.normal[3 * q + 1], n1[2] = R.normal[3 * q + 2];
+      k1 = R.chain_key[q], o1 = R.res_ordinal[q];
+      sid = R.ring_struct ? R.ring_struct[q] : 0u;
+    } else {
+      const uint32_t t = R.cations[q - R.n_rings];
+      const RecA a = R.recA[t];
       const RecB b = R.recB[t];
-      const double vx = dsub(b.x, cx), vy = dsub(b.y, cy), vz = dsub(b.z, cz);
-      const double d2 = dot3(vx, vy, vz, vx, vy, vz);
-      if (!(d2 <= P.rc2)) continue;  // tree.locate_within_distance(center, rc^2), complex.rs:310-313
-      if (!ring_atom_filter(wr, kr, orr, wy, b.chain_key, b.res_ordinal)) continue;
-      const double dist = __dsqrt_rn(d2);  // ring.point_dist
-      if (!(dist <= 4.5)) continue;
-      const double c = __ddiv_rn(dot3(nx_, ny_, nz_, vx, vy, vz), dmul(nn, dist));
-      if (!fold_pred(c, P.ang.f_le_30_pos, P.ang.f_le_30_neg)) continue;  // theta <= 30
-      push_row(R.rows, R.row_cap, R.ctr, r | ARP_RING_FLAG, R.recA[t].perm, ARP_CationPi, dist);
+      id1 = a.perm;
+      w1 = a.attr, k1 = a.chain_key, o1 = a.res_ordinal;
+      c1[0] = b.x, c1[1] = b.y, c1[2] = b.z;
+      sid = R.atom_struct ? R.atom_struct[a.perm] : 0u;
     }
-  }
-}
-
-// one warp per ring r1; lanes take the rings of the 27 cells of the ring-centroid grid around it
-__global__ void __launch_bounds__(256) k_ring_ring(const RingArgs R, const DevParams P) {
-  const int lane = threadIdx.x & 31;
-  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
-  for (uint32_t r1 = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r1 < R.n_rings; r1 += warps) {
-    const uint32_t w1 = R.attr[r1];
-    if (!(w1 & ARP_ATTR_LIGAND) || (w1 & ARP_ATTR_GHOST)) continue;  // complex.rs:363
-    const StructDesc& D = R.descs[R.ring_struct ? R.ring_struct[r1] : 0u];
-    const double c1[3] = {R.center[3 * r1], R.center[3 * r1 + 1], R.center[3 * r1 + 2]};
-    const double n1[3] = {R.normal[3 * r1], R.normal[3 * r1 + 1], R.normal[3 * r1 + 2]};
-    const uint32_t k1 = R.chain_key[r1], o1 = R.res_ordinal[r1];
+    const StructDesc& D = R.descs[sid];
     const int ix = min(max((int)floor((c1[0] - D.ox) * P.inv_redge), 0), D.rnx - 1);
     const int iy = min(max((int)floor((c1[1] - D.oy) * P.inv_redge), 0), D.rny - 1);
     const int iz = min(max((int)floor((c1[2] - D.oz) * P.inv_redge), 0), D.rnz - 1);
@@ -110,21 +95,34 @@ __global__ void __launch_bounds__(256) k_ring_ring(const RingArgs R, const DevPa
       if (j >= runs.total) continue;
       const uint32_t r2 = R.rperm[t];
       const uint32_t w2 = R.attr[r2];
-      if (!(w2 & ARP_ATTR_RECEPTOR)) continue;  // complex.rs:364
       const uint32_t k2 = R.chain_key[r2], o2 = R.res_ordinal[r2];
-      // should_compare_residues(k1, k2, true), complex.rs:94-131
-      if ((k1 ^ k2) >> 24) continue;
-      if (k1 == k2) {
-        if (!((o2 > 1u) && (o1 < o2 - 1u))) continue;
-      } else {
-        const bool both = (w1 & w2 & ARP_ATTR_LIGAND) && (w1 & w2 & ARP_ATTR_RECEPTOR);
-        if (both && k1 > k2) continue;
-      }
       const double c2[3] = {R.center[3 * r2], R.center[3 * r2 + 1], R.center[3 * r2 + 2]};
       const double n2[3] = {R.normal[3 * r2], R.normal[3 * r2 + 1], R.normal[3 * r2 + 2]};
-      double dist;
-      const int label = find_pi_pi(P, c1, n1, c2, n2, &dist);
-      if (label >= 0) push_row(R.rows, R.row_cap, R.ctr, r1 | ARP_RING_FLAG, r2 | ARP_RING_FLAG, (uint32_t)label, dist);
+      if (is_ring) {
+        if (!(w2 & ARP_ATTR_RECEPTOR)) continue;  // complex.rs:364
+        // should_compare_residues(k1, k2, true), complex.rs:94-131
+        if ((k1 ^ k2) >> 24) continue;
+        if (k1 == k2) {
+          if (!((o2 > 1u) && (o1 < o2 - 1u))) continue;
+        } else {
+          const bool both = (w1 & w2 & ARP_ATTR_LIGAND) && (w1 & w2 & ARP_ATTR_RECEPTOR);
+          if (both && k1 > k2) continue;
+        }
+        double dist;
+        const int label = find_pi_pi(P, c1, n1, c2, n2, &dist);
+        if (label >= 0) push_row(R.rows, R.row_cap, R.ctr, id1 | ARP_RING_FLAG, r2 | ARP_RING_FLAG, (uint32_t)label, dist);
+      } else {
+        // ring r2 (the `from` side, complex.rs:334-343) against cation atom id1
+        const double vx = dsub(c1[0], c2[0]), vy = dsub(c1[1], c2[1]), vz = dsub(c1[2], c2[2]);
+        const double d2 = dot3(vx, vy, vz, vx, vy, vz);
+        if (!(d2 <= P.rc2)) continue;  // tree.locate_within_distance(center, rc^2), complex.rs:310-313
+        if (!ring_atom_filter(w2, k2, o2, w1, k1, o1)) continue;
+        const double dist = __dsqrt_rn(d2);  // ring.point_dist
+        if (!(dist <= 4.5)) continue;
+        const double c = __ddiv_rn(dot3(n2[0], n2[1], n2[2], vx, vy, vz), dmul(norm3(n2[0], n2[1], n2[2]), dist));
+        if (!fold_pred(c, P.ang.f_le_30_pos, P.ang.f_le_30_neg)) continue;  // theta <= 30
+        push_row(R.rows, R.row_cap, R.ctr, r2 | ARP_RING_FLAG, id1, ARP_CationPi, dist);
+      }
     }
   }
 }

@@ -494,6 +494,23 @@ void Packed::finish() {
   t.ring_attr = ring_attr.data();
   t.ring_chain_key = ring_chain_key.data();
   t.ring_res_ordinal = ring_res_ordinal.data();
+  // bounding-box hint for the cell-grid layout (verified on the device)
+  t.has_bbox = 0;
+  if (!x.empty()) {
+    bool finite = true;
+    for (int a = 0; a < 3; ++a) {
+      const std::vector<double>& v = a == 0 ? x : (a == 1 ? y : z);
+      double lo = v[0], hi = v[0];
+      for (double q : v) {
+        if (!(q == q) || q - q != 0.0) finite = false;
+        lo = q < lo ? q : lo;
+        hi = q > hi ? q : hi;
+      }
+      t.bbox_min[a] = lo;
+      t.bbox_max[a] = hi;
+    }
+    t.has_bbox = finite ? 1 : 0;
+  }
 }
 
 }  // namespace arp

@@ -124,7 +124,7 @@ def pinned_structure(A, packed):
     keep, total = [], 0
     for name, ctype in _lib.Structure._fields_:
         v = getattr(src, name)
-        if name.startswith("n_"):
+        if name.startswith("n_") or name.startswith("bbox_") or name == "has_bbox":
             setattr(dst, name, v)
     sizes = {"x": 8, "y": 8, "z": 8, "attr": 4, "chain_key": 4, "res_ordinal": 4, "res_id": 4}
     n, nr, ng, nh = src.n_atoms, src.n_residues, src.n_rings, src.n_h

@@ -102,6 +102,14 @@ typedef struct arp_structure {
   const uint32_t* ring_attr;     /* n_rings: ARP_ATTR_LIGAND / ARP_ATTR_RECEPTOR of the ring's chain */
   const uint32_t* ring_chain_key;
   const uint32_t* ring_res_ordinal;
+  /* Optional hint: the axis-aligned bounding box of x / y / z, computed by whoever packed the atoms (the host packer
+   * walks every atom anyway).  With has_bbox != 0 the cell grid is laid out without a device reduction and a host round
+   * trip.  The box is verified on the device: if an atom lies outside it the job silently falls back to the computed
+   * box.  Leave has_bbox = 0 for device-resident or unpacked coordinates. */
+  double bbox_min[3];
+  double bbox_max[3];
+  int32_t has_bbox;
+  int32_t reserved_;
 } arp_structure;
 
 #define ARP_FLAG_EMIT_RADIUS_SCREEN 0x1u /* screen atom pairs at min(dist_cutoff, largest distance at which any

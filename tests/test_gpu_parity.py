@@ -145,3 +145,30 @@ def test_edge_cases_equal_oracle(ctx, ubq, case):
         got = ctx.contacts_table(atoms.view(A.ATOM_DTYPE), "/", 0.1, 6.5, flags=1)
         want = O.contacts(atoms, "/", 0.1, 6.5, flags=O.FLAG_NO_MULTIMODEL_QUIRK)
         assert_tables_equal(got, want, case + " (no quirk)")
+
+
+def test_bounding_box_hint_is_verified(ctx, bft):
+    """arp_structure.bbox_* is a hint: a box that misses atoms, or no box at all, must give the same rows."""
+    import ctypes as C
+
+    from arpeggia_b200 import _lib
+
+    packed = A.Packed(bft, "/")
+    assert packed.structure.has_bbox == 1
+    want = ctx.contacts_rows(packed, 0.1, 6.5)
+    for variant in ("none", "too_small", "shifted"):
+        st = _lib.Structure.from_buffer_copy(packed.structure)  # same pointers, own scalar fields
+        if variant == "none":
+            st.has_bbox = 0
+        elif variant == "too_small":
+            for a in range(3):
+                st.bbox_max[a] = st.bbox_min[a] + 0.25 * (st.bbox_max[a] - st.bbox_min[a])
+        else:
+            for a in range(3):
+                st.bbox_min[a] += 1000.0
+                st.bbox_max[a] += 1000.0
+        got = ctx.contacts_rows([C.pointer(st)], 0.1, 6.5)
+        assert got["pairs_in_cutoff"] == want["pairs_in_cutoff"], variant
+        a = np.sort(got["rows"], order=["from", "to", "label"])
+        b = np.sort(want["rows"], order=["from", "to", "label"])
+        assert np.array_equal(a, b), variant
