@@ -95,7 +95,8 @@ struct arp_ctx {
 
   // cell lists and sorted records
   DBuf<unsigned long long> bbox;
-  DBuf<uint32_t> cell_of, rank_of, cell_start, tile_sums;
+  DBuf<uint32_t> cell_of, rank_of, cell_start;
+  DBuf<unsigned long long> scan_status, rscan_status;
   DBuf<uint32_t> rcell_of, rrank_of, rcell_start, rperm, cations;
   DBuf<RecA> recA;
   DBuf<RecB> recB;

@@ -123,7 +123,7 @@ k_cell_assign(const double* __restrict__ px, const double* __restrict__ py, cons
   rank_of[i] = atomicAdd(&cell_count[c], 1u);
 }
 
-// ---- exclusive scan of the cell counts (in place), three small kernels --------------------------------
+// ---- exclusive scan of the cell counts (in place) ------------------------------------------------------------
 constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_PER_THREAD = 8;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_PER_THREAD;
@@ -155,8 +155,21 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* t
   return before + inc - v;
 }
 
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_tiles(uint32_t* __restrict__ data, uint32_t n, uint32_t* __restrict__ tile_sums) {
-  const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_PER_THREAD;
+// Exclusive scan in place, ONE pass over the data (decoupled look-back, Merrill & Garland): tiles take a ticket in
+// scheduling order, publish their aggregate, and sum the aggregates / inclusive prefixes of their predecessors 32 at a
+// time.  status[t] = flag << 62 | value (flag 1: aggregate of tile t, 2: inclusive prefix up to tile t), written with
+// a single 64-bit store; status[n_tiles] is the ticket counter.  A tile only ever waits for tiles with smaller tickets,
+// which are running or done; the wait is bounded all the same and reports through *error instead of hanging.
+#define SCAN_FLAG_A (1ull << 62)
+#define SCAN_FLAG_P (2ull << 62)
+#define SCAN_VALUE ((1ull << 62) - 1ull)
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_lookback(uint32_t* __restrict__ data, uint32_t n, unsigned long long* status,
+                                                                uint32_t n_tiles, unsigned int* __restrict__ error) {
+  __shared__ uint32_t s_tile, s_prefix;
+  if (threadIdx.x == 0) s_tile = atomicAdd(reinterpret_cast<unsigned int*>(status + n_tiles), 1u);
+  __syncthreads();
+  const uint32_t tile = s_tile;
+  const uint32_t base = tile * SCAN_TILE + threadIdx.x * SCAN_PER_THREAD;
   uint32_t v[SCAN_PER_THREAD], sum = 0;
 #pragma unroll
   for (int k = 0; k < SCAN_PER_THREAD; ++k) {
@@ -165,32 +178,53 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_tiles(uint32_t* __restric
   }
   uint32_t total;
   uint32_t run = block_exclusive_scan(sum, &total);
+  volatile unsigned long long* vs = status;
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    if (tile == 0) {
+      if (lane == 0) {
+        vs[0] = SCAN_FLAG_P | total;
+        s_prefix = 0u;
+      }
+    } else {
+      if (lane == 0) vs[tile] = SCAN_FLAG_A | total;
+      unsigned long long prefix = 0;
+      long long first = (long long)tile - 1;  // lane l looks at tile first - l
+      uint32_t spins = 0;
+      while (true) {
+        const long long j = first - lane;
+        unsigned long long w = SCAN_FLAG_P;
+        if (j >= 0) w = vs[j];
+        const uint32_t flag = (uint32_t)(w >> 62);
+        if (__any_sync(0xffffffffu, flag == 0u)) {
+          if (++spins > (1u << 22)) {  // cannot happen (see above); never hang a GPU over it
+            if (lane == 0) atomicOr(error, 4u);
+            break;
+          }
+          continue;
+        }
+        const uint32_t pm = __ballot_sync(0xffffffffu, flag == 2u);
+        const int stop = pm ? (__ffs(pm) - 1) : 31;  // nearest predecessor that already has its inclusive prefix
+        unsigned long long part = lane <= stop ? (w & SCAN_VALUE) : 0ull;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+        prefix += part;
+        if (pm) break;
+        first -= 32;
+      }
+      if (lane == 0) {
+        vs[tile] = SCAN_FLAG_P | ((prefix + total) & SCAN_VALUE);
+        s_prefix = (uint32_t)prefix;
+      }
+    }
+  }
+  __syncthreads();
+  run += s_prefix;
 #pragma unroll
   for (int k = 0; k < SCAN_PER_THREAD; ++k) {
     if (base + k < n) data[base + k] = run;
     run += v[k];
   }
-  if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
-}
-
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_sums(uint32_t* __restrict__ tile_sums, uint32_t n_tiles) {
-  uint32_t carry = 0;
-  for (uint32_t base = 0; base < n_tiles; base += SCAN_THREADS) {
-    const uint32_t i = base + threadIdx.x;
-    const uint32_t v = i < n_tiles ? tile_sums[i] : 0u;
-    uint32_t total;
-    const uint32_t ex = block_exclusive_scan(v, &total);
-    if (i < n_tiles) tile_sums[i] = carry + ex;
-    carry += total;
-  }
-}
-
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_add(uint32_t* __restrict__ data, uint32_t n, const uint32_t* __restrict__ tile_sums) {
-  const uint32_t off = tile_sums[blockIdx.x];
-  const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_PER_THREAD;
-#pragma unroll
-  for (int k = 0; k < SCAN_PER_THREAD; ++k)
-    if (base + k < n) data[base + k] += off;
 }
 
 // Pass 2 of the counting sort: write the cell-sorted records.  The atom that arrived first in a cell also
