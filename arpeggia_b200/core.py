@@ -204,7 +204,7 @@ class Context:
     def stats(self) -> dict:
         st = Stats()
         check(lib().arp_stage_stats(self._h, C.byref(st)), self._h)
-        return {k: getattr(st, k) for k, _ in Stats._fields_ if k != "reserved_"}
+        return {k: getattr(st, k) for k, _ in Stats._fields_ if not k.startswith("reserved")}
 
     def close(self):
         if getattr(self, "_h", None):

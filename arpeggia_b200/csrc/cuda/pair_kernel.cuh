@@ -158,33 +158,68 @@ __device__ __forceinline__ float label_limit2(const DevParams& P, const float* l
 }
 
 // ---- k_filter (B1) ----------------------------------------------------------------------------------------------
-// Grid-stride over the pair queue, one pair per lane: f32 re-test on the stored positions, in-cutoff counting, per-pair
-// label limit, pair filter.  One 32-byte gather per atom brings everything.  Survivors (about one in nine) are collected
-// per warp in shared memory and go to the second queue 32 at a time.
+// Grid-stride over the pair queue, one pair per lane, in two compacted phases so that the expensive half only runs on
+// full warps of pairs that need it:
+//   phase 1 (every pair)      one 32-byte gather per atom, f32 re-test on the stored positions, in-cutoff counting, and
+//                             the cheapest strong filter: same chain and residue ordinals at most 1 apart can pass
+//                             neither orientation (complex.rs:112-113) -- two pairs in three end here;
+//   phase 2 (32 at a time)    per-pair label limit, pair filter with its orientation; about one queue entry in nine goes
+//                             on to the second queue, 32 at a time.
+struct FilterOut {
+  bool go;
+  uint2 out;
+};
+__device__ __forceinline__ FilterOut filter_phase2(const PairArgs& G, const DevParams& P, const float* lim2, uint2 e, bool have,
+                                                   uint32_t& n_cls32) {
+  FilterOut r{false, make_uint2(0u, 0u)};
+  if (have) {
+    const uint4* pa = reinterpret_cast<const uint4*>(G.recA + e.x);
+    const uint4* pb = reinterpret_cast<const uint4*>(G.recA + e.y);
+    const uint4 a0 = pa[0], a1 = pa[1], b0 = pb[0], b1 = pb[1];  // just read by phase 1: L1 hits
+    const float dx = __uint_as_float(b0.x) - __uint_as_float(a0.x), dy = __uint_as_float(b0.y) - __uint_as_float(a0.y),
+                dz = __uint_as_float(b0.z) - __uint_as_float(a0.z);
+    const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));  // the same operations as phase 1: the same value
+    const bool cert = d2 <= P.thr_cert;
+    const bool amb = P.count_in_cutoff != 0 && !cert;  // the exact stage decides and counts
+    const bool pot = d2 <= P.thr_near && d2 <= label_limit2(P, lim2, a0.w, b0.w);
+    const int dir = pair_direction(a0.w, a1.x, a1.y, b0.w, b1.x, b1.y);
+    const bool valid = dir != 0;
+    if (P.count_classified && cert) n_cls32 += valid ? 1u : 0u;
+    r.go = amb || (pot && valid);
+    r.out.x = e.x | (amb ? QF_A : 0u) | (valid ? QF_B : 0u);
+    r.out.y = e.y | (dir == 2 ? QF_A : 0u) | (pot ? QF_B : 0u);
+  }
+  return r;
+}
+
 __global__ void __launch_bounds__(CLS_THREADS, 4) k_filter(const PairArgs G, const DevParams P) {
   __shared__ float lim2[256];  // per element-class pair: (max(cov sum, vdW sum) + |comp|)^2 + g, rounded up
-  __shared__ uint2 keep[CLS_WARPS][64];  // survivors waiting for a full 32-entry flush (carry-over < 32 + one trip)
+  __shared__ uint2 stash1[CLS_WARPS][64];  // phase-1 survivors waiting for a full warp (carry-over < 32 + one trip)
+  __shared__ uint2 stash2[CLS_WARPS][64];  // phase-2 survivors waiting for a full 32-entry flush
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   for (int k = threadIdx.x; k < 256; k += CLS_THREADS) lim2[k] = class_pair_limit2(P, k >> 4, k & 15);
   __syncthreads();
-  uint2* sq = keep[wid];
-  int sqlen = 0;
+  uint2* s1 = stash1[wid];
+  uint2* s2 = stash2[wid];
+  int n1 = 0, n2 = 0;
   uint32_t n_in32 = 0, n_cls32 = 0;
   const unsigned long long n_pairs = min(G.ctr->q_len, G.pairq_cap);
   const unsigned long long stride = (unsigned long long)gridDim.x * CLS_WARPS * 32ull;
   const bool counting = P.count_in_cutoff != 0;
+  const uint32_t lt = (1u << lane) - 1u;
   unsigned long long base = ((unsigned long long)blockIdx.x * CLS_WARPS + wid) * 32ull;
   // The only dependent memory round trip of a trip is the gather: the queue entry is read one trip ahead and the
-  // output atomic is paid once per 32 survivors.
-  uint2 e_next = make_uint2(0u, 0u);
-  if (base + lane < n_pairs) e_next = G.pairq[base + lane];
-  for (; base < n_pairs; base += stride) {
+  // output atomic is paid once per 32 survivors.  The trip after the last one flushes the stashes.
+  uint2 e_next = make_uint2(Q_SENTINEL, Q_SENTINEL);
+  if (base + lane < n_pairs) e_next = __ldcs(G.pairq + base + lane);  // streamed once: keep the atom records in L2 instead
+  while (true) {
+    const bool last = base >= n_pairs;
     const uint2 e = e_next;
-    const bool have = base + lane < n_pairs && e.x != Q_SENTINEL;  // sentinel: unused tail of a k_screen queue window
-    if (base + stride + lane < n_pairs) e_next = G.pairq[base + stride + lane];
-    bool go = false;
-    uint2 out = make_uint2(0u, 0u);
-    if (have) {
+    e_next = make_uint2(Q_SENTINEL, Q_SENTINEL);
+    if (base + stride + lane < n_pairs) e_next = __ldcs(G.pairq + base + stride + lane);
+    // ---- phase 1 ----------------------------------------------------------------------------------------------------
+    bool keep = false;
+    if (!last && e.x != Q_SENTINEL) {  // sentinel: past the end, or the unused tail of a k_screen queue window
       const uint4* pa = reinterpret_cast<const uint4*>(G.recA + e.x);
       const uint4* pb = reinterpret_cast<const uint4*>(G.recA + e.y);
       const uint4 a0 = pa[0], a1 = pa[1], b0 = pb[0], b1 = pb[1];  // position + attr | chain key, ordinal, ...
@@ -194,36 +229,43 @@ __global__ void __launch_bounds__(CLS_THREADS, 4) k_filter(const PairArgs G, con
       if (d2 <= P.thr_hit) {
         const bool cert = d2 <= P.thr_cert;
         if (counting && cert) n_in32 += eligible(a0.w) + eligible(b0.w);
-        const bool amb = counting && !cert;  // the exact stage decides and counts
-        const bool pot = d2 <= P.thr_near && d2 <= label_limit2(P, lim2, a0.w, b0.w);
-        if (amb || pot || P.count_classified) {
-          const int dir = pair_direction(a0.w, a1.x, a1.y, b0.w, b1.x, b1.y);
-          const bool valid = dir != 0;
-          if (P.count_classified && cert) n_cls32 += valid ? 1u : 0u;
-          go = amb || (pot && valid);
-          out.x = e.x | (amb ? QF_A : 0u) | (valid ? QF_B : 0u);
-          out.y = e.y | (dir == 2 ? QF_A : 0u) | (pot ? QF_B : 0u);
-        }
+        const bool close_in_chain = a1.x == b1.x && (a1.y - b1.y + 1u) <= 2u;  // same chain, |ordinal difference| <= 1
+        keep = (counting && !cert) || P.count_classified || (d2 <= P.thr_near && !close_in_chain);
       }
     }
-    const uint32_t bal = __ballot_sync(0xffffffffu, go);
-    if (go) sq[sqlen + __popc(bal & ((1u << lane) - 1u))] = out;
-    sqlen += __popc(bal);
+    const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+    if (keep) s1[n1 + __popc(bal & lt)] = e;
+    n1 += __popc(bal);
     __syncwarp();
-    if (sqlen >= 32) {
-      unsigned long long w = 0;
-      if (lane == 0) w = atomicAdd(&G.ctr->q2_len, 32ull);
-      w = __shfl_sync(0xffffffffu, w, 0) + lane;
-      sqlen -= 32;
-      if (w < G.pairq2_cap) G.pairq2[w] = sq[sqlen + lane];
+    // ---- phase 2 on full warps (on whatever is left after the last trip) ------------------------------------------------
+    while (n1 >= 32 || (last && n1 > 0)) {
+      const int m = min(n1, 32);
+      n1 -= m;
+      const FilterOut r = filter_phase2(G, P, lim2, s1[n1 + (lane < m ? lane : 0)], lane < m, n_cls32);
+      const uint32_t b2 = __ballot_sync(0xffffffffu, r.go);
+      if (r.go) s2[n2 + __popc(b2 & lt)] = r.out;
+      n2 += __popc(b2);
       __syncwarp();
+      if (n2 >= 32 || (last && n1 == 0 && n2 > 0)) {
+        const int k = min(n2, 32);
+        unsigned long long w = 0;
+        if (lane == 0) w = atomicAdd(&G.ctr->q2_len, (unsigned long long)k);
+        w = __shfl_sync(0xffffffffu, w, 0) + lane;
+        n2 -= k;
+        if (lane < k && w < G.pairq2_cap) __stcs(G.pairq2 + w, s2[n2 + lane]);
+        __syncwarp();
+      }
     }
-  }
-  if (sqlen > 0) {
-    unsigned long long w = 0;
-    if (lane == 0) w = atomicAdd(&G.ctr->q2_len, (unsigned long long)sqlen);
-    w = __shfl_sync(0xffffffffu, w, 0) + lane;
-    if (lane < sqlen && w < G.pairq2_cap) G.pairq2[w] = sq[lane];
+    if (last) {
+      if (n2 > 0) {  // phase 2 did not run on the last trip
+        unsigned long long w = 0;
+        if (lane == 0) w = atomicAdd(&G.ctr->q2_len, (unsigned long long)n2);
+        w = __shfl_sync(0xffffffffu, w, 0) + lane;
+        if (lane < n2 && w < G.pairq2_cap) __stcs(G.pairq2 + w, s2[lane]);
+      }
+      break;
+    }
+    base += stride;
   }
   unsigned long long n_in = n_in32, n_cls = n_cls32;
 #pragma unroll
@@ -323,7 +365,7 @@ struct QWindow {
 };
 __device__ __forceinline__ void qwindow_close(const PairArgs& G, QWindow& Q, int lane) {
   for (unsigned long long p = Q.pos + lane; p < Q.end; p += 32)
-    if (p < G.pairq_cap) G.pairq[p] = make_uint2(Q_SENTINEL, Q_SENTINEL);
+    if (p < G.pairq_cap) __stcs(G.pairq + p, make_uint2(Q_SENTINEL, Q_SENTINEL));
   Q.pos = Q.end;
 }
 
@@ -354,7 +396,7 @@ __device__ __forceinline__ void expand_masks(const PairArgs& G, uint32_t (&mask)
         do {
           const uint32_t i = __ffs(mask[u]) - 1;
           mask[u] &= mask[u] - 1;
-          *wp++ = make_uint2(from_slot0 + i, t);
+          __stcs(wp++, make_uint2(from_slot0 + i, t));  // streamed: the queue must not push the atom records out of L2
         } while (mask[u]);
       }
     }

@@ -42,34 +42,41 @@ def build_workload(dense: bool = False):
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe): one streaming
+    nvidia-smi process (-lms 50), samples time-stamped on arrival; summary() keeps the ones inside [t0, t1]."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int):
         super().__init__(daemon=True)
-        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+        self.index, self.rows, self.proc = index, [], None
 
     def run(self):
-        while not self._stop_evt.is_set():
-            try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([f.strip() for f in out.split(",")])
-            except Exception:
-                pass
-            self._stop_evt.wait(0.1)
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index),
+                                          "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                f = [x.strip() for x in line.split(",")]
+                if len(f) >= 7:
+                    self.rows.append((time.perf_counter(), f))
+        except Exception:
+            pass
 
-    def summary(self):
-        self._stop_evt.set()
-        self.join(timeout=6)
+    def summary(self, t0: float, t1: float):
+        if self.proc is not None:
+            self.proc.terminate()
+        self.join(timeout=3)
         if not self.rows:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
-        sm = sorted(float(r[0]) for r in self.rows)
+        inside = [f for t, f in self.rows if t0 <= t <= t1]
+        note = "inside the timed region"
+        if not inside:  # region shorter than the sampling period: the samples that bracket it
+            inside = [f for t, f in self.rows if t0 - 0.3 <= t <= t1 + 0.3] or [self.rows[-1][1]]
+            note = "timed region shorter than the 50 ms sampling period: samples within 0.3 s of it"
+        sm = sorted(float(r[0]) for r in inside)
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for k, n in enumerate(names) if any(r[3 + k].lower().startswith("active") for r in self.rows)]
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons, "samples": len(sm)}
+        reasons = [n for k, n in enumerate(names) if any(r[3 + k].lower().startswith("active") for r in inside)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(inside[0][1]), "reasons": reasons, "samples": len(sm), "window": note}
 
 
 def cpu_reference(atoms, sample_copies: int, threads: int):
@@ -145,7 +152,7 @@ def pinned_structure(A, packed):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=300)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dense", action="store_true", help="overlapping copies (protein-interior density) instead of config 3")
@@ -195,9 +202,11 @@ def main():
         ctx.run(0.1, 6.5, args.flags)
         ctx.download()
     sampler = ClockSampler(local)
-    barrier()
     sampler.start()
-    t_step = t_pairs = t_grid = t_rings = 0.0
+    time.sleep(0.4)  # let nvidia-smi come up before the timed region
+    barrier()
+    t_clock0 = time.perf_counter()
+    t_step = t_pairs = t_grid = t_rings = t_screen = t_filter = t_exact = 0.0
     with torch.cuda.stream(stream):
         for _ in range(args.steps):
             flush.zero_()  # evict L2 between timed steps
@@ -211,8 +220,11 @@ def main():
             t_pairs += s["ms_pairs"]
             t_grid += s["ms_grid"]
             t_rings += s["ms_rings"]
+            t_screen += s["ms_screen"]
+            t_filter += s["ms_filter"]
+            t_exact += s["ms_exact"]
     barrier()
-    clocks = sampler.summary()
+    clocks = sampler.summary(t_clock0, time.perf_counter())
     ms_step = t_step / args.steps
     times = torch.tensor([ms_step], dtype=torch.float64, device=f"cuda:{local}")
     if world > 1:
@@ -260,6 +272,12 @@ def main():
         ms_pairs = t_pairs / args.steps
         alg_bytes = 32 * n_atoms + 8 * st["n_cells"] + 16 * n_rows  # B_alg = 32 N + 8 C + 16 R
         achieved = alg_bytes / (ms_pairs * 1e-3) / 1e9
+        # DRAM bytes per launch of the three pair-stage kernels, from the committed ncu --set full capture
+        traffic, traffic_src = None, None
+        tj = ROOT / "profiles" / "pair_stage_traffic.json"
+        if tj.exists() and not args.dense and args.flags == 0:
+            t = json.loads(tj.read_text())
+            traffic, traffic_src = int(sum(k["dram_read_bytes"] + k["dram_write_bytes"] for k in t["kernels"].values())), t["source"]
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_max, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
@@ -267,9 +285,13 @@ def main():
             "config": {"workload": WORKLOAD + (" [dense pitch]" if args.dense else ""), "per_gpu": "one assembly per rank (sharded by structure)",
                        "l2": "512 MiB buffer written between timed steps (L2 flushed)", "flags": args.flags,
                        "atoms": n_atoms, "cells": st["n_cells"], "nonempty_cells": st["n_nonempty_cells"], "rows": n_rows,
-                       "pairs_within_cutoff": pairs, "candidate_tests": res["pairs_screened"]},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                         "kernel": "k_pairs", "kernel_ms": ms_pairs, "algorithmic_bytes": alg_bytes,
+                       "pairs_within_cutoff": pairs, "candidate_tests": res["pairs_screened"],
+                       "pair_queue_entries": st["n_screened_pairs"], "filtered_pairs": st["n_filtered_pairs"]},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                         "kernel": "pair stage = k_screen -> k_filter -> k_exact (neighbour search + classification, 3 launches per step)",
+                         "kernel_ms": ms_pairs, "kernel_ms_each": {"k_screen": t_screen / args.steps, "k_filter": t_filter / args.steps,
+                                                                   "k_exact": t_exact / args.steps},
+                         "algorithmic_bytes": alg_bytes, "traffic_source": traffic_src,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "ms_per_step": float(e2e_t.item()), "ms_h2d": st["ms_h2d"], "ms_run": st["ms_run"], "ms_d2h": st["ms_d2h"],
@@ -279,7 +301,7 @@ def main():
             "contacts_per_s": world * n_rows / (ms_max * 1e-3),
             "candidate_tests_per_s": world * res["pairs_screened"] / (ms_max * 1e-3),
             "atoms_per_s": world * n_atoms / (ms_max * 1e-3),
-            "stage_ms": {"grid": t_grid / args.steps, "pairs": ms_pairs, "rings": t_rings / args.steps},
+            "stage_ms": {"grid": t_grid / args.steps, "pairs": ms_pairs, "rings_overlapped": t_rings / args.steps},
         }
         if not args.no_cpu and world == 1:
             threads = os.cpu_count() or 1

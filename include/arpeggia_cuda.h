@@ -148,9 +148,12 @@ typedef struct arp_result {
 typedef struct arp_stats {
   int64_t n_atoms, n_rings, n_cells, n_nonempty_cells, n_rows;
   int64_t kernel_launches;        /* kernels of this library launched by the last run */
-  int32_t pair_kernel_retries;    /* re-runs because the row buffer was too small */
+  int32_t pair_kernel_retries;    /* re-runs because the row buffer or a pair queue was too small */
   int32_t reserved_;
-  float ms_h2d, ms_grid, ms_pairs, ms_rings, ms_d2h, ms_run; /* ms_run = grid + pairs + rings */
+  int64_t n_screened_pairs;       /* entries of the first pair queue (k_screen -> k_filter), unused window tails included */
+  int64_t n_filtered_pairs;       /* entries of the second pair queue (k_filter -> k_exact) */
+  float ms_h2d, ms_grid, ms_pairs, ms_rings, ms_d2h, ms_run; /* ms_run = the whole job; ms_rings overlaps ms_pairs (side stream) */
+  float ms_screen, ms_filter, ms_exact, reserved2_;          /* the three kernels of ms_pairs */
 } arp_stats;
 
 typedef struct arp_ctx arp_ctx;
