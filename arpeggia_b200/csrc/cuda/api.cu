@@ -118,7 +118,7 @@ struct arp_ctx {
   bool have_job = false, have_run = false;
   arp_params last_params{};
   DevParams dp{};
-  cudaEvent_t ev[12] = {};
+  cudaEvent_t ev[13] = {};
   int64_t launches = 0;
   int retries = 0;
   float ms_h2d = 0.f, ms_d2h = 0.f;

@@ -91,11 +91,10 @@ __device__ __forceinline__ float class_pair_limit2(const DevParams& P, int ea, i
 }
 
 // ---- B2: up to 32 filtered pairs, one per lane: exact distance, counters, label ladder, rows ----------------------
-__device__ __forceinline__ void exact_batch(const PairArgs& G, const DevParams& P, const uint2* q, int count, int lane, PairCounts& K) {
+__device__ __forceinline__ void exact_batch(const PairArgs& G, const DevParams& P, const uint2 e, bool have, int lane, PairCounts& K) {
   uint32_t m = 0, sp = 0, sq = 0;
   double dist = 0.0;
-  if (lane < count) {
-    const uint2 e = q[lane];
+  if (have) {
     const uint32_t sa = e.x & SLOT_MASK, sb = e.y & SLOT_MASK;
     const RecB a = G.recB[sa], b = G.recB[sb];
     const uint32_t wa = G.recA[sa].attr, wb = G.recA[sb].attr;
@@ -285,8 +284,15 @@ __global__ void __launch_bounds__(CLS_THREADS, 4) k_exact(const PairArgs G, cons
   PairCounts K{0ull, 0ull};
   const unsigned long long n_pairs = min(G.ctr->q2_len, G.pairq2_cap);
   const unsigned long long stride = (unsigned long long)gridDim.x * CLS_WARPS * 32ull;
-  for (unsigned long long base = ((unsigned long long)blockIdx.x * CLS_WARPS + wid) * 32ull; base < n_pairs; base += stride)
-    exact_batch(G, P, G.pairq2 + base, (int)min(32ull, n_pairs - base), lane, K);
+  unsigned long long base = ((unsigned long long)blockIdx.x * CLS_WARPS + wid) * 32ull;
+  uint2 e_next = make_uint2(0u, 0u);  // read one trip ahead
+  if (base + lane < n_pairs) e_next = __ldcs(G.pairq2 + base + lane);
+  for (; base < n_pairs; base += stride) {
+    const uint2 e = e_next;
+    const bool have = base + lane < n_pairs;
+    if (base + stride + lane < n_pairs) e_next = __ldcs(G.pairq2 + base + stride + lane);
+    exact_batch(G, P, e, have, lane, K);
+  }
   unsigned long long n_in = K.n_in, n_cls = K.n_cls;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {

@@ -15,16 +15,17 @@ __device__ __forceinline__ void push_row(arp_row* rows, unsigned long long cap, 
 }
 
 // The 27 cells around a point are 9 rows (y, z) of up to 3 x-adjacent cells = 9 contiguous runs of sorted slots.
-// Lane k < 9 fetches the bounds of run k (all nine in one memory round trip); the warp then walks the concatenation of
-// the runs, one entry per lane.  Returns this lane's run (begin, length) and the exclusive prefix / total over the runs.
+// A query is handled by a HALF WARP (16 lanes, `hm` = its shuffle mask, `l` = lane within it): lane k < 9 fetches the
+// bounds of run k (all nine in one memory round trip); the half warp then walks the concatenation of the runs, one entry
+// per lane.  Returns this lane's run (begin, length) and the exclusive prefix / total over the runs.
 struct Runs9 {
   uint32_t begin, len, off, total;
 };
 __device__ __forceinline__ Runs9 fetch_runs9(const uint32_t* __restrict__ cell_start, uint32_t cell_base, int nx, int ny, int nz, int ix,
-                                             int iy, int iz, int lane) {
+                                             int iy, int iz, int l, uint32_t hm) {
   Runs9 r{0u, 0u, 0u, 0u};
-  if (lane < 9) {
-    const int y = iy + lane % 3 - 1, z = iz + lane / 3 - 1;
+  if (l < 9) {
+    const int y = iy + l % 3 - 1, z = iz + l / 3 - 1;
     if (y >= 0 && y < ny && z >= 0 && z < nz) {
       const uint32_t row = cell_base + (uint32_t)((z * ny + y) * nx);
       r.begin = cell_start[row + (uint32_t)max(ix - 1, 0)];
@@ -34,35 +35,35 @@ __device__ __forceinline__ Runs9 fetch_runs9(const uint32_t* __restrict__ cell_s
   uint32_t inc = r.len;
 #pragma unroll
   for (int o = 1; o < 16; o <<= 1) {
-    const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-    if (lane >= o) inc += t;
+    const uint32_t t = __shfl_up_sync(hm, inc, o, 16);
+    if (l >= o) inc += t;
   }
   r.off = inc - r.len;
-  r.total = __shfl_sync(0xffffffffu, inc, 8);
+  r.total = __shfl_sync(hm, inc, 8, 16);
   return r;
 }
 // entry j of the concatenation -> sorted slot (every lane asks for its own j)
-__device__ __forceinline__ uint32_t runs9_slot(const Runs9& r, uint32_t j) {
+__device__ __forceinline__ uint32_t runs9_slot(const Runs9& r, uint32_t j, uint32_t hm) {
   uint32_t slot = 0;
 #pragma unroll
   for (int k = 0; k < 9; ++k) {
-    const uint32_t off = __shfl_sync(0xffffffffu, r.off, k), len = __shfl_sync(0xffffffffu, r.len, k),
-                   begin = __shfl_sync(0xffffffffu, r.begin, k);
+    const uint32_t off = __shfl_sync(hm, r.off, k, 16), len = __shfl_sync(hm, r.len, k, 16), begin = __shfl_sync(hm, r.begin, k, 16);
     if (j >= off && j < off + len) slot = begin + (j - off);
   }
   return slot;
 }
 
-// k_rings: one warp per QUERY -- a ring (pi-pi, complex.rs:354-405) or a cation (cation-pi, complex.rs:301-352) -- against
+// k_rings: one half warp per QUERY -- a ring (pi-pi, complex.rs:354-405) or a cation (cation-pi, complex.rs:301-352) -- against
 // the rings of the 27 ring-grid cells around it.  The reference searches the atoms around every ring centroid; only
 // atoms that are positively ionizable by residue name can give a row (aromatic.rs:18) and a row needs
 // dist <= 4.5 < ring-grid edge, so walking the few cations and looking for rings around them visits exactly the pairs
 // that can produce a row -- about 20x fewer tests than sweeping all atoms around all rings.
 __global__ void __launch_bounds__(256) k_rings(const RingArgs R, const DevParams P) {
-  const int lane = threadIdx.x & 31;
-  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  const int lane = threadIdx.x & 15;
+  const uint32_t hm = (threadIdx.x & 16) ? 0xffff0000u : 0x0000ffffu;  // the half warps of a warp run independently
+  const uint32_t groups = (gridDim.x * blockDim.x) >> 4;
   const uint32_t n_queries = R.n_rings + R.ctr->n_cations;
-  for (uint32_t q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; q < n_queries; q += warps) {
+  for (uint32_t q = (blockIdx.x * blockDim.x + threadIdx.x) >> 4; q < n_queries; q += groups) {
     const bool is_ring = q < R.n_rings;
     // query position, attributes, structure
     double c1[3], n1[3] = {0.0, 0.0, 0.0};
@@ -88,10 +89,10 @@ __global__ void __launch_bounds__(256) k_rings(const RingArgs R, const DevParams
     const int ix = min(max((int)floor((c1[0] - D.ox) * P.inv_redge), 0), D.rnx - 1);
     const int iy = min(max((int)floor((c1[1] - D.oy) * P.inv_redge), 0), D.rny - 1);
     const int iz = min(max((int)floor((c1[2] - D.oz) * P.inv_redge), 0), D.rnz - 1);
-    const Runs9 runs = fetch_runs9(R.rcell_start, D.rcell_base, D.rnx, D.rny, D.rnz, ix, iy, iz, lane);
-    for (uint32_t j0 = 0; j0 < runs.total; j0 += 32) {
+    const Runs9 runs = fetch_runs9(R.rcell_start, D.rcell_base, D.rnx, D.rny, D.rnz, ix, iy, iz, lane, hm);
+    for (uint32_t j0 = 0; j0 < runs.total; j0 += 16) {
       const uint32_t j = j0 + lane;
-      const uint32_t t = runs9_slot(runs, j);
+      const uint32_t t = runs9_slot(runs, j, hm);
       if (j >= runs.total) continue;
       const uint32_t r2 = R.rperm[t];
       const uint32_t w2 = R.attr[r2];
