@@ -102,6 +102,36 @@ class Table(C.Structure):
     )
 
 
+class FrameSide(C.Structure):
+    """arp_frame_side"""
+    _fields_ = [("chain", C.c_int32), ("resn", C.c_int32), ("resi", C.c_int32), ("icode", C.c_int32), ("altloc", C.c_int32),
+                ("model", C.c_uint32), ("chain_rank", C.c_uint32), ("has_sc", C.c_uint32)]
+
+
+class FrameTables(C.Structure):
+    """arp_frame_tables"""
+    _fields_ = [
+        ("n_atoms", C.c_int64), ("n_rings", C.c_int64), ("n_sides", C.c_int64),
+        ("sides", C.POINTER(FrameSide)), ("side_sc", _F64P), ("ent_side", _U32P), ("ent_atomn", _I32P), ("ent_atomi", _I32P),
+        ("ent_rank", _U32P), ("ent_tie", _U32P), ("label_rank", C.c_uint8 * 32),
+        ("n_chain_ranks", C.c_uint32), ("n_ent_ranks", C.c_uint32), ("max_tie", C.c_uint32),
+    ]
+
+
+class Frame(C.Structure):
+    """arp_frame"""
+    _fields_ = (
+        [("n_rows", C.c_int64), ("model", _U32P), ("interaction", C.POINTER(C.c_uint8)), ("distance", _F32P)]
+        + [(f"{s}_{c}", _I32P) for s in ("from", "to")
+           for c in ("chain", "resn", "resi", "insertion", "altloc", "atomn", "atomi")]
+        + [("sc_centroid_dist", _F32P), ("sc_dihedral", _F32P), ("sc_centroid_angle", _F32P),
+           ("sc_valid", C.POINTER(C.c_uint8)), ("from", _U32P), ("to", _U32P),
+           ("pairs_in_cutoff", C.c_int64), ("pairs_classified", C.c_int64),
+           ("ms_sort", C.c_float), ("ms_columns", C.c_float), ("ms_d2h", C.c_float),
+           ("sort_passes", C.c_int32), ("key_bits", C.c_int32)]
+    )
+
+
 class ArpeggiaError(RuntimeError):
     """Raised for every non-zero arp_status; `.code` is the status (include/arpeggia_cuda.h)."""
 
@@ -129,6 +159,10 @@ SIGNATURES = {
     "arp_stage_run": (C.c_int, [_P, C.POINTER(Params)]),
     "arp_stage_download": (C.c_int, [_P, C.POINTER(C.POINTER(Result))]),
     "arp_stage_stats": (C.c_int, [_P, C.POINTER(Stats)]),
+    "arp_stage_frame": (C.c_int, [_P, C.POINTER(FrameTables), C.POINTER(C.POINTER(Frame))]),
+    "arp_contacts_frame": (C.c_int, [_P, C.POINTER(Structure), C.POINTER(Params), C.POINTER(FrameTables),
+                                     C.POINTER(C.POINTER(Frame))]),
+    "arp_frame_free": (None, [_P, C.POINTER(Frame)]),
     "arp_host_alloc": (C.c_int, [C.POINTER(_P), C.c_int64]),
     "arp_host_free": (None, [_P]),
     # arpeggia_host.h
@@ -140,6 +174,8 @@ SIGNATURES = {
     "arph_packed_n_warnings": (C.c_int64, [_P]),
     "arph_packed_warning": (C.c_char_p, [_P, C.c_int64]),
     "arph_packed_free": (None, [_P]),
+    "arph_packed_frame_tables": (C.c_int, [_P, C.POINTER(C.POINTER(FrameTables))]),
+    "arph_table_from_frame": (C.c_int, [_P, C.POINTER(Frame), C.POINTER(C.POINTER(Table))]),
     "arph_build_table": (C.c_int, [_P, _P, C.c_int64, C.POINTER(C.POINTER(Table))]),
     "arph_table_free": (None, [C.POINTER(Table)]),
     "arph_contacts": (C.c_int, [_P, _P, C.c_int64, C.c_char_p, C.c_double, C.c_double, C.c_int, C.c_uint32,

@@ -12,7 +12,8 @@ import threading
 import numpy as np
 
 from . import _lib
-from ._lib import ATOM_DTYPE, LABELS, ROW_DTYPE, ArpeggiaError, Params, Result, Stats, Structure, Table, check, lib
+from ._lib import (ATOM_DTYPE, LABELS, ROW_DTYPE, ArpeggiaError, Frame, FrameTables, Params, Result, Stats, Structure, Table,
+                   check, lib)
 
 STRING_COLS = ("chain", "resn", "insertion", "altloc", "atomn")
 COLUMNS = (
@@ -200,6 +201,24 @@ class Context:
             return _read_result(rp.contents)
         finally:
             L.arp_result_free(self._h, rp)
+
+    def frame(self, packed: "Packed") -> dict:
+        """arp_stage_frame after run(): sort + decode + sc join on the device -> the table of get_contacts, plus the
+        device timings of the frame stage under "frame_stats"."""
+        L = lib()
+        tp = C.POINTER(FrameTables)()
+        check(L.arph_packed_frame_tables(packed._h, C.byref(tp)))
+        fp = C.POINTER(Frame)()
+        check(L.arp_stage_frame(self._h, tp, C.byref(fp)), self._h)
+        fs = {k: getattr(fp.contents, k) for k in ("ms_sort", "ms_columns", "ms_d2h", "sort_passes", "key_bits")}
+        tb = C.POINTER(Table)()
+        check(L.arph_table_from_frame(packed._h, fp, C.byref(tb)))  # owns the frame from here on
+        try:
+            out = read_table(tb.contents)
+        finally:
+            L.arph_table_free(tb)
+        out["frame_stats"] = fs
+        return out
 
     def stats(self) -> dict:
         st = Stats()

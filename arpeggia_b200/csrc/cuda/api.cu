@@ -12,6 +12,7 @@
 #include "grid_kernels.cuh"
 #include "pair_kernel.cuh"
 #include "ring_kernels.cuh"
+#include "frame_kernels.cuh"
 
 using namespace arpd;
 
@@ -107,6 +108,16 @@ struct arp_ctx {
   DBuf<uint2> pairq, pairq2;  // pairs between k_screen -> k_filter -> k_exact
   uint64_t pairq_cap = 0, pairq2_cap = 0;
   int64_t n_cells = 0, n_rcells = 0;
+
+  // the frame (arp_stage_frame): the caller's tables, sort ping-pong buffers, output columns
+  DBuf<arp_frame_side> f_sides;
+  DBuf<double> f_side_sc;
+  DBuf<uint32_t> f_ent_side, f_ent_rank, f_ent_tie;
+  DBuf<int32_t> f_ent_atomn, f_ent_atomi;
+  DBuf<unsigned long long> f_klo[2], f_khi[2], f_status;
+  DBuf<uint32_t> f_idx[2], f_hist;
+  DBuf<unsigned char> f_out;
+  cudaEvent_t fev[4] = {};
 
   // host staging
   HBuf<unsigned long long> h_bbox;

@@ -26,23 +26,33 @@ int arph_contacts(arp_ctx* ctx, const arp_atom_record* atoms, int64_t n, const c
   prm.vdw_comp = vdw_comp;
   prm.dist_cutoff = dist_cutoff;
   prm.flags = ARP_FLAG_COUNT_CLASSIFIED;  // the table reports both workload counters
-  arp_result* res = nullptr;
-  rc = arp_contacts(ctx, arph_packed_structure(pk), &prm, &res);
-  if (rc != ARP_OK) {
-    arp::last_error() = arp_last_error(ctx);
-    arph_packed_free(pk);
-    return rc;
+  // rows stay on the device: sorted, decoded and joined there (arp_stage_frame), only the columns come back
+  arp::FrameTables ft;
+  arp_frame* frame = nullptr;
+  double t2 = t1, t3 = t1;
+  try {
+    arp::build_frame_tables(arph_packed_ref(pk), ft);
+    t2 = now_s();
+    rc = arp_contacts_frame(ctx, arph_packed_structure(pk), &prm, &ft.t, &frame);
+    if (rc != ARP_OK) {
+      arp::last_error() = arp_last_error(ctx);
+      arph_packed_free(pk);
+      return rc;
+    }
+    t3 = now_s();
+    *out = arp::table_from_frame(arph_packed_ref(pk), frame);
+    frame = nullptr;
+    (*out)->t_setup_s = t2 - t0;
+    (*out)->t_classify_s = t3 - t2;
+    (*out)->t_table_s = now_s() - t3;
+  } catch (const arp::Error& e) {
+    arp::last_error() = e.msg;
+    rc = e.code;
+  } catch (const std::exception& e) {
+    arp::last_error() = e.what();
+    rc = ARP_ERR_OOM;
   }
-  const double t2 = now_s();
-  rc = arph_build_table(pk, res->rows, res->n_rows, out);
-  if (rc == ARP_OK) {
-    (*out)->pairs_in_cutoff = res->pairs_in_cutoff;
-    (*out)->pairs_classified = res->pairs_classified;
-    (*out)->t_setup_s = t1 - t0;
-    (*out)->t_classify_s = t2 - t1;
-    (*out)->t_table_s = now_s() - t2;
-  }
-  arp_result_free(ctx, res);
+  if (frame) arp_frame_free(ctx, frame);
   arph_packed_free(pk);
   return rc;
 }

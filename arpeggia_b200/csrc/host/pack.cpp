@@ -517,6 +517,8 @@ void Packed::finish() {
 
 struct arph_packed {
   arp::Packed p;
+  arp::FrameTables frame_tables;  // built on first use (arph_packed_frame_tables)
+  bool have_frame_tables = false;
 };
 
 extern "C" {
@@ -543,6 +545,28 @@ const arp_structure* arph_packed_structure(const arph_packed* p) { return &p->p.
 int64_t arph_packed_n_warnings(const arph_packed* p) { return (int64_t)p->p.warnings.size(); }
 const char* arph_packed_warning(const arph_packed* p, int64_t i) { return p->p.warnings[(size_t)i].c_str(); }
 void arph_packed_free(arph_packed* p) { delete p; }
+
+int arph_packed_frame_tables(arph_packed* p, const arp_frame_tables** out) {
+  *out = nullptr;
+  if (!p) {
+    arp::last_error() = "null packed structure";
+    return ARP_ERR_ARG;
+  }
+  try {
+    if (!p->have_frame_tables) {
+      arp::build_frame_tables(p->p, p->frame_tables);
+      p->have_frame_tables = true;
+    }
+  } catch (const arp::Error& e) {
+    arp::last_error() = e.msg;
+    return e.code;
+  } catch (const std::exception& e) {
+    arp::last_error() = e.what();
+    return ARP_ERR_OOM;
+  }
+  *out = &p->frame_tables.t;
+  return ARP_OK;
+}
 
 int arph_parse_groups(const char* chains_csv, const char* groups, char* ligand_out, char* receptor_out, int64_t cap) {
   try {

@@ -46,6 +46,17 @@ void pack_records(const arp_atom_record* recs, int64_t n, const std::string& gro
 struct TableStore;
 arph_table* build_table(const Packed& p, const arp_row* rows, int64_t n_rows);
 
+// the integer side tables of arp_stage_frame (include/arpeggia_cuda.h) and the table that wraps a device-built frame
+struct FrameTables {
+  arp_frame_tables t{};
+  std::vector<arp_frame_side> sides;
+  std::vector<double> side_sc;
+  std::vector<uint32_t> ent_side, ent_rank, ent_tie;
+  std::vector<int32_t> ent_atomn, ent_atomi;
+};
+void build_frame_tables(const Packed& p, FrameTables& out);
+arph_table* table_from_frame(const Packed& p, arp_frame* f);  // takes ownership of f (released by arph_table_free)
+
 }  // namespace arp
 
 struct arph_packed;

@@ -16,6 +16,7 @@ namespace arp {
 
 struct TableStore {
   arph_table t{};  // must stay the first member (arph_table_free casts back)
+  arp_frame* frame = nullptr;  // device-built tables borrow the frame's page-locked columns
   std::vector<uint32_t> model;
   std::vector<uint8_t> interaction, sc_valid;
   std::vector<float> distance, scd, sch, sca;
@@ -29,25 +30,122 @@ int32_t narrow(int64_t v, const char* what) {  // mod.rs:150-178
   if (v > INT32_MAX || v < INT32_MIN) throw Error{ARP_ERR_NARROWING, std::string(what) + " " + std::to_string(v) + " exceeds i32 limits"};
   return (int32_t)v;
 }
+bool fits_i32(int64_t v) { return v <= INT32_MAX && v >= INT32_MIN; }
+
+// rank of every dictionary string in byte order (polars sorts strings bytewise)
+std::vector<int32_t> string_ranks(const Packed& P) {
+  const size_t ns = P.strings.size();
+  std::vector<int32_t> by_rank(ns), srank(ns);
+  std::iota(by_rank.begin(), by_rank.end(), 0);
+  std::sort(by_rank.begin(), by_rank.end(), [&](int32_t a, int32_t b) { return P.strings[a] < P.strings[b]; });
+  for (size_t r = 0; r < ns; ++r) srank[by_rank[r]] = (int32_t)r;
+  return srank;
+}
+void label_ranks(int32_t* lrank) {  // the interaction column is a string: sort key 10 orders by the label's name
+  int order[ARP_N_LABELS];
+  std::iota(order, order + ARP_N_LABELS, 0);
+  std::sort(order, order + ARP_N_LABELS, [](int a, int b) { return std::strcmp(arp_label_name(a), arp_label_name(b)) < 0; });
+  for (int r = 0; r < ARP_N_LABELS; ++r) lrank[order[r]] = r;
+}
 }  // namespace
+
+// The integer side tables arp_stage_frame sorts and decodes with (include/arpeggia_cuda.h).  Entities = atoms, then
+// rings; ent_rank orders (resi, altloc, atomi) = sort keys 4-6 / 7-9 of mod.rs:123-134, ent_tie breaks the ties the
+// reference leaves open by entity order -- build_table below uses the same order, so both paths give the same frame.
+void build_frame_tables(const Packed& P, FrameTables& T) {
+  const std::vector<int32_t> srank = string_ranks(P);
+  const size_t n_sides = P.resconfs.size(), n_atoms = P.x.size(), n_rings = P.ring_rc.size(), E = n_atoms + n_rings;
+  T.sides.assign(n_sides, arp_frame_side{});
+  T.side_sc.assign(6 * n_sides, 0.0);
+  std::vector<uint8_t> side_bad(n_sides, 0);
+  {  // chain_rank: dense rank of (model serial, chain id bytes)
+    std::vector<std::pair<int64_t, int32_t>> keys(n_sides);
+    for (size_t k = 0; k < n_sides; ++k) keys[k] = {P.resconfs[k].model_serial, srank[P.resconfs[k].chain]};
+    std::vector<std::pair<int64_t, int32_t>> uniq(keys);
+    std::sort(uniq.begin(), uniq.end());
+    uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
+    T.t.n_chain_ranks = (uint32_t)std::max<size_t>(uniq.size(), 1);
+    for (size_t k = 0; k < n_sides; ++k) {
+      const Packed::ResConf& r = P.resconfs[k];
+      arp_frame_side& s = T.sides[k];
+      s.chain = r.chain, s.resn = r.resn, s.icode = r.icode, s.altloc = r.altloc;
+      side_bad[k] = !fits_i32(r.resi) || r.model_serial < 0 || r.model_serial > (int64_t)UINT32_MAX;
+      s.resi = side_bad[k] ? 0 : (int32_t)r.resi;
+      s.model = side_bad[k] ? 0u : (uint32_t)r.model_serial;
+      s.chain_rank = (uint32_t)(std::lower_bound(uniq.begin(), uniq.end(), keys[k]) - uniq.begin());
+      s.has_sc = r.has_sc ? 1u : 0u;
+      if (r.has_sc)
+        for (int a = 0; a < 3; ++a) T.side_sc[6 * k + a] = r.sc.c[a], T.side_sc[6 * k + 3 + a] = r.sc.n[a];
+    }
+  }
+  T.ent_side.resize(E);
+  T.ent_atomn.resize(E);
+  T.ent_atomi.resize(E);
+  T.ent_rank.resize(E);
+  T.ent_tie.resize(E);
+  struct Key {
+    int64_t resi, atomi;
+    int32_t alt;
+    uint32_t id;
+  };
+  std::vector<Key> keys(E);
+  for (size_t e = 0; e < E; ++e) {
+    const bool ring = e >= n_atoms;
+    const uint32_t rc = ring ? P.ring_rc[e - n_atoms] : P.atom_rc[e];
+    const int64_t serial = ring ? 0 : P.atom_serial[e];  // InteractingEntity::new(.., "Ring", 0), complex.rs:334-342
+    T.ent_side[e] = rc;
+    T.ent_atomn[e] = ring ? P.ring_name : P.atom_name[e];
+    const bool bad = !fits_i32(serial) || side_bad[rc];
+    T.ent_atomi[e] = fits_i32(serial) ? (int32_t)serial : 0;
+    T.ent_tie[e] = bad ? ARP_ENT_NARROW : 0u;
+    keys[e] = Key{P.resconfs[rc].resi, serial, srank[P.resconfs[rc].altloc], (uint32_t)e};
+  }
+  std::sort(keys.begin(), keys.end(), [](const Key& a, const Key& b) {
+    if (a.resi != b.resi) return a.resi < b.resi;
+    if (a.alt != b.alt) return a.alt < b.alt;
+    if (a.atomi != b.atomi) return a.atomi < b.atomi;
+    return a.id < b.id;
+  });
+  uint32_t rank = 0, tie = 0, max_tie = 0;
+  for (size_t k = 0; k < E; ++k) {
+    if (k > 0) {
+      const bool same = keys[k].resi == keys[k - 1].resi && keys[k].alt == keys[k - 1].alt && keys[k].atomi == keys[k - 1].atomi;
+      if (same) {
+        tie += 1;
+      } else {
+        rank += 1;
+        tie = 0;
+      }
+    }
+    T.ent_rank[keys[k].id] = rank;
+    T.ent_tie[keys[k].id] |= tie;
+    max_tie = std::max(max_tie, tie);
+  }
+  int32_t lrank[ARP_N_LABELS];
+  label_ranks(lrank);
+  std::memset(T.t.label_rank, 0, sizeof T.t.label_rank);
+  for (int l = 0; l < ARP_N_LABELS; ++l) T.t.label_rank[l] = (uint8_t)lrank[l];
+  T.t.n_atoms = (int64_t)n_atoms;
+  T.t.n_rings = (int64_t)n_rings;
+  T.t.n_sides = (int64_t)n_sides;
+  T.t.sides = T.sides.data();
+  T.t.side_sc = T.side_sc.data();
+  T.t.ent_side = T.ent_side.data();
+  T.t.ent_atomn = T.ent_atomn.data();
+  T.t.ent_atomi = T.ent_atomi.data();
+  T.t.ent_rank = T.ent_rank.data();
+  T.t.ent_tie = T.ent_tie.data();
+  T.t.n_ent_ranks = E ? rank + 1 : 1;
+  T.t.max_tie = max_tie;
+}
 
 arph_table* build_table(const Packed& P, const arp_row* rows, int64_t n) {
   auto* T = new TableStore();
   try {
     T->strings = P.strings;
-    // rank of every dictionary string in byte order (polars sorts strings bytewise)
-    const size_t ns = P.strings.size();
-    std::vector<int32_t> by_rank(ns), srank(ns);
-    std::iota(by_rank.begin(), by_rank.end(), 0);
-    std::sort(by_rank.begin(), by_rank.end(), [&](int32_t a, int32_t b) { return P.strings[a] < P.strings[b]; });
-    for (size_t r = 0; r < ns; ++r) srank[by_rank[r]] = (int32_t)r;
+    const std::vector<int32_t> srank = string_ranks(P);
     int32_t lrank[ARP_N_LABELS];
-    {
-      int order[ARP_N_LABELS];
-      std::iota(order, order + ARP_N_LABELS, 0);
-      std::sort(order, order + ARP_N_LABELS, [](int a, int b) { return std::strcmp(arp_label_name(a), arp_label_name(b)) < 0; });
-      for (int r = 0; r < ARP_N_LABELS; ++r) lrank[order[r]] = r;
-    }
+    label_ranks(lrank);
     const int64_t n_atoms = (int64_t)P.x.size(), n_rings = (int64_t)P.ring_rc.size();
 
     struct Side {
@@ -63,6 +161,7 @@ arph_table* build_table(const Packed& P, const arp_row* rows, int64_t n) {
       if ((int64_t)v >= n_atoms) throw Error{ARP_ERR_ARG, "row references an atom outside the structure"};
       return Side{P.atom_rc[v], P.atom_name[v], narrow(P.atom_serial[v], "Atom index")};
     };
+    auto entity_pos = [&](uint32_t v) -> uint64_t { return (v & ARP_RING_FLAG) ? (uint64_t)n_atoms + (v & ~ARP_RING_FLAG) : v; };
     std::vector<Side> F((size_t)n), G((size_t)n);
     for (int64_t k = 0; k < n; ++k) {
       F[k] = side(rows[k].from);
@@ -85,16 +184,11 @@ arph_table* build_table(const Packed& P, const arp_row* rows, int64_t n) {
       if (ta.altloc != tb.altloc) return srank[ta.altloc] < srank[tb.altloc];
       if (G[ia].atomi != G[ib].atomi) return G[ia].atomi < G[ib].atomi;
       if (rows[ia].label != rows[ib].label) return lrank[rows[ia].label] < lrank[rows[ib].label];
-      if (fa.icode != fb.icode) return srank[fa.icode] < srank[fb.icode];
-      if (ta.icode != tb.icode) return srank[ta.icode] < srank[tb.icode];
-      if (F[ia].atomn != F[ib].atomn) return srank[F[ia].atomn] < srank[F[ib].atomn];
-      if (G[ia].atomn != G[ib].atomn) return srank[G[ia].atomn] < srank[G[ib].atomn];
-      if (fa.resn != fb.resn) return srank[fa.resn] < srank[fb.resn];
-      if (ta.resn != tb.resn) return srank[ta.resn] < srank[tb.resn];
-      uint32_t da, db;
-      std::memcpy(&da, &rows[ia].distance, 4);
-      std::memcpy(&db, &rows[ib].distance, 4);
-      return da < db;
+      // ties on all ten keys (unspecified in the reference): entity order, atoms before rings -- the order
+      // arp_frame_tables.ent_tie encodes for the device sort
+      const uint64_t pfa = entity_pos(rows[ia].from), pfb = entity_pos(rows[ib].from);
+      if (pfa != pfb) return pfa < pfb;
+      return entity_pos(rows[ia].to) < entity_pos(rows[ib].to);
     };
     std::sort(order.begin(), order.end(), less);
 
@@ -159,6 +253,56 @@ arph_table* build_table(const Packed& P, const arp_row* rows, int64_t n) {
   return &T->t;
 }
 
+// A frame built on the device becomes the host table without copying a column: the table borrows the frame's
+// page-locked arrays.  Rows the device marked sc_valid = 2 (an angle too close to an f32 rounding boundary for the
+// device's acos, or NaN) are recomputed with the host libm, so the sc_* columns carry the same bits as build_table's.
+arph_table* table_from_frame(const Packed& P, arp_frame* f) {
+  auto* T = new TableStore();
+  try {
+    T->strings = P.strings;
+    const int64_t n = f->n_rows, n_atoms = (int64_t)P.x.size();
+    for (int64_t k = 0; k < n; ++k) {
+      if (f->sc_valid[k] != 2) continue;
+      auto rc_of = [&](uint32_t v) { return (v & ARP_RING_FLAG) ? P.ring_rc[v & ~ARP_RING_FLAG] : P.atom_rc[v]; };
+      if (((f->from[k] & ARP_RING_FLAG) ? (int64_t)(f->from[k] & ~ARP_RING_FLAG) >= (int64_t)P.ring_rc.size() : (int64_t)f->from[k] >= n_atoms) ||
+          ((f->to[k] & ARP_RING_FLAG) ? (int64_t)(f->to[k] & ~ARP_RING_FLAG) >= (int64_t)P.ring_rc.size() : (int64_t)f->to[k] >= n_atoms))
+        throw Error{ARP_ERR_ARG, "frame row references an entity outside the structure"};
+      const Packed::ResConf& a = P.resconfs[rc_of(f->from[k])];
+      const Packed::ResConf& b = P.resconfs[rc_of(f->to[k])];
+      f->sc_dihedral[k] = (float)plane_dihedral(a.sc.n, b.sc.n);
+      f->sc_centroid_angle[k] = (float)plane_point_angle(a.sc, b.sc.c);
+      f->sc_valid[k] = 1;
+    }
+    // null statistics carry the same quiet-NaN bits as build_table's (the validity column says they are null)
+    for (int64_t k = 0; k < n; ++k)
+      if (!f->sc_valid[k]) f->sc_centroid_dist[k] = f->sc_dihedral[k] = f->sc_centroid_angle[k] = std::nanf("");
+  } catch (...) {
+    delete T;
+    throw;
+  }
+  T->frame = f;
+  arph_table& t = T->t;
+  t.n_rows = f->n_rows;
+  t.model = f->model;
+  t.interaction = f->interaction;
+  t.distance = f->distance;
+  t.from_chain = f->from_chain, t.from_resn = f->from_resn, t.from_resi = f->from_resi, t.from_insertion = f->from_insertion;
+  t.from_altloc = f->from_altloc, t.from_atomn = f->from_atomn, t.from_atomi = f->from_atomi;
+  t.to_chain = f->to_chain, t.to_resn = f->to_resn, t.to_resi = f->to_resi, t.to_insertion = f->to_insertion;
+  t.to_altloc = f->to_altloc, t.to_atomn = f->to_atomn, t.to_atomi = f->to_atomi;
+  t.sc_centroid_dist = f->sc_centroid_dist;
+  t.sc_dihedral = f->sc_dihedral;
+  t.sc_centroid_angle = f->sc_centroid_angle;
+  t.sc_valid = f->sc_valid;
+  for (auto& s : T->strings) T->cstrs.push_back(s.c_str());
+  t.n_strings = (int32_t)T->cstrs.size();
+  t.strings = T->cstrs.data();
+  t.n_atoms = (int64_t)P.x.size();
+  t.pairs_in_cutoff = f->pairs_in_cutoff;
+  t.pairs_classified = f->pairs_classified;
+  return &T->t;
+}
+
 }  // namespace arp
 
 extern "C" {
@@ -175,7 +319,30 @@ int arph_build_table(const arph_packed* p, const arp_row* rows, int64_t n_rows, 
     return ARP_ERR_OOM;
   }
 }
+int arph_table_from_frame(const arph_packed* p, arp_frame* f, arph_table** out) {
+  *out = nullptr;
+  if (!p || !f) {
+    if (f) arp_frame_free(nullptr, f);
+    arp::last_error() = "null argument";
+    return ARP_ERR_ARG;
+  }
+  try {
+    *out = arp::table_from_frame(arph_packed_ref(p), f);
+    return ARP_OK;
+  } catch (const arp::Error& e) {
+    arp_frame_free(nullptr, f);
+    arp::last_error() = e.msg;
+    return e.code;
+  } catch (const std::exception& e) {
+    arp_frame_free(nullptr, f);
+    arp::last_error() = e.what();
+    return ARP_ERR_OOM;
+  }
+}
 void arph_table_free(arph_table* t) {
-  if (t) delete reinterpret_cast<arp::TableStore*>(t);
+  if (!t) return;
+  auto* T = reinterpret_cast<arp::TableStore*>(t);
+  if (T->frame) arp_frame_free(nullptr, T->frame);
+  delete T;
 }
 }

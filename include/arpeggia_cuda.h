@@ -176,6 +176,65 @@ int  arp_stage_run(arp_ctx* ctx, const arp_params* p);
 int  arp_stage_download(arp_ctx* ctx, arp_result** out);
 int  arp_stage_stats(arp_ctx* ctx, arp_stats* out); /* synchronises the stream */
 
+/* ---- the 20-column frame, built on the device -----------------------------------------------
+ *   arp_stage_frame()  <->  results_to_df                          src/contacts/mod.rs:140-181
+ *                           collect_sc_stats + sc_results_to_df    src/contacts/complex.rs:137-174, mod.rs:184-214
+ *                           concat + left join + 10-key sort       src/contacts/mod.rs:111-136
+ * The rows of the last run never leave the GPU: they are keyed (one 128-bit key per row from dense integer ranks
+ * the caller prepares once per structure), radix-sorted, decoded into dictionary-encoded columns and joined with the
+ * side-chain plane statistics on the device; only the finished columns cross PCIe.  String columns are int32 ids
+ * into the CALLER's dictionary (the library never sees a string).  Single-structure jobs only.
+ *
+ * An "entity" is what a row end points at: atoms 0..n_atoms-1, then rings n_atoms..n_atoms+n_rings-1
+ * (InteractingEntity, structs.rs:54-71; rings carry atomn "Ring", atomi 0, complex.rs:334-342).
+ * A "side" is one (model, chain, residue, conformer): the fields of InteractingEntity that are not per atom. */
+typedef struct arp_frame_side { /* 32 bytes */
+  int32_t  chain, resn, resi, icode, altloc; /* string ids; resi already narrowed to i32 (mod.rs:150-178) */
+  uint32_t model;      /* model serial, narrowed to u32 (mod.rs:142-146) */
+  uint32_t chain_rank; /* dense rank of (model serial, chain id bytes): sort keys model, from_chain, to_chain */
+  uint32_t has_sc;     /* a side-chain plane exists for this residue (complex.rs:486-514) */
+} arp_frame_side;
+
+#define ARP_ENT_NARROW 0x80000000u /* ent_tie bit 31: a field of this entity does not fit the frame's integer types;
+                                      a row that references it fails the call with ARP_ERR_NARROWING (the reference panics) */
+typedef struct arp_frame_tables {
+  int64_t n_atoms, n_rings, n_sides;
+  const arp_frame_side* sides; /* [n_sides] */
+  const double*   side_sc;     /* [6 * n_sides] side-chain plane: centre xyz, normal xyz (ignored where !has_sc) */
+  const uint32_t* ent_side;    /* [n_atoms + n_rings] entity -> side */
+  const int32_t*  ent_atomn;   /* string id of the atom name */
+  const int32_t*  ent_atomi;   /* atom serial number as i32; 0 for rings */
+  const uint32_t* ent_rank;    /* dense rank of (resi, altloc bytes, atomi) over all entities: sort keys 4-6 and 7-9 */
+  const uint32_t* ent_tie;     /* position among the entities of equal ent_rank, in entity order (makes the order
+                                  total; the reference leaves ties unspecified) | ARP_ENT_NARROW */
+  uint8_t  label_rank[32];     /* rank of arp_label_name(l) in byte order: sort key 10 (the column is a string) */
+  uint32_t n_chain_ranks, n_ent_ranks, max_tie; /* exclusive upper bounds of chain_rank / ent_rank, largest ent_tie */
+} arp_frame_tables;
+
+/* Library-owned, page-locked host memory; valid until arp_frame_free.  Rows are in the frame's final order. */
+typedef struct arp_frame {
+  int64_t   n_rows;
+  uint32_t* model;
+  uint8_t*  interaction; /* arp_label */
+  float*    distance;
+  int32_t  *from_chain, *from_resn, *from_resi, *from_insertion, *from_altloc, *from_atomn, *from_atomi;
+  int32_t  *to_chain,   *to_resn,   *to_resi,   *to_insertion,   *to_altloc,   *to_atomn,   *to_atomi;
+  float    *sc_centroid_dist, *sc_dihedral, *sc_centroid_angle;
+  uint8_t  *sc_valid; /* 0 = null (either residue has no plane, mod.rs:112-122); 1 = values present; 2 = present, but
+                         an angle sits within 4 ulp (f64) of an f32 rounding boundary or is NaN: a caller that
+                         needs the host libm's bits recomputes these rows (arph_contacts does) */
+  uint32_t *from, *to; /* the row ends as arp_row carries them (entity = v & ARP_RING_FLAG ? n_atoms + index : v) */
+  int64_t pairs_in_cutoff, pairs_classified;
+  float ms_sort, ms_columns, ms_d2h; /* device times of the key + radix-sort passes, the column kernel, the copy */
+  int32_t sort_passes, key_bits;
+} arp_frame;
+
+/* After arp_stage_run of a single-structure job: sort + decode + join on the device, columns to the host. */
+int  arp_stage_frame(arp_ctx* ctx, const arp_frame_tables* t, arp_frame** out);
+/* One-shot: arp_stage_upload + arp_stage_run + arp_stage_frame. */
+int  arp_contacts_frame(arp_ctx* ctx, const arp_structure* s, const arp_params* p, const arp_frame_tables* t, arp_frame** out);
+void arp_frame_free(arp_ctx* ctx, arp_frame* f); /* ctx may be NULL; the memory returns to a process-wide pool */
+
 /* Page-locked host memory for callers that want true asynchronous H2D/D2H (optional). */
 int  arp_host_alloc(void** out, int64_t bytes);
 void arp_host_free(void* p);

@@ -78,6 +78,11 @@ const arp_structure* arph_packed_structure(const arph_packed* p);
 int64_t arph_packed_n_warnings(const arph_packed* p);           /* ring residues with < 3 ring atoms (mod.rs:64-68) */
 const char* arph_packed_warning(const arph_packed* p, int64_t i);
 void arph_packed_free(arph_packed* p);
+/* The integer side tables arp_stage_frame / arp_contacts_frame need (dense sort ranks of the string keys, per-entity
+ * and per-residue columns).  Built on first use, owned by the packed structure, valid until arph_packed_free. */
+int  arph_packed_frame_tables(arph_packed* p, const arp_frame_tables** out);
+/* Wrap a device-built frame as the host table (no column is copied; takes ownership of f, also on failure). */
+int  arph_table_from_frame(const arph_packed* p, arp_frame* f, arph_table** out);
 
 /* rows (structure-local atom / ring indices) -> sorted 20-column table. */
 int  arph_build_table(const arph_packed* p, const arp_row* rows, int64_t n_rows, arph_table** out);

@@ -172,3 +172,76 @@ def test_bounding_box_hint_is_verified(ctx, bft):
         a = np.sort(got["rows"], order=["from", "to", "label"])
         b = np.sort(want["rows"], order=["from", "to", "label"])
         assert np.array_equal(a, b), variant
+
+
+# ---- the frame built on the device (arp_stage_frame) ------------------------------------------------
+def _staged_tables(ctx, atoms, flags=0, groups="/"):
+    """(frame built on the device, table built on the host from the same run's rows)"""
+    p = A.Packed(atoms, groups, flags=flags)
+    ctx.upload(p)
+    ctx.run(0.1, 6.5, flags=2)
+    host = p.build_table(ctx.download()["rows"])
+    dev = ctx.frame(p)
+    return dev, host, p
+
+
+@pytest.mark.parametrize("case", ["1ubq", "6bft", "altloc", "insertion", "two_models", "protonated"])
+def test_device_frame_equals_host_table(ctx, ubq, bft, case):
+    """Sort + decode + side-chain join on the device give the very frame results_to_df / collect_sc_stats / sort give on
+    the host (mod.rs:61-214): same order, same dictionary ids, same f32 bits."""
+    from tests import fixtures as F
+
+    atoms = {"1ubq": ubq, "6bft": bft}.get(case)
+    if atoms is None:
+        atoms = F.all_cases(ubq.view(O.ATOM_DTYPE))[case].view(A.ATOM_DTYPE)
+    dev, host, _ = _staged_tables(ctx, atoms)
+    assert_tables_equal(dev, host, case)
+    assert np.array_equal(dev["interaction_code"], host["interaction_code"]) and np.array_equal(dev["model"], host["model"])
+    fs = dev["frame_stats"]
+    assert fs["key_bits"] <= 64 and fs["sort_passes"] == (fs["key_bits"] + 7) // 8
+
+
+def test_device_frame_wide_keys(ctx, bft):
+    """Keys wider than 64 bits take the two-word path of the radix sort: same frame."""
+    import ctypes as C
+    from arpeggia_b200 import _lib
+
+    p = A.Packed(bft)
+    ctx.upload(p)
+    ctx.run(0.1, 6.5, flags=2)
+    host = p.build_table(ctx.download()["rows"])
+    L = _lib.lib()
+    tp = C.POINTER(_lib.FrameTables)()
+    _lib.check(L.arph_packed_frame_tables(p._h, C.byref(tp)))
+    wide = _lib.FrameTables.from_buffer_copy(tp.contents)
+    wide.n_chain_ranks, wide.n_ent_ranks, wide.max_tie = 1 << 24, 1 << 28, 200  # legal upper bounds, 117-bit keys
+    fp = C.POINTER(_lib.Frame)()
+    _lib.check(L.arp_stage_frame(ctx._h, C.byref(wide), C.byref(fp)), ctx._h)
+    assert fp.contents.key_bits == 2 * 24 + 2 * 28 + 5 + 2 * 8 and fp.contents.sort_passes == 16
+    tb = C.POINTER(_lib.Table)()
+    _lib.check(L.arph_table_from_frame(p._h, fp, C.byref(tb)))
+    try:
+        dev = A.read_table(tb.contents)
+    finally:
+        L.arph_table_free(tb)
+    assert_tables_equal(dev, host, "wide keys")
+
+
+def test_device_frame_1m_rows_sorted(ctx, bft):
+    """Config 3 at full size: 0.9 M rows sorted on the device equal the host's comparator sort of the same rows."""
+    from arpeggia_b200 import synth
+
+    dev, host, _ = _staged_tables(ctx, synth.assembly_1m(bft), flags=2)
+    assert dev["n_rows"] == host["n_rows"] > 900000
+    assert_tables_equal(dev, host, "1M frame")
+
+
+def test_frame_narrowing_error(ctx, ubq):
+    """mod.rs:150-178: an atom serial beyond i32 panics in the reference when a row carries it."""
+    got = ctx.contacts_table(ubq, "/", 0.1, 6.5)
+    atoms = ubq.copy()
+    k = int(np.nonzero(atoms["serial"] == got["from_atomi"][0])[0][0])
+    atoms["serial"][k] = (1 << 31) + 5
+    with pytest.raises(A.ArpeggiaError) as e:
+        ctx.contacts_table(atoms, "/", 0.1, 6.5)
+    assert e.value.code == 6
