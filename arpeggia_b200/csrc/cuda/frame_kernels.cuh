@@ -14,7 +14,7 @@
 
 namespace arpd {
 
-constexpr int RS_TILE_ROUNDS = 32;               // elements per warp tile = 32 lanes x 32 rounds
+constexpr int RS_TILE_ROUNDS = 16;               // elements per warp tile = 32 lanes x 32 rounds
 constexpr int RS_TILE = 32 * RS_TILE_ROUNDS;     // the sort is stable because a tile is walked in order by ONE warp
 constexpr int RS_WARPS = 8, RS_THREADS = 32 * RS_WARPS;
 

@@ -83,8 +83,11 @@ void build_frame_tables(const Packed& P, FrameTables& T) {
   T.ent_atomi.resize(E);
   T.ent_rank.resize(E);
   T.ent_tie.resize(E);
+  // ent_rank / ent_tie are only ever compared between entities of the same chain (the chain ranks precede them in the
+  // key), so both are counted per chain: small numbers, few key bits, few sort passes
   struct Key {
     int64_t resi, atomi;
+    uint32_t chain;
     int32_t alt;
     uint32_t id;
   };
@@ -98,17 +101,18 @@ void build_frame_tables(const Packed& P, FrameTables& T) {
     const bool bad = !fits_i32(serial) || side_bad[rc];
     T.ent_atomi[e] = fits_i32(serial) ? (int32_t)serial : 0;
     T.ent_tie[e] = bad ? ARP_ENT_NARROW : 0u;
-    keys[e] = Key{P.resconfs[rc].resi, serial, srank[P.resconfs[rc].altloc], (uint32_t)e};
+    keys[e] = Key{P.resconfs[rc].resi, serial, T.sides[rc].chain_rank, srank[P.resconfs[rc].altloc], (uint32_t)e};
   }
   std::sort(keys.begin(), keys.end(), [](const Key& a, const Key& b) {
+    if (a.chain != b.chain) return a.chain < b.chain;
     if (a.resi != b.resi) return a.resi < b.resi;
     if (a.alt != b.alt) return a.alt < b.alt;
     if (a.atomi != b.atomi) return a.atomi < b.atomi;
     return a.id < b.id;
   });
-  uint32_t rank = 0, tie = 0, max_tie = 0;
+  uint32_t rank = 0, tie = 0, max_tie = 0, max_rank = 0;
   for (size_t k = 0; k < E; ++k) {
-    if (k > 0) {
+    if (k > 0 && keys[k].chain == keys[k - 1].chain) {
       const bool same = keys[k].resi == keys[k - 1].resi && keys[k].alt == keys[k - 1].alt && keys[k].atomi == keys[k - 1].atomi;
       if (same) {
         tie += 1;
@@ -116,10 +120,13 @@ void build_frame_tables(const Packed& P, FrameTables& T) {
         rank += 1;
         tie = 0;
       }
+    } else {
+      rank = tie = 0;
     }
     T.ent_rank[keys[k].id] = rank;
     T.ent_tie[keys[k].id] |= tie;
     max_tie = std::max(max_tie, tie);
+    max_rank = std::max(max_rank, rank);
   }
   int32_t lrank[ARP_N_LABELS];
   label_ranks(lrank);
@@ -135,7 +142,7 @@ void build_frame_tables(const Packed& P, FrameTables& T) {
   T.t.ent_atomi = T.ent_atomi.data();
   T.t.ent_rank = T.ent_rank.data();
   T.t.ent_tie = T.ent_tie.data();
-  T.t.n_ent_ranks = E ? rank + 1 : 1;
+  T.t.n_ent_ranks = max_rank + 1;
   T.t.max_tie = max_tie;
 }
 

@@ -260,6 +260,26 @@ def main():
     if world > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
     e2e_value = world * pairs / (float(e2e_t.item()) * 1e-3)
+
+    # ---- rows -> sorted 20-column frame on the device, beside the host comparator sort ---------
+    frame_info = None
+    if rank == 0 and world == 1:
+        ctx.upload(packed)
+        ctx.run(0.1, 6.5, args.flags)
+        rows_host = ctx.download()["rows"]
+        ctx.frame(packed)  # warm-up: builds the side tables, sizes the buffers, fills the pinned pool
+        t0 = time.perf_counter()
+        fr = ctx.frame(packed)
+        t_dev_wall = 1e3 * (time.perf_counter() - t0)
+        t0 = time.perf_counter()
+        host_tab = packed.build_table(rows_host)
+        t_host = 1e3 * (time.perf_counter() - t0)
+        same = all(np.array_equal(fr[c], host_tab[c]) for c in ("from_atomi", "to_atomi", "interaction_code", "from_resi", "to_resi"))
+        frame_info = {"rows": int(fr["n_rows"]), "ms_sort": fr["frame_stats"]["ms_sort"], "ms_columns": fr["frame_stats"]["ms_columns"],
+                      "ms_d2h": fr["frame_stats"]["ms_d2h"], "sort_passes": fr["frame_stats"]["sort_passes"],
+                      "key_bits": fr["frame_stats"]["key_bits"], "ms_wall_incl_numpy_copy": t_dev_wall,
+                      "host_table_ms_incl_numpy_copy": t_host, "equals_host_table": bool(same),
+                      "api": "arp_stage_frame (keys + radix sort + decode + sc join on the device, columns D2H)"}
     d2h_bytes = int(n_rows_e2e * 16)
     st = ctx.stats()
 
@@ -296,6 +316,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "ms_per_step": float(e2e_t.item()), "ms_h2d": st["ms_h2d"], "ms_run": st["ms_run"], "ms_d2h": st["ms_d2h"],
                     "api": "arp_contacts (C ABI, pinned host SoA in, host rows out)"},
+            "frame": frame_info,
             "gpu_launches": int(st0["kernel_launches"]) * args.steps,
             "clocks": clocks,
             "contacts_per_s": world * n_rows / (ms_max * 1e-3),

@@ -204,9 +204,10 @@ typedef struct arp_frame_tables {
   const uint32_t* ent_side;    /* [n_atoms + n_rings] entity -> side */
   const int32_t*  ent_atomn;   /* string id of the atom name */
   const int32_t*  ent_atomi;   /* atom serial number as i32; 0 for rings */
-  const uint32_t* ent_rank;    /* dense rank of (resi, altloc bytes, atomi) over all entities: sort keys 4-6 and 7-9 */
-  const uint32_t* ent_tie;     /* position among the entities of equal ent_rank, in entity order (makes the order
-                                  total; the reference leaves ties unspecified) | ARP_ENT_NARROW */
+  const uint32_t* ent_rank;    /* dense rank of (resi, altloc bytes, atomi) among the entities of the same chain_rank:
+                                  sort keys 4-6 and 7-9 (only compared once the chain keys are equal) */
+  const uint32_t* ent_tie;     /* position among the entities of equal (chain_rank, ent_rank), in entity order (makes
+                                  the order total; the reference leaves such ties unspecified) | ARP_ENT_NARROW */
   uint8_t  label_rank[32];     /* rank of arp_label_name(l) in byte order: sort key 10 (the column is a string) */
   uint32_t n_chain_ranks, n_ent_ranks, max_tie; /* exclusive upper bounds of chain_rank / ent_rank, largest ent_tie */
 } arp_frame_tables;
