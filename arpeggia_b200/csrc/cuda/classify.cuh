@@ -105,6 +105,7 @@ __device__ __forceinline__ int hbond_body(const PairArgs& G, const DevParams& P,
 }
 
 // Labels of the ordered pair (e1 = a, e2 = b) as a bit mask over arp_label.  complex.rs:217-296.
+// sa / sb: residue ids (arp_structure.res_id) of the two atoms
 __device__ __forceinline__ uint32_t classify_pair(const PairArgs& G, const DevParams& P, const RecB& a, uint32_t wa, uint32_t sa,
                                                   const RecB& b, uint32_t wb, uint32_t sb, double dist) {
   const uint32_t ea = wa & ARP_ATTR_ELEM_MASK, eb = wb & ARP_ATTR_ELEM_MASK;
@@ -113,7 +114,7 @@ __device__ __forceinline__ uint32_t classify_pair(const PairArgs& G, const DevPa
   uint32_t m = 0;
   if (dist < dsub(sum_cov, P.comp)) return LBIT(ARP_StericClash);  // complex.rs:233-235: a clash suppresses the rest
   if (dist < dadd(sum_cov, P.comp)) {
-    const bool ss = (wa & wb & ARP_ATTR_CYS_SG) && is_disulfide(G, P, G.recA[sa].res_id, G.recA[sb].res_id);
+    const bool ss = (wa & wb & ARP_ATTR_CYS_SG) && is_disulfide(G, P, sa, sb);
     m |= ss ? LBIT(ARP_Disulfide) : LBIT(ARP_CovalentBond);
   } else if (dist < dadd(sum_vdw, P.comp)) {
     m |= LBIT(ARP_VanDerWaalsContact);
@@ -131,7 +132,7 @@ __device__ __forceinline__ uint32_t classify_pair(const PairArgs& G, const DevPa
     const bool fb = !fa && (wb & dflag) && (wa & ARP_ATTR_ACCEPTOR);
     if (!(fa || fb)) continue;
     const int r = hbond_body(G, P, fa ? a.x : b.x, fa ? a.y : b.y, fa ? a.z : b.z, fa ? b.x : a.x, fa ? b.y : a.y, fa ? b.z : a.z,
-                             G.recA[fa ? sa : sb].res_id, fa ? eb : ea, dist, k ? P.ang.a_ge_130 : P.ang.a_ge_90);
+                             fa ? sa : sb, fa ? eb : ea, dist, k ? P.ang.a_ge_130 : P.ang.a_ge_90);
     if (k) wk = r; else hb = r;
   }
   // complex.rs:240-251

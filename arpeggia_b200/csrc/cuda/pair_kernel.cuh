@@ -91,13 +91,49 @@ __device__ __forceinline__ float class_pair_limit2(const DevParams& P, int ea, i
 }
 
 // ---- B2: up to 32 filtered pairs, one per lane: exact distance, counters, label ladder, rows ----------------------
-__device__ __forceinline__ void exact_batch(const PairArgs& G, const DevParams& P, const uint2 e, bool have, int lane, PairCounts& K) {
-  uint32_t m = 0, sp = 0, sq = 0;
+// The rows of a trip are written one trip later: the atomicAdd that reserves their slots is issued at the end of a trip
+// and its result is first needed after the next trip's gathers have been issued, so neither latency is exposed.
+struct PendingRows {
+  unsigned long long base;  // lane 31: result of the reservation
+  uint32_t m, ip, iq, off;  // this lane's label bits, row ends, offset within the reservation
+  float fd;
+};
+__device__ __forceinline__ void flush_rows(const PairArgs& G, PendingRows& R) {
+  const unsigned long long base = __shfl_sync(0xffffffffu, R.base, 31);
+  unsigned long long w = base + R.off;
+  uint32_t m = R.m;
+  while (m) {
+    const uint32_t l = __ffs(m) - 1;
+    m &= m - 1;
+    if (w < G.row_cap) G.rows[w] = arp_row{R.ip, R.iq, l, R.fd};
+    ++w;
+  }
+  R.m = 0u;
+}
+// the records of one queue entry: everything the exact stage reads, gathered in ONE round (both 32-byte RecB sectors,
+// attr and the second half of both RecA sectors: residue id for the disulfide / hydrogen tests, perm for the row)
+struct ExactOperands {
+  RecB a, b;
+  uint32_t wa, wb;
+  uint4 ta, tb;  // chain_key, res_ordinal, res_id, perm
+};
+__device__ __forceinline__ void exact_gather(const PairArgs& G, const uint2 e, bool have, ExactOperands& X) {
+  if (!have) return;
+  const uint32_t sa = e.x & SLOT_MASK, sb = e.y & SLOT_MASK;
+  X.a = G.recB[sa];
+  X.b = G.recB[sb];
+  X.wa = G.recA[sa].attr;
+  X.wb = G.recA[sb].attr;
+  X.ta = *(reinterpret_cast<const uint4*>(G.recA + sa) + 1);
+  X.tb = *(reinterpret_cast<const uint4*>(G.recA + sb) + 1);
+}
+__device__ __forceinline__ void exact_batch(const PairArgs& G, const DevParams& P, const uint2 e, bool have, const ExactOperands& X, int lane,
+                                            PairCounts& K, PendingRows& R) {
+  uint32_t m = 0, ip = 0, iq = 0;
   double dist = 0.0;
   if (have) {
-    const uint32_t sa = e.x & SLOT_MASK, sb = e.y & SLOT_MASK;
-    const RecB a = G.recB[sa], b = G.recB[sb];
-    const uint32_t wa = G.recA[sa].attr, wb = G.recA[sb].attr;
+    const RecB &a = X.a, &b = X.b;
+    const uint32_t wa = X.wa, wb = X.wb;
     // rstar distance_2 / pdbtbx Atom::distance: ((dx*dx + dy*dy) + dz*dz), every operation rounded once
     const double dx = dsub(b.x, a.x), dy = dsub(b.y, a.y), dz = dsub(b.z, a.z);
     const double d2 = dadd(dadd(dmul(dx, dx), dmul(dy, dy)), dmul(dz, dz));
@@ -109,36 +145,25 @@ __device__ __forceinline__ void exact_batch(const PairArgs& G, const DevParams& 
       if ((e.x & QF_B) && (e.y & QF_B) && d2 <= P.emit_d2_max) {
         dist = __dsqrt_rn(d2);
         const bool swap = (e.y & QF_A) != 0u;
-        sp = swap ? sb : sa;
-        sq = swap ? sa : sb;
+        ip = swap ? X.tb.w : X.ta.w;
+        iq = swap ? X.ta.w : X.tb.w;
         // one instance of the ladder (instruction-cache footprint): operands selected, not two inlined calls
         RecB p, r;
         p.x = swap ? b.x : a.x, p.y = swap ? b.y : a.y, p.z = swap ? b.z : a.z;
         r.x = swap ? a.x : b.x, r.y = swap ? a.y : b.y, r.z = swap ? a.z : b.z;
         p.chain_key = r.chain_key = 0u;      // classify_pair reads positions only
         p.res_ordinal = r.res_ordinal = 0u;
-        m = classify_pair(G, P, p, swap ? wb : wa, sp, r, swap ? wa : wb, sq, dist);
+        m = classify_pair(G, P, p, swap ? wb : wa, swap ? X.tb.z : X.ta.z, r, swap ? wa : wb, swap ? X.ta.z : X.tb.z, dist);
       }
     }
   }
   const uint32_t mine = __popc(m);
   if (!__any_sync(0xffffffffu, mine != 0u)) return;
   const uint32_t inc = warp_inclusive_sum(mine, lane);
-  const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
-  unsigned long long base = 0;
-  if (lane == 31) base = atomicAdd(&G.ctr->rows, (unsigned long long)total);
-  base = __shfl_sync(0xffffffffu, base, 31);
-  unsigned long long w = base + (inc - mine);
-  if (mine) {
-    const uint32_t ip = G.recA[sp].perm, iq = G.recA[sq].perm;
-    const float fd = __double2float_rn(dist);  // Rust `as f32`, mod.rs:148
-    while (m) {
-      const uint32_t l = __ffs(m) - 1;
-      m &= m - 1;
-      if (w < G.row_cap) G.rows[w] = arp_row{ip, iq, l, fd};
-      ++w;
-    }
-  }
+  R.base = 0ull;
+  if (lane == 31) R.base = atomicAdd(&G.ctr->rows, (unsigned long long)inc);
+  R.m = m, R.ip = ip, R.iq = iq, R.off = inc - mine;
+  R.fd = __double2float_rn(dist);  // Rust `as f32`, mod.rs:148
 }
 
 // largest squared distance (f32, guard included) at which any label of complex.rs:217-296 can fire for this pair
@@ -279,7 +304,10 @@ __global__ void __launch_bounds__(CLS_THREADS, 4) k_filter(const PairArgs G, con
 }
 
 // ---- k_exact (B2) -----------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(CLS_THREADS, 4) k_exact(const PairArgs G, const DevParams P) {
+#ifndef EXACT_MIN_BLOCKS
+#define EXACT_MIN_BLOCKS 3
+#endif
+__global__ void __launch_bounds__(CLS_THREADS, EXACT_MIN_BLOCKS) k_exact(const PairArgs G, const DevParams P) {
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   PairCounts K{0ull, 0ull};
   const unsigned long long n_pairs = min(G.ctr->q2_len, G.pairq2_cap);
@@ -287,12 +315,17 @@ __global__ void __launch_bounds__(CLS_THREADS, 4) k_exact(const PairArgs G, cons
   unsigned long long base = ((unsigned long long)blockIdx.x * CLS_WARPS + wid) * 32ull;
   uint2 e_next = make_uint2(0u, 0u);  // read one trip ahead
   if (base + lane < n_pairs) e_next = __ldcs(G.pairq2 + base + lane);
+  PendingRows R{0ull, 0u, 0u, 0u, 0u, 0.f};
   for (; base < n_pairs; base += stride) {
     const uint2 e = e_next;
     const bool have = base + lane < n_pairs;
     if (base + stride + lane < n_pairs) e_next = __ldcs(G.pairq2 + base + stride + lane);
-    exact_batch(G, P, e, have, lane, K);
+    ExactOperands X;
+    exact_gather(G, e, have, X);
+    if (__any_sync(0xffffffffu, R.m != 0u)) flush_rows(G, R);  // the previous trip's rows, while the gathers fly
+    exact_batch(G, P, e, have, X, lane, K, R);
   }
+  if (__any_sync(0xffffffffu, R.m != 0u)) flush_rows(G, R);
   unsigned long long n_in = K.n_in, n_cls = K.n_cls;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
