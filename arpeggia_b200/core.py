@@ -90,6 +90,8 @@ class Packed:
             out[k] = view(getattr(s, k), s.n_h, np.float64)
         for k in ("res_cb", "res_sg"):
             out[k] = view(getattr(s, k), s.n_residues, np.int32)
+        for k in ("res_chain_key", "res_res_ordinal"):
+            out[k] = view(getattr(s, k), s.n_residues, np.uint32)
         for k in ("ring_center", "ring_normal"):
             out[k] = view(getattr(s, k), 3 * s.n_rings, np.float64).reshape(-1, 3)
         for k in ("ring_attr", "ring_chain_key", "ring_res_ordinal"):

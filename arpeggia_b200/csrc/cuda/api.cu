@@ -85,6 +85,8 @@ struct arp_ctx {
   int64_t n_struct = 0, n_atoms = 0, n_res = 0, n_rings = 0, n_h = 0;
   DBuf<double> x, y, z, hx, hy, hz, ring_c, ring_n;
   DBuf<uint32_t> attr, chain_key, res_ordinal, res_id, res_h_begin, ring_attr, ring_chain_key, ring_res_ordinal;
+  DBuf<uint32_t> res_chain_key, res_res_ordinal;  // compact per-residue form of chain_key / res_ordinal
+  bool per_residue_keys = false;                  // every structure of the job came with it
   DBuf<int32_t> res_cb, res_sg;
   DBuf<uint32_t> atom_struct, ring_struct;
   DBuf<StructDesc> descs;
@@ -235,8 +237,19 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
   UP(y, y, nat);
   UP(z, z, nat);
   UP(attr, attr, nat);
-  UP(chain_key, chain_key, nat);
-  UP(res_ordinal, res_ordinal, nat);
+  c->per_residue_keys = true;
+  for (int64_t k = 0; k < n; ++k)
+    if (!s[k]->res_chain_key || !s[k]->res_res_ordinal) c->per_residue_keys = false;
+  if (c->per_residue_keys) {
+    UP(res_chain_key, res_chain_key, nrs);
+    UP(res_res_ordinal, res_res_ordinal, nrs);
+  } else {
+    for (int64_t k = 0; k < n; ++k)
+      if (s[k]->n_atoms > 0 && (!s[k]->chain_key || !s[k]->res_ordinal))
+        throw arp::Error{ARP_ERR_ARG, "structure has neither per-atom nor per-residue chain_key / res_ordinal"};
+    UP(chain_key, chain_key, nat);
+    UP(res_ordinal, res_ordinal, nat);
+  }
   UP(hx, h_x, nh);
   UP(hy, h_y, nh);
   UP(hz, h_z, nh);

@@ -232,8 +232,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_lookback(uint32_t* __rest
 __global__ void __launch_bounds__(256)
 k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, const double* __restrict__ z,
                 const uint32_t* __restrict__ attr, const uint32_t* __restrict__ chain_key, const uint32_t* __restrict__ res_ordinal,
-                const uint32_t* __restrict__ res_id, const uint32_t* __restrict__ atom_struct, const StructDesc* __restrict__ descs,
-                const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of, const uint32_t* __restrict__ cell_start,
+                const uint32_t* __restrict__ res_id, const uint32_t* __restrict__ res_chain_key, const uint32_t* __restrict__ res_res_ordinal,
+                const uint32_t* __restrict__ atom_struct, const StructDesc* __restrict__ descs, const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of, const uint32_t* __restrict__ cell_start,
                 uint32_t n, double edge, RecA* __restrict__ recA, RecB* __restrict__ recB, Item* __restrict__ items,
                 uint32_t* __restrict__ cations, Counters* __restrict__ ctr) {
   const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
@@ -250,9 +250,10 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
   // bit 31 of the sorted attribute word (internal): the atom may start a row / counts as `from` (complex.rs:200-202)
   const uint32_t w = attr[a] & 0x7fffffffu;
   ra.attr = w | (((w & ARP_ATTR_LIGAND) && (w & ARP_ATTR_ELEM_MASK) && !(w & ARP_ATTR_GHOST)) ? 0x80000000u : 0u);
-  ra.chain_key = chain_key[a];
-  ra.res_ordinal = res_ordinal[a];
   ra.res_id = res_id[a];
+  // per-atom arrays, or the compact per-residue form (arp_structure.res_chain_key): the residue tables are L2-resident
+  ra.chain_key = res_chain_key ? res_chain_key[ra.res_id] : chain_key[a];
+  ra.res_ordinal = res_chain_key ? res_res_ordinal[ra.res_id] : res_ordinal[a];
   ra.perm = a;
   recA[slot] = ra;
   RecB rb;

@@ -51,12 +51,25 @@ constexpr uint32_t QF_A = 0x80000000u;   // q2.x: in-cutoff still undecided (cou
 constexpr uint32_t QF_B = 0x40000000u;   // q2.x: the pair filter passed                     q2.y: a label may fire
 
 // One from-atom as the screen reads it (two LDS.128 broadcasts).
+#ifndef SCREEN_F32X2
+#define SCREEN_F32X2 0  // 1: the screen's dot products run as packed fma.rn.f32x2 (two candidate slots per instruction)
+#endif
+#if SCREEN_F32X2
+struct __align__(16) FromRec {  // 48 bytes: coordinates duplicated so that a 64-bit shared load yields the (f, f) operand
+  float x, x2, y, y2;        // cell-local position
+  float z, z2, k_hit, k_cert;  // s >= k_hit <=> d^2 <= T_hit; s >= k_cert <=> d^2 <= T_cert
+  float k_near;              // s < k_near <=> d^2 > T_near
+  uint32_t w;                // (eligible as `from` ? 1 << 16 : 0) | 1
+  uint32_t pad[2];
+};
+#else
 struct __align__(16) FromRec {
   float x, y, z, k_hit;      // cell-local position; s >= k_hit <=> d^2 <= T_hit
   float k_cert, k_near;      // s >= k_cert <=> d^2 <= T_cert; s < k_near <=> d^2 > T_near
   uint32_t w;                // (eligible as `from` ? 1 << 16 : 0) | 1
   uint32_t pad;
 };
+#endif
 
 struct ScreenSmem {
   uint4 buf[PAIR_WARPS][2][CHUNK];      // staged candidate records (RecA bits), double buffered
@@ -343,6 +356,87 @@ struct Cand {
   float x[SLOTS], y[SLOTS], z[SLOTS], h[SLOTS];
 };
 
+#if SCREEN_F32X2
+// sm_100 has packed FP32: fma.rn.f32x2 does two independent FMAs per issue slot.  The kernel is issue-bound, so the
+// three FMAs of a test are issued once per PAIR of candidate slots: 6.5 instead of 8 instructions per test.
+struct CandP {
+  unsigned long long x[SLOTS / 2], y[SLOTS / 2], z[SLOTS / 2], h[SLOTS / 2];  // (slot 2p, slot 2p + 1)
+};
+__device__ __forceinline__ unsigned long long pack2(float a, float b) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+  unsigned long long r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+// inside = tri && s >= k_cert && s < k_near;  push = tri && s >= k_hit && !inside; predicated add / or
+// (written in PTX: the compiler otherwise turns both updates into SEL + ALU pairs)
+template <bool TRI>
+__device__ __forceinline__ void screen_test(float s, float k_hit, float k_cert, float k_near, uint32_t w, uint32_t bit, uint32_t i, uint32_t lim,
+                                            uint32_t& cnt, uint32_t& mask) {
+  if (TRI) {
+    asm("{\n\t.reg .pred pt, pi, pp;\n\t"
+        "setp.lt.u32 pt, %8, %9;\n\t"
+        "setp.ge.and.f32 pi, %2, %3, pt;\n\t"
+        "setp.lt.and.f32 pi, %2, %4, pi;\n\t"
+        "setp.ge.and.f32 pp, %2, %5, pt;\n\t"
+        "and.pred pp, pp, !pi;\n\t"
+        "@pi add.u32 %0, %0, %6;\n\t"
+        "@pp or.b32 %1, %1, %7;\n\t}"
+        : "+r"(cnt), "+r"(mask)
+        : "f"(s), "f"(k_cert), "f"(k_near), "f"(k_hit), "r"(w), "r"(bit), "r"(i), "r"(lim));
+  } else {
+    asm("{\n\t.reg .pred pi, pp;\n\t"
+        "setp.ge.f32 pi, %2, %3;\n\t"
+        "setp.lt.and.f32 pi, %2, %4, pi;\n\t"
+        "setp.ge.and.f32 pp, %2, %5, !pi;\n\t"
+        "@pi add.u32 %0, %0, %6;\n\t"
+        "@pp or.b32 %1, %1, %7;\n\t}"
+        : "+r"(cnt), "+r"(mask)
+        : "f"(s), "f"(k_cert), "f"(k_near), "f"(k_hit), "r"(w), "r"(bit));
+  }
+}
+// one from-atom against the NS candidates of this lane
+template <bool ALL, int NS>
+__device__ __forceinline__ void screen_one(const FromRec* f, int i, const CandP& C, const uint32_t (&lim)[SLOTS], uint32_t (&mask)[SLOTS],
+                                           uint32_t (&cnt)[SLOTS]) {
+  const ulonglong2 A = *reinterpret_cast<const ulonglong2*>(f);        // (x, x), (y, y)
+  const ulonglong2 B = *(reinterpret_cast<const ulonglong2*>(f) + 1);  // (z, z), (k_hit, k_cert)
+  const uint2 D = *reinterpret_cast<const uint2*>(&f->k_near);         // k_near, w
+  float k_hit, k_cert;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(k_hit), "=f"(k_cert) : "l"(B.y));
+  const float k_near = __uint_as_float(D.x);
+  const uint32_t w = D.y, bit = 1u << i;
+#pragma unroll
+  for (int p = 0; p < (NS + 1) / 2; ++p) {
+    const unsigned long long s2 = fma2(A.x, C.x[p], fma2(A.y, C.y[p], fma2(B.x, C.z[p], C.h[p])));
+    float s0, s1;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(s0), "=f"(s1) : "l"(s2));
+    if (ALL || p == 0)
+      screen_test<true>(s0, k_hit, k_cert, k_near, w, bit, (uint32_t)i, lim[2 * p], cnt[2 * p], mask[2 * p]);
+    else
+      screen_test<false>(s0, k_hit, k_cert, k_near, w, bit, 0u, 0u, cnt[2 * p], mask[2 * p]);
+    if (2 * p + 1 < NS) {
+      if (ALL)
+        screen_test<true>(s1, k_hit, k_cert, k_near, w, bit, (uint32_t)i, lim[2 * p + 1], cnt[2 * p + 1], mask[2 * p + 1]);
+      else
+        screen_test<false>(s1, k_hit, k_cert, k_near, w, bit, 0u, 0u, cnt[2 * p + 1], mask[2 * p + 1]);
+    }
+  }
+}
+template <bool ALL, int NS>
+__device__ __forceinline__ void screen_pass(const FromRec* sf, int nf, const CandP& C, const uint32_t (&lim)[SLOTS], uint32_t (&mask)[SLOTS],
+                                            uint32_t (&cnt)[SLOTS]) {
+#pragma unroll 1
+  for (int i = 0; i < nf; i += 2) {  // two from-atoms per trip; sf has FROM_PASS + 1 entries
+    screen_one<ALL, NS>(sf + i, i, C, lim, mask, cnt);
+    if (i + 1 < nf) screen_one<ALL, NS>(sf + i + 1, i + 1, C, lim, mask, cnt);
+  }
+}
+#else
 // one from-atom (f = x, y, z, k_hit; g = k_cert, k_near, w) against the NS candidates of this lane
 template <bool ALL, int NS>
 __device__ __forceinline__ void screen_one(const float4 f, const float4 g, int i, const Cand& C, const uint32_t (&lim)[SLOTS],
@@ -396,6 +490,8 @@ __device__ __forceinline__ void screen_pass(const FromRec* sf, int nf, const Can
     if (i + 1 < nf) screen_one<ALL, NS>(f1, g1, i + 1, C, lim, mask, cnt);
   }
 }
+
+#endif
 
 // Per-warp window into the pair queue: space is reserved CHUNKQ entries at a time (one atomicAdd per ~10 work items
 // instead of one per item); the unused tail of a window is filled with sentinel entries that k_filter skips.
@@ -541,7 +637,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_screen(const 
     cp_async_wait_all();
     const uint4* buf = S.buf[wid][pb];
     const uint32_t* tbuf = S.tbuf[wid][pb];
-    Cand C;
+    Cand C1;
     uint32_t eligm = 0;                // bit u: candidate u may start a row / is counted as `from`
     const uint4 own_raw = buf[lane];  // chunk 0: lane < n_own holds own atom `lane`
 #pragma unroll
@@ -549,16 +645,28 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_screen(const 
       if (u < ns) {
         const uint4 r = buf[32 * u + lane];
         const float x = __uint_as_float(r.x) - ccx, y = __uint_as_float(r.y) - ccy, z = __uint_as_float(r.z) - ccz;
-        C.x[u] = x;
-        C.y[u] = y;
-        C.z[u] = z;
-        C.h[u] = -0.5f * fmaf(z, z, fmaf(y, y, x * x));  // "no candidate": h = -1.5e36 fails every test
+        C1.x[u] = x;
+        C1.y[u] = y;
+        C1.z[u] = z;
+        C1.h[u] = -0.5f * fmaf(z, z, fmaf(y, y, x * x));  // "no candidate": h = -1.5e36 fails every test
         eligm |= (r.w >> 31) << u;
       } else {
-        C.x[u] = C.y[u] = C.z[u] = 0.f;
-        C.h[u] = -1.0e30f;
+        C1.x[u] = C1.y[u] = C1.z[u] = 0.f;
+        C1.h[u] = -1.0e30f;
       }
     }
+#if SCREEN_F32X2
+    CandP C;
+#pragma unroll
+    for (int p = 0; p < SLOTS / 2; ++p) {
+      C.x[p] = pack2(C1.x[2 * p], C1.x[2 * p + 1]);
+      C.y[p] = pack2(C1.y[2 * p], C1.y[2 * p + 1]);
+      C.z[p] = pack2(C1.z[2 * p], C1.z[2 * p + 1]);
+      C.h[p] = pack2(C1.h[2 * p], C1.h[2 * p + 1]);
+    }
+#else
+    const Cand& C = C1;
+#endif
     // ---- stage the next unit: the next chunk of this item, or chunk 0 of the next item ------------------------------
     const bool more = chunk0 + CHUNK < total;
     uint32_t word_nn = word_n, w_raw_n = w_raw;
@@ -583,6 +691,9 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_screen(const 
         f.x = __uint_as_float(fr.x) - ccx;
         f.y = __uint_as_float(fr.y) - ccy;
         f.z = __uint_as_float(fr.z) - ccz;
+#if SCREEN_F32X2
+        f.x2 = f.x, f.y2 = f.y, f.z2 = f.z;
+#endif
         const float hf = 0.5f * fmaf(f.z, f.z, fmaf(f.y, f.y, f.x * f.x));
         // no label can fire for this atom beyond its own limit: a per-atom T_near (conservative; B1 applies the pair limit)
         const float t_near = P.count_classified ? P.scr_near : fminf(P.scr_near, atom_limit2(P, S.lim1, fr.w) + P.guard_a);
@@ -590,7 +701,11 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_screen(const 
         f.k_cert = hf - half_cert;
         f.k_near = hf - 0.5f * t_near;
         f.w = ((fr.w >> 31) << 16) | 1u;
+#if SCREEN_F32X2
+        f.pad[0] = f.pad[1] = 0u;
+#else
         f.pad = 0u;
+#endif
         sfrom[lane] = f;
       }
       __syncwarp();

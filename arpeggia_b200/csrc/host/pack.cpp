@@ -494,6 +494,15 @@ void Packed::finish() {
   t.ring_attr = ring_attr.data();
   t.ring_chain_key = ring_chain_key.data();
   t.ring_res_ordinal = ring_res_ordinal.data();
+  // compact per-residue form of chain_key / res_ordinal (what the device path uploads when it is present)
+  res_chain_key.assign(res_cb.size(), 0u);
+  res_res_ordinal.assign(res_cb.size(), 0u);
+  for (size_t a = 0; a < res_id.size(); ++a) {
+    res_chain_key[res_id[a]] = chain_key[a];
+    res_res_ordinal[res_id[a]] = res_ordinal[a];
+  }
+  t.res_chain_key = res_chain_key.data();
+  t.res_res_ordinal = res_res_ordinal.data();
   // bounding-box hint for the cell-grid layout (verified on the device)
   t.has_bbox = 0;
   if (!x.empty()) {

@@ -13,6 +13,7 @@ struct Packed {
   // device SoA (arp_structure points into these)
   std::vector<double> x, y, z, hx, hy, hz, ring_c, ring_n;
   std::vector<uint32_t> attr, chain_key, res_ordinal, res_id, res_h_begin, ring_attr, ring_chain_key, ring_res_ordinal;
+  std::vector<uint32_t> res_chain_key, res_res_ordinal;  // per residue (compact form of chain_key / res_ordinal)
   std::vector<int32_t> res_cb, res_sg;
   arp_structure s{};
 

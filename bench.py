@@ -133,9 +133,11 @@ def pinned_structure(A, packed):
         v = getattr(src, name)
         if name.startswith("n_") or name.startswith("bbox_") or name == "has_bbox":
             setattr(dst, name, v)
-    sizes = {"x": 8, "y": 8, "z": 8, "attr": 4, "chain_key": 4, "res_ordinal": 4, "res_id": 4}
+    # chain_key / res_ordinal travel in their compact per-residue form (arp_structure.res_chain_key); the per-atom
+    # arrays stay NULL and are neither copied here nor uploaded
+    sizes = {"x": 8, "y": 8, "z": 8, "attr": 4, "res_id": 4}
     n, nr, ng, nh = src.n_atoms, src.n_residues, src.n_rings, src.n_h
-    lens = {**{k: n * s for k, s in sizes.items()}, "res_h_begin": 4 * (nr + 1), "h_x": 8 * nh, "h_y": 8 * nh, "h_z": 8 * nh,
+    lens = {**{k: n * s for k, s in sizes.items()}, "res_chain_key": 4 * nr, "res_res_ordinal": 4 * nr, "res_h_begin": 4 * (nr + 1), "h_x": 8 * nh, "h_y": 8 * nh, "h_z": 8 * nh,
             "res_cb": 4 * nr, "res_sg": 4 * nr, "ring_center": 24 * ng, "ring_normal": 24 * ng, "ring_attr": 4 * ng,
             "ring_chain_key": 4 * ng, "ring_res_ordinal": 4 * ng}
     for name, nbytes in lens.items():
@@ -261,6 +263,8 @@ def main():
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
     e2e_value = world * pairs / (float(e2e_t.item()) * 1e-3)
 
+    st = ctx.stats()  # of the last end-to-end call
+
     # ---- rows -> sorted 20-column frame on the device, beside the host comparator sort ---------
     frame_info = None
     if rank == 0 and world == 1:
@@ -281,7 +285,6 @@ def main():
                       "host_table_ms_incl_numpy_copy": t_host, "equals_host_table": bool(same),
                       "api": "arp_stage_frame (keys + radix sort + decode + sc join on the device, columns D2H)"}
     d2h_bytes = int(n_rows_e2e * 16)
-    st = ctx.stats()
 
     if rank == 0:
         peaks = {}

@@ -110,6 +110,12 @@ typedef struct arp_structure {
   double bbox_max[3];
   int32_t has_bbox;
   int32_t reserved_;
+  /* Optional compact form: chain_key and res_ordinal are the same for every atom of a residue.  When BOTH per-residue
+   * arrays are given (n_residues entries, indexed by res_id), the per-atom chain_key / res_ordinal arrays are not read
+   * (they may be NULL) and the device expands the values while it sorts the atoms: 8 bytes per atom less to move over
+   * PCIe, a fifth of the upload. */
+  const uint32_t* res_chain_key;
+  const uint32_t* res_res_ordinal;
 } arp_structure;
 
 #define ARP_FLAG_EMIT_RADIUS_SCREEN 0x1u /* screen atom pairs at min(dist_cutoff, largest distance at which any

@@ -1,4 +1,5 @@
 """GPU parity: the CUDA path (through the C ABI) against the CPU oracle on the same inputs.  Needs a B200."""
+import ctypes
 import numpy as np
 import pytest
 
@@ -245,3 +246,20 @@ def test_frame_narrowing_error(ctx, ubq):
     with pytest.raises(A.ArpeggiaError) as e:
         ctx.contacts_table(atoms, "/", 0.1, 6.5)
     assert e.value.code == 6
+
+
+def test_per_atom_and_per_residue_keys_same_rows(ctx, bft):
+    """chain_key / res_ordinal per atom (slab mode, hand-packed callers) or per residue (the packer's compact form)."""
+    from arpeggia_b200 import _lib
+
+    p = A.Packed(bft)
+    want = ctx.contacts_rows(p, 0.1, 6.5)  # per-residue form
+    s = _lib.Structure.from_buffer_copy(p.structure)
+    s.res_chain_key = s.res_res_ordinal = None
+    got = ctx.contacts_rows([ctypes.pointer(s)], 0.1, 6.5)
+    key = ["from", "to", "label"]
+    assert np.array_equal(np.sort(got["rows"], order=key), np.sort(want["rows"], order=key))
+    s.chain_key = None
+    with pytest.raises(A.ArpeggiaError) as e:
+        ctx.contacts_rows([ctypes.pointer(s)], 0.1, 6.5)
+    assert e.value.code == 8

@@ -158,3 +158,17 @@ def test_table_builder_rejects_bad_rows(ubq):
     rows["from"] = 100000
     with pytest.raises(A.ArpeggiaError, match="outside the structure"):
         p.build_table(rows)
+
+
+@pytest.mark.parametrize("which", ["1ubq", "6bft", "altloc", "insertion", "two_models"])
+def test_per_residue_keys_expand_to_the_per_atom_arrays(which, ubq, bft):
+    """arp_structure.res_chain_key / res_res_ordinal (what the device path uploads) expand to chain_key / res_ordinal."""
+    from tests import fixtures as F
+
+    atoms = {"1ubq": ubq, "6bft": bft}.get(which)
+    if atoms is None:
+        atoms = F.all_cases(ubq.view(O.ATOM_DTYPE))[which].view(A.ATOM_DTYPE)
+    a = A.Packed(atoms).arrays()
+    assert len(a["res_chain_key"]) == a["n_residues"] == len(a["res_res_ordinal"])
+    assert np.array_equal(a["res_chain_key"][a["res_id"]], a["chain_key"])
+    assert np.array_equal(a["res_res_ordinal"][a["res_id"]], a["res_ordinal"])
