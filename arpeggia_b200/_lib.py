@@ -59,7 +59,7 @@ class Structure(C.Structure):
         ("ring_center", _F64P), ("ring_normal", _F64P),
         ("ring_attr", _U32P), ("ring_chain_key", _U32P), ("ring_res_ordinal", _U32P),
         ("bbox_min", C.c_double * 3), ("bbox_max", C.c_double * 3), ("has_bbox", C.c_int32), ("reserved_", C.c_int32),
-        ("res_chain_key", _U32P), ("res_res_ordinal", _U32P),
+        ("res_chain_key", _U32P), ("res_res_ordinal", _U32P), ("res_atom_begin", _U32P),
     ]
 
 

@@ -86,6 +86,7 @@ struct arp_ctx {
   DBuf<double> x, y, z, hx, hy, hz, ring_c, ring_n;
   DBuf<uint32_t> attr, chain_key, res_ordinal, res_id, res_h_begin, ring_attr, ring_chain_key, ring_res_ordinal;
   DBuf<uint32_t> res_chain_key, res_res_ordinal;  // compact per-residue form of chain_key / res_ordinal
+  DBuf<uint32_t> res_atom_begin;                  // CSR of the residues' atoms (res_id is expanded from it on the device)
   bool per_residue_keys = false;                  // every structure of the job came with it
   DBuf<int32_t> res_cb, res_sg;
   DBuf<uint32_t> atom_struct, ring_struct;
@@ -262,7 +263,27 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
   std::vector<int64_t> res_adj(res_begin.begin(), res_begin.end() - 1), atom_adj(c->atom_begin.begin(), c->atom_begin.end() - 1),
       h_adj(h_begin.begin(), h_begin.end() - 1);
   const bool multi = n > 1;
-  upload_concat(c, c->res_id, s, n, [](const arp_structure* t) { return t->res_id; }, nat, 0, multi ? &res_adj : nullptr, false);
+  bool expand_res_id = c->n_res > 0;
+  for (int64_t k = 0; k < n; ++k)
+    if (!s[k]->res_atom_begin) expand_res_id = false;
+  if (expand_res_id) {
+    // like res_h_begin below: every structure contributes its first n_residues offsets, the tail closes the CSR
+    upload_concat(c, c->res_atom_begin, s, n, [](const arp_structure* t) { return t->res_atom_begin; }, nrs, 1, multi ? &atom_adj : nullptr, false);
+    const uint32_t tail = (uint32_t)c->n_atoms;
+    CK(cudaStreamSynchronize(c->stream));
+    c->stage.need(64);
+    std::memcpy(c->stage.p, &tail, 4);
+    CK(cudaMemcpyAsync(c->res_atom_begin.p + c->n_res, c->stage.p, 4, cudaMemcpyDefault, c->stream));
+    c->res_id.need(std::max<int64_t>(c->n_atoms, 1));
+    if (c->n_atoms > 0) {
+      k_expand_res_id<<<(unsigned)((c->n_atoms + 255) / 256), 256, 0, c->stream>>>(c->res_atom_begin.p, (uint32_t)c->n_res, (uint32_t)c->n_atoms, c->res_id.p);
+      CK(cudaGetLastError());
+    }
+  } else {
+    for (int64_t k = 0; k < n; ++k)
+      if (s[k]->n_atoms > 0 && !s[k]->res_id) throw arp::Error{ARP_ERR_ARG, "structure has neither res_id nor res_atom_begin"};
+    upload_concat(c, c->res_id, s, n, [](const arp_structure* t) { return t->res_id; }, nat, 0, multi ? &res_adj : nullptr, false);
+  }
   upload_concat(c, c->res_cb, s, n, [](const arp_structure* t) { return t->res_cb; }, nrs, 0, multi ? &atom_adj : nullptr, true);
   upload_concat(c, c->res_sg, s, n, [](const arp_structure* t) { return t->res_sg; }, nrs, 0, multi ? &atom_adj : nullptr, true);
   // res_h_begin: n_res + 1 entries; each structure contributes its first n_residues offsets, the tail closes the CSR

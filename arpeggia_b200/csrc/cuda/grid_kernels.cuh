@@ -227,6 +227,20 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_lookback(uint32_t* __rest
   }
 }
 
+// res_id from the residues' atom ranges (arp_structure.res_atom_begin): one thread per atom, binary search in the
+// L2-resident CSR
+__global__ void __launch_bounds__(256) k_expand_res_id(const uint32_t* __restrict__ res_atom_begin, uint32_t n_res, uint32_t n_atoms,
+                                                       uint32_t* __restrict__ res_id) {
+  const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= n_atoms) return;
+  uint32_t lo = 0, hi = n_res;  // largest r with begin[r] <= a
+  while (hi - lo > 1u) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (res_atom_begin[mid] <= a) lo = mid; else hi = mid;
+  }
+  res_id[a] = lo;
+}
+
 // Pass 2 of the counting sort: write the cell-sorted records.  The atom that arrived first in a cell also
 // publishes the cell as a work item of the pair kernel.
 __global__ void __launch_bounds__(256)

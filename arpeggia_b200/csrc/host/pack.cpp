@@ -503,6 +503,18 @@ void Packed::finish() {
   }
   t.res_chain_key = res_chain_key.data();
   t.res_res_ordinal = res_res_ordinal.data();
+  // atoms_with_hierarchy() order keeps the atoms of a residue together: res_id as a CSR (left out if it ever does not)
+  t.res_atom_begin = nullptr;
+  {
+    bool grouped = true;
+    for (size_t a = 1; a < res_id.size() && grouped; ++a) grouped = res_id[a] == res_id[a - 1] || res_id[a] == res_id[a - 1] + 1;
+    if (grouped && (res_id.empty() || (res_id.front() == 0 && (size_t)res_id.back() + 1 == res_cb.size()))) {
+      res_atom_begin.assign(res_cb.size() + 1, 0u);
+      for (uint32_t r : res_id) res_atom_begin[r + 1] += 1;
+      for (size_t r = 0; r < res_cb.size(); ++r) res_atom_begin[r + 1] += res_atom_begin[r];
+      t.res_atom_begin = res_atom_begin.data();
+    }
+  }
   // bounding-box hint for the cell-grid layout (verified on the device)
   t.has_bbox = 0;
   if (!x.empty()) {

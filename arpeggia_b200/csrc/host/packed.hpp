@@ -14,6 +14,7 @@ struct Packed {
   std::vector<double> x, y, z, hx, hy, hz, ring_c, ring_n;
   std::vector<uint32_t> attr, chain_key, res_ordinal, res_id, res_h_begin, ring_attr, ring_chain_key, ring_res_ordinal;
   std::vector<uint32_t> res_chain_key, res_res_ordinal;  // per residue (compact form of chain_key / res_ordinal)
+  std::vector<uint32_t> res_atom_begin;                  // CSR of the residues' atoms (compact form of res_id)
   std::vector<int32_t> res_cb, res_sg;
   arp_structure s{};
 

@@ -116,6 +116,10 @@ typedef struct arp_structure {
    * PCIe, a fifth of the upload. */
   const uint32_t* res_chain_key;
   const uint32_t* res_res_ordinal;
+  /* Optional: the atoms of residue r are [res_atom_begin[r], res_atom_begin[r+1]) (n_residues+1 entries; true for
+   * atoms_with_hierarchy() order).  When given, res_id is not read (may be NULL): the device expands it -- another
+   * 4 bytes per atom that stay off PCIe. */
+  const uint32_t* res_atom_begin;
 } arp_structure;
 
 #define ARP_FLAG_EMIT_RADIUS_SCREEN 0x1u /* screen atom pairs at min(dist_cutoff, largest distance at which any

@@ -255,7 +255,7 @@ def test_per_atom_and_per_residue_keys_same_rows(ctx, bft):
     p = A.Packed(bft)
     want = ctx.contacts_rows(p, 0.1, 6.5)  # per-residue form
     s = _lib.Structure.from_buffer_copy(p.structure)
-    s.res_chain_key = s.res_res_ordinal = None
+    s.res_chain_key = s.res_res_ordinal = s.res_atom_begin = None
     got = ctx.contacts_rows([ctypes.pointer(s)], 0.1, 6.5)
     key = ["from", "to", "label"]
     assert np.array_equal(np.sort(got["rows"], order=key), np.sort(want["rows"], order=key))

@@ -172,3 +172,6 @@ def test_per_residue_keys_expand_to_the_per_atom_arrays(which, ubq, bft):
     assert len(a["res_chain_key"]) == a["n_residues"] == len(a["res_res_ordinal"])
     assert np.array_equal(a["res_chain_key"][a["res_id"]], a["chain_key"])
     assert np.array_equal(a["res_res_ordinal"][a["res_id"]], a["res_ordinal"])
+    b = a["res_atom_begin"]  # res_id as a CSR
+    assert b is not None and b[0] == 0 and b[-1] == a["n_atoms"]
+    assert np.array_equal(np.repeat(np.arange(a["n_residues"], dtype=np.uint32), np.diff(b.astype(np.int64))), a["res_id"])
