@@ -14,8 +14,9 @@
 
 namespace arpd {
 
-constexpr int RS_TILE_ROUNDS = 16;               // elements per warp tile = 32 lanes x 32 rounds
-constexpr int RS_TILE = 32 * RS_TILE_ROUNDS;     // the sort is stable because a tile is walked in order by ONE warp
+// A tile (32 lanes x `rounds` elements) is walked in order by ONE warp: that is what makes a pass stable without any
+// block-level synchronisation.  `rounds` grows with the input (host: rs_rounds) so that the digit-major histogram and
+// the scattered runs stay coarse when the rows no longer fit L2.
 constexpr int RS_WARPS = 8, RS_THREADS = 32 * RS_WARPS;
 
 struct KeyLayout {  // bit position of the least significant bit of every field, widths; total <= 128
@@ -97,7 +98,7 @@ __device__ __forceinline__ uint32_t rs_digit(unsigned long long lo, unsigned lon
 // One counting pass = k_rsort_hist -> exclusive scan of hist (k_scan_lookback) -> k_rsort_scatter.
 // hist is digit-major: hist[d * n_tiles + tile], so its flat exclusive scan is the first output slot of (digit, tile).
 __global__ void __launch_bounds__(RS_THREADS) k_rsort_hist(const unsigned long long* __restrict__ klo, const unsigned long long* __restrict__ khi,
-                                                           uint32_t n, int shift, uint32_t n_tiles, uint32_t* __restrict__ hist) {
+                                                           uint32_t n, int shift, uint32_t n_tiles, int rounds, uint32_t* __restrict__ hist) {
   __shared__ uint32_t sh[RS_WARPS][256];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   for (int d = lane; d < 256; d += 32) sh[wid][d] = 0u;
@@ -106,9 +107,9 @@ __global__ void __launch_bounds__(RS_THREADS) k_rsort_hist(const unsigned long l
   if (tile >= n_tiles) return;
   const unsigned long long* src = shift < 64 ? klo : khi;
   const int s = shift & 63;
-  const uint32_t base = tile * RS_TILE;
+  const uint32_t base = tile * (uint32_t)(32 * rounds);
 #pragma unroll 8
-  for (int r = 0; r < RS_TILE_ROUNDS; ++r) {
+  for (int r = 0; r < rounds; ++r) {
     const uint32_t e = base + 32u * r + lane;
     if (e < n) atomicAdd(&sh[wid][(uint32_t)(src[e] >> s) & 255u], 1u);
   }
@@ -119,14 +120,14 @@ __global__ void __launch_bounds__(RS_THREADS) k_rsort_hist(const unsigned long l
 __global__ void __launch_bounds__(RS_THREADS) k_rsort_scatter(const unsigned long long* __restrict__ klo_in, const unsigned long long* __restrict__ khi_in,
                                                               const uint32_t* __restrict__ idx_in, unsigned long long* __restrict__ klo_out,
                                                               unsigned long long* __restrict__ khi_out, uint32_t* __restrict__ idx_out, uint32_t n,
-                                                              int shift, uint32_t n_tiles, const uint32_t* __restrict__ hist) {
+                                                              int shift, uint32_t n_tiles, int rounds, const uint32_t* __restrict__ hist) {
   __shared__ uint32_t offs[RS_WARPS][256];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const uint32_t tile = blockIdx.x * RS_WARPS + wid;
   if (tile >= n_tiles) return;
   for (int d = lane; d < 256; d += 32) offs[wid][d] = hist[(size_t)d * n_tiles + tile];
   __syncwarp();
-  const uint32_t base = tile * RS_TILE;
+  const uint32_t base = tile * (uint32_t)(32 * rounds);
   const uint32_t lt = (1u << lane) - 1u;
   // software pipeline: the next round's loads are in flight while this round is ranked
   uint32_t e = base + lane;
@@ -137,11 +138,11 @@ __global__ void __launch_bounds__(RS_THREADS) k_rsort_scatter(const unsigned lon
     if (khi_in) hi = khi_in[e];
     id = idx_in[e];
   }
-  for (int r = 0; r < RS_TILE_ROUNDS; ++r) {
+  for (int r = 0; r < rounds; ++r) {
     const uint32_t e_n = e + 32u;
     unsigned long long lo_n = 0ull, hi_n = 0ull;
     uint32_t id_n = 0u;
-    if (r + 1 < RS_TILE_ROUNDS && e_n < n) {
+    if (r + 1 < rounds && e_n < n) {
       lo_n = klo_in[e_n];
       if (khi_in) hi_n = khi_in[e_n];
       id_n = idx_in[e_n];
