@@ -25,9 +25,12 @@ out = {"atoms": int(st["n_atoms"]), "copies": copies, "rows": int(len(res["rows"
 # up to the contacts between neighbouring copies; every row's distance is within the cutoff; no duplicate (from, to, label)
 rows = res["rows"]
 assert (rows["distance"] <= 6.5 + 1e-6).all() or ((rows["from"] >> 31) & 1).any()
-key = (rows["from"].astype(np.uint64) << 37) | (rows["to"].astype(np.uint64) << 5) | rows["label"].astype(np.uint64)
-out["duplicate_rows"] = int(len(key) - len(np.unique(key)))
-ctx.frame(p)
-t0 = time.perf_counter(); fr = ctx.frame(p); out["s_frame_wall"] = time.perf_counter() - t0
-out["frame_stats"] = fr["frame_stats"]; out["frame_rows"] = int(fr["n_rows"])
+if copies <= 2000:
+    key = (rows["from"].astype(np.uint64) << 37) | (rows["to"].astype(np.uint64) << 5) | rows["label"].astype(np.uint64)
+    out["duplicate_rows"] = int(len(key) - len(np.unique(key)))
+out["label_histogram"] = np.bincount(rows["label"], minlength=19).tolist()
+if copies <= 2000:
+    ctx.frame(p)
+    t0 = time.perf_counter(); fr = ctx.frame(p); out["s_frame_wall"] = time.perf_counter() - t0
+    out["frame_stats"] = fr["frame_stats"]; out["frame_rows"] = int(fr["n_rows"])
 print(json.dumps(out))

@@ -263,3 +263,49 @@ def test_per_atom_and_per_residue_keys_same_rows(ctx, bft):
     with pytest.raises(A.ArpeggiaError) as e:
         ctx.contacts_rows([ctypes.pointer(s)], 0.1, 6.5)
     assert e.value.code == 8
+
+
+def test_config4_batch_of_1000_complexes(ctx, bft):
+    """BASELINE config 4 at a tenth of its size (scratch/batch.py runs the 10 000): one arp_contacts_batch job; a
+    structure's rows in the batch are exactly the rows of that structure alone, the counters add up."""
+    from arpeggia_b200 import synth
+
+    packs = [A.Packed(synth.jittered_complex(bft, k), "/", flags=2) for k in range(1000)]
+    res = ctx.contacts_rows(packs, 0.1, 6.5)
+    parts = A.split_rows(res)
+    assert len(parts) == 1000 and sum(len(p) for p in parts) == len(res["rows"])
+    key = ["from", "to", "label"]
+    total_in = 0
+    for k in (0, 1, 499, 998, 999):
+        single = ctx.contacts_rows(packs[k], 0.1, 6.5)
+        assert np.array_equal(np.sort(parts[k], order=key), np.sort(single["rows"], order=key)), k
+        total_in += single["pairs_in_cutoff"]
+    assert abs(res["pairs_in_cutoff"] / 1000 - total_in / 5) < 0.01 * total_in / 5  # jitter moves a few pairs across the cutoff
+
+
+def test_config5_100m_atoms_properties(ctx, bft):
+    """BASELINE config 5 at full size on ONE GPU: 6bft tiled 16 x 32 x 24 = 100 515 840 atoms.  The copies sit more than
+    dist_cutoff apart, so every counter must be exactly 12 288 times the single-structure value (size-independent
+    property; the oracle would need minutes and the table gigabytes)."""
+    import psutil
+    import torch
+    from arpeggia_b200 import synth
+
+    if psutil.virtual_memory().total < 100 << 30 or torch.cuda.get_device_properties(0).total_memory < 100 << 30:
+        pytest.skip("needs ~60 GB of host memory and ~30 GB of HBM")
+    p1 = A.Packed(bft)
+    one = ctx.contacts_rows(p1, 0.1, 6.5)
+    n_at, n_rg = p1.structure.n_atoms, p1.structure.n_rings
+    copies = 16 * 32 * 24
+    p = A.Packed(synth.assembly_100m(bft), "/", flags=2)
+    assert p.arrays(copy=False)["n_atoms"] == 100515840
+    res = ctx.contacts_rows(p, 0.1, 6.5)
+    del p
+    assert len(res["rows"]) == copies * len(one["rows"]) == copies * 7236
+    assert res["pairs_in_cutoff"] == copies * one["pairs_in_cutoff"] == copies * 396474
+    assert np.array_equal(np.bincount(res["rows"]["label"], minlength=19), copies * np.bincount(one["rows"]["label"], minlength=19))
+    # every copy's rows are the single structure's rows shifted by the copy's atom / ring offset
+    rows = res["rows"]
+    ring = (rows["from"] >> 31) == 1
+    copy_of = np.where(ring, (rows["from"] & 0x7FFFFFFF) // n_rg, rows["from"] // n_at)
+    assert np.array_equal(np.bincount(copy_of, minlength=copies), np.full(copies, 7236))
