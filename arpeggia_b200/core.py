@@ -111,7 +111,10 @@ class Packed:
 
     def close(self):
         if getattr(self, "_h", None):
-            lib().arph_packed_free(self._h)
+            try:
+                lib().arph_packed_free(self._h)
+            except Exception:  # interpreter teardown
+                pass
             self._h = None
 
     __del__ = close
@@ -230,7 +233,10 @@ class Context:
 
     def close(self):
         if getattr(self, "_h", None):
-            lib().arp_ctx_destroy(self._h)
+            try:
+                lib().arp_ctx_destroy(self._h)
+            except Exception:  # interpreter teardown: the module globals are already gone
+                pass
             self._h = None
 
     __del__ = close
