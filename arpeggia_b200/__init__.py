@@ -9,11 +9,11 @@ C ABI in include/arpeggia_cuda.h; there is no CPU fallback.
 from __future__ import annotations
 
 from ._lib import ArpeggiaError, ATOM_DTYPE, LABELS, ROW_DTYPE
-from .core import COLUMNS, Context, Packed, default_context, load_atoms, parse_pdb, read_table, split_rows
+from .core import COLUMNS, Context, Packed, default_context, load_atoms, parse_cif, parse_pdb, read_table, split_rows
 from .frame import to_arrow, to_frame
 
 __version__ = "0.1.0"
-__all__ = ["contacts", "Context", "Packed", "ArpeggiaError", "parse_pdb", "load_atoms", "to_arrow", "to_frame", "COLUMNS"]
+__all__ = ["contacts", "Context", "Packed", "ArpeggiaError", "parse_pdb", "parse_cif", "load_atoms", "to_arrow", "to_frame", "COLUMNS"]
 
 
 def contacts(input_file: str, groups: str = "/", vdw_comp: float = 0.1, dist_cutoff: float = 6.5,

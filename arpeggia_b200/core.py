@@ -24,12 +24,11 @@ COLUMNS = (
 )
 
 
-def parse_pdb(path) -> np.ndarray:
-    """ATOM/HETATM records of a PDB file as a structured array (ATOM_DTYPE)."""
+def _parse_with(fn_name: str, path) -> np.ndarray:
     L = lib()
     p = C.c_void_p()
     n = C.c_int64()
-    check(L.arph_parse_pdb(os.fspath(path).encode(), C.byref(p), C.byref(n)))
+    check(getattr(L, fn_name)(os.fspath(path).encode(), C.byref(p), C.byref(n)))
     try:
         if n.value == 0:
             return np.zeros(0, dtype=ATOM_DTYPE)
@@ -39,14 +38,19 @@ def parse_pdb(path) -> np.ndarray:
         L.arph_free(p)
 
 
-def load_atoms(path) -> np.ndarray:
-    """pdbtbx-style dispatch on the file extension (src/utils.rs:51-57)."""
-    ext = os.path.splitext(os.fspath(path))[1].lower()
-    if ext in (".cif", ".mmcif"):
-        from .mmcif import parse_mmcif
+def parse_pdb(path) -> np.ndarray:
+    """ATOM/HETATM records of a PDB file as a structured array (ATOM_DTYPE)."""
+    return _parse_with("arph_parse_pdb", path)
 
-        return parse_mmcif(path)
-    return parse_pdb(path)
+
+def parse_cif(path) -> np.ndarray:
+    """The _atom_site loop of an mmCIF file as a structured array (ATOM_DTYPE)."""
+    return _parse_with("arph_parse_cif", path)
+
+
+def load_atoms(path) -> np.ndarray:
+    """pdbtbx-style dispatch on the file extension (src/utils.rs:51-57): .cif / .mmcif -> mmCIF, else PDB."""
+    return _parse_with("arph_parse_file", path)
 
 
 class Packed:

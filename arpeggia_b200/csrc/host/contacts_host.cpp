@@ -62,7 +62,7 @@ int arph_contacts_file(arp_ctx* ctx, const char* path, const char* groups, doubl
   *out = nullptr;
   arp_atom_record* recs = nullptr;
   int64_t n = 0;
-  int rc = arph_parse_pdb(path, &recs, &n);
+  int rc = arph_parse_file(path, &recs, &n);
   if (rc != ARP_OK) return rc;
   rc = arph_contacts(ctx, recs, n, groups, vdw_comp, dist_cutoff, ignore_zero_occupancy, flags, out);
   arph_free(recs);

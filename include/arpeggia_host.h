@@ -3,7 +3,7 @@
  *
  * Mirrors the reference's host functions for this path (same argument meaning and error behaviour):
  *
- *   arph_parse_pdb        <->  pdbtbx ReadOptions{only_atomic_coords, Loose}.read()   src/utils.rs:53-57
+ *   arph_parse_pdb / _cif / _file <-> pdbtbx ReadOptions{only_atomic_coords, Loose}.read()   src/utils.rs:53-57
  *   arph_pack             <->  load_model residue filter                              src/utils.rs:60
  *                              optional zero-occupancy filter                         src/python.rs:45-47
  *                              InteractionComplex::new (parse_groups, build_residue_index,
@@ -68,6 +68,11 @@ const char* arph_last_error(void);
 
 /* Fixed-column PDB reader (ATOM / HETATM / MODEL). *out is malloc'd; release with arph_free. */
 int  arph_parse_pdb(const char* path, arp_atom_record** out, int64_t* n);
+/* mmCIF: the _atom_site loop (author chain / residue numbers where present).  pdbtbx's own column choice is not
+ * under /root/reference: parity unpinned. */
+int  arph_parse_cif(const char* path, arp_atom_record** out, int64_t* n);
+/* Dispatch on the extension like pdbtbx (src/utils.rs:51-57): .cif / .mmcif -> mmCIF, anything else -> PDB. */
+int  arph_parse_file(const char* path, arp_atom_record** out, int64_t* n);
 void arph_free(void* p);
 
 /* Packed structure: hierarchy + device SoA + the dictionaries needed to decode rows. */

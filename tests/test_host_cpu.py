@@ -1,4 +1,5 @@
 """Host side of the product (parser, packer, plane fit, table builder) against the oracle.  CPU only."""
+import os
 import collections
 
 import numpy as np
@@ -175,3 +176,87 @@ def test_per_residue_keys_expand_to_the_per_atom_arrays(which, ubq, bft):
     b = a["res_atom_begin"]  # res_id as a CSR
     assert b is not None and b[0] == 0 and b[-1] == a["n_atoms"]
     assert np.array_equal(np.repeat(np.arange(a["n_residues"], dtype=np.uint32), np.diff(b.astype(np.int64))), a["res_id"])
+
+
+CIF_COLS = ["group_PDB", "id", "type_symbol", "label_atom_id", "label_alt_id", "label_comp_id", "label_asym_id", "label_entity_id",
+            "label_seq_id", "pdbx_PDB_ins_code", "Cartn_x", "Cartn_y", "Cartn_z", "occupancy", "B_iso_or_equiv", "pdbx_formal_charge",
+            "auth_seq_id", "auth_comp_id", "auth_asym_id", "auth_atom_id", "pdbx_PDB_model_num"]
+
+
+def write_cif(atoms, path, model=1):
+    """A PDBx/mmCIF file the way the PDB writes them: label_* and auth_* identifiers differ (waters get their own label
+    chain and no label_seq_id), a quoted value and a text field precede the _atom_site loop."""
+    def q(b):
+        s = b.decode().strip()
+        return "." if not s else (f'"{s}"' if ("'" in s or " " in s) else s)
+
+    out = ["data_TEST", "#", "_entry.id TEST", "_struct.title 'a title with loop_ and _atom_site.fake inside quotes'", "#",
+           "loop_", "_citation.id", "_citation.title", "primary", ";A multi-line", "text field with loop_ at its start", ";", "#",
+           "loop_"] + [f"_atom_site.{c}" for c in CIF_COLS]
+    for k, a in enumerate(atoms):
+        hoh = a["resn"] == b"HOH"
+        label_asym = "W" if hoh else {"A": "A"}.get(a["chain"].decode(), "L" + a["chain"].decode())
+        out.append(" ".join([
+            "HETATM" if a["hetero"] else "ATOM", str(int(a["serial"])), q(a["element"]).title() if a["element"] else "?", q(a["name"]),
+            q(a["altloc"]), q(a["resn"]), label_asym, "1", "." if hoh else str(k // 7 + 1), q(a["icode"]).replace(".", "?"),
+            f"{a['x']:.3f}", f"{a['y']:.3f}", f"{a['z']:.3f}", f"{a['occupancy']:.2f}", "10.00", "?", str(int(a["resi"])), q(a["resn"]),
+            q(a["chain"]), q(a["name"]), str(model)]))
+    out.append("#")
+    out += ["loop_", "_pdbx_after.id", "_pdbx_after.value", "1 x", "2 y", "#"]
+    path.write_text("\n".join(out) + "\n")
+
+
+@pytest.mark.parametrize("which", ["1ubq", "6bft", "altloc", "insertion"])
+def test_mmcif_reader_gives_the_pdb_readers_records(which, ubq, bft, tmp_path):
+    """arph_parse_cif (pdbtbx reads mmCIF by extension, utils.rs:51-57): the _atom_site loop of a file
+    written PDB-style parses to the records the fixed-column reader gives for the same atoms."""
+    from tests import fixtures as F
+
+    atoms = {"1ubq": ubq, "6bft": bft}.get(which)
+    if atoms is None:
+        atoms = F.all_cases(ubq.view(O.ATOM_DTYPE))[which].view(A.ATOM_DTYPE)
+    p = tmp_path / "s.cif"
+    write_cif(atoms, p)
+    got = A.parse_cif(p)
+    assert len(got) == len(atoms)
+    for f in ("x", "y", "z", "occupancy", "serial", "resi", "chain", "resn", "name", "element", "altloc", "icode", "hetero"):
+        assert np.array_equal(got[f], atoms[f]), f
+    assert (got["model"] == 1).all()
+    assert np.array_equal(A.load_atoms(p), got)  # dispatch on the extension
+    q = tmp_path / "s.pdb1"
+    q.write_bytes(open(os.path.join(os.path.dirname(__file__), "data", "1ubq.pdb"), "rb").read())
+    assert len(A.load_atoms(q)) == 660  # anything else is read as PDB
+    # same packed structure -> same contacts, whatever the format
+    a, b = A.Packed(atoms).arrays(), A.Packed(got).arrays()
+    for k in ("x", "attr", "chain_key", "res_ordinal", "res_id", "ring_center", "ring_normal"):
+        assert np.array_equal(a[k], b[k]), k
+
+
+def test_mmcif_tokenizer_edge_cases(tmp_path):
+    p = tmp_path / "t.cif"
+    p.write_text("""data_X
+loop_
+_atom_site.group_PDB
+_atom_site.id
+_atom_site.label_atom_id
+_atom_site.label_comp_id
+_atom_site.label_asym_id
+_atom_site.label_seq_id
+_atom_site.Cartn_x
+_atom_site.Cartn_y
+_atom_site.Cartn_z
+ATOM 1 "O5'" ALA A 1 1.0 2.0 3.0 # trailing comment
+ATOM 2 'C"x' ALA
+A 1 -1.5e0 +2.25 3
+HETATM 3 O HOH B . 0 0 0
+_other.tag value
+""")
+    got = A.parse_cif(p)
+    assert [n.decode() for n in got["name"]] == ["O5'", 'C"x', "O"]
+    assert got["x"].tolist() == [1.0, -1.5, 0.0] and got["y"].tolist() == [2.0, 2.25, 0.0]
+    assert got["hetero"].tolist() == [0, 0, 1] and got["resi"].tolist() == [1, 1, 0] and got["chain"].tolist() == [b"A", b"A", b"B"]
+    assert got["element"].tolist() == [b"O", b"C", b"O"]  # no type_symbol: from the atom name
+    bad = tmp_path / "bad.cif"
+    bad.write_text("data_X\nloop_\n_atom_site.id\n_atom_site.Cartn_x\n1 2.0\n")
+    with pytest.raises(A.ArpeggiaError):
+        A.parse_cif(bad)
