@@ -66,25 +66,35 @@ def n_res(s: dict) -> int:
 
 
 def extract(s: dict, res_mask: torch.Tensor) -> dict:
-    """Sub-structure made of the residues selected by `res_mask` (whole residues: atoms, hydrogens, rings)."""
+    """Sub-structure made of the residues selected by `res_mask` (whole residues: atoms, hydrogens, rings).
+    Index lists are built once (four host syncs for their sizes) and every array is gathered with index_select."""
     dev = s["x"].device
     amask = res_mask[s["res_id"]]
     res_new = torch.cumsum(res_mask.to(torch.int64), 0) - 1
     atom_new = torch.cumsum(amask.to(torch.int64), 0) - 1
-    out = {k: s[k][amask] for k in ("x", "y", "z", "attr", "chain_key", "res_ordinal", "gid")}
-    out["res_id"] = res_new[s["res_id"][amask]]
+    aidx = torch.nonzero(amask).squeeze(1)
+    ridx = torch.nonzero(res_mask).squeeze(1)
+    out = {k: s[k].index_select(0, aidx) for k in ("x", "y", "z", "attr", "chain_key", "res_ordinal", "gid")}
+    out["res_id"] = res_new[s["res_id"].index_select(0, aidx)]
     for k in ("res_cb", "res_sg"):
-        v = s[k][res_mask]
+        v = s[k].index_select(0, ridx)
         out[k] = torch.where(v >= 0, atom_new[v.clamp(min=0)], v)
     counts = (s["h_begin"][1:] - s["h_begin"][:-1])
-    hmask = torch.repeat_interleave(res_mask, counts) if counts.numel() else torch.zeros(0, dtype=torch.bool, device=dev)
-    for k in ("hx", "hy", "hz"):
-        out[k] = s[k][hmask]
-    out["h_begin"] = torch.cat([torch.zeros(1, dtype=torch.int64, device=dev), torch.cumsum(counts[res_mask], 0)])
-    rmask = res_mask[s["ring_res"]] if s["ring_res"].numel() else torch.zeros(0, dtype=torch.bool, device=dev)
+    if s["hx"].numel():
+        hidx = torch.nonzero(torch.repeat_interleave(res_mask, counts)).squeeze(1)
+        for k in ("hx", "hy", "hz"):
+            out[k] = s[k].index_select(0, hidx)
+    else:
+        for k in ("hx", "hy", "hz"):
+            out[k] = s[k][:0]
+    out["h_begin"] = torch.cat([torch.zeros(1, dtype=torch.int64, device=dev), torch.cumsum(counts.index_select(0, ridx), 0)])
+    if s["ring_res"].numel():
+        gidx = torch.nonzero(res_mask[s["ring_res"]]).squeeze(1)
+    else:
+        gidx = torch.zeros(0, dtype=torch.int64, device=dev)
     for k in ("ring_c", "ring_n", "ring_attr", "ring_chain_key", "ring_res_ordinal", "ring_gid"):
-        out[k] = s[k][rmask]
-    out["ring_res"] = res_new[s["ring_res"][rmask]]
+        out[k] = s[k].index_select(0, gidx)
+    out["ring_res"] = res_new[s["ring_res"].index_select(0, gidx)]
     return out
 
 
@@ -188,12 +198,13 @@ def exchange_halos(own: dict, width: float, group=None) -> tuple[dict, dict]:
     if world == 1:
         return own, info
     # every rank's actual x-range of owned atoms (residues stick out of their slab)
-    has = own["x"].numel() > 0
-    mine = torch.tensor([float(own["x"].min()) if has else float("inf"), float(own["x"].max()) if has else float("-inf")],
-                        dtype=torch.float64, device=dev)
+    if own["x"].numel() > 0:
+        mine = torch.stack([own["x"].min(), own["x"].max()]).to(torch.float64)  # stays on the device: no host sync here
+    else:
+        mine = torch.tensor([float("inf"), float("-inf")], dtype=torch.float64, device=dev)
     ranges = [torch.zeros(2, dtype=torch.float64, device=dev) for _ in range(world)]
     dist.all_gather(ranges, mine, group=group)
-    ranges = [(float(r[0]), float(r[1])) for r in ranges]
+    ranges = [(r[0], r[1]) for r in torch.stack(ranges).cpu().tolist()]  # one sync for every rank's range
     sends = {}
     for peer in range(world):
         if peer == rank or ranges[peer][0] > ranges[peer][1]:
