@@ -248,21 +248,32 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
                 const uint32_t* __restrict__ attr, const uint32_t* __restrict__ chain_key, const uint32_t* __restrict__ res_ordinal,
                 const uint32_t* __restrict__ res_id, const uint32_t* __restrict__ res_chain_key, const uint32_t* __restrict__ res_res_ordinal,
                 const uint32_t* __restrict__ atom_struct, const StructDesc* __restrict__ descs, const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of, const uint32_t* __restrict__ cell_start,
-                uint32_t n, double edge, RecA* __restrict__ recA, RecB* __restrict__ recB, Item* __restrict__ items,
+                uint32_t n, double edge, double inv_edge, RecA* __restrict__ recA, RecB* __restrict__ recB, Item* __restrict__ items,
                 uint32_t* __restrict__ cations, Counters* __restrict__ ctr) {
+  // slots in `items` / `cations` are reserved per BLOCK (shared-memory counters, one global atomicAdd each): the 110 000
+  // same-address atomics of a one-per-cell reservation were 40 % of this kernel's stall samples
+  __shared__ uint32_t s_items, s_cat, s_items_base, s_cat_base;
+  if (threadIdx.x == 0) s_items = s_cat = 0u;
+  __syncthreads();
   const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
-  if (a >= n) return;
-  const uint32_t s = atom_struct ? atom_struct[a] : 0u;
+  const bool valid = a < n;
+  const int lane = threadIdx.x & 31;
+  const uint32_t lt = (1u << lane) - 1u;
+  uint32_t s = 0u, c = 0u, r = 1u, slot = 0u, w = 0u;
+  double px = 0.0;
+  double py = 0.0, pz = 0.0;
+  if (valid) {
+  s = atom_struct ? atom_struct[a] : 0u;
   const StructDesc& d = descs[s];
-  const uint32_t c = cell_of[a], r = rank_of[a];
-  const uint32_t slot = cell_start[c] + r;
-  const double px = x[a], py = y[a], pz = z[a];
+  c = cell_of[a], r = rank_of[a];
+  slot = cell_start[c] + r;
+  px = x[a], py = y[a], pz = z[a];
   RecA ra;
   ra.x = (float)(px - d.ox);
   ra.y = (float)(py - d.oy);
   ra.z = (float)(pz - d.oz);
   // bit 31 of the sorted attribute word (internal): the atom may start a row / counts as `from` (complex.rs:200-202)
-  const uint32_t w = attr[a] & 0x7fffffffu;
+  w = attr[a] & 0x7fffffffu;
   ra.attr = w | (((w & ARP_ATTR_LIGAND) && (w & ARP_ATTR_ELEM_MASK) && !(w & ARP_ATTR_GHOST)) ? 0x80000000u : 0u);
   ra.res_id = res_id[a];
   // per-atom arrays, or the compact per-residue form (arp_structure.res_chain_key): the residue tables are L2-resident
@@ -277,12 +288,33 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
   rb.chain_key = ra.chain_key;
   rb.res_ordinal = ra.res_ordinal;
   recB[slot] = rb;
-  // the few atoms that can make a cation-pi contact (aromatic.rs:18) are listed for the ring kernel
-  if (w & ARP_ATTR_POS_RES) cations[atomicAdd(&ctr->n_cations, 1u)] = slot;
-  if (r == 0) {  // first arrival publishes the cell as a work item: its half shell as 5 runs of sorted slots
-    const uint32_t local = c - d.cell_base;
+  }
+  // the few atoms that can make a cation-pi contact (aromatic.rs:18) are listed for the ring kernel; the first arrival
+  // of a cell publishes the cell as a work item
+  const bool is_cat = valid && (w & ARP_ATTR_POS_RES), first = valid && r == 0u;
+  uint32_t my_cat = 0u, my_item = 0u;
+  {
+    const uint32_t bc = __ballot_sync(0xffffffffu, is_cat), bi = __ballot_sync(0xffffffffu, first);
+    uint32_t wc = 0u, wi = 0u;
+    if (lane == 0) {
+      if (bc) wc = atomicAdd(&s_cat, (uint32_t)__popc(bc));
+      if (bi) wi = atomicAdd(&s_items, (uint32_t)__popc(bi));
+    }
+    my_cat = __shfl_sync(0xffffffffu, wc, 0) + __popc(bc & lt);
+    my_item = __shfl_sync(0xffffffffu, wi, 0) + __popc(bi & lt);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    s_cat_base = s_cat ? atomicAdd(&ctr->n_cations, s_cat) : 0u;
+    s_items_base = s_items ? atomicAdd(&ctr->n_items, s_items) : 0u;
+  }
+  __syncthreads();
+  if (is_cat) cations[s_cat_base + my_cat] = slot;
+  if (first) {  // the cell's half shell as 5 runs of sorted slots
+    const StructDesc& d = descs[s];
     const int nx = d.nx, ny = d.ny, nz = d.nz;
-    const int ix = (int)(local % (uint32_t)nx), iy = (int)((local / (uint32_t)nx) % (uint32_t)ny), iz = (int)(local / ((uint32_t)nx * (uint32_t)ny));
+    // the cell coordinates from the position, exactly as k_cell_assign computed them (no integer divisions)
+    const int ix = cell_coord(px, d.ox, inv_edge, nx), iy = cell_coord(py, d.oy, inv_edge, ny), iz = cell_coord(pz, d.oz, inv_edge, nz);
     Item it;
     it.cb = cell_start[c];
     it.n_own = cell_start[c + 1] - it.cb;
@@ -308,7 +340,7 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
     it.cy = (float)(((double)iy + 0.5) * edge);
     it.cz = (float)(((double)iz + 0.5) * edge);
     it.pad = 0;
-    items[atomicAdd(&ctr->n_items, 1u)] = it;
+    items[s_items_base + my_item] = it;
   }
 }
 
