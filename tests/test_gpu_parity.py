@@ -309,3 +309,30 @@ def test_config5_100m_atoms_properties(ctx, bft):
     ring = (rows["from"] >> 31) == 1
     copy_of = np.where(ring, (rows["from"] & 0x7FFFFFFF) // n_rg, rows["from"] // n_at)
     assert np.array_equal(np.bincount(copy_of, minlength=copies), np.full(copies, 7236))
+
+
+def test_frame_argument_errors(ctx, ubq, bft):
+    """arp_stage_frame refuses what it cannot describe: batch jobs, tables of another structure, rows outside the tables."""
+    import ctypes as C
+    from arpeggia_b200 import _lib
+
+    L = _lib.lib()
+    pu, pb = A.Packed(ubq), A.Packed(bft)
+    tu = C.POINTER(_lib.FrameTables)()
+    _lib.check(L.arph_packed_frame_tables(pu._h, C.byref(tu)))
+    fp = C.POINTER(_lib.Frame)()
+    ctx.upload([pu, pb])
+    ctx.run(0.1, 6.5)
+    assert L.arp_stage_frame(ctx._h, tu, C.byref(fp)) == 8 and not fp  # a frame belongs to one structure
+    ctx.upload(pb)
+    ctx.run(0.1, 6.5)
+    assert L.arp_stage_frame(ctx._h, tu, C.byref(fp)) == 8 and not fp  # 1ubq's tables for 6bft's rows
+    ctx.upload(pu)
+    ctx.run(0.1, 6.5)
+    bad = _lib.FrameTables.from_buffer_copy(tu.contents)
+    bad.n_sides = 3  # rows reference sides beyond the table: caught on the device, no out-of-bounds read
+    assert L.arp_stage_frame(ctx._h, C.byref(bad), C.byref(fp)) == 8 and not fp
+    assert b"outside the frame tables" in L.arp_last_error(ctx._h)
+    _lib.check(L.arp_stage_frame(ctx._h, tu, C.byref(fp)), ctx._h)  # and the context is still usable
+    assert fp.contents.n_rows == 532
+    L.arp_frame_free(ctx._h, fp)
