@@ -125,7 +125,10 @@ k_cell_assign(const double* __restrict__ px, const double* __restrict__ py, cons
 
 // ---- exclusive scan of the cell counts (in place) ------------------------------------------------------------
 constexpr int SCAN_THREADS = 256;
-constexpr int SCAN_PER_THREAD = 8;
+#ifndef SCAN_PT
+#define SCAN_PT 8
+#endif
+constexpr int SCAN_PER_THREAD = SCAN_PT;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_PER_THREAD;
 
 __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* total) {
