@@ -62,3 +62,20 @@ def test_no_cpu_fallback():
     atoms = A.parse_pdb(ROOT / "tests" / "data" / "1ubq.pdb")
     rc = L.arph_contacts(None, atoms.ctypes.data, len(atoms), b"/", 0.1, 6.5, 0, 0, C.byref(tp))
     assert rc == 9 and b"no CPU fallback" in L.arph_last_error()
+
+
+def test_rust_bindings_declare_the_device_abi():
+    """bindings/rust/arpeggia-cuda-sys cannot be compiled here (no Rust toolchain): keep it in step with the header by
+    text -- every function of arpeggia_cuda.h is declared, every struct has the header's field count."""
+    text = (ROOT / "bindings" / "rust" / "arpeggia-cuda-sys" / "src" / "lib.rs").read_text()
+    header = (ROOT / "include" / "arpeggia_cuda.h").read_text()
+    funcs = set(re.findall(r"\b(arp_[a-z0-9_]+)\s*\(", header))
+    assert len(funcs) >= 19
+    for name in funcs:
+        assert re.search(rf"pub fn {name}\(", text), f"{name} missing from the Rust bindings"
+    for struct, ctype in (("arp_structure", _lib.Structure), ("arp_params", _lib.Params), ("arp_result", _lib.Result),
+                          ("arp_stats", _lib.Stats), ("arp_frame_side", _lib.FrameSide), ("arp_frame_tables", _lib.FrameTables),
+                          ("arp_frame", _lib.Frame)):
+        body = re.search(rf"pub struct {struct} \{{(.*?)\n\}}", text, re.S).group(1)
+        rust_fields = re.findall(r"pub (\w+):", body)
+        assert rust_fields == [f for f, _ in ctype._fields_], struct
