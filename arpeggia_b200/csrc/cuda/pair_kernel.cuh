@@ -229,6 +229,21 @@ __device__ __forceinline__ FilterOut filter_phase2(const PairArgs& G, const DevP
   return r;
 }
 
+// what phase 1 reads of a queue entry: the first half of both 32-byte records and (chain key, ordinal) of the second
+struct FilterGather {
+  uint4 a0, b0;
+  uint2 a1, b1;
+};
+__device__ __forceinline__ void filter_gather(const PairArgs& G, const uint2 e, FilterGather& g) {
+  if (e.x == Q_SENTINEL) return;
+  const uint4* pa = reinterpret_cast<const uint4*>(G.recA + e.x);
+  const uint4* pb = reinterpret_cast<const uint4*>(G.recA + e.y);
+  g.a0 = pa[0];
+  g.b0 = pb[0];
+  g.a1 = *reinterpret_cast<const uint2*>(pa + 1);
+  g.b1 = *reinterpret_cast<const uint2*>(pb + 1);
+}
+
 __global__ void __launch_bounds__(CLS_THREADS, 4) k_filter(const PairArgs G, const DevParams P) {
   __shared__ float lim2[256];  // per element-class pair: (max(cov sum, vdW sum) + |comp|)^2 + g, rounded up
   __shared__ uint2 stash1[CLS_WARPS][64];  // phase-1 survivors waiting for a full warp (carry-over < 32 + one trip)
@@ -245,21 +260,27 @@ __global__ void __launch_bounds__(CLS_THREADS, 4) k_filter(const PairArgs G, con
   const bool counting = P.count_in_cutoff != 0;
   const uint32_t lt = (1u << lane) - 1u;
   unsigned long long base = ((unsigned long long)blockIdx.x * CLS_WARPS + wid) * 32ull;
-  // The only dependent memory round trip of a trip is the gather: the queue entry is read one trip ahead and the
-  // output atomic is paid once per 32 survivors.  The trip after the last one flushes the stashes.
-  uint2 e_next = make_uint2(Q_SENTINEL, Q_SENTINEL);
-  if (base + lane < n_pairs) e_next = __ldcs(G.pairq + base + lane);  // streamed once: keep the atom records in L2 instead
+  // No dependent memory round trip inside a trip: the queue entry is read two trips ahead, the records of its two atoms
+  // are gathered one trip ahead (the loads fly while the current trip computes), and the output atomic is paid once per
+  // 32 survivors.  The trip after the last one flushes the stashes.
+  FilterGather g_next{};
+  uint2 e_gath = make_uint2(Q_SENTINEL, Q_SENTINEL), e_next = make_uint2(Q_SENTINEL, Q_SENTINEL);
+  if (base + lane < n_pairs) e_gath = __ldcs(G.pairq + base + lane);  // streamed once: keep the atom records in L2 instead
+  if (base + stride + lane < n_pairs) e_next = __ldcs(G.pairq + base + stride + lane);
+  filter_gather(G, e_gath, g_next);
   while (true) {
     const bool last = base >= n_pairs;
-    const uint2 e = e_next;
+    const uint2 e = e_gath;
+    const FilterGather g = g_next;
+    e_gath = e_next;
     e_next = make_uint2(Q_SENTINEL, Q_SENTINEL);
-    if (base + stride + lane < n_pairs) e_next = __ldcs(G.pairq + base + stride + lane);
+    if (base + 2ull * stride + lane < n_pairs) e_next = __ldcs(G.pairq + base + 2ull * stride + lane);
+    filter_gather(G, e_gath, g_next);
     // ---- phase 1 ----------------------------------------------------------------------------------------------------
     bool keep = false;
     if (!last && e.x != Q_SENTINEL) {  // sentinel: past the end, or the unused tail of a k_screen queue window
-      const uint4* pa = reinterpret_cast<const uint4*>(G.recA + e.x);
-      const uint4* pb = reinterpret_cast<const uint4*>(G.recA + e.y);
-      const uint4 a0 = pa[0], a1 = pa[1], b0 = pb[0], b1 = pb[1];  // position + attr | chain key, ordinal, ...
+      const uint4 a0 = g.a0, b0 = g.b0;  // position + attr
+      const uint2 a1 = g.a1, b1 = g.b1;  // chain key, ordinal
       const float dx = __uint_as_float(b0.x) - __uint_as_float(a0.x), dy = __uint_as_float(b0.y) - __uint_as_float(a0.y),
                   dz = __uint_as_float(b0.z) - __uint_as_float(a0.z);
       const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));

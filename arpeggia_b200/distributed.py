@@ -209,6 +209,8 @@ def exchange_halos(own: dict, width: float, group=None) -> tuple[dict, dict]:
     for peer in range(world):
         if peer == rank or ranges[peer][0] > ranges[peer][1]:
             continue
+        if ranges[peer][0] - width > ranges[rank][1] or ranges[peer][1] + width < ranges[rank][0]:
+            continue  # not a neighbour: nothing of mine reaches into its range (ranges are already on the host)
         sel = halo_selection(own, ranges[peer][0] - width, ranges[peer][1] + width)
         sends[peer] = serialize(extract(own, sel))
     # sizes first (every pair of ranks talks, mostly empty), then the payloads
