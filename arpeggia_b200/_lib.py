@@ -60,6 +60,7 @@ class Structure(C.Structure):
         ("ring_attr", _U32P), ("ring_chain_key", _U32P), ("ring_res_ordinal", _U32P),
         ("bbox_min", C.c_double * 3), ("bbox_max", C.c_double * 3), ("has_bbox", C.c_int32), ("reserved_", C.c_int32),
         ("res_chain_key", _U32P), ("res_res_ordinal", _U32P), ("res_atom_begin", _U32P),
+        ("x_milli", _I32P), ("y_milli", _I32P), ("z_milli", _I32P),
     ]
 
 

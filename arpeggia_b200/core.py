@@ -97,6 +97,8 @@ class Packed:
         for k in ("res_chain_key", "res_res_ordinal"):
             out[k] = view(getattr(s, k), s.n_residues, np.uint32)
         out["res_atom_begin"] = view(s.res_atom_begin, s.n_residues + 1, np.uint32) if s.res_atom_begin else None
+        for k in ("x_milli", "y_milli", "z_milli"):  # on-lattice form of the coordinates, None when a coordinate is off it
+            out[k] = view(getattr(s, k), s.n_atoms, np.int32) if getattr(s, k) else None
         for k in ("ring_center", "ring_normal"):
             out[k] = view(getattr(s, k), 3 * s.n_rings, np.float64).reshape(-1, 3)
         for k in ("ring_attr", "ring_chain_key", "ring_res_ordinal"):

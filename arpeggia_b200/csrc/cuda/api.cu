@@ -76,7 +76,7 @@ struct HBuf {
 struct arp_ctx {
   int device = 0;
   int sm_count = 148;
-  int occ_screen = 1, occ_filter = 1, occ_exact = 1;  // resident CTAs per SM (grids are sized to one full wave)
+  int occ_screen = 1, occ_filter = 1, occ_exact = 1, occ_screen_atoms = 1;  // resident CTAs per SM (grids are sized to one full wave)
   cudaStream_t stream = nullptr;
   cudaStream_t side = nullptr;  // k_rings runs here, concurrently with the pair kernels (forked / joined with events)
   std::string err;
@@ -89,6 +89,7 @@ struct arp_ctx {
   DBuf<uint32_t> res_atom_begin;                  // CSR of the residues' atoms (res_id is expanded from it on the device)
   bool per_residue_keys = false;                  // every structure of the job came with it
   DBuf<int32_t> res_cb, res_sg;
+  DBuf<int32_t> xm, ym, zm;                       // on-lattice coordinates as uploaded (arp_structure.x_milli)
   DBuf<uint32_t> atom_struct, ring_struct;
   DBuf<StructDesc> descs;
   std::vector<StructDesc> h_descs;
@@ -102,6 +103,7 @@ struct arp_ctx {
   DBuf<uint32_t> cell_of, rank_of, cell_start;
   DBuf<unsigned long long> scan_status, rscan_status;
   DBuf<uint32_t> rcell_of, rrank_of, rcell_start, rperm, cations;
+  DBuf<uint32_t> slot_item;  // sorted slot -> work item of its cell (k_screen_atoms)
   DBuf<RecA> recA;
   DBuf<RecB> recB;
   DBuf<Item> items;
@@ -252,9 +254,25 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
   auto nrg3 = [](const arp_structure* t) { return 3 * t->n_rings; };
   auto nh = [](const arp_structure* t) { return t->n_h; };
 #define UP(buf, field, lenf) upload_concat(c, c->buf, s, n, [](const arp_structure* t) { return t->field; }, lenf, 0, nullptr, false)
-  UP(x, x, nat);
-  UP(y, y, nat);
-  UP(z, z, nat);
+  bool milli = c->n_atoms > 0;
+  for (int64_t k = 0; k < n; ++k)
+    if (!s[k]->x_milli || !s[k]->y_milli || !s[k]->z_milli) milli = false;
+  if (milli) {  // on-lattice coordinates: half the bytes over PCIe, f64 rebuilt here
+    UP(xm, x_milli, nat);
+    UP(ym, y_milli, nat);
+    UP(zm, z_milli, nat);
+    c->x.need(c->n_atoms);
+    c->y.need(c->n_atoms);
+    c->z.need(c->n_atoms);
+    k_expand_milli<<<(unsigned)((c->n_atoms + 255) / 256), 256, 0, c->stream>>>(c->xm.p, c->ym.p, c->zm.p, (uint32_t)c->n_atoms, c->x.p, c->y.p, c->z.p);
+    CK(cudaGetLastError());
+  } else {
+    for (int64_t k = 0; k < n; ++k)
+      if (s[k]->n_atoms > 0 && (!s[k]->x || !s[k]->y || !s[k]->z)) throw arp::Error{ARP_ERR_ARG, "structure has neither x / y / z nor x_milli / y_milli / z_milli"};
+    UP(x, x, nat);
+    UP(y, y, nat);
+    UP(z, z, nat);
+  }
   UP(attr, attr, nat);
   c->per_residue_keys = true;
   for (int64_t k = 0; k < n; ++k)

@@ -244,6 +244,18 @@ __global__ void __launch_bounds__(256) k_expand_res_id(const uint32_t* __restric
   res_id[a] = lo;
 }
 
+// f64 coordinates from the on-lattice form (arp_structure.x_milli): one IEEE division per coordinate, the correctly
+// rounded double of the decimal v/1000 -- what the packer verified against the parsed value bit for bit
+__global__ void __launch_bounds__(256) k_expand_milli(const int32_t* __restrict__ xm, const int32_t* __restrict__ ym,
+                                                      const int32_t* __restrict__ zm, uint32_t n_atoms, double* __restrict__ x,
+                                                      double* __restrict__ y, double* __restrict__ z) {
+  const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= n_atoms) return;
+  x[a] = __ddiv_rn((double)xm[a], 1000.0);
+  y[a] = __ddiv_rn((double)ym[a], 1000.0);
+  z[a] = __ddiv_rn((double)zm[a], 1000.0);
+}
+
 // Pass 2 of the counting sort: write the cell-sorted records.  The atom that arrived first in a cell also
 // publishes the cell as a work item of the pair kernel.
 __global__ void __launch_bounds__(256)
@@ -252,7 +264,7 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
                 const uint32_t* __restrict__ res_id, const uint32_t* __restrict__ res_chain_key, const uint32_t* __restrict__ res_res_ordinal,
                 const uint32_t* __restrict__ atom_struct, const StructDesc* __restrict__ descs, const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of, const uint32_t* __restrict__ cell_start,
                 uint32_t n, double edge, double inv_edge, RecA* __restrict__ recA, RecB* __restrict__ recB, Item* __restrict__ items,
-                uint32_t* __restrict__ cations, Counters* __restrict__ ctr) {
+                uint32_t* __restrict__ cations, Counters* __restrict__ ctr, uint32_t* __restrict__ slot_item) {
   // slots in `items` / `cations` are reserved per BLOCK (shared-memory counters, one global atomicAdd each): the 110 000
   // same-address atomics of a one-per-cell reservation were 40 % of this kernel's stall samples
   __shared__ uint32_t s_items, s_cat, s_items_base, s_cat_base;
@@ -344,6 +356,9 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
     it.cz = (float)(((double)iz + 0.5) * edge);
     it.pad = 0;
     items[s_items_base + my_item] = it;
+    // k_screen_atoms (one lane per atom) finds its cell's half shell through this
+    if (slot_item)
+      for (uint32_t k = 0; k < it.n_own; ++k) slot_item[it.cb + k] = s_items_base + my_item;
   }
 }
 

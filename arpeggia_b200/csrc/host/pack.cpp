@@ -14,6 +14,7 @@
 // (name, altloc) within a residue, blank-altloc atoms appended to every other conformer of the residue;
 // SURVEY.md 8.2) is rebuilt with interned strings and flat index vectors.
 #include <algorithm>
+#include <cmath>
 #include <array>
 #include <map>
 #include <set>
@@ -513,6 +514,32 @@ void Packed::finish() {
       for (uint32_t r : res_id) res_atom_begin[r + 1] += 1;
       for (size_t r = 0; r < res_cb.size(); ++r) res_atom_begin[r + 1] += res_atom_begin[r];
       t.res_atom_begin = res_atom_begin.data();
+    }
+  }
+  // on-lattice form of the coordinates (arp_structure.x_milli): offered only when EVERY coordinate is bit for bit the
+  // double (double)v / 1000.0 of a 32-bit v -- true for anything read from PDB fixed columns -- so the device rebuilds the
+  // same f64 values from half the bytes
+  t.x_milli = t.y_milli = t.z_milli = nullptr;
+  {
+    bool lattice = !x.empty();
+    for (int a = 0; a < 3 && lattice; ++a) {
+      const std::vector<double>& v = a == 0 ? x : (a == 1 ? y : z);
+      std::vector<int32_t>& m = a == 0 ? x_milli : (a == 1 ? y_milli : z_milli);
+      m.resize(v.size());
+      for (size_t k = 0; k < v.size(); ++k) {
+        const double q = v[k] * 1000.0;
+        if (!(q > -2147483000.0 && q < 2147483000.0)) { lattice = false; break; }
+        const int32_t r = (int32_t)std::llrint(q);
+        if ((double)r / 1000.0 != v[k] || (r == 0 && std::signbit(v[k]))) { lattice = false; break; }
+        m[k] = r;
+      }
+    }
+    if (lattice) {
+      t.x_milli = x_milli.data();
+      t.y_milli = y_milli.data();
+      t.z_milli = z_milli.data();
+    } else {
+      x_milli.clear(), y_milli.clear(), z_milli.clear();
     }
   }
   // bounding-box hint for the cell-grid layout (verified on the device)

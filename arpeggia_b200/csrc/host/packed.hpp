@@ -16,6 +16,7 @@ struct Packed {
   std::vector<uint32_t> res_chain_key, res_res_ordinal;  // per residue (compact form of chain_key / res_ordinal)
   std::vector<uint32_t> res_atom_begin;                  // CSR of the residues' atoms (compact form of res_id)
   std::vector<int32_t> res_cb, res_sg;
+  std::vector<int32_t> x_milli, y_milli, z_milli;        // on-lattice form of x / y / z (empty when a coordinate is off the lattice)
   arp_structure s{};
 
   // decode side: one ResConf per (residue, conformer) = one ResidueId of the reference (residues.rs:7-21)

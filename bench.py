@@ -136,7 +136,8 @@ def pinned_structure(A, packed):
     # chain_key / res_ordinal travel in their compact per-residue form (arp_structure.res_chain_key); the per-atom
     # arrays stay NULL and are neither copied here nor uploaded
     # ... and res_id as the residues' atom ranges (res_atom_begin)
-    sizes = {"x": 8, "y": 8, "z": 8, "attr": 4}
+    # ... and the coordinates on the 0.001 A lattice (x_milli) when the packer offers that form: 12 instead of 24 B / atom
+    sizes = {"x_milli": 4, "y_milli": 4, "z_milli": 4, "attr": 4} if src.x_milli else {"x": 8, "y": 8, "z": 8, "attr": 4}
     n, nr, ng, nh = src.n_atoms, src.n_residues, src.n_rings, src.n_h
     lens = {**{k: n * s for k, s in sizes.items()}, "res_chain_key": 4 * nr, "res_res_ordinal": 4 * nr, "res_atom_begin": 4 * (nr + 1), "res_h_begin": 4 * (nr + 1), "h_x": 8 * nh, "h_y": 8 * nh, "h_z": 8 * nh,
             "res_cb": 4 * nr, "res_sg": 4 * nr, "ring_center": 24 * ng, "ring_normal": 24 * ng, "ring_attr": 4 * ng,

@@ -68,6 +68,9 @@ pub struct arp_structure {
     pub res_chain_key: *const u32,
     pub res_res_ordinal: *const u32,
     pub res_atom_begin: *const u32,
+    pub x_milli: *const i32,
+    pub y_milli: *const i32,
+    pub z_milli: *const i32,
 }
 
 #[repr(C)]

@@ -120,6 +120,15 @@ typedef struct arp_structure {
    * atoms_with_hierarchy() order).  When given, res_id is not read (may be NULL): the device expands it -- another
    * 4 bytes per atom that stay off PCIe. */
   const uint32_t* res_atom_begin;
+  /* Optional on-lattice form of the atom coordinates: integer thousandths of an angstrom, the resolution of a PDB
+   * fixed-column field (columns 31-54, "%8.3f").  The coordinate is (double)v / 1000.0 with one IEEE division -- the
+   * correctly rounded double of the decimal v/1000, i.e. the value a correctly rounded parser returns for that field.
+   * When ALL THREE are given, x / y / z are not read (may be NULL) and the device rebuilds the f64 coordinates itself:
+   * 12 instead of 24 bytes per atom over PCIe.  The packer only offers this form after checking every coordinate of
+   * the structure against that identity bit for bit; hydrogens (h_*) and ring planes stay f64. */
+  const int32_t* x_milli;
+  const int32_t* y_milli;
+  const int32_t* z_milli;
 } arp_structure;
 
 #define ARP_FLAG_EMIT_RADIUS_SCREEN 0x1u /* screen atom pairs at min(dist_cutoff, largest distance at which any

@@ -265,6 +265,56 @@ def test_per_atom_and_per_residue_keys_same_rows(ctx, bft):
     assert e.value.code == 8
 
 
+def test_lattice_coordinates_same_rows(ctx, bft):
+    """x / y / z as f64, or on the 0.001 A lattice as int32 (arp_structure.x_milli, what the packer offers for anything
+    read from PDB columns): the device rebuilds the same doubles, rows and counters are identical."""
+    from arpeggia_b200 import _lib
+
+    p = A.Packed(bft)
+    assert p.structure.x_milli and p.structure.y_milli and p.structure.z_milli
+    a = p.arrays()
+    for k in "xyz":
+        assert np.array_equal(a[k + "_milli"] / 1000.0, a[k])  # one IEEE division gives back the parsed double
+    s = _lib.Structure.from_buffer_copy(p.structure)
+    s.x = s.y = s.z = None  # only the lattice form
+    lat = ctx.contacts_rows([ctypes.pointer(s)], 0.1, 6.5)
+    s = _lib.Structure.from_buffer_copy(p.structure)
+    s.x_milli = s.y_milli = s.z_milli = None  # only f64
+    f64 = ctx.contacts_rows([ctypes.pointer(s)], 0.1, 6.5)
+    key = ["from", "to", "label", "distance"]
+    assert np.array_equal(np.sort(lat["rows"], order=key), np.sort(f64["rows"], order=key))
+    assert lat["pairs_in_cutoff"] == f64["pairs_in_cutoff"] == 396474
+    s.x = None
+    with pytest.raises(A.ArpeggiaError) as e:
+        ctx.contacts_rows([ctypes.pointer(s)], 0.1, 6.5)
+    assert e.value.code == 8
+
+
+def test_emit_radius_screen_rows_at_scale(ctx, bft):
+    """ARP_FLAG_EMIT_RADIUS_SCREEN (k_screen_atoms, cells at r_emit): the same rows as the default screen on config 3,
+    on interpenetrating copies (crowded cells), on a batch job and for parameters that move r_emit."""
+    from arpeggia_b200 import synth
+
+    key = ["from", "to", "label", "distance"]
+
+    def same(packed, comp=0.1, rc=6.5):
+        a = ctx.contacts_rows(packed, comp, rc, flags=0)
+        b = ctx.contacts_rows(packed, comp, rc, flags=1)
+        assert len(a["rows"]) == len(b["rows"]) > 0
+        assert np.array_equal(np.sort(a["rows"], order=key), np.sort(b["rows"], order=key))
+        return a, b
+
+    a, b = same(A.Packed(synth.assembly_1m(bft), "/", flags=2))
+    assert len(a["rows"]) == 904500 and b["pairs_in_cutoff"] == -1 and b["pairs_screened"] < a["pairs_screened"] / 2
+    same(A.Packed(synth.tile(bft, 2, 2, 2, pitch=(20.0, 15.0, 10.0)), "/", flags=2))
+    same([A.Packed(synth.jittered_complex(bft, k), "/", flags=2) for k in range(7)] + [A.Packed(bft)])
+    p = A.Packed(bft)
+    for comp, rc in [(0.3, 5.0), (1.0, 6.5), (0.1, 12.5), (0.1, 4.6), (0.0, 3.0)]:
+        same(p, comp, rc)
+    for groups in ["A,B/G", "H,L/", "A/A"]:
+        same(A.Packed(bft, groups))
+
+
 def test_config4_batch_of_1000_complexes(ctx, bft):
     """BASELINE config 4 at a tenth of its size (scratch/batch.py runs the 10 000): one arp_contacts_batch job; a
     structure's rows in the batch are exactly the rows of that structure alone, the counters add up."""

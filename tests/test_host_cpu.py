@@ -178,6 +178,25 @@ def test_per_residue_keys_expand_to_the_per_atom_arrays(which, ubq, bft):
     assert np.array_equal(np.repeat(np.arange(a["n_residues"], dtype=np.uint32), np.diff(b.astype(np.int64))), a["res_id"])
 
 
+def test_lattice_form_of_the_coordinates(ubq, bft):
+    """arp_structure.x_milli: offered only when (double)v / 1000.0 reproduces every coordinate bit for bit."""
+    from arpeggia_b200 import synth
+
+    for atoms in (ubq, bft, synth.tile(bft, 2, 1, 1), synth.jittered_complex(bft, 3)):
+        a = A.Packed(atoms, "/", flags=2).arrays()
+        for k in "xyz":
+            m = a[k + "_milli"]
+            assert m is not None and m.dtype == np.int32
+            assert np.array_equal((m.astype(np.float64) / 1000.0).view(np.uint64), a[k].view(np.uint64))
+    off = ubq.copy()
+    off["x"][17] += 1e-7  # one coordinate off the lattice: the form is withdrawn for the whole structure
+    a = A.Packed(off).arrays()
+    assert a["x_milli"] is None and a["y_milli"] is None and a["z_milli"] is None
+    neg0 = ubq.copy()
+    neg0["z"][3] = -0.0  # "-0.000" parses to -0.0, which 0 / 1000.0 does not give back
+    assert A.Packed(neg0).arrays()["z_milli"] is None
+
+
 CIF_COLS = ["group_PDB", "id", "type_symbol", "label_atom_id", "label_alt_id", "label_comp_id", "label_asym_id", "label_entity_id",
             "label_seq_id", "pdbx_PDB_ins_code", "Cartn_x", "Cartn_y", "Cartn_z", "occupancy", "B_iso_or_equiv", "pdbx_formal_charge",
             "auth_seq_id", "auth_comp_id", "auth_asym_id", "auth_atom_id", "pdbx_PDB_model_num"]
