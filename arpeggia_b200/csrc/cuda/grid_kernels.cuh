@@ -264,7 +264,8 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
                 const uint32_t* __restrict__ res_id, const uint32_t* __restrict__ res_chain_key, const uint32_t* __restrict__ res_res_ordinal,
                 const uint32_t* __restrict__ atom_struct, const StructDesc* __restrict__ descs, const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of, const uint32_t* __restrict__ cell_start,
                 uint32_t n, double edge, double inv_edge, RecA* __restrict__ recA, RecB* __restrict__ recB, Item* __restrict__ items,
-                uint32_t* __restrict__ cations, Counters* __restrict__ ctr, uint32_t* __restrict__ slot_item) {
+                uint32_t* __restrict__ cations, Counters* __restrict__ ctr, uint32_t* __restrict__ slot_item,
+                float* __restrict__ pos2, uint2* __restrict__ skey) {
   // slots in `items` / `cations` are reserved per BLOCK (shared-memory counters, one global atomicAdd each): the 110 000
   // same-address atomics of a one-per-cell reservation were 40 % of this kernel's stall samples
   __shared__ uint32_t s_items, s_cat, s_items_base, s_cat_base;
@@ -303,6 +304,11 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
   rb.chain_key = ra.chain_key;
   rb.res_ordinal = ra.res_ordinal;
   recB[slot] = rb;
+  if (pos2) {  // what k_screen_atoms reads: positions interleaved per slot PAIR (x0 x1 | y0 y1 | z0 z1 | pad: 32 bytes), keys per slot
+    float* q = pos2 + 8u * (size_t)(slot >> 1) + (slot & 1u);
+    q[0] = ra.x, q[2] = ra.y, q[4] = ra.z;
+    skey[slot] = make_uint2(ra.chain_key, ra.res_ordinal);
+  }
   }
   // the few atoms that can make a cation-pi contact (aromatic.rs:18) are listed for the ring kernel; the first arrival
   // of a cell publishes the cell as a work item

@@ -782,118 +782,237 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_screen(const 
 // warp-per-cell screen above then spends nine tenths of its instructions on per-cell bookkeeping (measured: 0.195 ms for
 // 47 M tests against 0.155 ms for 119 M at dist_cutoff).  Here nothing is staged: a warp takes 32 consecutive sorted slots
 // (atoms of 6-9 neighbouring cells), each lane walks the five runs of ITS cell's half shell -- run 0 from its own slot + 1,
-// so every unordered pair is tested once -- and reads the candidates' 16-byte position records straight through L1 (lanes
-// of a cell read the same addresses: broadcasts).  No in-cutoff counting in this mode, so a test is the plain f32
-// difference form k_filter uses (same operations, same value): one load, 3 FADD, FMUL + 2 FFMA, one compare against the
-// from-atom's own largest label limit.  A hit reads (chain key, ordinal) of the candidate and drops the pairs no
-// orientation of should_compare_entities can pass (same chain, ordinals <= 1 apart, complex.rs:112-113: two hits in
-// three), the rest goes to the pair queue through a per-warp window (ballot + popc, one atomicAdd per SA_WINDOW entries).
+// so every unordered pair is tested once.  Candidates are read two at a time from the pair-interleaved position array
+// (x0 x1 | y0 y1 | z0 z1 | pad, 32 bytes per slot pair, written by k_scatter_atoms): a 16- and an 8-byte load through L1 (lanes of a cell read the
+// same addresses: broadcasts) feed packed f32x2 arithmetic -- 3 add, 1 mul, 2 fma for TWO tests, the same operations in the
+// same order as k_filter's difference form, so the same value -- and one compare each against the from-atom's own largest
+// label limit (no in-cutoff counting in this mode).  A hit appends the candidate's slot to a per-lane list in shared
+// memory (a predicated store and add: no vote, no atomic in the loop).  Every SA_ROUND trips the warp checks the lists;
+// a flush drops the pairs no orientation of should_compare_entities can pass (same chain, ordinals <= 1 apart,
+// complex.rs:112-113: two hits in three), and writes the rest to the pair queue through a per-warp window (warp prefix
+// sum, one atomicAdd per SA_WINDOW entries).
 constexpr int SA_THREADS = 256;
 constexpr int SA_WARPS = SA_THREADS / 32;
-constexpr uint32_t SA_WINDOW = 256;
+constexpr uint32_t SA_WINDOW = 512;
+#ifndef SA_BUF_N
+#define SA_BUF_N 16
+#endif
+#ifndef SA_ROUND_N
+#define SA_ROUND_N 4
+#endif
+constexpr int SA_BUF = SA_BUF_N;      // entries of a lane's hit list
+constexpr int SA_ROUND = SA_ROUND_N;  // trips between two looks at the lists (a trip appends at most 2)
 #ifndef SA_MIN_BLOCKS
 #define SA_MIN_BLOCKS 4
 #endif
-#ifndef SA_UNROLL
-#define SA_UNROLL 2
-#endif
+
+__device__ __forceinline__ unsigned long long sa_add2(unsigned long long a, unsigned long long b) {
+  unsigned long long r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ unsigned long long sa_mul2(unsigned long long a, unsigned long long b) {
+  unsigned long long r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ unsigned long long sa_fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+  unsigned long long r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ unsigned long long sa_dup(float a) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %1};" : "=l"(r) : "f"(a));
+  return r;
+}
+
+constexpr int SA_RUNS = 6;      // rows of a thread's run table: up to 5 non-empty runs + the closing row
+constexpr int SA_STASH1 = 160;  // a warp's residue-filter survivors: carry-over < 32 + four rows of up to 32
+struct SaSmem {
+  float lim1[16];
+  float lim2[256];                                                   // per element-class pair: see k_filter
+  uint32_t run_b[SA_RUNS][SA_THREADS], run_e[SA_RUNS][SA_THREADS];  // every thread's non-empty runs, then the closing row
+  uint32_t hits[SA_BUF][SA_THREADS];                                // per-lane hit lists (candidate slots)
+  uint2 stash1[SA_WARPS][SA_STASH1];                                // (from slot, candidate slot) waiting for a full warp
+  uint2 stash2[SA_WARPS][64];                                       // pairs for k_exact waiting for a full 32-entry flush
+};
+// a warp's carry-over between flushes, tiles and the final drain
+struct SaCarry {
+  int n1, n2;
+  unsigned long long n_q;  // pairs that passed the residue filter (statistics: arp_stats.n_screened_pairs)
+};
+
+// Stage B1 on a warp's stash, exactly k_filter's phase 2 (per-pair label limit, both orientations of the pair filter),
+// 32 pairs at a time; survivors go to the queue of k_exact, one atomicAdd per 32.  drain: also the incomplete last batches.
+__device__ __forceinline__ void sa_filter(const PairArgs& G, const DevParams& P, SaSmem& S, int wid, int lane, SaCarry& K, bool drain) {
+  uint2* s1 = S.stash1[wid];
+  uint2* s2 = S.stash2[wid];
+  const uint32_t lt = (1u << lane) - 1u;
+  uint32_t unused = 0;
+  while (K.n1 >= 32 || (drain && K.n1 > 0)) {
+    const int m = min(K.n1, 32);
+    K.n1 -= m;
+    const FilterOut r = filter_phase2(G, P, S.lim2, s1[K.n1 + (lane < m ? lane : 0)], lane < m, unused);
+    const uint32_t b2 = __ballot_sync(0xffffffffu, r.go);
+    if (r.go) s2[K.n2 + __popc(b2 & lt)] = r.out;
+    K.n2 += __popc(b2);
+    __syncwarp();
+    if (K.n2 >= 32 || (drain && K.n1 == 0 && K.n2 > 0)) {
+      const int k = min(K.n2, 32);
+      unsigned long long w = 0;
+      if (lane == 0) w = atomicAdd(&G.ctr->q2_len, (unsigned long long)k);
+      w = __shfl_sync(0xffffffffu, w, 0) + lane;
+      K.n2 -= k;
+      if (lane < k && w < G.pairq2_cap) __stcs(G.pairq2 + w, s2[K.n2 + lane]);
+      __syncwarp();
+    }
+  }
+  if (drain && K.n2 > 0) {  // nothing was left in the first stash: the loop above did not run
+    unsigned long long w = 0;
+    if (lane == 0) w = atomicAdd(&G.ctr->q2_len, (unsigned long long)K.n2);
+    w = __shfl_sync(0xffffffffu, w, 0) + lane;
+    if (lane < K.n2 && w < G.pairq2_cap) __stcs(G.pairq2 + w, s2[lane]);
+    K.n2 = 0;
+  }
+}
+
+// the hit lists of a warp -> in-chain neighbour filter -> the warp's stash -> sa_filter.  key = (chain key, residue
+// ordinal) per sorted slot.  Entry j of every lane at a time: the survivors of a row are ranked by a ballot.
+__device__ __forceinline__ void sa_flush(const PairArgs& G, const DevParams& P, const uint2* __restrict__ key, SaSmem& S, int tid, int lane,
+                                         uint32_t slot, uint2 mine, uint32_t cnt, SaCarry& K) {
+  const uint32_t maxc = __reduce_max_sync(0xffffffffu, cnt);
+  const uint32_t lt = (1u << lane) - 1u;
+  uint2* s1 = S.stash1[tid >> 5];
+  for (uint32_t j0 = 0; j0 < maxc; j0 += 4u) {  // four gathers in flight
+    uint32_t c[4];
+    uint2 b[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      c[u] = 0u, b[u] = mine;  // "same residue": dropped
+      if (j0 + u < cnt) {
+        c[u] = S.hits[j0 + u][tid];
+        b[u] = key[c[u]];
+      }
+    }
+    int n1 = K.n1;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const bool keep = !(mine.x == b[u].x && (mine.y - b[u].y + 1u) <= 2u);  // not: same chain, |ordinal difference| <= 1
+      const uint32_t m = __ballot_sync(0xffffffffu, keep);
+      if (keep) s1[n1 + __popc(m & lt)] = make_uint2(slot, c[u]);
+      n1 += __popc(m);
+    }
+    K.n_q += (unsigned long long)(n1 - K.n1);
+    K.n1 = n1;
+    __syncwarp();
+    sa_filter(G, P, S, tid >> 5, lane, K, false);
+  }
+}
 
 __global__ void __launch_bounds__(SA_THREADS, SA_MIN_BLOCKS) k_screen_atoms(const PairArgs G, const DevParams P, const uint32_t* __restrict__ slot_item,
+                                                                            const unsigned long long* __restrict__ pos2, const uint2* __restrict__ key,
                                                                             uint32_t n_atoms) {
-  __shared__ float lim1[16];
-  __shared__ uint32_t run_b[4][SA_THREADS], run_e[4][SA_THREADS];  // runs 1..4 of every thread's half shell
+  __shared__ SaSmem S;
   const int lane = threadIdx.x & 31, tid = threadIdx.x;
   if (tid < 16) {
     float m = 0.f;
     for (int eb = 0; eb < 16; ++eb) m = fmaxf(m, class_pair_limit2(P, tid, eb));
-    lim1[tid] = m;
+    S.lim1[tid] = m;
   }
+  for (int k = tid; k < 256; k += SA_THREADS) S.lim2[k] = class_pair_limit2(P, k >> 4, k & 15);
   __syncthreads();
-  const uint32_t lt = (1u << lane) - 1u;
   const uint32_t n_tiles = (n_atoms + 31u) >> 5, n_warps = gridDim.x * SA_WARPS;
-  QWindow Q{0ull, 0ull};
+  SaCarry K{0, 0, 0ull};
   unsigned long long n_tests = 0;
-  const uint4* __restrict__ rec = reinterpret_cast<const uint4*>(G.recA);  // two uint4 per record
+  const uint32_t hp0 = (uint32_t)__cvta_generic_to_shared(&S.hits[0][tid]);
+  const uint32_t rp0 = (uint32_t)__cvta_generic_to_shared(&S.run_b[0][tid]);
+  constexpr uint32_t ROW = 4u * SA_THREADS, B_TO_E = 4u * SA_THREADS * SA_RUNS;  // byte strides of the two tables
   for (uint32_t tile = blockIdx.x * SA_WARPS + (tid >> 5); tile < n_tiles; tile += n_warps) {
     const uint32_t slot = (tile << 5) + lane;
-    bool active = slot < n_atoms;
-    uint32_t s = 0, end = 0, r = 0, ck = 0, ord = 0;
-    float ax = 0.f, ay = 0.f, az = 0.f, tlim = -1.f;
-    if (active) {
-      const uint4 a0 = rec[2 * slot];
-      const uint2 a1 = *reinterpret_cast<const uint2*>(rec + 2 * slot + 1);
+    uint32_t s = 0, rb = 0, re = 0, rp = rp0;
+    uint2 mine = make_uint2(0u, 0u);
+    unsigned long long nax = 0, nay = 0, naz = 0;  // (-x, -x), (-y, -y), (-z, -z) of the from-atom
+    float tlim = -1.f;
+    if (slot < n_atoms) {
+      const uint4 a0 = *reinterpret_cast<const uint4*>(G.recA + slot);
+      mine = key[slot];
       const uint4* ip = reinterpret_cast<const uint4*>(G.items + slot_item[slot]);
       const uint4 i0 = ip[0], off = ip[1], dl = ip[2];  // (cb, n_own, total, sid), off[4], delta[4]
-      ax = __uint_as_float(a0.x), ay = __uint_as_float(a0.y), az = __uint_as_float(a0.z);
-      ck = a1.x, ord = a1.y;
-      tlim = fminf(P.thr_near, atom_limit2(P, lim1, a0.w));  // no label can fire for this atom beyond its own limit
-      s = slot + 1u;
-      end = i0.x + off.x;
-      run_b[0][tid] = off.x + dl.x, run_e[0][tid] = off.y + dl.x;
-      run_b[1][tid] = off.y + dl.y, run_e[1][tid] = off.z + dl.y;
-      run_b[2][tid] = off.z + dl.z, run_e[2][tid] = off.w + dl.z;
-      run_b[3][tid] = off.w + dl.w, run_e[3][tid] = i0.z + dl.w;
-      n_tests += (end - s) + (i0.z - off.x);
-      while (s >= end) {  // skip empty runs
-        if (r == 4u) { active = false; break; }
-        s = run_b[r][tid], end = run_e[r][tid], ++r;
+      nax = sa_dup(-__uint_as_float(a0.x)), nay = sa_dup(-__uint_as_float(a0.y)), naz = sa_dup(-__uint_as_float(a0.z));
+      tlim = fminf(P.thr_near, atom_limit2(P, S.lim1, a0.w));  // no label can fire for this atom beyond its own limit
+      // runs 1..4 first: the lanes of a cell walk them in step (same addresses: one wavefront); run 0 -- the rest of the
+      // own cell and its +x neighbour, from the lane's own slot + 1 -- differs per lane and goes last
+      const uint32_t b5[5] = {off.x + dl.x, off.y + dl.y, off.z + dl.z, off.w + dl.w, slot + 1u};
+      const uint32_t e5[5] = {off.y + dl.x, off.z + dl.y, off.w + dl.z, i0.z + dl.w, i0.x + off.x};
+      uint32_t n = 0;
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        if (b5[k] < e5[k]) {
+          S.run_b[n][tid] = b5[k], S.run_e[n][tid] = e5[k];
+          ++n;
+          n_tests += e5[k] - b5[k];
+        }
+      }
+      S.run_b[n][tid] = 0xffffffffu, S.run_e[n][tid] = 0u;  // the closing row: no s reaches rb or stays below re (s keeps stepping)
+      rb = S.run_b[0][tid], re = S.run_e[0][tid];
+      rp = rp0 + ROW;
+      s = rb & ~1u;
+    } else {
+      rb = 0xffffffffu;
+    }
+    // A lane is active while s < re.  The trips are branch-free (a lane that has finished keeps computing on slot pair 0
+    // and appends nothing), so a round of SA_ROUND trips is straight-line code; the candidates of trip t + 1 are loaded
+    // before trip t computes.
+    uint32_t ld = s < re ? s : 0u;
+    ulonglong2 XY = *reinterpret_cast<const ulonglong2*>(pos2 + 2u * ld);  // slot pair (s, s + 1): 32 bytes
+    unsigned long long Z = pos2[2u * ld + 2u];
+    uint32_t hp = hp0;  // shared-memory address of the next free entry of this lane's hit list
+    while (__any_sync(0xffffffffu, s < re)) {
+#pragma unroll
+      for (int trip = 0; trip < SA_ROUND; ++trip) {
+        // where the next trip reads: two slots on, or the start of the next run
+        uint32_t sn = s + 2u, rbn = rb, ren = re;
+        asm volatile("{\n\t.reg .pred p, q;\n\t"
+                     "setp.lt.u32 q, %6, %2;\n\t"
+                     "setp.ge.and.u32 p, %0, %2, q;\n\t"
+                     "@p ld.shared.u32 %1, [%3];\n\t"
+                     "@p ld.shared.u32 %2, [%3+%4];\n\t"
+                     "@p add.u32 %3, %3, %5;\n\t"
+                     "@p and.b32 %0, %1, 0xfffffffe;\n\t}"
+                     : "+r"(sn), "+r"(rbn), "+r"(ren), "+r"(rp) : "n"(B_TO_E), "n"(ROW), "r"(s) : "memory");
+        ld = sn < ren ? sn : 0u;
+        const ulonglong2 XYn = *reinterpret_cast<const ulonglong2*>(pos2 + 2u * ld);
+        const unsigned long long Zn = pos2[2u * ld + 2u];
+        const unsigned long long dx = sa_add2(XY.x, nax), dy = sa_add2(XY.y, nay), dz = sa_add2(Z, naz);
+        const unsigned long long d2 = sa_fma2(dz, dz, sa_fma2(dy, dy, sa_mul2(dx, dx)));
+        float d0, d1;
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(d2));
+        const uint32_t s1 = s + 1u;
+        // predicated store + add (written in PTX: the compiler otherwise keeps a count and rebuilds the address)
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "setp.le.f32 p, %1, %2;\n\t"
+                     "setp.ge.and.u32 p, %3, %4, p;\n\t"
+                     "@p st.shared.u32 [%0], %3;\n\t"
+                     "@p add.u32 %0, %0, %5;\n\t}"
+                     : "+r"(hp) : "f"(d0), "f"(tlim), "r"(s), "r"(rb), "n"(ROW) : "memory");
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "setp.le.f32 p, %1, %2;\n\t"
+                     "setp.lt.and.u32 p, %3, %4, p;\n\t"
+                     "@p st.shared.u32 [%0], %3;\n\t"
+                     "@p add.u32 %0, %0, %5;\n\t}"
+                     : "+r"(hp) : "f"(d1), "f"(tlim), "r"(s1), "r"(re), "n"(ROW) : "memory");
+        s = sn, rb = rbn, re = ren, XY = XYn, Z = Zn;
+      }
+      if (__any_sync(0xffffffffu, hp > hp0 + (uint32_t)(SA_BUF - 2 * SA_ROUND) * ROW)) {
+        sa_flush(G, P, key, S, tid, lane, slot, mine, (hp - hp0) / ROW, K);
+        hp = hp0;
       }
     }
-    while (__any_sync(0xffffffffu, active)) {
-      bool hit[SA_UNROLL];
-      uint4 b0[SA_UNROLL];
-#pragma unroll
-      for (int u = 0; u < SA_UNROLL; ++u) {
-        hit[u] = active && s + u < end;
-        if (hit[u]) b0[u] = rec[2 * (s + u)];
-      }
-#pragma unroll
-      for (int u = 0; u < SA_UNROLL; ++u) {
-        if (hit[u]) {
-          const float dx = __uint_as_float(b0[u].x) - ax, dy = __uint_as_float(b0[u].y) - ay, dz = __uint_as_float(b0[u].z) - az;
-          const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-          hit[u] = d2 <= tlim;
-          if (hit[u]) {
-            const uint2 b1 = *reinterpret_cast<const uint2*>(rec + 2 * (s + u) + 1);
-            hit[u] = !(ck == b1.x && (ord - b1.y + 1u) <= 2u);  // same chain, |ordinal difference| <= 1
-          }
-        }
-      }
-      uint32_t bal[SA_UNROLL], n = 0;
-#pragma unroll
-      for (int u = 0; u < SA_UNROLL; ++u) {
-        bal[u] = __ballot_sync(0xffffffffu, hit[u]);
-        n += __popc(bal[u]);
-      }
-      if (n) {  // warp-uniform
-        if (Q.pos + n > Q.end) {
-          qwindow_close(G, Q, lane);
-          const unsigned long long need = (unsigned long long)max(n, SA_WINDOW);
-          unsigned long long base = 0;
-          if (lane == 0) base = atomicAdd(&G.ctr->q_len, need);
-          Q.pos = __shfl_sync(0xffffffffu, base, 0);
-          Q.end = Q.pos + need;
-        }
-        if (Q.end <= G.pairq_cap) {
-          uint2* wp = G.pairq + Q.pos;
-#pragma unroll
-          for (int u = 0; u < SA_UNROLL; ++u) {
-            if (hit[u]) __stcs(wp + __popc(bal[u] & lt), make_uint2(slot, s + u));
-            wp += __popc(bal[u]);
-          }
-        }
-        Q.pos += n;
-      }
-      if (active) {
-        s += SA_UNROLL;
-        while (s >= end) {
-          if (r == 4u) { active = false; break; }
-          s = run_b[r][tid], end = run_e[r][tid], ++r;
-        }
-      }
-    }
+    if (__any_sync(0xffffffffu, hp != hp0)) sa_flush(G, P, key, S, tid, lane, slot, mine, (hp - hp0) / ROW, K);
   }
-  qwindow_close(G, Q, lane);
+  sa_filter(G, P, S, tid >> 5, lane, K, true);
+  if (lane == 0 && K.n_q) atomicAdd(&G.ctr->q_len, K.n_q);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) n_tests += __shfl_xor_sync(0xffffffffu, n_tests, o);
   if (lane == 0 && n_tests) atomicAdd(&G.ctr->screened, n_tests);

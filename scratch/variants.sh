@@ -7,5 +7,5 @@ while [ $# -ge 2 ]; do
   out=$PWD/scratch/variants/$name
   mkdir -p $out
   make -s -C arpeggia_b200/csrc -j8 OUT=$out EXTRA="$flags" 2>&1 | grep -i "error" || true
-  grep -A2 "k_pairs" $out/ptxas.log | tail -2 | tr '\n' ' '; echo " <- $name"
+  grep -A2 "k_screen_atoms" $out/ptxas.log | tail -2 | tr '\n' ' '; echo " <- $name"
 done
