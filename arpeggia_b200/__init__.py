@@ -8,7 +8,7 @@ C ABI in include/arpeggia_cuda.h; there is no CPU fallback.
 """
 from __future__ import annotations
 
-from ._lib import ArpeggiaError, ATOM_DTYPE, LABELS, ROW_DTYPE
+from ._lib import ArpeggiaError, ATOM_DTYPE, HOST_FLAG_NO_COUNTERS as FLAG_NO_COUNTERS, LABELS, ROW_DTYPE
 from .core import COLUMNS, Context, Packed, default_context, load_atoms, parse_cif, parse_pdb, read_table, split_rows
 from .frame import to_arrow, to_frame
 
@@ -41,5 +41,7 @@ def contacts(input_file: str, groups: str = "/", vdw_comp: float = 0.1, dist_cut
     """
     del num_threads
     atoms = load_atoms(input_file)
-    table = default_context(device).contacts_table(atoms, groups, float(vdw_comp), float(dist_cutoff), bool(ignore_zero_occupancy))
+    # the reference's DataFrame carries no workload counters: let the device screen at the emit radius (same rows)
+    table = default_context(device).contacts_table(atoms, groups, float(vdw_comp), float(dist_cutoff), bool(ignore_zero_occupancy),
+                                                   flags=FLAG_NO_COUNTERS)
     return to_frame(table)

@@ -33,6 +33,7 @@ FLAG_EMIT_RADIUS_SCREEN = 1
 FLAG_COUNT_CLASSIFIED = 2
 HOST_FLAG_NO_MULTIMODEL_QUIRK = 1
 HOST_FLAG_SKIP_LOAD_FILTER = 2
+HOST_FLAG_NO_COUNTERS = 4
 
 LABELS = [
     "StericClash", "CovalentBond", "Disulfide", "VanDerWaalsContact", "IonicBond", "HydrogenBond",

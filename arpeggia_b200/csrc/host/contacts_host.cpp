@@ -25,7 +25,8 @@ int arph_contacts(arp_ctx* ctx, const arp_atom_record* atoms, int64_t n, const c
   arp_params prm{};
   prm.vdw_comp = vdw_comp;
   prm.dist_cutoff = dist_cutoff;
-  prm.flags = ARP_FLAG_COUNT_CLASSIFIED;  // the table reports both workload counters
+  // the table reports both workload counters, unless the caller only wants the frame the reference returns
+  prm.flags = (flags & ARPH_FLAG_NO_COUNTERS) ? ARP_FLAG_EMIT_RADIUS_SCREEN : ARP_FLAG_COUNT_CLASSIFIED;
   // rows stay on the device: sorted, decoded and joined there (arp_stage_frame), only the columns come back
   arp::FrameTables ft;
   arp_frame* frame = nullptr;

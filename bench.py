@@ -8,6 +8,14 @@ the data path): weak scaling.  Metric: atom pairs screened per second = ordered 
 (what the reference's R*-tree query returns and its classification loop consumes), a property of the workload
 and therefore identical for every implementation; contacts/s, candidate tests/s and atoms/s ride along.
 
+The timed path is the one arpeggia.contacts() runs: the emit-radius screen (arp_params.flags = 1: no label of
+complex.rs:217-296 can fire beyond r_emit = 4.5 A at the default vdw_comp, so cells and the screen use r_emit instead
+of dist_cutoff = 6.5 A; rows are identical, tests/test_gpu_parity.py).  The pair count of the metric is then the
+workload constant, counted by one plain run (flags 0) BEFORE the timed region, as SURVEY.md 8(d) defines it
+("implementation-independent pairs-in-cutoff/s so that pruning does not deflate the figure"); the same loop in the
+counting mode (flags 0: screen at dist_cutoff, every in-cutoff pair counted on the device) is timed right after and
+reported under "counting_mode".  --flags 0 makes the counting mode the headline instead.
+
   python bench.py [--gpus N] [--steps K] [--warmup W]            # our arm (GPU)
   python bench.py --impl reference [...]                         # the CPU restatement of the reference
 """
@@ -160,8 +168,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dense", action="store_true", help="overlapping copies (protein-interior density) instead of config 3")
-    ap.add_argument("--flags", type=int, default=0, help="arp_params.flags (1 = emit-radius screen)")
+    ap.add_argument("--flags", type=int, default=1, help="arp_params.flags (1 = emit-radius screen, the drop-in's path; 0 = counting mode)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-counting", action="store_true", help="skip the counting-mode (flags 0) side measurement")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
@@ -236,6 +245,32 @@ def main():
     ms_max = float(times.item())
     value = world * pairs / (ms_max * 1e-3)
 
+    # ---- the same loop in the counting mode (screen at dist_cutoff, in-cutoff pairs counted on the device) ----------------
+    counting = None
+    if args.flags != 0 and rank == 0 and world == 1 and not args.no_counting:
+        for _ in range(3):
+            ctx.run(0.1, 6.5, 0)
+        k = max(20, min(args.steps, 100))
+        tc = tp = 0.0
+        with torch.cuda.stream(stream):
+            for _ in range(k):
+                flush.zero_()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                ctx.run(0.1, 6.5, 0)
+                e1.record(stream)
+                e1.synchronize()
+                tc += e0.elapsed_time(e1)
+                tp += ctx.stats()["ms_pairs"]
+        rc = ctx.download()
+        sc = ctx.stats()
+        counting = {"flags": 0, "steps": k, "ms_per_step": tc / k, "pair_stage_ms": tp / k, "value": rc["pairs_in_cutoff"] / (tc / k * 1e-3),
+                    "pairs_within_cutoff_counted_on_device": int(rc["pairs_in_cutoff"]), "candidate_tests": int(rc["pairs_screened"]),
+                    "cells": int(sc["n_cells"]), "rows": int(sc["n_rows"]),
+                    "pair_stage": "k_screen -> k_filter -> k_exact"}
+        ctx.run(0.1, 6.5, args.flags)
+        ctx.download()
+
     # ---- end to end through the C ABI with pinned HOST buffers (H2D + kernels + D2H inside the timed region) ------
     hs, keep, h2d_bytes = pinned_structure(A, packed)
     from arpeggia_b200 import _lib as AL
@@ -300,28 +335,40 @@ def main():
         # DRAM bytes per launch of the three pair-stage kernels, from the committed ncu --set full capture
         traffic, traffic_src = None, None
         tj = ROOT / "profiles" / "pair_stage_traffic.json"
-        if tj.exists() and not args.dense and args.flags == 0:
+        tight = bool(args.flags & 1)
+        stage_kernels = ("k_screen_atoms", "k_exact") if tight else ("k_screen", "k_filter", "k_exact")
+        if tj.exists() and not args.dense:
             t = json.loads(tj.read_text())
-            traffic, traffic_src = int(sum(k["dram_read_bytes"] + k["dram_write_bytes"] for k in t["kernels"].values())), t["source"]
+            ks = {**t.get("kernels", {}), **t.get("other_kernels_of_the_step", {}), **t.get("counting_mode_kernels", {})}
+            if all(k in ks for k in stage_kernels):
+                traffic = int(sum(ks[k]["dram_read_bytes"] + ks[k]["dram_write_bytes"] for k in stage_kernels))
+                traffic_src = t["source"]
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_max, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
             "config": {"workload": WORKLOAD + (" [dense pitch]" if args.dense else ""), "per_gpu": "one assembly per rank (sharded by structure)",
                        "l2": "512 MiB buffer written between timed steps (L2 flushed)", "flags": args.flags,
+                       "screen": ("emit radius (cells and screen at r_emit = 4.5 A, rows identical; pairs_within_cutoff is the workload "
+                                  "constant, counted by a flags=0 run before the timed region: SURVEY 8(d))") if args.flags & 1 else
+                                 "dist_cutoff (every in-cutoff pair counted on the device inside the timed region)",
                        "atoms": n_atoms, "cells": st["n_cells"], "nonempty_cells": st["n_nonempty_cells"], "rows": n_rows,
                        "pairs_within_cutoff": pairs, "candidate_tests": res["pairs_screened"],
                        "pair_queue_entries": st["n_screened_pairs"], "filtered_pairs": st["n_filtered_pairs"]},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                         "kernel": "pair stage = k_screen -> k_filter -> k_exact (neighbour search + classification, 3 launches per step)",
-                         "kernel_ms": ms_pairs, "kernel_ms_each": {"k_screen": t_screen / args.steps, "k_filter": t_filter / args.steps,
-                                                                   "k_exact": t_exact / args.steps},
+                         "kernel": ("pair stage = k_screen_atoms -> k_exact (neighbour search + pair filter | classification, 2 launches per step)"
+                                    if tight else
+                                    "pair stage = k_screen -> k_filter -> k_exact (neighbour search + classification, 3 launches per step)"),
+                         "kernel_ms": ms_pairs,
+                         "kernel_ms_each": ({"k_screen_atoms": t_screen / args.steps, "k_exact": t_exact / args.steps} if tight else
+                                            {"k_screen": t_screen / args.steps, "k_filter": t_filter / args.steps, "k_exact": t_exact / args.steps}),
                          "algorithmic_bytes": alg_bytes, "traffic_source": traffic_src,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "ms_per_step": float(e2e_t.item()), "ms_h2d": st["ms_h2d"], "ms_run": st["ms_run"], "ms_d2h": st["ms_d2h"],
                     "api": "arp_contacts (C ABI, pinned host SoA in, host rows out)"},
             "frame": frame_info,
+            "counting_mode": counting,
             "gpu_launches": int(st0["kernel_launches"]) * args.steps,
             "clocks": clocks,
             "contacts_per_s": world * n_rows / (ms_max * 1e-3),

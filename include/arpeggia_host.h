@@ -63,6 +63,9 @@ typedef struct arph_table {
 
 #define ARPH_FLAG_NO_MULTIMODEL_QUIRK 1u /* do NOT reproduce complex.rs:447-449 (planes of every model = last model's) */
 #define ARPH_FLAG_SKIP_LOAD_FILTER    2u /* records are already restricted to the 20 amino acids + HOH */
+#define ARPH_FLAG_NO_COUNTERS          4u /* arph_contacts: the caller only wants the frame (what get_contacts returns).  The
+                                            device then screens at the emit radius (ARP_FLAG_EMIT_RADIUS_SCREEN) and the
+                                            table's pairs_in_cutoff / pairs_classified are -1.  Rows are identical. */
 
 const char* arph_last_error(void);
 

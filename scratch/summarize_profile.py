@@ -28,15 +28,18 @@ for r in rows[2:]:
 open(f'profiles/{tag}_kernels_summary.txt', 'w').write(
     'ncu --set full --clock-control none --import-source on -k regex:^k_ --launch-skip 30 --launch-count 10 python bench.py --no-cpu --steps 2 --warmup 3\n'
     '(config 3, 1 022 500 atoms; per-launch values; caches flushed between replays, so durations are cold-cache)\n\n' + '\n'.join(out) + '\n')
-pair = {k: v for k, v in kern.items() if k in ('k_screen', 'k_filter', 'k_exact')}
+pair = {k: v for k, v in kern.items() if k in ('k_screen_atoms', 'k_screen', 'k_filter', 'k_exact')}
 other = {k: v for k, v in kern.items() if k not in pair}
-json.dump({'source': f'profiles/{tag}_kernels_summary.txt (ncu --set full, one launch of each kernel of a config-3 step)', 'kernels': pair,
+prev = json.load(open('profiles/pair_stage_traffic.json')) if os.path.exists('profiles/pair_stage_traffic.json') else {}
+cm = {k: v for k, v in {**prev.get('counting_mode_kernels', {}), **prev.get('kernels', {})}.items() if k in ('k_screen', 'k_filter', 'k_exact') and k not in pair or k == 'k_exact' and 'k_screen_atoms' in pair}
+json.dump({'counting_mode_kernels': cm, 'counting_mode_source': prev.get('counting_mode_source', prev.get('source', '')), 'source': f'profiles/{tag}_kernels_summary.txt (ncu --set full, one launch of each kernel of a config-3 step)', 'kernels': pair,
            'other_kernels_of_the_step': other}, open('profiles/pair_stage_traffic.json', 'w'), indent=1)
 shutil.copy(f'gpurun_out/{tag}_launches.csv', f'profiles/{tag}_launches.csv')
 os.makedirs('/tmp/prof', exist_ok=True)
 subprocess.run('cd /tmp/prof && rm -f *.cubin && cuobjdump -xelf all /root/repo/arpeggia_b200/_build/libarpeggia_b200.so >/dev/null && nvdisasm -g -c api.sm_100a.cubin > dis.txt 2>/dev/null', shell=True)
-for k in ('k_screen', 'k_filter', 'k_exact', 'k_rings', 'k_scatter_atoms'):
-    src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "-k", f"regex:{k}"], capture_output=True, text=True).stdout
+for k in ('k_screen_atoms', 'k_screen', 'k_filter', 'k_exact', 'k_rings', 'k_scatter_atoms'):
+    if k not in kern: continue
+    src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "-k", f"regex:^{k}$"], capture_output=True, text=True).stdout
     open(f'/tmp/prof/src_{k}.csv', 'w').write(src)
     t = subprocess.run(["python", "scratch/ncu_lines.py", f"/tmp/prof/src_{k}.csv", "/tmp/prof/dis.txt", k, "25"], capture_output=True, text=True).stdout
     open(f'profiles/{tag}_{k}_by_line.txt', 'w').write('\n'.join(l[:200] for l in t.splitlines()) + '\n')

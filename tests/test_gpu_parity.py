@@ -71,6 +71,15 @@ def test_screen_modes_give_identical_rows(ctx, bft):
     assert tight["pairs_in_cutoff"] == -1 and tight["pairs_screened"] < dflt["pairs_screened"]
 
 
+def test_frame_without_counters_equals_frame_with_them(ctx, bft, ubq):
+    """ARPH_FLAG_NO_COUNTERS (what arpeggia.contacts() passes): emit-radius screen on the device, the same table."""
+    for atoms, tag in ((ubq, "1ubq"), (bft, "6bft")):
+        full = ctx.contacts_table(atoms, "/", 0.1, 6.5)
+        fast = ctx.contacts_table(atoms, "/", 0.1, 6.5, flags=4)
+        assert fast["pairs_in_cutoff"] == -1 and fast["pairs_classified"] == -1 and full["pairs_in_cutoff"] > 0
+        assert_tables_equal(fast, full, tag)
+
+
 def test_errors_match_reference_panics(ctx, bft):
     with pytest.raises(A.ArpeggiaError, match="Invalid chain groups format"):
         ctx.contacts_table(bft, "A,B", 0.1, 6.5)
