@@ -339,10 +339,11 @@ def main():
         stage_kernels = ("k_screen_atoms", "k_exact") if tight else ("k_screen", "k_filter", "k_exact")
         if tj.exists() and not args.dense:
             t = json.loads(tj.read_text())
-            ks = {**t.get("kernels", {}), **t.get("other_kernels_of_the_step", {}), **t.get("counting_mode_kernels", {})}
+            ks = ({**t.get("counting_mode_kernels", {}), **t.get("kernels", {})} if tight else
+                  {**t.get("kernels", {}), **t.get("counting_mode_kernels", {})})
             if all(k in ks for k in stage_kernels):
                 traffic = int(sum(ks[k]["dram_read_bytes"] + ks[k]["dram_write_bytes"] for k in stage_kernels))
-                traffic_src = t["source"]
+                traffic_src = t["source"] if tight else t.get("counting_mode_source", t["source"])
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_max, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",

@@ -28,4 +28,14 @@ for k in rng.choice(n, size=min(n, 8), replace=False):
     single = ctx.contacts_rows(packs[int(k)], 0.1, 6.5)["rows"]
     assert np.array_equal(np.sort(parts[int(k)], order=key), np.sort(single, order=key)), k
 out["spot_checked"] = min(n, 8)
+ctx.upload(packs)
+for _ in range(3):
+    ctx.run(0.1, 6.5, 1)
+    st1 = ctx.stats()
+res1 = ctx.download()
+k3 = ["from", "to", "label", "distance"]
+out["emit_radius"] = {"ms_run": st1["ms_run"], "ms_grid": st1["ms_grid"], "ms_pairs": st1["ms_pairs"], "cells": int(st1["n_cells"]),
+                      "rows": int(len(res1["rows"])), "pairs_per_s": res["pairs_in_cutoff"] / (st1["ms_run"] * 1e-3),
+                      "structures_per_s": n / (st1["ms_run"] * 1e-3),
+                      "rows_identical": bool(np.array_equal(np.sort(res1["rows"], order=k3), np.sort(res["rows"], order=k3)))}
 print(json.dumps(out))
