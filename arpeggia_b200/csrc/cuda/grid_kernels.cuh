@@ -230,46 +230,6 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_lookback(uint32_t* __rest
   }
 }
 
-// ---- the same scan in three launches, for large cell arrays ---------------------------------------------------------
-// The look-back of k_scan_lookback advances 32 tiles per L2 round trip, so its critical path grows with the tile count:
-// 26 us for the 2.6 M cells (1 269 tiles) of config 3 at the emit radius, nearly all of it waiting.  Above
-// SCAN_SPLIT_TILES tiles the scan is split: tile sums (one pass, no dependency), the scan of the sums (k_scan_lookback on
-// an array 2 048 times shorter: one tile up to 4 M cells), tile-local scans seeded with the scanned sums.
-constexpr uint32_t SCAN_SPLIT_TILES = 128;
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_tile_sums(const uint32_t* __restrict__ data, uint32_t n, uint32_t* __restrict__ sums) {
-  __shared__ uint32_t wsum[SCAN_THREADS / 32];
-  const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_PER_THREAD;
-  uint32_t sum = 0;
-#pragma unroll
-  for (int k = 0; k < SCAN_PER_THREAD; ++k) sum += base + k < n ? data[base + k] : 0u;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = sum;
-  __syncthreads();
-  if (threadIdx.x < 32) {
-    uint32_t t = threadIdx.x < SCAN_THREADS / 32 ? wsum[threadIdx.x] : 0u;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-    if (threadIdx.x == 0) sums[blockIdx.x] = t;
-  }
-}
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(uint32_t* __restrict__ data, uint32_t n, const uint32_t* __restrict__ tile_prefix) {
-  const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_PER_THREAD;
-  uint32_t v[SCAN_PER_THREAD], sum = 0;
-#pragma unroll
-  for (int k = 0; k < SCAN_PER_THREAD; ++k) {
-    v[k] = base + k < n ? data[base + k] : 0u;
-    sum += v[k];
-  }
-  uint32_t total;
-  uint32_t run = block_exclusive_scan(sum, &total) + tile_prefix[blockIdx.x];
-#pragma unroll
-  for (int k = 0; k < SCAN_PER_THREAD; ++k) {
-    if (base + k < n) data[base + k] = run;
-    run += v[k];
-  }
-}
-
 // res_id from the residues' atom ranges (arp_structure.res_atom_begin): one thread per atom, binary search in the
 // L2-resident CSR
 __global__ void __launch_bounds__(256) k_expand_res_id(const uint32_t* __restrict__ res_atom_begin, uint32_t n_res, uint32_t n_atoms,
