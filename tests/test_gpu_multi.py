@@ -37,7 +37,7 @@ def _atoms(case):
     return F.all_cases(ubq)[case].view(A.ATOM_DTYPE)
 
 
-def _slab_worker(rank, world, port, case, nccl, out_dir):
+def _slab_worker(rank, world, port, case, nccl, out_dir, flags=0):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dev = rank if nccl else 0
     torch.cuda.set_device(dev)
@@ -48,23 +48,28 @@ def _slab_worker(rank, world, port, case, nccl, out_dir):
         whole = D.soa_from_arrays(arr, device=f"cuda:{dev}" if nccl else "cpu")
         own = D.owned_part(whole, rank, world)
         ctx = A.Context(dev)
-        res = D.run_slab(ctx, own, 0.1, 6.5)
+        res = D.run_slab(ctx, own, 0.1, 6.5, flags)
         np.save(os.path.join(out_dir, f"rows_{rank}.npy"), res["rows"])
         np.save(os.path.join(out_dir, f"cnt_{rank}.npy"), np.array([res["pairs_in_cutoff"], res["halo"]["ghost_atoms"], own["x"].numel()]))
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("case,world", [("bft", 2), ("protonated", 2), ("altloc_protonated", 2), ("tiled", 3)])
-def test_slab_union_equals_single_gpu(case, world, tmp_path):
+@pytest.mark.parametrize("case,world,flags", [("bft", 2, 0), ("protonated", 2, 0), ("altloc_protonated", 2, 0), ("tiled", 3, 0),
+                                              ("bft", 2, 1), ("protonated", 2, 1), ("tiled", 3, 1)])
+def test_slab_union_equals_single_gpu(case, world, flags, tmp_path):
+    """flags = 1: the emit-radius screen (k_screen_atoms) with ghost atoms in the slabs."""
     nccl = torch.cuda.device_count() >= world
-    mp.spawn(_slab_worker, args=(world, _free_port(), case, nccl, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_slab_worker, args=(world, _free_port(), case, nccl, str(tmp_path), flags), nprocs=world, join=True)
     rows = np.concatenate([np.load(tmp_path / f"rows_{r}.npy") for r in range(world)])
     cnt = np.stack([np.load(tmp_path / f"cnt_{r}.npy") for r in range(world)])
     p = A.Packed(_atoms(case), flags=2 if case == "tiled" else 0)
     single = A.Context(0).contacts_rows(p, 0.1, 6.5)
     assert np.array_equal(np.sort(rows, order=KEY), np.sort(single["rows"], order=KEY))
-    assert cnt[:, 0].sum() == single["pairs_in_cutoff"]  # every in-cutoff pair is counted by exactly one owner
+    if flags == 0:
+        assert cnt[:, 0].sum() == single["pairs_in_cutoff"]  # every in-cutoff pair is counted by exactly one owner
+    else:
+        assert (cnt[:, 0] == -1).all()
     assert cnt[:, 2].sum() == p.arrays()["n_atoms"] and (cnt[:, 1] > 0).all()
 
 
