@@ -11,6 +11,7 @@ from __future__ import annotations
 from ._lib import ArpeggiaError, ATOM_DTYPE, HOST_FLAG_NO_COUNTERS as FLAG_NO_COUNTERS, LABELS, ROW_DTYPE
 from .core import COLUMNS, Context, Packed, default_context, load_atoms, parse_cif, parse_pdb, read_table, split_rows
 from .frame import to_arrow, to_frame
+from . import sap  # noqa: F401  (the neighbour sum of the SAP score)
 
 __version__ = "0.1.0"
 __all__ = ["contacts", "Context", "Packed", "ArpeggiaError", "parse_pdb", "parse_cif", "load_atoms", "to_arrow", "to_frame", "COLUMNS"]

@@ -162,6 +162,8 @@ SIGNATURES = {
     "arp_stage_run": (C.c_int, [_P, C.POINTER(Params)]),
     "arp_stage_download": (C.c_int, [_P, C.POINTER(C.POINTER(Result))]),
     "arp_stage_stats": (C.c_int, [_P, C.POINTER(Stats)]),
+    "arp_stage_neighbor_sum": (C.c_int, [_P, _P, _P, C.c_float, _P]),
+    "arp_neighbor_sum_stats": (C.c_int, [_P, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_int64)]),
     "arp_stage_frame": (C.c_int, [_P, C.POINTER(FrameTables), C.POINTER(C.POINTER(Frame))]),
     "arp_contacts_frame": (C.c_int, [_P, C.POINTER(Structure), C.POINTER(Params), C.POINTER(FrameTables),
                                      C.POINTER(C.POINTER(Frame))]),

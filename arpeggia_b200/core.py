@@ -105,6 +105,16 @@ class Packed:
             out[k] = view(getattr(s, k), s.n_rings, np.uint32)
         return out
 
+    def atom_serials(self) -> np.ndarray:
+        """Serial number of every packed atom (atoms_with_hierarchy() order can differ from the record order)."""
+        import ctypes as _C
+
+        from ._lib import FrameTables
+        tp = _C.POINTER(FrameTables)()
+        check(lib().arph_packed_frame_tables(self._h, _C.byref(tp)))
+        n = self.structure.n_atoms
+        return np.ctypeslib.as_array(tp.contents.ent_atomi, shape=(max(n, 1),))[:n].astype(np.int64)
+
     def build_table(self, rows: np.ndarray) -> dict:
         L = lib()
         rows = np.ascontiguousarray(rows, dtype=ROW_DTYPE)
@@ -204,6 +214,21 @@ class Context:
     def run(self, vdw_comp=0.1, dist_cutoff=6.5, flags=0):
         prm = Params(vdw_comp, dist_cutoff, flags, 0)
         check(lib().arp_stage_run(self._h, C.byref(prm)), self._h)
+
+    def neighbor_sum(self, weight: np.ndarray, select: np.ndarray, radius: float = 5.0) -> np.ndarray:
+        """arp_stage_neighbor_sum on the uploaded single-structure job: the radius query of the SAP score
+        (src/sap.rs:181-215).  out[x] = sum of weight[y] over the selected atoms y within `radius` of the selected atom x
+        (x included), 0 where x is not selected.  Arrays are in the job's atom order (Packed.arrays())."""
+        w = np.ascontiguousarray(weight, dtype=np.float32)
+        sel = np.ascontiguousarray(select, dtype=np.uint8)
+        out = np.zeros(len(w), dtype=np.float32)
+        check(lib().arp_stage_neighbor_sum(self._h, w.ctypes.data, sel.ctypes.data, C.c_float(radius), out.ctypes.data), self._h)
+        return out
+
+    def neighbor_sum_stats(self) -> dict:
+        g, s_, n = C.c_float(), C.c_float(), C.c_int64()
+        check(lib().arp_neighbor_sum_stats(self._h, C.byref(g), C.byref(s_), C.byref(n)), self._h)
+        return {"ms_grid": g.value, "ms_sum": s_.value, "n_cells": n.value}
 
     def download(self) -> dict:
         L = lib()

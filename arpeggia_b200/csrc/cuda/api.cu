@@ -13,6 +13,7 @@
 #include "pair_kernel.cuh"
 #include "ring_kernels.cuh"
 #include "frame_kernels.cuh"
+#include "nsum_kernels.cuh"
 
 using namespace arpd;
 
@@ -115,6 +116,17 @@ struct arp_ctx {
   DBuf<uint2> pairq, pairq2;  // pairs between k_screen -> k_filter -> k_exact
   uint64_t pairq_cap = 0, pairq2_cap = 0;
   int64_t n_cells = 0, n_rcells = 0;
+
+  // the weighted neighbour sum (arp_stage_neighbor_sum): its own cell list over the job's atoms
+  DBuf<StructDesc> ns_desc;
+  DBuf<uint32_t> ns_cell_of, ns_rank_of, ns_cell_start;
+  DBuf<unsigned long long> ns_status;
+  DBuf<NsRec> ns_rec;
+  DBuf<float> ns_weight, ns_out;
+  DBuf<unsigned char> ns_select;
+  cudaEvent_t nev[4] = {};
+  float ns_ms_grid = 0.f, ns_ms_sum = 0.f;
+  int64_t ns_cells = 0;
 
   // the frame (arp_stage_frame): the caller's tables, sort ping-pong buffers, output columns
   DBuf<arp_frame_side> f_sides;
@@ -359,3 +371,4 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
 }  // namespace
 
 #include "api_run.inc"
+#include "api_nsum.inc"

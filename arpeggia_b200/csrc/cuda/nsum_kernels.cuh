@@ -1,0 +1,67 @@
+// Weighted neighbour sum over the atoms of the resident job: the radius query of the SAP score,
+// src/sap.rs:181-215 -- for every selected atom x: sum of weight[y] over the selected atoms y (x itself included) with
+// distance_2(x, y) <= radius^2, the same create_hierarchy_rtree().locate_within_distance primitive as the contacts path
+// (inclusive, rstar), with the squared radius formed in f32 and widened (sap.rs:184).  Same cell-list build as the
+// contacts job (k_cell_assign + k_scan_lookback), its own sorted record and a full 27-cell sweep: the sum is not
+// symmetric in (x, y), every atom needs all of its neighbours.
+#pragma once
+#include "grid_kernels.cuh"
+
+namespace arpd {
+
+struct __align__(32) NsRec {  // one sector per atom
+  double x, y, z;
+  float w;
+  uint32_t perm_sel;  // input-order index | selected << 31
+};
+
+__global__ void __launch_bounds__(256)
+k_ns_scatter(const double* __restrict__ x, const double* __restrict__ y, const double* __restrict__ z, const float* __restrict__ weight,
+             const unsigned char* __restrict__ select, const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of,
+             const uint32_t* __restrict__ cell_start, uint32_t n, NsRec* __restrict__ rec) {
+  const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= n) return;
+  NsRec r;
+  r.x = x[a], r.y = y[a], r.z = z[a];
+  r.w = weight[a];
+  r.perm_sel = a | (select[a] ? 0x80000000u : 0u);
+  rec[cell_start[cell_of[a]] + rank_of[a]] = r;
+}
+
+// One lane per sorted slot.  Exact FP64 distance in the reference's operation order ((dx*dx + dy*dy) + dz*dz), every
+// operation rounded once; the sum is accumulated in f64 and rounded to f32 once (the reference adds f32 terms in the
+// R*-tree's iteration order, which is unspecified: any order of the same terms lies within n * 2^-24 * sum|w| of this).
+__global__ void __launch_bounds__(256)
+k_neighbor_sum(const NsRec* __restrict__ rec, const uint32_t* __restrict__ cell_start, const StructDesc d, double inv_edge, double r2,
+               uint32_t n, float* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const NsRec me = rec[i];
+  const uint32_t perm = me.perm_sel & 0x7fffffffu;
+  if (!(me.perm_sel >> 31)) {
+    out[perm] = 0.f;
+    return;
+  }
+  const int ix = cell_coord(me.x, d.ox, inv_edge, d.nx), iy = cell_coord(me.y, d.oy, inv_edge, d.ny), iz = cell_coord(me.z, d.oz, inv_edge, d.nz);
+  const int x0 = max(ix - 1, 0), x1 = min(ix + 1, d.nx - 1);
+  double acc = 0.0;
+  for (int dz = -1; dz <= 1; ++dz) {
+    const int zc = iz + dz;
+    if (zc < 0 || zc >= d.nz) continue;
+    for (int dy = -1; dy <= 1; ++dy) {
+      const int yc = iy + dy;
+      if (yc < 0 || yc >= d.ny) continue;
+      const uint32_t row = d.cell_base + (uint32_t)((zc * d.ny + yc) * d.nx);
+      const uint32_t b = cell_start[row + (uint32_t)x0], e = cell_start[row + (uint32_t)x1 + 1u];
+      for (uint32_t j = b; j < e; ++j) {
+        const NsRec q = rec[j];
+        const double dx = dsub(q.x, me.x), dyy = dsub(q.y, me.y), dzz = dsub(q.z, me.z);
+        const double d2 = dadd(dadd(dmul(dx, dx), dmul(dyy, dyy)), dmul(dzz, dzz));
+        if (d2 <= r2 && (q.perm_sel >> 31)) acc += (double)q.w;
+      }
+    }
+  }
+  out[perm] = (float)acc;
+}
+
+}  // namespace arpd

@@ -333,6 +333,35 @@ def main():
                       "api": "arp_stage_frame (keys + radix sort + decode + sc join on the device, columns D2H)"}
     d2h_bytes = int(n_rows_e2e * 16)
 
+    # ---- the SAP radius query (src/sap.rs:181-215) on the same assembly, beside the oracle ---------
+    sap_info = None
+    if rank == 0 and world == 1 and not args.no_counting:
+        from arpeggia_b200 import sap
+        from oracle import oracle as O
+
+        arr = packed.arrays()
+        sel = sap.sidechain_mask(atoms) if len(atoms) == arr["n_atoms"] else np.ones(arr["n_atoms"], dtype=bool)
+        wts = np.random.default_rng(3).integers(-4, 5, size=arr["n_atoms"]).astype(np.float32)  # exact sums: bit-exact check
+        ctx.upload(packed)
+        got = ctx.neighbor_sum(wts, sel, 5.0)
+        t_ns = [0.0, 0.0]
+        for _ in range(5):
+            flush.zero_()
+            torch.cuda.synchronize()
+            ctx.neighbor_sum(wts, sel, 5.0)
+            sn = ctx.neighbor_sum_stats()
+            t_ns[0] += sn["ms_grid"] / 5
+            t_ns[1] += sn["ms_sum"] / 5
+        sap_info = {"atoms": int(arr["n_atoms"]), "selected": int(sel.sum()), "radius": 5.0, "ms_grid": t_ns[0], "ms_sum": t_ns[1],
+                    "atoms_per_s": arr["n_atoms"] / ((t_ns[0] + t_ns[1]) * 1e-3), "cells": sn["n_cells"],
+                    "api": "arp_stage_neighbor_sum (device times: cell-list build, sum kernel; weights / mask H2D and sums D2H excluded)"}
+        if not args.no_cpu:
+            t0 = time.perf_counter()
+            want = O.neighbor_sum(arr["x"], arr["y"], arr["z"], wts, sel, 5.0)
+            sap_info["cpu_port_s"] = time.perf_counter() - t0
+            sap_info["cpu_cores"] = os.cpu_count() or 1
+            sap_info["equals_oracle"] = bool(np.array_equal(got.view(np.uint32), want.view(np.uint32)))
+
     if rank == 0:
         peaks = {}
         pk = ROOT / "MEASURED_PEAKS.json"
@@ -380,6 +409,7 @@ def main():
                     "api": "arp_contacts (C ABI, pinned host SoA in, host rows out)"},
             "frame": frame_info,
             "counting_mode": counting,
+            "sap_neighbor_sum": sap_info,
             "gpu_launches": int(st0["kernel_launches"]) * args.steps,
             "clocks": clocks,
             "contacts_per_s": world * n_rows / (ms_max * 1e-3),

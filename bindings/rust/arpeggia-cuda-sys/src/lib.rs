@@ -213,6 +213,8 @@ extern "C" {
     pub fn arp_stage_run(ctx: *mut arp_ctx, p: *const arp_params) -> c_int;
     pub fn arp_stage_download(ctx: *mut arp_ctx, out: *mut *mut arp_result) -> c_int;
     pub fn arp_stage_stats(ctx: *mut arp_ctx, out: *mut arp_stats) -> c_int;
+    pub fn arp_stage_neighbor_sum(ctx: *mut arp_ctx, weight: *const f32, select: *const u8, radius: f32, out: *mut f32) -> c_int;
+    pub fn arp_neighbor_sum_stats(ctx: *mut arp_ctx, ms_grid: *mut f32, ms_sum: *mut f32, n_cells: *mut i64) -> c_int;
     pub fn arp_stage_frame(ctx: *mut arp_ctx, t: *const arp_frame_tables, out: *mut *mut arp_frame) -> c_int;
     pub fn arp_contacts_frame(ctx: *mut arp_ctx, s: *const arp_structure, p: *const arp_params, t: *const arp_frame_tables, out: *mut *mut arp_frame) -> c_int;
     pub fn arp_frame_free(ctx: *mut arp_ctx, f: *mut arp_frame);

@@ -1448,4 +1448,75 @@ int orc_residue_plane(const orc_atom_record* recs, int64_t n, const char* chain,
   }
 }
 
+// src/sap.rs:181-215 (the loop over side-chain atoms and their neighbours), on caller-supplied weights.
+//   sap.rs:184      let sap_radius_sq = f64::from(sap_radius * sap_radius);
+//   sap.rs:193-197  tree.locate_within_distance(x.atom().pos(), sap_radius_sq).filter(|y| y.is_sidechain())  -- inclusive, x included
+//   sap.rs:199-212  .map(contribution).sum::<f32>()
+// The spatial index is a uniform grid here (any index returns the same set); terms are added in increasing atom order.
+int orc_neighbor_sum(const double* x, const double* y, const double* z, int64_t n, const float* weight, const unsigned char* select,
+                     float radius, float* out) {
+  if (n < 0 || (n > 0 && (!x || !y || !z || !weight || !select || !out)) || !(radius > 0.f)) {
+    g_err = "orc_neighbor_sum: bad argument";
+    return ORC_ERR_ARG;
+  }
+  if (n == 0) return ORC_OK;
+  const float r2f = radius * radius;
+  const double r2 = (double)r2f;
+  const double edge = std::sqrt(r2) * (1.0 + 1e-9) + 1e-9;
+  double lo[3] = {x[0], y[0], z[0]}, hi[3] = {x[0], y[0], z[0]};
+  for (int64_t i = 1; i < n; ++i) {
+    lo[0] = std::min(lo[0], x[i]), hi[0] = std::max(hi[0], x[i]);
+    lo[1] = std::min(lo[1], y[i]), hi[1] = std::max(hi[1], y[i]);
+    lo[2] = std::min(lo[2], z[i]), hi[2] = std::max(hi[2], z[i]);
+  }
+  double e = edge;
+  int64_t dim[3];
+  while (true) {
+    for (int a = 0; a < 3; ++a) dim[a] = (int64_t)std::floor((hi[a] - lo[a]) / e) + 1;
+    if ((double)dim[0] * (double)dim[1] * (double)dim[2] <= 64.0 * (double)n + 4194304.0) break;
+    e *= 1.26;
+  }
+  auto coord = [&](double p, int a) {
+    int64_t c = (int64_t)std::floor((p - lo[a]) / e);
+    return std::min(std::max<int64_t>(c, 0), dim[a] - 1);
+  };
+  const int64_t cells = dim[0] * dim[1] * dim[2];
+  std::vector<int64_t> start(cells + 1, 0), cell(n);
+  for (int64_t i = 0; i < n; ++i) {
+    cell[i] = (coord(z[i], 2) * dim[1] + coord(y[i], 1)) * dim[0] + coord(x[i], 0);
+    start[cell[i] + 1] += 1;
+  }
+  for (int64_t c = 0; c < cells; ++c) start[c + 1] += start[c];
+  std::vector<int64_t> order(n), fill(start.begin(), start.end() - 1);
+  for (int64_t i = 0; i < n; ++i) order[fill[cell[i]]++] = i;  // atoms of a cell in increasing index
+#pragma omp parallel for schedule(dynamic, 256)
+  for (int64_t i = 0; i < n; ++i) {
+    if (!select[i]) {
+      out[i] = 0.f;
+      continue;
+    }
+    const int64_t cx = coord(x[i], 0), cy = coord(y[i], 1), cz = coord(z[i], 2);
+    std::vector<int64_t> hit;
+    for (int64_t dz = -1; dz <= 1; ++dz)
+      for (int64_t dy = -1; dy <= 1; ++dy)
+        for (int64_t dx = -1; dx <= 1; ++dx) {
+          const int64_t ax = cx + dx, ay = cy + dy, az = cz + dz;
+          if (ax < 0 || ay < 0 || az < 0 || ax >= dim[0] || ay >= dim[1] || az >= dim[2]) continue;
+          const int64_t c = (az * dim[1] + ay) * dim[0] + ax;
+          for (int64_t k = start[c]; k < start[c + 1]; ++k) {
+            const int64_t j = order[k];
+            if (!select[j]) continue;
+            const double ex = x[j] - x[i], ey = y[j] - y[i], ez = z[j] - z[i];
+            const double d2 = (ex * ex + ey * ey) + ez * ez;  // rstar distance_2
+            if (d2 <= r2) hit.push_back(j);
+          }
+        }
+    std::sort(hit.begin(), hit.end());
+    float acc = 0.f;
+    for (int64_t j : hit) acc += weight[j];
+    out[i] = acc;
+  }
+  return ORC_OK;
+}
+
 }  // extern "C"

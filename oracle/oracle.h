@@ -99,6 +99,14 @@ int  orc_parse_groups(const char* chains_csv, const char* groups, char* ligand_o
 int  orc_residue_plane(const orc_atom_record* atoms, int64_t n, const char* chain, int64_t resi, int kind,
                        int64_t* n_atoms_out, double center[3], double normal[3]);
 
+/* The radius query of the SAP score, src/sap.rs:181-215, on caller-supplied weights: for every atom x with select[x]
+ *   out[x] = sum of weight[y] over the atoms y with select[y] and distance_2(x, y) <= (double)(radius * radius)
+ * (x included; rstar locate_within_distance is inclusive; sap.rs:184 squares the radius in f32), summed in f32 in
+ * increasing atom order (the R*-tree's iteration order is unspecified); out[x] = 0 where !select[x].
+ * In the reference select = is_sidechain() and weight = hydrophobicity * clamp(sasa / max_asa, 0, 1). */
+int  orc_neighbor_sum(const double* x, const double* y, const double* z, int64_t n, const float* weight,
+                      const unsigned char* select, float radius, float* out);
+
 /* error codes */
 enum {
   ORC_OK = 0, ORC_ERR_IO = 1, ORC_ERR_BAD_GROUPS = 2, ORC_ERR_EMPTY_GROUP = 3, ORC_ERR_NO_RINGS = 4,

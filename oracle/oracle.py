@@ -97,6 +97,7 @@ def lib():
         L.orc_plane_point_dist.restype = C.c_double
         L.orc_plane_dihedral.argtypes = [C.c_void_p] * 2
         L.orc_plane_dihedral.restype = C.c_double
+        L.orc_neighbor_sum.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p]
         L.orc_parse_groups.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int64]
         L.orc_residue_plane.argtypes = [C.c_void_p, C.c_int64, C.c_char_p, C.c_int64, C.c_int,
                                         C.POINTER(C.c_int64), C.c_void_p, C.c_void_p]
@@ -220,3 +221,15 @@ def residue_plane(atoms: np.ndarray, chain: str, resi: int, kind: str = "ring"):
     if rc != 0:
         return n.value, None, None
     return n.value, c, nrm
+
+
+def neighbor_sum(x, y, z, weight, select, radius: float) -> np.ndarray:
+    """src/sap.rs:181-215 on caller-supplied weights: per selected atom, the f32 sum of weight over the selected atoms
+    within `radius` (itself included, inclusive comparison), in increasing atom order; 0 where not selected."""
+    x, y, z = (np.ascontiguousarray(v, dtype=np.float64) for v in (x, y, z))
+    w = np.ascontiguousarray(weight, dtype=np.float32)
+    sel = np.ascontiguousarray(select, dtype=np.uint8)
+    out = np.zeros(len(x), dtype=np.float32)
+    _check(lib().orc_neighbor_sum(x.ctypes.data, y.ctypes.data, z.ctypes.data, len(x), w.ctypes.data, sel.ctypes.data,
+                                  C.c_float(radius), out.ctypes.data))
+    return out
