@@ -122,6 +122,7 @@ struct arp_ctx {
   DBuf<uint32_t> ns_cell_of, ns_rank_of, ns_cell_start;
   DBuf<unsigned long long> ns_status;
   DBuf<NsRec> ns_rec;
+  DBuf<NsRecF> ns_recf;
   DBuf<float> ns_weight, ns_out;
   DBuf<unsigned char> ns_select;
   cudaEvent_t nev[4] = {};

@@ -15,25 +15,35 @@ struct __align__(32) NsRec {  // one sector per atom
   uint32_t perm_sel;  // input-order index | selected << 31
 };
 
+struct __align__(16) NsRecF {  // what the f32 screen reads: position relative to the grid origin, weight (0 when not selected)
+  float x, y, z, w;
+};
+
 __global__ void __launch_bounds__(256)
 k_ns_scatter(const double* __restrict__ x, const double* __restrict__ y, const double* __restrict__ z, const float* __restrict__ weight,
              const unsigned char* __restrict__ select, const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of,
-             const uint32_t* __restrict__ cell_start, uint32_t n, NsRec* __restrict__ rec) {
+             const uint32_t* __restrict__ cell_start, uint32_t n, double ox, double oy, double oz, NsRec* __restrict__ rec,
+             NsRecF* __restrict__ recf) {
   const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
   if (a >= n) return;
   NsRec r;
   r.x = x[a], r.y = y[a], r.z = z[a];
-  r.w = weight[a];
+  r.w = select[a] ? weight[a] : 0.f;  // an unselected atom contributes nothing (and never receives: perm_sel)
   r.perm_sel = a | (select[a] ? 0x80000000u : 0u);
-  rec[cell_start[cell_of[a]] + rank_of[a]] = r;
+  const uint32_t slot = cell_start[cell_of[a]] + rank_of[a];
+  rec[slot] = r;
+  recf[slot] = NsRecF{(float)(r.x - ox), (float)(r.y - oy), (float)(r.z - oz), r.w};
 }
 
-// One lane per sorted slot.  Exact FP64 distance in the reference's operation order ((dx*dx + dy*dy) + dz*dz), every
-// operation rounded once; the sum is accumulated in f64 and rounded to f32 once (the reference adds f32 terms in the
+// One lane per sorted slot.  Every candidate of the 27-cell shell is screened in f32 on the origin-relative positions
+// (difference form; |d2_f32 - d2| < g, the guard band of the contacts path, api_run.inc): d2_f32 <= r2 - g is certainly
+// inside, d2_f32 > r2 + g certainly outside, and only the shell in between takes the exact FP64 test in the reference's
+// operation order ((dx*dx + dy*dy) + dz*dz, every operation rounded once, inclusive comparison) -- so the neighbour SET
+// is the reference's.  The sum is accumulated in f64 and rounded to f32 once (the reference adds f32 terms in the
 // R*-tree's iteration order, which is unspecified: any order of the same terms lies within n * 2^-24 * sum|w| of this).
 __global__ void __launch_bounds__(256)
-k_neighbor_sum(const NsRec* __restrict__ rec, const uint32_t* __restrict__ cell_start, const StructDesc d, double inv_edge, double r2,
-               uint32_t n, float* __restrict__ out) {
+k_neighbor_sum(const NsRec* __restrict__ rec, const NsRecF* __restrict__ recf, const uint32_t* __restrict__ cell_start, const StructDesc d,
+               double inv_edge, double r2, float thr_cert, float thr_hit, uint32_t n, float* __restrict__ out) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const NsRec me = rec[i];
@@ -42,6 +52,7 @@ k_neighbor_sum(const NsRec* __restrict__ rec, const uint32_t* __restrict__ cell_
     out[perm] = 0.f;
     return;
   }
+  const NsRecF mf = recf[i];
   const int ix = cell_coord(me.x, d.ox, inv_edge, d.nx), iy = cell_coord(me.y, d.oy, inv_edge, d.ny), iz = cell_coord(me.z, d.oz, inv_edge, d.nz);
   const int x0 = max(ix - 1, 0), x1 = min(ix + 1, d.nx - 1);
   double acc = 0.0;
@@ -53,12 +64,21 @@ k_neighbor_sum(const NsRec* __restrict__ rec, const uint32_t* __restrict__ cell_
       if (yc < 0 || yc >= d.ny) continue;
       const uint32_t row = d.cell_base + (uint32_t)((zc * d.ny + yc) * d.nx);
       const uint32_t b = cell_start[row + (uint32_t)x0], e = cell_start[row + (uint32_t)x1 + 1u];
+      double exact = 0.0;
       for (uint32_t j = b; j < e; ++j) {
-        const NsRec q = rec[j];
-        const double dx = dsub(q.x, me.x), dyy = dsub(q.y, me.y), dzz = dsub(q.z, me.z);
-        const double d2 = dadd(dadd(dmul(dx, dx), dmul(dyy, dyy)), dmul(dzz, dzz));
-        if (d2 <= r2 && (q.perm_sel >> 31)) acc += (double)q.w;
+        const NsRecF q = recf[j];
+        const float fx = q.x - mf.x, fy = q.y - mf.y, fz = q.z - mf.z;
+        const float d2f = fmaf(fz, fz, fmaf(fy, fy, fx * fx));
+        if (d2f <= thr_cert) {
+          exact += (double)q.w;
+        } else if (d2f <= thr_hit) {  // too close to the radius to call in f32
+          const NsRec p = rec[j];
+          const double dx = dsub(p.x, me.x), dyy = dsub(p.y, me.y), dzz = dsub(p.z, me.z);
+          const double d2 = dadd(dadd(dmul(dx, dx), dmul(dyy, dyy)), dmul(dzz, dzz));
+          if (d2 <= r2) exact += (double)q.w;
+        }
       }
+      acc += exact;
     }
   }
   out[perm] = (float)acc;
