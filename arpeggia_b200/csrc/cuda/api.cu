@@ -165,6 +165,9 @@ struct arp_ctx {
   arp_params last_params{};
   DevParams dp{};
   cudaEvent_t ev[13] = {};  // timing marks (recorded as external event nodes inside a capture: still readable after a replay)
+  cudaEvent_t udep[3] = {};  // upload: fork / join edges to the side stream (the expand kernels run beside the copies)
+  HBuf<uint32_t> h_words;   // page-locked single words of an upload (CSR closing entries)
+  HBuf<StructDesc> h_descs_up;  // page-locked source of the upload's descriptor copy
   cudaEvent_t dep[3] = {};  // fork / join edges between the main and the side stream (plain records: captured as dependencies)
   bool capturing = false;
   int64_t launches = 0;
@@ -263,6 +266,8 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
     throw arp::Error{ARP_ERR_LIMIT, "job exceeds 2^30 atoms / 2^31 rings"};
 
   CK(cudaEventRecord(c->ev[0], c->stream));
+  c->h_words.need(32);
+  bool side_used = false;
   auto nat = [](const arp_structure* t) { return t->n_atoms; };
   auto nrs = [](const arp_structure* t) { return t->n_residues; };
   auto nrg = [](const arp_structure* t) { return t->n_rings; };
@@ -279,8 +284,11 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
     c->x.need(c->n_atoms);
     c->y.need(c->n_atoms);
     c->z.need(c->n_atoms);
-    k_expand_milli<<<(unsigned)((c->n_atoms + 255) / 256), 256, 0, c->stream>>>(c->xm.p, c->ym.p, c->zm.p, (uint32_t)c->n_atoms, c->x.p, c->y.p, c->z.p);
+    CK(cudaEventRecord(c->udep[0], c->stream));  // on the side stream: the next copies do not wait for the kernel
+    CK(cudaStreamWaitEvent(c->side, c->udep[0], 0));
+    k_expand_milli<<<(unsigned)((c->n_atoms + 255) / 256), 256, 0, c->side>>>(c->xm.p, c->ym.p, c->zm.p, (uint32_t)c->n_atoms, c->x.p, c->y.p, c->z.p);
     CK(cudaGetLastError());
+    side_used = true;
   } else {
     for (int64_t k = 0; k < n; ++k)
       if (s[k]->n_atoms > 0 && (!s[k]->x || !s[k]->y || !s[k]->z)) throw arp::Error{ARP_ERR_ARG, "structure has neither x / y / z nor x_milli / y_milli / z_milli"};
@@ -320,15 +328,16 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
   if (expand_res_id) {
     // like res_h_begin below: every structure contributes its first n_residues offsets, the tail closes the CSR
     upload_concat(c, c->res_atom_begin, s, n, [](const arp_structure* t) { return t->res_atom_begin; }, nrs, 1, multi ? &atom_adj : nullptr, false);
-    const uint32_t tail = (uint32_t)c->n_atoms;
-    CK(cudaStreamSynchronize(c->stream));
-    c->stage.need(64);
-    std::memcpy(c->stage.p, &tail, 4);
-    CK(cudaMemcpyAsync(c->res_atom_begin.p + c->n_res, c->stage.p, 4, cudaMemcpyDefault, c->stream));
+    // the closing word comes from a page-locked slot of its own (nothing else writes it during this upload: no wait)
+    c->h_words.p[0] = (uint32_t)c->n_atoms;
+    CK(cudaMemcpyAsync(c->res_atom_begin.p + c->n_res, c->h_words.p, 4, cudaMemcpyDefault, c->stream));
     c->res_id.need(std::max<int64_t>(c->n_atoms, 1));
-    if (c->n_atoms > 0) {
-      k_expand_res_id<<<(unsigned)((c->n_atoms + 255) / 256), 256, 0, c->stream>>>(c->res_atom_begin.p, (uint32_t)c->n_res, (uint32_t)c->n_atoms, c->res_id.p);
+    if (c->n_atoms > 0) {  // on the side stream: the copy engine keeps going underneath
+      CK(cudaEventRecord(c->udep[1], c->stream));
+      CK(cudaStreamWaitEvent(c->side, c->udep[1], 0));
+      k_expand_res_id<<<(unsigned)((c->n_atoms + 255) / 256), 256, 0, c->side>>>(c->res_atom_begin.p, (uint32_t)c->n_res, (uint32_t)c->n_atoms, c->res_id.p);
       CK(cudaGetLastError());
+      side_used = true;
     }
   } else {
     for (int64_t k = 0; k < n; ++k)
@@ -340,11 +349,8 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
   // res_h_begin: n_res + 1 entries; each structure contributes its first n_residues offsets, the tail closes the CSR
   upload_concat(c, c->res_h_begin, s, n, [](const arp_structure* t) { return t->res_h_begin; }, nrs, 1, multi ? &h_adj : nullptr, false);
   {
-    const uint32_t tail = (uint32_t)c->n_h;
-    CK(cudaStreamSynchronize(c->stream));
-    c->stage.need(64);
-    std::memcpy(c->stage.p, &tail, 4);
-    CK(cudaMemcpyAsync(c->res_h_begin.p + c->n_res, c->stage.p, 4, cudaMemcpyDefault, c->stream));
+    c->h_words.p[16] = (uint32_t)c->n_h;  // its own page-locked slot, see above
+    CK(cudaMemcpyAsync(c->res_h_begin.p + c->n_res, c->h_words.p + 16, 4, cudaMemcpyDefault, c->stream));
   }
   // structure descriptors (grids are filled in by the run, they depend on the cutoff)
   c->h_descs.assign(n, StructDesc{});
@@ -355,8 +361,13 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
     c->h_descs[k].ring_end = (uint32_t)c->ring_begin[k + 1];
   }
   c->descs.need(n);
-  CK(cudaStreamSynchronize(c->stream));
-  CK(cudaMemcpyAsync(c->descs.p, c->h_descs.data(), n * sizeof(StructDesc), cudaMemcpyDefault, c->stream));
+  c->h_descs_up.need((size_t)n);  // page-locked, this upload's own (h_descs_pin belongs to the run: it compares against it)
+  std::memcpy(c->h_descs_up.p, c->h_descs.data(), n * sizeof(StructDesc));
+  CK(cudaMemcpyAsync(c->descs.p, c->h_descs_up.p, n * sizeof(StructDesc), cudaMemcpyDefault, c->stream));
+  if (side_used) {  // join
+    CK(cudaEventRecord(c->udep[2], c->side));
+    CK(cudaStreamWaitEvent(c->stream, c->udep[2], 0));
+  }
   if (multi) {
     c->atom_struct.need(std::max<int64_t>(c->n_atoms, 1));
     c->ring_struct.need(std::max<int64_t>(c->n_rings, 1));
