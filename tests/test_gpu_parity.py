@@ -55,6 +55,8 @@ def test_parameters(ctx, bft, vdw_comp, rc):
     want = O.contacts(bft.view(O.ATOM_DTYPE), "/", vdw_comp, rc)
     assert_tables_equal(got, want, f"comp={vdw_comp} rc={rc}")
     assert got["pairs_in_cutoff"] == want["pairs_in_cutoff"]
+    fast = ctx.contacts_table(bft, "/", vdw_comp, rc, flags=4)  # emit-radius screen where r_emit < rc, else the same path
+    assert_tables_equal(fast, want, f"comp={vdw_comp} rc={rc} (emit-radius screen)")
 
 
 def test_screen_modes_give_identical_rows(ctx, bft):
@@ -151,6 +153,10 @@ def test_edge_cases_equal_oracle(ctx, ubq, case):
     want = O.contacts(atoms, "/", 0.1, 6.5, ignore_zero_occupancy=zero)
     assert_tables_equal(got, want, case)
     assert got["pairs_in_cutoff"] == want["pairs_in_cutoff"] and got["pairs_classified"] == want["pairs_classified"]
+    # the path arpeggia.contacts() takes: emit-radius screen (k_screen_atoms), no counters
+    fast = ctx.contacts_table(atoms.view(A.ATOM_DTYPE), "/", 0.1, 6.5, ignore_zero_occupancy=zero, flags=4)
+    assert_tables_equal(fast, want, case + " (emit-radius screen)")
+    assert fast["pairs_in_cutoff"] == -1
     if case == "two_models":  # and without reproducing complex.rs:447-449
         got = ctx.contacts_table(atoms.view(A.ATOM_DTYPE), "/", 0.1, 6.5, flags=1)
         want = O.contacts(atoms, "/", 0.1, 6.5, flags=O.FLAG_NO_MULTIMODEL_QUIRK)
