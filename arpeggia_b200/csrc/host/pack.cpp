@@ -167,12 +167,21 @@ void parse_groups(const std::set<std::string>& all, const std::string& groups, s
   if (lig.empty() || rec.empty()) throw Error{ARP_ERR_EMPTY_GROUP, "Empty chain groups!"};
 }
 
+static bool is_ring_residue_name(const std::string& s) { return s == "HIS" || s == "PHE" || s == "TYR" || s == "TRP"; }
+
 void pack_records(const arp_atom_record* recs, int64_t n, const std::string& groups, bool ignore_zero_occupancy, uint32_t flags,
                   Packed& P) {
   if (n >= (int64_t)1 << 31) throw Error{ARP_ERR_LIMIT, "more than 2^31 atom records"};
   // ---- 1. group records into the hierarchy --------------------------------------------------------
   std::vector<ModelT> models;
+  std::vector<int32_t> name_id((size_t)n);
   {
+    struct NameSlot {
+      uint64_t raw;
+      int32_t id;
+    };
+    NameSlot name_cache[64];
+    for (auto& e : name_cache) e = NameSlot{0, -1};
     int64_t mi = -1, ci = -1, ri = -1;
     // one-entry caches so that runs of equal fields cost no hashing
     char last_chain[8] = {1}, last_resn[8] = {1}, last_alt[2] = {1}, last_ic[2] = {1};
@@ -238,6 +247,15 @@ void pack_records(const arp_atom_record* recs, int64_t n, const std::string& gro
         cf = &R.confs.back();
       }
       cf->recs.push_back(k);
+      // atom-name id of the record: a direct-mapped cache on the 8 raw bytes in front of the string table
+      uint64_t raw;
+      std::memcpy(&raw, r.name, 8);
+      NameSlot& ns = name_cache[(raw * 0x9E3779B97F4A7C15ull) >> 58];
+      if (ns.id < 0 || ns.raw != raw) {
+        ns.raw = raw;
+        ns.id = P.intern(fixed_field(r.name, 8));
+      }
+      name_id[k] = ns.id;
     }
   }
   const int32_t blank = P.intern("");
@@ -292,35 +310,81 @@ void pack_records(const arp_atom_record* recs, int64_t n, const std::string& gro
 
   // ---- 5. planes (complex.rs:442-514), including the multi-model key overwrite (ledger item 12) ------
   const bool quirk = models.size() > 1 && !(flags & ARPH_FLAG_NO_MULTIMODEL_QUIRK);
-  auto residue_plane = [&](const ResT& R, const std::string& resn, uint32_t want, Plane& out) {
+  // table bits of every record by RESIDUE name (residue().name(): planes, hydrophobic.rs:16, aromatic.rs:18, vdw.rs:50),
+  // looked up once per (residue name, atom name) pair and shared by the plane fits and the attribute words below
+  std::unordered_map<uint64_t, uint32_t> bits_cache;
+  auto bits_of = [&](int32_t resn_id, int32_t atom_id) {
+    const uint64_t key = ((uint64_t)(uint32_t)resn_id << 32) | (uint32_t)atom_id;
+    auto it = bits_cache.find(key);
+    if (it != bits_cache.end()) return it->second;
+    const uint32_t b = table_bits(P.strings[resn_id], P.strings[atom_id]);
+    bits_cache.emplace(key, b);
+    return b;
+  };
+  std::vector<uint32_t> bits_res((size_t)n, 0u);
+  std::vector<const ResT*> all_res;  // every residue, models / chains / residues in order
+  for (auto& M : models)
+    for (auto& Cn : M.chains)
+      for (auto& R : Cn.residues) {
+        all_res.push_back(&R);
+        const int32_t nm = uniform_name(R);
+        int32_t last_atom = -1;
+        uint32_t last_bits = 0;
+        for (auto& c : R.confs)
+          for (int64_t k : c.recs) {
+            if (name_id[k] != last_atom) {
+              last_atom = name_id[k];
+              last_bits = bits_of(nm, last_atom);
+            }
+            bits_res[k] = last_bits;
+          }
+      }
+  auto residue_plane = [&](const ResT& R, uint32_t want, Plane& out) {  // thread-safe: reads only
     std::vector<double> pts;
     for (auto& c : R.confs)
       for (int64_t k : c.recs)
-        if (table_bits(resn, fixed_field(recs[k].name, 8)) & want) {
+        if (bits_res[k] & want) {
           pts.push_back(recs[k].x);
           pts.push_back(recs[k].y);
           pts.push_back(recs[k].z);
         }
     return fit_plane(pts.data(), (int64_t)pts.size() / 3, out);
   };
-  auto is_ring_residue = [](const std::string& s) { return s == "HIS" || s == "PHE" || s == "TYR" || s == "TRP"; };
+  // the plane fits (one small SVD per residue, two for ring residues) are independent: all host threads
+  struct ResPlanes {
+    Plane ring, sc;
+    bool ok_ring, ok_sc, ring_res;
+  };
+  std::vector<ResPlanes> planes(all_res.size());
+  {
+    std::vector<char> ring_name_flag(P.strings.size(), 0);
+    for (size_t i = 0; i < P.strings.size(); ++i) ring_name_flag[i] = is_ring_residue_name(P.strings[i]) ? 1 : 0;
+    const int64_t nres_all = (int64_t)all_res.size();
+#pragma omp parallel for schedule(static, 256) if (nres_all > 8192)
+    for (int64_t i = 0; i < nres_all; ++i) {
+      const ResT& R = *all_res[i];
+      ResPlanes& o = planes[i];
+      o.ring_res = ring_name_flag[uniform_name(R)] != 0;
+      o.ok_ring = o.ring_res && residue_plane(R, T_RING, o.ring);
+      o.ok_sc = residue_plane(R, T_SCP, o.sc);
+    }
+  }
   using PKey = std::array<int64_t, 5>;  // chain, resi, icode, altloc, resn
   std::map<PKey, Plane> last_ring, last_sc;
-  if (quirk)
+  if (quirk) {
+    size_t ri_all = 0;
     for (auto& M : models)
       for (auto& Cn : M.chains)
         for (auto& R : Cn.residues) {
           const int32_t nm = uniform_name(R);
-          const std::string& resn = P.strings[nm];
-          Plane pr, ps;
-          const bool okr = is_ring_residue(resn) && residue_plane(R, resn, T_RING, pr);
-          const bool oks = residue_plane(R, resn, T_SCP, ps);
+          const ResPlanes& pl = planes[ri_all++];
           for (auto& c : R.confs) {
             const PKey key{Cn.id, R.resi, R.icode, c.altloc, nm};
-            if (okr) last_ring[key] = pr;
-            if (oks) last_sc[key] = ps;
+            if (pl.ok_ring) last_ring[key] = pl.ring;
+            if (pl.ok_sc) last_sc[key] = pl.sc;
           }
         }
+  }
 
   // ---- 6. flatten in atoms_with_hierarchy() order ------------------------------------------------------
   int64_t n_atoms = 0, n_res = 0;
@@ -344,22 +408,10 @@ void pack_records(const arp_atom_record* recs, int64_t n, const std::string& gro
   P.res_cb.reserve(n_res);
   P.res_sg.reserve(n_res);
 
-  // cache: (resn id, atom name bytes) -> table bits, to avoid string building per atom
-  std::unordered_map<uint64_t, uint32_t> bits_cache;
-  std::unordered_map<std::string, int32_t> name_ids;
-  auto bits_of = [&](int32_t resn_id, int32_t atom_id) {
-    const uint64_t key = ((uint64_t)(uint32_t)resn_id << 32) | (uint32_t)atom_id;
-    auto it = bits_cache.find(key);
-    if (it != bits_cache.end()) return it->second;
-    const uint32_t b = table_bits(P.strings[resn_id], P.strings[atom_id]);
-    bits_cache.emplace(key, b);
-    return b;
-  };
   const int32_t id_CB = P.intern("CB"), id_SG = P.intern("SG"), id_C = P.intern("C"), id_CYS = P.intern("CYS");
-  char last_name[8] = {1};
-  int32_t last_name_id = -1;
   char last_el[4] = {1};
   int last_el_class = -2;
+  size_t res_all = 0;  // index into planes[]
 
   for (size_t mi = 0; mi < models.size(); ++mi) {
     const ModelT& M = models[mi];
@@ -375,12 +427,13 @@ void pack_records(const arp_atom_record* recs, int64_t n, const std::string& gro
         P.res_cb.push_back(-1);
         P.res_sg.push_back(-1);
         P.res_h_begin.push_back((uint32_t)P.hx.size());
+        const ResPlanes& pl = planes[res_all++];
         Plane pr{}, ps{};
         bool okr = false, oks = false;
-        const bool ring_res = is_ring_residue(resn);
+        const bool ring_res = pl.ring_res;
         if (!quirk) {
-          okr = ring_res && residue_plane(R, resn, T_RING, pr);
-          oks = residue_plane(R, resn, T_SCP, ps);
+          okr = pl.ok_ring, oks = pl.ok_sc;
+          pr = pl.ring, ps = pl.sc;
         }
         for (auto& c : R.confs) {
           if (quirk) {
@@ -418,10 +471,7 @@ void pack_records(const arp_atom_record* recs, int64_t n, const std::string& gro
           }
           for (int64_t k : c.recs) {
             const arp_atom_record& a = recs[k];
-            if (std::memcmp(last_name, a.name, 8) != 0 || last_name_id < 0) {
-              std::memcpy(last_name, a.name, 8);
-              last_name_id = P.intern(fixed_field(a.name, 8));
-            }
+            const int32_t last_name_id = name_id[k];
             if (std::memcmp(last_el, a.element, 4) != 0 || last_el_class == -2) {
               std::memcpy(last_el, a.element, 4);
               last_el_class = arp_element_class(fixed_field(a.element, 4).c_str());
@@ -431,8 +481,8 @@ void pack_records(const arp_atom_record* recs, int64_t n, const std::string& gro
               throw Error{ARP_ERR_ELEMENT, el.empty() ? "atom " + std::to_string(a.serial) + " has no element"
                                                       : "element '" + el + "' has no van der Waals radius"};
             }
-            const uint32_t by_conf = bits_of(c.name, last_name_id);   // conformer().name(): ionic.rs:45-46, hbond.rs:120-121
-            const uint32_t by_res = bits_of(resn_id, last_name_id);   // residue().name(): hydrophobic.rs:16, aromatic.rs:18, vdw.rs:50
+            const uint32_t by_res = bits_res[k];                      // residue().name(): hydrophobic.rs:16, aromatic.rs:18, vdw.rs:50
+            const uint32_t by_conf = c.name == resn_id ? by_res : bits_of(c.name, last_name_id);  // conformer().name(): ionic.rs:45-46, hbond.rs:120-121
             uint32_t w = (uint32_t)last_el_class | group_bits;
             if (by_conf & T_POS) w |= ARP_ATTR_POS_CONF;
             if (by_conf & T_NEG) w |= ARP_ATTR_NEG_CONF;

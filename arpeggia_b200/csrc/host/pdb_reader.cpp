@@ -1,7 +1,8 @@
 // Fixed-column PDB reader for the host side: the ATOM / HETATM / MODEL subset that
 // pdbtbx ReadOptions{only_atomic_coords: true, level: Loose} keeps (src/utils.rs:53-57).
-// Whole-file read, then a single pass over line views; numbers via std::from_chars (correctly rounded,
-// like Rust's str::parse::<f64>).
+// Whole-file read, then one pass over line views per host thread (the text is cut at line boundaries); numbers via
+// std::from_chars (correctly rounded, like Rust's str::parse::<f64>).
+#include <algorithm>
 #include <charconv>
 #include <cstdio>
 #include <cstdlib>
@@ -10,6 +11,9 @@
 #include <vector>
 
 #include "common.hpp"
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 namespace {
 
@@ -63,57 +67,110 @@ int arph_parse_pdb(const char* path, arp_atom_record** out, int64_t* n) {
   }
   std::string text;
   {
+    // one read of the whole file when its size is known (regular files), 64 KB pieces otherwise (pipes)
+    long size = -1;
+    if (std::fseek(f, 0, SEEK_END) == 0) size = std::ftell(f);
+    std::rewind(f);
+    if (size > 0) {
+      text.resize((size_t)size);
+      const size_t got = std::fread(text.data(), 1, (size_t)size, f);
+      text.resize(got);
+    }
     char chunk[1 << 16];
     size_t got;
     while ((got = std::fread(chunk, 1, sizeof chunk, f)) > 0) text.append(chunk, got);
   }
   std::fclose(f);
 
-  std::vector<arp_atom_record> recs;
-  recs.reserve(text.size() / 81 + 1);
-  int64_t model = 0;
-  size_t pos = 0;
-  while (pos < text.size()) {
-    size_t eol = text.find('\n', pos);
-    if (eol == std::string::npos) eol = text.size();
-    std::string_view line(text.data() + pos, eol - pos);
-    pos = eol + 1;
-    if (!line.empty() && line.back() == '\r') line.remove_suffix(1);
-    if (line.size() < 6) continue;
-    const std::string_view tag = line.substr(0, 6);
-    if (tag.substr(0, 5) == "MODEL") {
-      int64_t m = 0;
-      if (number(field(line, 7, 20), m)) model = m;
-      continue;
-    }
-    const bool het = tag == "HETATM";
-    if (!het && tag != "ATOM  ") continue;
-    arp_atom_record r;
-    std::memset(&r, 0, sizeof r);
-    r.hetero = het ? 1 : 0;
-    r.model = model;
-    number(field(line, 7, 11), r.serial);
-    store(r.name, sizeof r.name, field(line, 13, 16));
-    store(r.altloc, sizeof r.altloc, field(line, 17, 17));
-    store(r.resn, sizeof r.resn, field(line, 18, 20));
-    store(r.chain, sizeof r.chain, field(line, 22, 22));
-    number(field(line, 23, 26), r.resi);
-    store(r.icode, sizeof r.icode, field(line, 27, 27));
-    number(field(line, 31, 38), r.x);
-    number(field(line, 39, 46), r.y);
-    number(field(line, 47, 54), r.z);
-    r.occupancy = 1.0;
-    number(field(line, 55, 60), r.occupancy);
-    element_of(line, r.element);
-    recs.push_back(r);
+  // Lines are independent except for the MODEL serial they inherit: the text is cut into one chunk per host thread at line
+  // boundaries, every chunk is parsed on its own (records + the MODEL lines it saw), then the serials are carried across
+  // the chunks in order and the records concatenated.
+  struct Chunk {
+    std::vector<arp_atom_record> recs;
+    std::vector<std::pair<size_t, int64_t>> marks;  // (records of this chunk before the MODEL line, its serial)
+  };
+  int T = 1;
+#ifdef _OPENMP
+  T = std::max(1, std::min(omp_get_max_threads(), (int)(text.size() / (1u << 20)) + 1));
+#endif
+  std::vector<size_t> cut((size_t)T + 1, text.size());
+  cut[0] = 0;
+  for (int t = 1; t < T; ++t) {
+    size_t p = text.size() / (size_t)T * (size_t)t;
+    p = text.find('\n', std::max(p, cut[(size_t)t - 1]));
+    cut[(size_t)t] = p == std::string::npos ? text.size() : p + 1;
   }
-  *n = (int64_t)recs.size();
-  *out = (arp_atom_record*)std::malloc(std::max<size_t>(1, recs.size()) * sizeof(arp_atom_record));
+  std::vector<Chunk> chunks((size_t)T);
+#pragma omp parallel for schedule(static, 1) num_threads(T)
+  for (int t = 0; t < T; ++t) {
+    Chunk& C = chunks[(size_t)t];
+    const size_t end = cut[(size_t)t + 1];
+    C.recs.reserve((end - cut[(size_t)t]) / 81 + 1);
+    size_t pos = cut[(size_t)t];
+    while (pos < end) {
+      size_t eol = text.find('\n', pos);
+      if (eol == std::string::npos) eol = text.size();
+      std::string_view line(text.data() + pos, eol - pos);
+      pos = eol + 1;
+      if (!line.empty() && line.back() == '\r') line.remove_suffix(1);
+      if (line.size() < 6) continue;
+      const std::string_view tag = line.substr(0, 6);
+      if (tag.substr(0, 5) == "MODEL") {
+        int64_t m = 0;
+        if (number(field(line, 7, 20), m)) C.marks.emplace_back(C.recs.size(), m);
+        continue;
+      }
+      const bool het = tag == "HETATM";
+      if (!het && tag != "ATOM  ") continue;
+      arp_atom_record r;
+      std::memset(&r, 0, sizeof r);
+      r.hetero = het ? 1 : 0;
+      number(field(line, 7, 11), r.serial);
+      store(r.name, sizeof r.name, field(line, 13, 16));
+      store(r.altloc, sizeof r.altloc, field(line, 17, 17));
+      store(r.resn, sizeof r.resn, field(line, 18, 20));
+      store(r.chain, sizeof r.chain, field(line, 22, 22));
+      number(field(line, 23, 26), r.resi);
+      store(r.icode, sizeof r.icode, field(line, 27, 27));
+      number(field(line, 31, 38), r.x);
+      number(field(line, 39, 46), r.y);
+      number(field(line, 47, 54), r.z);
+      r.occupancy = 1.0;
+      number(field(line, 55, 60), r.occupancy);
+      element_of(line, r.element);
+      C.recs.push_back(r);
+    }
+  }
+  size_t total = 0;
+  std::vector<size_t> first((size_t)T + 1, 0);
+  std::vector<int64_t> model_in((size_t)T, 0);  // MODEL serial in force where the chunk starts
+  {
+    int64_t model = 0;
+    for (int t = 0; t < T; ++t) {
+      model_in[(size_t)t] = model;
+      if (!chunks[(size_t)t].marks.empty()) model = chunks[(size_t)t].marks.back().second;
+      first[(size_t)t] = total;
+      total += chunks[(size_t)t].recs.size();
+    }
+    first[(size_t)T] = total;
+  }
+  *n = (int64_t)total;
+  *out = (arp_atom_record*)std::malloc(std::max<size_t>(1, total) * sizeof(arp_atom_record));
   if (!*out) {
     arp::last_error() = "out of host memory";
     return ARP_ERR_OOM;
   }
-  if (!recs.empty()) std::memcpy(*out, recs.data(), recs.size() * sizeof(arp_atom_record));
+#pragma omp parallel for schedule(static, 1) num_threads(T)
+  for (int t = 0; t < T; ++t) {
+    Chunk& C = chunks[(size_t)t];
+    int64_t model = model_in[(size_t)t];
+    size_t mk = 0;
+    for (size_t i = 0; i < C.recs.size(); ++i) {
+      while (mk < C.marks.size() && C.marks[mk].first <= i) model = C.marks[mk++].second;
+      C.recs[i].model = model;
+    }
+    if (!C.recs.empty()) std::memcpy(*out + first[(size_t)t], C.recs.data(), C.recs.size() * sizeof(arp_atom_record));
+  }
   return ARP_OK;
 }
 }
