@@ -104,7 +104,6 @@ struct arp_ctx {
   DBuf<uint32_t> cell_of, rank_of, cell_start;
   DBuf<unsigned long long> scan_status, rscan_status;
   DBuf<uint32_t> rcell_of, rrank_of, rcell_start, rperm, cations;
-  DBuf<uint32_t> slot_item;  // sorted slot -> work item of its cell (k_screen_atoms)
   DBuf<float> pos2;          // sorted positions interleaved per slot pair (k_screen_atoms)
   DBuf<uint2> skey;          // (chain key, residue ordinal) per sorted slot (k_screen_atoms)
   DBuf<RecA> recA;

@@ -130,6 +130,9 @@ constexpr int SCAN_THREADS = 256;
 #endif
 constexpr int SCAN_PER_THREAD = SCAN_PT;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_PER_THREAD;
+#ifndef SCAN_LOOK
+#define SCAN_LOOK 4  // windows of 32 predecessor tiles fetched per look-back round trip
+#endif
 
 __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* total) {
   __shared__ uint32_t wsum[SCAN_THREADS / 32];
@@ -174,11 +177,20 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_lookback(uint32_t* __rest
   const uint32_t tile = s_tile;
   const uint32_t base = tile * SCAN_TILE + threadIdx.x * SCAN_PER_THREAD;
   uint32_t v[SCAN_PER_THREAD], sum = 0;
+  // whole tiles move as 16-byte words (cudaMalloc'ed base, SCAN_PER_THREAD a multiple of 4); the last tile goes word by word
+  const bool wide = (SCAN_PER_THREAD % 4 == 0) && (unsigned long long)(tile + 1u) * SCAN_TILE <= n && (reinterpret_cast<uintptr_t>(data) & 15u) == 0u;
+  if (wide) {
 #pragma unroll
-  for (int k = 0; k < SCAN_PER_THREAD; ++k) {
-    v[k] = base + k < n ? data[base + k] : 0u;
-    sum += v[k];
+    for (int k = 0; k < SCAN_PER_THREAD / 4; ++k) {
+      const uint4 q = reinterpret_cast<const uint4*>(data + base)[k];
+      v[4 * k] = q.x, v[4 * k + 1] = q.y, v[4 * k + 2] = q.z, v[4 * k + 3] = q.w;
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < SCAN_PER_THREAD; ++k) v[k] = base + k < n ? data[base + k] : 0u;
   }
+#pragma unroll
+  for (int k = 0; k < SCAN_PER_THREAD; ++k) sum += v[k];
   uint32_t total;
   uint32_t run = block_exclusive_scan(sum, &total);
   volatile unsigned long long* vs = status;
@@ -191,42 +203,67 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_lookback(uint32_t* __rest
       }
     } else {
       if (lane == 0) vs[tile] = SCAN_FLAG_A | total;
-      unsigned long long prefix = 0;
-      long long first = (long long)tile - 1;  // lane l looks at tile first - l
+      // The look-back is the serial part of the scan (all tiles of a cell table are resident at once, so the inclusive
+      // prefixes spread at one window per memory round trip): a round trip fetches SCAN_LOOK windows of 32 predecessors,
+      // lane l of window k looking at tile first - 32 k - l, and consumes them in order up to the first window that still
+      // has an unpublished tile.
+      unsigned long long part = 0;            // per lane; summed over the warp once at the end
+      long long first = (long long)tile - 1;
       uint32_t spins = 0;
-      while (true) {
-        const long long j = first - lane;
-        unsigned long long w = SCAN_FLAG_P;
-        if (j >= 0) w = vs[j];
-        const uint32_t flag = (uint32_t)(w >> 62);
-        if (__any_sync(0xffffffffu, flag == 0u)) {
-          if (++spins > (1u << 22)) {  // cannot happen (see above); never hang a GPU over it
-            if (lane == 0) atomicOr(error, 4u);
-            break;
-          }
-          continue;
-        }
-        const uint32_t pm = __ballot_sync(0xffffffffu, flag == 2u);
-        const int stop = pm ? (__ffs(pm) - 1) : 31;  // nearest predecessor that already has its inclusive prefix
-        unsigned long long part = lane <= stop ? (w & SCAN_VALUE) : 0ull;
+      bool found = false;
+      while (!found) {
+        unsigned long long w[SCAN_LOOK];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-        prefix += part;
-        if (pm) break;
-        first -= 32;
+        for (int k = 0; k < SCAN_LOOK; ++k) {
+          const long long j = first - 32 * k - lane;
+          w[k] = j >= 0 ? vs[j] : SCAN_FLAG_P;  // before tile 0: an inclusive prefix of 0
+        }
+        int used = 0;
+#pragma unroll
+        for (int k = 0; k < SCAN_LOOK; ++k) {
+          if (!found && used == k) {
+            const uint32_t flag = (uint32_t)(w[k] >> 62);
+            if (!__any_sync(0xffffffffu, flag == 0u)) {
+              const uint32_t pm = __ballot_sync(0xffffffffu, flag == 2u);
+              const int stop = pm ? (__ffs(pm) - 1) : 31;  // nearest predecessor that already has its inclusive prefix
+              if (lane <= stop) part += w[k] & SCAN_VALUE;
+              used = k + 1;
+              found = pm != 0u;
+            }
+          }
+        }
+        first -= 32 * used;
+        if (used == 0 && ++spins > (1u << 22)) {  // cannot happen (see above); never hang a GPU over it
+          if (lane == 0) atomicOr(error, 4u);
+          break;
+        }
       }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
       if (lane == 0) {
-        vs[tile] = SCAN_FLAG_P | ((prefix + total) & SCAN_VALUE);
-        s_prefix = (uint32_t)prefix;
+        vs[tile] = SCAN_FLAG_P | ((part + total) & SCAN_VALUE);
+        s_prefix = (uint32_t)part;
       }
     }
   }
   __syncthreads();
   run += s_prefix;
+  if (wide) {
 #pragma unroll
-  for (int k = 0; k < SCAN_PER_THREAD; ++k) {
-    if (base + k < n) data[base + k] = run;
-    run += v[k];
+    for (int k = 0; k < SCAN_PER_THREAD / 4; ++k) {
+      uint4 q;
+      q.x = run, run += v[4 * k];
+      q.y = run, run += v[4 * k + 1];
+      q.z = run, run += v[4 * k + 2];
+      q.w = run, run += v[4 * k + 3];
+      reinterpret_cast<uint4*>(data + base)[k] = q;
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < SCAN_PER_THREAD; ++k) {
+      if (base + k < n) data[base + k] = run;
+      run += v[k];
+    }
   }
 }
 
@@ -264,11 +301,12 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
                 const uint32_t* __restrict__ res_id, const uint32_t* __restrict__ res_chain_key, const uint32_t* __restrict__ res_res_ordinal,
                 const uint32_t* __restrict__ atom_struct, const StructDesc* __restrict__ descs, const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of, const uint32_t* __restrict__ cell_start,
                 uint32_t n, double edge, double inv_edge, RecA* __restrict__ recA, RecB* __restrict__ recB, Item* __restrict__ items,
-                uint32_t* __restrict__ cations, Counters* __restrict__ ctr, uint32_t* __restrict__ slot_item,
-                float* __restrict__ pos2, uint2* __restrict__ skey) {
+                uint32_t* __restrict__ cations, Counters* __restrict__ ctr, float* __restrict__ pos2, uint2* __restrict__ skey) {
   // slots in `items` / `cations` are reserved per BLOCK (shared-memory counters, one global atomicAdd each): the 110 000
   // same-address atomics of a one-per-cell reservation were 40 % of this kernel's stall samples
   __shared__ uint32_t s_items, s_cat, s_items_base, s_cat_base;
+  __shared__ uint32_t s_fc[256], s_fs[256];  // cell, structure and position of the block's first arrivals, compacted
+  __shared__ double s_fp[3][256];
   if (threadIdx.x == 0) s_items = s_cat = 0u;
   __syncthreads();
   const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
@@ -304,9 +342,10 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
   rb.chain_key = ra.chain_key;
   rb.res_ordinal = ra.res_ordinal;
   recB[slot] = rb;
-  if (pos2) {  // what k_screen_atoms reads: positions interleaved per slot PAIR (x0 x1 | y0 y1 | z0 z1 | pad: 32 bytes), keys per slot
+  if (pos2) {  // what k_screen_atoms reads: positions interleaved per slot PAIR (x0 x1 | y0 y1 | z0 z1 | c0 c1: 32 bytes), keys per slot
     float* q = pos2 + 8u * (size_t)(slot >> 1) + (slot & 1u);
     q[0] = ra.x, q[2] = ra.y, q[4] = ra.z;
+    q[6] = __uint_as_float(slot - r);  // the cell's first slot = where its work item sits (below)
     skey[slot] = make_uint2(ra.chain_key, ra.res_ordinal);
   }
   }
@@ -324,6 +363,7 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
     my_cat = __shfl_sync(0xffffffffu, wc, 0) + __popc(bc & lt);
     my_item = __shfl_sync(0xffffffffu, wi, 0) + __popc(bi & lt);
   }
+  if (first) s_fc[my_item] = c, s_fs[my_item] = s, s_fp[0][my_item] = px, s_fp[1][my_item] = py, s_fp[2][my_item] = pz;
   __syncthreads();
   if (threadIdx.x == 0) {
     s_cat_base = s_cat ? atomicAdd(&ctr->n_cations, s_cat) : 0u;
@@ -331,17 +371,21 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
   }
   __syncthreads();
   if (is_cat) cations[s_cat_base + my_cat] = slot;
-  if (first) {  // the cell's half shell as 5 runs of sorted slots
-    const StructDesc& d = descs[s];
+  // the cells' half shells as 5 runs of sorted slots, one THREAD per first arrival of the block (one atom in four starts a
+  // cell at the emit-radius edge: built in place, three quarters of every warp idled through these 150 instructions)
+  for (uint32_t i = threadIdx.x; i < s_items; i += blockDim.x) {
+    const uint32_t fc = s_fc[i], fs = s_fs[i];
+    const StructDesc& d = descs[fs];
     const int nx = d.nx, ny = d.ny, nz = d.nz;
     // the cell coordinates from the position, exactly as k_cell_assign computed them (no integer divisions)
-    const int ix = cell_coord(px, d.ox, inv_edge, nx), iy = cell_coord(py, d.oy, inv_edge, ny), iz = cell_coord(pz, d.oz, inv_edge, nz);
+    const int ix = cell_coord(s_fp[0][i], d.ox, inv_edge, nx), iy = cell_coord(s_fp[1][i], d.oy, inv_edge, ny),
+              iz = cell_coord(s_fp[2][i], d.oz, inv_edge, nz);
     Item it;
-    it.cb = cell_start[c];
-    it.n_own = cell_start[c + 1] - it.cb;
-    it.sid = s;
+    it.cb = cell_start[fc];
+    it.n_own = cell_start[fc + 1] - it.cb;
+    it.sid = fs;
     // run 0: own cell and its +x neighbour; runs 1..4: rows (dy, dz) = (+1,0) (-1,+1) (0,+1) (+1,+1), x from ix-1 to ix+1
-    uint32_t acc = cell_start[c + (ix + 1 < nx ? 2 : 1)] - it.cb;
+    uint32_t acc = cell_start[fc + (ix + 1 < nx ? 2 : 1)] - it.cb;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const int dy = (k == 0) ? 1 : (k - 2), dz = (k == 0) ? 0 : 1;
@@ -361,10 +405,9 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
     it.cy = (float)(((double)iy + 0.5) * edge);
     it.cz = (float)(((double)iz + 0.5) * edge);
     it.pad = 0;
-    items[s_items_base + my_item] = it;
-    // k_screen_atoms (one lane per atom) finds its cell's half shell through this
-    if (slot_item)
-      for (uint32_t k = 0; k < it.n_own; ++k) slot_item[it.cb + k] = s_items_base + my_item;
+    // counting mode: a compact list (k_screen hands the items out to warps); emit-radius mode: the item sits at the cell's
+    // first slot, which every atom of the cell knows (slot - rank) and leaves in its position record for k_screen_atoms
+    items[pos2 ? it.cb : s_items_base + i] = it;
   }
 }
 

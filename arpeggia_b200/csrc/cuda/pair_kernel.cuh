@@ -910,7 +910,7 @@ __device__ __forceinline__ void sa_flush(const PairArgs& G, const DevParams& P, 
   }
 }
 
-__global__ void __launch_bounds__(SA_THREADS, SA_MIN_BLOCKS) k_screen_atoms(const PairArgs G, const DevParams P, const uint32_t* __restrict__ slot_item,
+__global__ void __launch_bounds__(SA_THREADS, SA_MIN_BLOCKS) k_screen_atoms(const PairArgs G, const DevParams P,
                                                                             const unsigned long long* __restrict__ pos2, const uint2* __restrict__ key,
                                                                             uint32_t n_atoms) {
   __shared__ SaSmem S;
@@ -937,7 +937,8 @@ __global__ void __launch_bounds__(SA_THREADS, SA_MIN_BLOCKS) k_screen_atoms(cons
     if (slot < n_atoms) {
       const uint4 a0 = *reinterpret_cast<const uint4*>(G.recA + slot);
       mine = key[slot];
-      const uint4* ip = reinterpret_cast<const uint4*>(G.items + slot_item[slot]);
+      // the pair record's fourth word pair holds the cells' first slots (k_scatter_atoms): the work item sits there
+      const uint4* ip = reinterpret_cast<const uint4*>(G.items + reinterpret_cast<const uint32_t*>(pos2)[8u * (slot >> 1) + 6u + (slot & 1u)]);
       const uint4 i0 = ip[0], off = ip[1], dl = ip[2];  // (cb, n_own, total, sid), off[4], delta[4]
       nax = sa_dup(-__uint_as_float(a0.x)), nay = sa_dup(-__uint_as_float(a0.y)), naz = sa_dup(-__uint_as_float(a0.z));
       tlim = fminf(P.thr_near, atom_limit2(P, S.lim1, a0.w));  // no label can fire for this atom beyond its own limit

@@ -401,3 +401,33 @@ def test_frame_argument_errors(ctx, ubq, bft):
     _lib.check(L.arp_stage_frame(ctx._h, tu, C.byref(fp)), ctx._h)  # and the context is still usable
     assert fp.contents.n_rows == 532
     L.arp_frame_free(ctx._h, fp)
+
+
+def test_contexts_on_several_host_threads_same_rows(ubq, bft):
+    """One arp_ctx per host thread (include/arpeggia_cuda.h): jobs of different contexts overlap on the device and must
+    not see each other -- every thread gets the rows a lone context gets, for two different structures in alternation."""
+    import threading
+
+    packed = [A.Packed(ubq, "/"), A.Packed(bft, "/")]
+    lone = A.Context(0)
+    want = [np.sort(lone.contacts_rows(p, 0.1, 6.5, flags=f)["rows"], order=["from", "to", "label"]) for p in packed for f in (0, 1)]
+    errors = []
+
+    def worker(k):
+        try:
+            c = A.Context(0)
+            for it in range(12):
+                j = (it + k) % 4
+                got = np.sort(c.contacts_rows(packed[j // 2], 0.1, 6.5, flags=j % 2)["rows"], order=["from", "to", "label"])
+                if not np.array_equal(got, want[j]):
+                    errors.append((k, it, j, len(got), len(want[j])))
+            c.close()
+        except Exception as e:  # noqa: BLE001
+            errors.append((k, repr(e)))
+
+    th = [threading.Thread(target=worker, args=(k,)) for k in range(4)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not errors, errors
