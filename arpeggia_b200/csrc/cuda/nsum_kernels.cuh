@@ -9,33 +9,57 @@
 
 namespace arpd {
 
-struct __align__(32) NsRec {  // one sector per atom
+struct __align__(32) NsRec {  // one sector per selected atom
   double x, y, z;
   float w;
-  uint32_t perm_sel;  // input-order index | selected << 31
+  uint32_t perm;  // input-order index
 };
 
-struct __align__(16) NsRecF {  // what the f32 screen reads: position relative to the grid origin, weight (0 when not selected)
+struct __align__(16) NsRecF {  // what the f32 screen reads: position relative to the grid origin, weight
   float x, y, z, w;
 };
 
+constexpr uint32_t NS_UNSELECTED = 0xffffffffu;
+
+// The cell list holds the SELECTED atoms only (SAP selects the side-chain atoms, about half of a protein): an unselected
+// atom neither contributes nor receives (sap.rs:181-215 iterates over the selected set), so it gets its 0 here and is
+// never sorted, screened or given a lane in the sum.
+__global__ void __launch_bounds__(256)
+k_ns_cell_assign(const double* __restrict__ x, const double* __restrict__ y, const double* __restrict__ z,
+                 const unsigned char* __restrict__ select, uint32_t n, const StructDesc d, double inv_edge, uint32_t* __restrict__ cell_of,
+                 uint32_t* __restrict__ rank_of, uint32_t* __restrict__ cell_count, float* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (!select[i]) {
+    cell_of[i] = NS_UNSELECTED;
+    out[i] = 0.f;
+    return;
+  }
+  const int ix = cell_coord(x[i], d.ox, inv_edge, d.nx), iy = cell_coord(y[i], d.oy, inv_edge, d.ny), iz = cell_coord(z[i], d.oz, inv_edge, d.nz);
+  const uint32_t c = d.cell_base + (uint32_t)((iz * d.ny + iy) * d.nx + ix);
+  cell_of[i] = c;
+  rank_of[i] = atomicAdd(&cell_count[c], 1u);
+}
+
 __global__ void __launch_bounds__(256)
 k_ns_scatter(const double* __restrict__ x, const double* __restrict__ y, const double* __restrict__ z, const float* __restrict__ weight,
-             const unsigned char* __restrict__ select, const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of,
-             const uint32_t* __restrict__ cell_start, uint32_t n, double ox, double oy, double oz, NsRec* __restrict__ rec,
-             NsRecF* __restrict__ recf) {
+             const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of, const uint32_t* __restrict__ cell_start, uint32_t n,
+             double ox, double oy, double oz, NsRec* __restrict__ rec, NsRecF* __restrict__ recf) {
   const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
   if (a >= n) return;
+  const uint32_t c = cell_of[a];
+  if (c == NS_UNSELECTED) return;
   NsRec r;
   r.x = x[a], r.y = y[a], r.z = z[a];
-  r.w = select[a] ? weight[a] : 0.f;  // an unselected atom contributes nothing (and never receives: perm_sel)
-  r.perm_sel = a | (select[a] ? 0x80000000u : 0u);
-  const uint32_t slot = cell_start[cell_of[a]] + rank_of[a];
+  r.w = weight[a];
+  r.perm = a;
+  const uint32_t slot = cell_start[c] + rank_of[a];
   rec[slot] = r;
   recf[slot] = NsRecF{(float)(r.x - ox), (float)(r.y - oy), (float)(r.z - oz), r.w};
 }
 
-// One lane per sorted slot.  Every candidate of the 27-cell shell is screened in f32 on the origin-relative positions
+// One lane per sorted slot (= per selected atom; cell_start[n_cells] is their number).  Every candidate of the 27-cell
+// shell is screened in f32 on the origin-relative positions
 // (difference form; |d2_f32 - d2| < g, the guard band of the contacts path, api_run.inc): d2_f32 <= r2 - g is certainly
 // inside, d2_f32 > r2 + g certainly outside, and only the shell in between takes the exact FP64 test in the reference's
 // operation order ((dx*dx + dy*dy) + dz*dz, every operation rounded once, inclusive comparison) -- so the neighbour SET
@@ -43,15 +67,10 @@ k_ns_scatter(const double* __restrict__ x, const double* __restrict__ y, const d
 // R*-tree's iteration order, which is unspecified: any order of the same terms lies within n * 2^-24 * sum|w| of this).
 __global__ void __launch_bounds__(256)
 k_neighbor_sum(const NsRec* __restrict__ rec, const NsRecF* __restrict__ recf, const uint32_t* __restrict__ cell_start, const StructDesc d,
-               double inv_edge, double r2, float thr_cert, float thr_hit, uint32_t n, float* __restrict__ out) {
+               uint32_t n_cells, double inv_edge, double r2, float thr_cert, float thr_hit, float* __restrict__ out) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
+  if (i >= cell_start[n_cells]) return;
   const NsRec me = rec[i];
-  const uint32_t perm = me.perm_sel & 0x7fffffffu;
-  if (!(me.perm_sel >> 31)) {
-    out[perm] = 0.f;
-    return;
-  }
   const NsRecF mf = recf[i];
   const int ix = cell_coord(me.x, d.ox, inv_edge, d.nx), iy = cell_coord(me.y, d.oy, inv_edge, d.ny), iz = cell_coord(me.z, d.oz, inv_edge, d.nz);
   const int x0 = max(ix - 1, 0), x1 = min(ix + 1, d.nx - 1);
@@ -81,7 +100,7 @@ k_neighbor_sum(const NsRec* __restrict__ rec, const NsRecF* __restrict__ recf, c
       acc += exact;
     }
   }
-  out[perm] = (float)acc;
+  out[me.perm] = (float)acc;
 }
 
 }  // namespace arpd
