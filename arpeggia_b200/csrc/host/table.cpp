@@ -92,6 +92,7 @@ void build_frame_tables(const Packed& P, FrameTables& T) {
     uint32_t id;
   };
   std::vector<Key> keys(E);
+#pragma omp parallel for schedule(static) if (E > 65536)
   for (size_t e = 0; e < E; ++e) {
     const bool ring = e >= n_atoms;
     const uint32_t rc = ring ? P.ring_rc[e - n_atoms] : P.atom_rc[e];
@@ -103,13 +104,40 @@ void build_frame_tables(const Packed& P, FrameTables& T) {
     T.ent_tie[e] = bad ? ARP_ENT_NARROW : 0u;
     keys[e] = Key{P.resconfs[rc].resi, serial, T.sides[rc].chain_rank, srank[P.resconfs[rc].altloc], (uint32_t)e};
   }
-  std::sort(keys.begin(), keys.end(), [](const Key& a, const Key& b) {
+  const auto key_less = [](const Key& a, const Key& b) {  // a total order (id breaks every tie): one result on any number of threads
     if (a.chain != b.chain) return a.chain < b.chain;
     if (a.resi != b.resi) return a.resi < b.resi;
     if (a.alt != b.alt) return a.alt < b.alt;
     if (a.atomi != b.atomi) return a.atomi < b.atomi;
     return a.id < b.id;
-  });
+  };
+  // The chain rank leads the key: entities are bucketed by chain first (a stable counting sort, O(E)), then every chain
+  // is put in order on its own, chains in parallel.  Within a chain the atoms come first, in file order -- residue by
+  // residue, serials rising, i.e. usually in key order already -- and its few rings after them: each part is sorted only
+  // if it is not sorted yet, then the two are merged.
+  {
+    const size_t n_chains = T.t.n_chain_ranks;
+    std::vector<size_t> begin(n_chains + 1, 0);
+    for (size_t e = 0; e < E; ++e) begin[keys[e].chain + 1] += 1;
+    for (size_t c = 0; c < n_chains; ++c) begin[c + 1] += begin[c];
+    std::vector<Key> by_chain(E);
+    {
+      std::vector<size_t> at(begin.begin(), begin.end() - 1);
+      for (size_t e = 0; e < E; ++e) by_chain[at[keys[e].chain]++] = keys[e];
+    }
+    keys.swap(by_chain);
+    const auto sort_range = [&](Key* b, Key* e) {
+      if (!std::is_sorted(b, e, key_less)) std::sort(b, e, key_less);
+    };
+#pragma omp parallel for schedule(dynamic, 1) if (E > 65536 && n_chains > 1)
+    for (size_t c = 0; c < n_chains; ++c) {
+      Key *b = keys.data() + begin[c], *e = keys.data() + begin[c + 1];
+      Key* mid = std::find_if(b, e, [&](const Key& k) { return k.id >= n_atoms; });  // first ring of the chain
+      sort_range(b, mid);
+      sort_range(mid, e);
+      if (mid != b && mid != e && key_less(*mid, *(mid - 1))) std::inplace_merge(b, mid, e, key_less);
+    }
+  }
   uint32_t rank = 0, tie = 0, max_tie = 0, max_rank = 0;
   for (size_t k = 0; k < E; ++k) {
     if (k > 0 && keys[k].chain == keys[k - 1].chain) {

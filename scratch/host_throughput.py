@@ -18,4 +18,8 @@ t = time.perf_counter(); a = A.parse_pdb(path); out["parse_s"] = time.perf_count
 atoms = synth.assembly_1m(A.parse_pdb(os.path.join(ROOT, "tests", "data", "6bft.pdb")))
 t = time.perf_counter(); p = A.Packed(atoms, "/", flags=2); out["pack_s"] = time.perf_counter() - t
 out["atoms"] = int(p.structure.n_atoms)
+import ctypes as C
+from arpeggia_b200 import _lib
+tp = C.POINTER(_lib.FrameTables)()
+t = time.perf_counter(); _lib.check(_lib.lib().arph_packed_frame_tables(p._h, C.byref(tp))); out["frame_tables_s"] = time.perf_counter() - t
 print(json.dumps(out))
