@@ -360,7 +360,7 @@ void pack_records(const arp_atom_record* recs, int64_t n, const std::string& gro
     std::vector<char> ring_name_flag(P.strings.size(), 0);
     for (size_t i = 0; i < P.strings.size(); ++i) ring_name_flag[i] = is_ring_residue_name(P.strings[i]) ? 1 : 0;
     const int64_t nres_all = (int64_t)all_res.size();
-#pragma omp parallel for schedule(static, 256) if (nres_all > 8192)
+#pragma omp parallel for schedule(static, 32) if (nres_all > 256)  // ~1 us per plane fit: worth the fork from a few hundred residues on
     for (int64_t i = 0; i < nres_all; ++i) {
       const ResT& R = *all_res[i];
       ResPlanes& o = planes[i];
