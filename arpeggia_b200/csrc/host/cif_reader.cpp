@@ -13,6 +13,9 @@
 #include <vector>
 
 #include "common.hpp"
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 namespace {
 
@@ -102,6 +105,105 @@ const char* const kColName[N_COLS] = {"group_PDB",     "id",           "type_sym
                                       "label_comp_id", "auth_comp_id", "label_asym_id", "auth_asym_id",  "label_seq_id",      "auth_seq_id",
                                       "pdbx_PDB_ins_code", "Cartn_x",  "Cartn_y",      "Cartn_z",       "occupancy",         "pdbx_PDB_model_num"};
 
+
+size_t piece_bytes() {  // text per host thread (ARPH_CIF_PIECE_BYTES: a small value lets the tests cut small files)
+  const char* e = std::getenv("ARPH_CIF_PIECE_BYTES");
+  const long v = e ? std::atol(e) : 0;
+  return v > 0 ? (size_t)v : (size_t)1 << 20;
+}
+
+bool is_loop_end(std::string_view tok) {  // an unquoted keyword or tag where a row would start ends the loop
+  return iequals(tok, "loop_") || istarts(tok, "data_") || istarts(tok, "save_") || (!tok.empty() && tok.front() == '_');
+}
+
+// one _atom_site row -> one record; false when a coordinate does not parse
+bool row_to_record(const std::string_view* row, const int* where, arp_atom_record& r) {
+  auto get = [&](int c) -> std::string_view {
+    if (where[c] < 0) return {};
+    const std::string_view v = row[where[c]];
+    return is_null(v) ? std::string_view{} : v;
+  };
+  auto first_of = [&](int a, int b) {
+    const std::string_view v = get(a);
+    return v.empty() ? get(b) : v;
+  };
+  std::memset(&r, 0, sizeof r);
+  r.hetero = iequals(get(GROUP), "HETATM") ? 1 : 0;
+  number(get(ID), r.serial);
+  number(get(MODEL), r.model);
+  store(r.name, sizeof r.name, first_of(LABEL_ATOM, AUTH_ATOM));
+  store(r.resn, sizeof r.resn, first_of(LABEL_COMP, AUTH_COMP));
+  store(r.chain, sizeof r.chain, first_of(AUTH_ASYM, LABEL_ASYM));
+  store(r.altloc, sizeof r.altloc, get(ALT));
+  store(r.icode, sizeof r.icode, get(INS));
+  number(first_of(AUTH_SEQ, LABEL_SEQ), r.resi);
+  if (!number(get(X), r.x) || !number(get(Y), r.y) || !number(get(Z), r.z)) return false;
+  r.occupancy = 1.0;
+  number(get(OCC), r.occupancy);
+  char sym[4] = {0, 0, 0, 0};
+  size_t ns = 0;
+  for (char ch : get(SYMBOL))
+    if (ns < 3) sym[ns++] = (char)std::toupper((unsigned char)ch);
+  if (ns == 0) {  // no type_symbol: leading letters of the atom name, like the fixed-column reader
+    for (char ch : std::string_view(r.name, strnlen(r.name, sizeof r.name)).substr(0, 2))
+      if (std::isalpha((unsigned char)ch)) sym[ns++] = (char)std::toupper((unsigned char)ch);
+    if (ns == 2 && arp_element_class(sym) < 0) sym[1] = 0, ns = 1;
+  }
+  store(r.element, sizeof r.element, std::string_view(sym, ns));
+  return true;
+}
+
+// The _atom_site loop the way every archive file writes it -- one row per line -- on all host threads: the text from the
+// first value on is cut at line ends, every piece tokenises its lines on its own.  A line that is not exactly one row
+// (values wrapped over lines, two rows on a line, a text field) makes the piece give up, and the caller reads the loop
+// with the serial tokenizer instead; the first line that starts with a keyword or tag ends the loop.
+struct CifPiece {
+  std::vector<arp_atom_record> recs;
+  bool irregular = false, ended = false;
+  int64_t bad_row = -1;  // piece-local index of a row with an unreadable coordinate
+};
+
+void parse_piece(std::string_view text, size_t width, const int* where, CifPiece& P) {
+  std::vector<std::string_view> row(width);
+  P.recs.reserve(text.size() / 80 + 1);
+  size_t pos = 0;
+  while (pos < text.size()) {
+    size_t eol = text.find('\n', pos);
+    if (eol == std::string_view::npos) eol = text.size();
+    const std::string_view line = text.substr(pos, eol - pos);
+    pos = eol + 1;
+    if (!line.empty() && line.front() == ';') {
+      P.irregular = true;
+      return;
+    }
+    Tokenizer T{line};
+    T.line_start = false;
+    std::string_view tok;
+    size_t k = 0;
+    bool first_quoted = false;
+    while (T.next(tok)) {
+      if (k == 0) first_quoted = T.quoted;
+      if (k < width) row[k] = tok;
+      ++k;
+    }
+    if (k == 0) continue;  // blank or comment line
+    if (!first_quoted && is_loop_end(row[0])) {
+      P.ended = true;
+      return;
+    }
+    if (k != width) {
+      P.irregular = true;
+      return;
+    }
+    arp_atom_record r;
+    if (!row_to_record(row.data(), where, r)) {
+      P.bad_row = (int64_t)P.recs.size();
+      return;
+    }
+    P.recs.push_back(r);
+  }
+}
+
 }  // namespace
 
 extern "C" {
@@ -116,6 +218,14 @@ int arph_parse_cif(const char* path, arp_atom_record** out, int64_t* n) {
   }
   std::string text;
   {
+    // one read of the whole file when its size is known (regular files), 64 KB pieces otherwise (pipes)
+    long size = -1;
+    if (std::fseek(f, 0, SEEK_END) == 0) size = std::ftell(f);
+    std::rewind(f);
+    if (size > 0) {
+      text.resize((size_t)size);
+      text.resize(std::fread(text.data(), 1, (size_t)size, f));
+    }
     char chunk[1 << 16];
     size_t got;
     while ((got = std::fread(chunk, 1, sizeof chunk, f)) > 0) text.append(chunk, got);
@@ -155,50 +265,71 @@ int arph_parse_cif(const char* path, arp_atom_record** out, int64_t* n) {
       return ARP_ERR_IO;
     }
     const size_t width = col_of.size();
+    if (have) {  // one row per line? then on all host threads
+      const size_t data_begin = (size_t)(tok.data() - text.data()) - (T.quoted ? 1 : 0);
+      const std::string_view body = std::string_view(text).substr(data_begin);
+      int NT = 1;
+#ifdef _OPENMP
+      NT = std::max(1, std::min(omp_get_max_threads(), (int)(body.size() / piece_bytes()) + 1));
+#endif
+      std::vector<size_t> cut((size_t)NT + 1, body.size());
+      cut[0] = 0;
+      for (int t = 1; t < NT; ++t) {
+        size_t p = body.find('\n', std::max(body.size() / (size_t)NT * (size_t)t, cut[(size_t)t - 1]));
+        cut[(size_t)t] = p == std::string_view::npos ? body.size() : p + 1;
+      }
+      std::vector<CifPiece> pieces((size_t)NT);
+#pragma omp parallel for schedule(static, 1) num_threads(NT)
+      for (int t = 0; t < NT; ++t) parse_piece(body.substr(cut[(size_t)t], cut[(size_t)t + 1] - cut[(size_t)t]), width, where, pieces[(size_t)t]);
+      bool regular = true;
+      size_t total = 0;
+      int last = NT - 1;
+      for (int t = 0; t < NT; ++t) {
+        if (pieces[(size_t)t].irregular) {
+          regular = false;
+          break;
+        }
+        if (pieces[(size_t)t].bad_row >= 0) {
+          arp::last_error() = "mmCIF _atom_site row " + std::to_string(total + (size_t)pieces[(size_t)t].bad_row + 1) + ": unreadable coordinate";
+          return ARP_ERR_IO;
+        }
+        total += pieces[(size_t)t].recs.size();
+        if (pieces[(size_t)t].ended) {
+          last = t;
+          break;
+        }
+      }
+      if (regular) {  // the first _atom_site loop is the structure: the pieces go straight into the caller's array
+        *n = (int64_t)total;
+        *out = (arp_atom_record*)std::malloc(std::max<size_t>(1, total) * sizeof(arp_atom_record));
+        if (!*out) {
+          arp::last_error() = "out of host memory";
+          return ARP_ERR_OOM;
+        }
+        std::vector<size_t> first((size_t)last + 1, 0);
+        for (int t = 1; t <= last; ++t) first[(size_t)t] = first[(size_t)t - 1] + pieces[(size_t)t - 1].recs.size();
+#pragma omp parallel for schedule(static, 1) num_threads(last + 1)
+        for (int t = 0; t <= last; ++t)
+          if (!pieces[(size_t)t].recs.empty())
+            std::memcpy(*out + first[(size_t)t], pieces[(size_t)t].recs.data(), pieces[(size_t)t].recs.size() * sizeof(arp_atom_record));
+        return ARP_OK;
+      }
+    }
     std::vector<std::string_view> row(width);
     while (have) {
       // a row ends the loop when its first token is a keyword or a tag
-      if (!T.quoted && (iequals(tok, "loop_") || istarts(tok, "data_") || istarts(tok, "save_") || (!tok.empty() && tok.front() == '_'))) break;
+      if (!T.quoted && is_loop_end(tok)) break;
       size_t k = 0;
       for (; k < width && have; ++k) {
         row[k] = tok;
         have = T.next(tok);
       }
       if (k < width) break;  // truncated last row (Loose: dropped)
-      auto get = [&](int c) -> std::string_view {
-        if (where[c] < 0) return {};
-        const std::string_view v = row[where[c]];
-        return is_null(v) ? std::string_view{} : v;
-      };
-      auto first_of = [&](int a, int b) {
-        const std::string_view v = get(a);
-        return v.empty() ? get(b) : v;
-      };
       arp_atom_record r;
-      std::memset(&r, 0, sizeof r);
-      r.hetero = iequals(get(GROUP), "HETATM") ? 1 : 0;
-      number(get(ID), r.serial);
-      number(get(MODEL), r.model);
-      store(r.name, sizeof r.name, first_of(LABEL_ATOM, AUTH_ATOM));
-      store(r.resn, sizeof r.resn, first_of(LABEL_COMP, AUTH_COMP));
-      store(r.chain, sizeof r.chain, first_of(AUTH_ASYM, LABEL_ASYM));
-      store(r.altloc, sizeof r.altloc, get(ALT));
-      store(r.icode, sizeof r.icode, get(INS));
-      number(first_of(AUTH_SEQ, LABEL_SEQ), r.resi);
-      if (!number(get(X), r.x) || !number(get(Y), r.y) || !number(get(Z), r.z)) {
+      if (!row_to_record(row.data(), where, r)) {
         arp::last_error() = "mmCIF _atom_site row " + std::to_string(recs.size() + 1) + ": unreadable coordinate";
         return ARP_ERR_IO;
       }
-      r.occupancy = 1.0;
-      number(get(OCC), r.occupancy);
-      std::string sym;
-      for (char ch : get(SYMBOL)) sym.push_back((char)std::toupper((unsigned char)ch));
-      if (sym.empty()) {  // no type_symbol: leading letters of the atom name, like the fixed-column reader
-        for (char ch : std::string_view(r.name, strnlen(r.name, sizeof r.name)).substr(0, 2))
-          if (std::isalpha((unsigned char)ch)) sym.push_back((char)std::toupper((unsigned char)ch));
-        if (sym.size() == 2 && arp_element_class(sym.c_str()) < 0) sym.resize(1);
-      }
-      store(r.element, sizeof r.element, sym);
       recs.push_back(r);
     }
     done = true;  // the first _atom_site loop is the structure

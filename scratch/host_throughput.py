@@ -15,6 +15,20 @@ if not os.path.exists(path):
             f.write("MODEL     %4d\n" % m + "\n".join(lines) + "\nENDMDL\n")
 out = {"threads": os.environ.get("OMP_NUM_THREADS", "all"), "cores": os.cpu_count()}
 t = time.perf_counter(); a = A.parse_pdb(path); out["parse_s"] = time.perf_counter() - t; out["records"] = int(len(a))
+cif = "/tmp/big_models.cif"
+if not os.path.exists(cif):
+    from pathlib import Path
+    from tests.test_host_cpu import write_cif
+    small = Path("/tmp/one.cif"); write_cif(A.parse_pdb(os.path.join(ROOT, "tests", "data", "6bft.pdb")), small)
+    L = small.read_text().split("\n")
+    rows = [l for l in L if l.startswith(("ATOM", "HETATM"))]
+    first = L.index(rows[0])
+    with open(cif, "w") as f:
+        f.write("\n".join(L[:first]) + "\n")
+        for m in range(125):
+            f.write("\n".join(rows) + "\n")
+        f.write("#\n")
+t = time.perf_counter(); c = A.parse_cif(cif); out["parse_cif_s"] = time.perf_counter() - t; out["cif_records"] = int(len(c))
 atoms = synth.assembly_1m(A.parse_pdb(os.path.join(ROOT, "tests", "data", "6bft.pdb")))
 t = time.perf_counter(); p = A.Packed(atoms, "/", flags=2); out["pack_s"] = time.perf_counter() - t
 out["atoms"] = int(p.structure.n_atoms)

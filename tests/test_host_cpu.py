@@ -279,3 +279,35 @@ _other.tag value
     bad.write_text("data_X\nloop_\n_atom_site.id\n_atom_site.Cartn_x\n1 2.0\n")
     with pytest.raises(A.ArpeggiaError):
         A.parse_cif(bad)
+
+
+def test_mmcif_reader_pieces_on_all_threads(bft, tmp_path, monkeypatch):
+    """The one-row-per-line path of arph_parse_cif cuts the loop into pieces (ARPH_CIF_PIECE_BYTES makes them small): the
+    same records whatever the cut; a wrapped row or a text-field line anywhere sends the whole loop to the serial tokenizer;
+    an unreadable coordinate reports its row number across pieces."""
+    p = tmp_path / "s.cif"
+    write_cif(bft, p)
+    whole = A.parse_cif(p)
+    assert len(whole) == len(bft)
+    for piece in ("97", "1000", "65536"):
+        monkeypatch.setenv("ARPH_CIF_PIECE_BYTES", piece)
+        assert np.array_equal(A.parse_cif(p), whole), piece
+    lines = p.read_text().split("\n")
+    first = next(i for i, l in enumerate(lines) if l.startswith(("ATOM", "HETATM")))
+    # row 6000 wrapped over two lines, row 7000 followed by a comment line and a blank line: still the same records
+    k = first + 6000
+    toks = lines[k].split(" ")
+    wrapped = lines[:k] + [" ".join(toks[:5]), " ".join(toks[5:])] + lines[k + 1:first + 7000] + ["# a comment", ""] + lines[first + 7000:]
+    q = tmp_path / "w.cif"
+    q.write_text("\n".join(wrapped))
+    for piece in ("500", "1048576"):
+        monkeypatch.setenv("ARPH_CIF_PIECE_BYTES", piece)
+        assert np.array_equal(A.parse_cif(q), whole), piece
+    # unreadable coordinate in row 5001
+    toks = lines[first + 5000].split(" ")
+    toks[10] = "abc"
+    bad = tmp_path / "b.cif"
+    bad.write_text("\n".join(lines[:first + 5000] + [" ".join(toks)] + lines[first + 5001:]))
+    monkeypatch.setenv("ARPH_CIF_PIECE_BYTES", "700")
+    with pytest.raises(A.ArpeggiaError, match="row 5001"):
+        A.parse_cif(bad)
