@@ -1,11 +1,10 @@
 #!/bin/bash
-# run bench.py for every built variant (GPU box)
+# bench every kernel-tuning variant under scratch/variants (built by scratch/variants.sh) in emit-radius mode: run_variants.sh name ...
 cd "$(dirname "$0")/.."
-for d in scratch/variants/*/; do
-  n=$(basename $d)
-  ARPEGGIA_B200_LIB=$PWD/$d/libarpeggia_b200.so python bench.py --no-cpu --steps 30 2>/dev/null | tail -1 > /tmp/v.json
-  python - "$n" <<PY
+for v in default "$@"; do
+  if [ "$v" = default ]; then unset ARPEGGIA_B200_LIB; else export ARPEGGIA_B200_LIB=$PWD/scratch/variants/$v/libarpeggia_b200.so; fi
+  python bench.py --no-cpu --no-counting --steps 300 --flags 1 2>/dev/null | python -c "
 import json,sys
-l=json.loads(open('/tmp/v.json').read()); print(sys.argv[1], 'step', round(l['ms_per_step'],4), {k:round(v,4) for k,v in l['stage_ms'].items()}, {k:round(v,4) for k,v in l['roofline']['kernel_ms_each'].items()}, 'rows', l['config']['rows'], 'frame_sort', round(l['frame']['ms_sort'],3))
-PY
+d=json.loads(sys.stdin.readline())
+print('$v', 'step',round(d['ms_per_step'],4),'pairs',round(d['roofline']['kernel_ms'],4),{k:round(v,4) for k,v in d['roofline']['kernel_ms_each'].items()},'grid',round(d['stage_ms']['grid'],4), d['config']['rows'])"
 done
