@@ -802,6 +802,11 @@ constexpr uint32_t SA_WINDOW = 512;
 #endif
 constexpr int SA_BUF = SA_BUF_N;      // entries of a lane's hit list
 constexpr int SA_ROUND = SA_ROUND_N;  // trips between two looks at the lists (a trip appends at most 2)
+// tiles handed out through the work cursor instead of a static stride: measured (r1t) k_screen_atoms 0.128 -> 0.126 ms, but
+// k_exact behind it 0.045 -> 0.050 ms (its queue comes out less local) -- off
+#ifndef SA_DYNAMIC_TILES
+#define SA_DYNAMIC_TILES 0
+#endif
 #ifndef SA_MIN_BLOCKS
 #define SA_MIN_BLOCKS 4
 #endif
@@ -835,6 +840,7 @@ struct SaSmem {
   uint32_t run_b[SA_RUNS][SA_THREADS], run_e[SA_RUNS][SA_THREADS];  // every thread's non-empty runs, then the closing row
   uint32_t hits[SA_BUF][SA_THREADS];                                // per-lane hit lists (candidate slots)
   uint2 stash1[SA_WARPS][SA_STASH1];                                // (from slot, candidate slot) waiting for a full warp
+  unsigned int* cursor[32];  // &ctr->work, one copy per lane (see draw_cursor)
   uint2 stash2[SA_WARPS][64];                                       // pairs for k_exact waiting for a full 32-entry flush
 };
 // a warp's carry-over between flushes, tiles and the final drain
@@ -921,14 +927,27 @@ __global__ void __launch_bounds__(SA_THREADS, SA_MIN_BLOCKS) k_screen_atoms(cons
     S.lim1[tid] = m;
   }
   for (int k = tid; k < 256; k += SA_THREADS) S.lim2[k] = class_pair_limit2(P, k >> 4, k & 15);
+  if (tid < 32) S.cursor[tid] = &G.ctr->work;
   __syncthreads();
-  const uint32_t n_tiles = (n_atoms + 31u) >> 5, n_warps = gridDim.x * SA_WARPS;
+  const uint32_t n_tiles = (n_atoms + 31u) >> 5;
+#if !SA_DYNAMIC_TILES
+  const uint32_t n_warps = gridDim.x * SA_WARPS;
+#endif
   SaCarry K{0, 0, 0ull};
   unsigned long long n_tests = 0;
   const uint32_t hp0 = (uint32_t)__cvta_generic_to_shared(&S.hits[0][tid]);
   const uint32_t rp0 = (uint32_t)__cvta_generic_to_shared(&S.run_b[0][tid]);
   constexpr uint32_t ROW = 4u * SA_THREADS, B_TO_E = 4u * SA_THREADS * SA_RUNS;  // byte strides of the two tables
+#if SA_DYNAMIC_TILES
+  // tiles are handed out through the work cursor (free in this mode: k_screen is not launched): their cost varies with
+  // the local density, a static stride leaves the last wave ragged.  The next ticket is requested before the tile is
+  // processed, so its round trip is hidden.
+  uint32_t tile = __shfl_sync(0xffffffffu, draw_cursor(S.cursor[lane], lane), 0);
+  while (tile < n_tiles) {
+    const uint32_t next_tile = draw_cursor(S.cursor[lane], lane);
+#else
   for (uint32_t tile = blockIdx.x * SA_WARPS + (tid >> 5); tile < n_tiles; tile += n_warps) {
+#endif
     const uint32_t slot = (tile << 5) + lane;
     uint32_t s = 0, rb = 0, re = 0, rp = rp0;
     uint2 mine = make_uint2(0u, 0u);
@@ -1012,6 +1031,9 @@ __global__ void __launch_bounds__(SA_THREADS, SA_MIN_BLOCKS) k_screen_atoms(cons
       }
     }
     if (__any_sync(0xffffffffu, hp != hp0)) sa_flush(G, P, key, S, tid, lane, slot, mine, (hp - hp0) / ROW, K);
+#if SA_DYNAMIC_TILES
+    tile = __shfl_sync(0xffffffffu, next_tile, 0);
+#endif
   }
   sa_filter(G, P, S, tid >> 5, lane, K, true);
   if (lane == 0 && K.n_q) atomicAdd(&G.ctr->q_len, K.n_q);
