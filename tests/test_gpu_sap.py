@@ -85,3 +85,21 @@ def test_neighbor_sum_1m_atoms(ctx, bft_path):
     st = ctx.neighbor_sum_stats()
     assert st["ms_sum"] > 0 and st["n_cells"] > 0
     print("neighbor_sum 1M atoms:", st)
+
+
+def test_selection_edge_cases(ctx, ubq_path):
+    """The cell list holds the selected atoms only: nothing selected -> all zeros (also right after a run that selected
+    many: the output buffer is reused), everything selected -> the oracle's sums over all atoms, one atom -> its own weight."""
+    atoms = sap.prepare_atoms(A.parse_pdb(ubq_path))
+    n = len(atoms)
+    w = np.random.default_rng(2).integers(1, 6, size=n).astype(np.float32)
+    every = np.ones(n, dtype=bool)
+    got, want = run_both(ctx, atoms, w, every, 5.0)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32)) and (got >= w).all()
+    none = np.zeros(n, dtype=bool)
+    got, want = run_both(ctx, atoms, w, none, 5.0)
+    assert not got.any() and not want.any()
+    one = none.copy()
+    one[n // 2] = True
+    got, want = run_both(ctx, atoms, w, one, 5.0)
+    assert got[n // 2] == w[n // 2] == want[n // 2] and np.count_nonzero(got) == 1
