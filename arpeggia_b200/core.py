@@ -216,7 +216,7 @@ class Context:
         check(lib().arp_stage_run(self._h, C.byref(prm)), self._h)
 
     def neighbor_sum(self, weight: np.ndarray, select: np.ndarray, radius: float = 5.0) -> np.ndarray:
-        """arp_stage_neighbor_sum on the uploaded single-structure job: the radius query of the SAP score
+        """arp_stage_neighbor_sum on the uploaded job (a batch: every structure on its own): the radius query of the SAP score
         (src/sap.rs:181-215).  out[x] = sum of weight[y] over the selected atoms y within `radius` of the selected atom x
         (x included), 0 where x is not selected.  Arrays are in the job's atom order (Packed.arrays())."""
         w = np.ascontiguousarray(weight, dtype=np.float32)

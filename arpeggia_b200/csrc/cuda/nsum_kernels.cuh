@@ -26,8 +26,9 @@ constexpr uint32_t NS_UNSELECTED = 0xffffffffu;
 // never sorted, screened or given a lane in the sum.
 __global__ void __launch_bounds__(256)
 k_ns_cell_assign(const double* __restrict__ x, const double* __restrict__ y, const double* __restrict__ z,
-                 const unsigned char* __restrict__ select, uint32_t n, const StructDesc d, double inv_edge, uint32_t* __restrict__ cell_of,
-                 uint32_t* __restrict__ rank_of, uint32_t* __restrict__ cell_count, float* __restrict__ out) {
+                 const unsigned char* __restrict__ select, uint32_t n, const uint32_t* __restrict__ atom_struct,
+                 const StructDesc* __restrict__ descs, double inv_edge, uint32_t* __restrict__ cell_of, uint32_t* __restrict__ rank_of,
+                 uint32_t* __restrict__ cell_count, float* __restrict__ out) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   if (!select[i]) {
@@ -35,6 +36,7 @@ k_ns_cell_assign(const double* __restrict__ x, const double* __restrict__ y, con
     out[i] = 0.f;
     return;
   }
+  const StructDesc& d = descs[atom_struct ? atom_struct[i] : 0u];  // batch jobs: every structure has its own grid
   const int ix = cell_coord(x[i], d.ox, inv_edge, d.nx), iy = cell_coord(y[i], d.oy, inv_edge, d.ny), iz = cell_coord(z[i], d.oz, inv_edge, d.nz);
   const uint32_t c = d.cell_base + (uint32_t)((iz * d.ny + iy) * d.nx + ix);
   cell_of[i] = c;
@@ -44,7 +46,8 @@ k_ns_cell_assign(const double* __restrict__ x, const double* __restrict__ y, con
 __global__ void __launch_bounds__(256)
 k_ns_scatter(const double* __restrict__ x, const double* __restrict__ y, const double* __restrict__ z, const float* __restrict__ weight,
              const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of, const uint32_t* __restrict__ cell_start, uint32_t n,
-             double ox, double oy, double oz, NsRec* __restrict__ rec, NsRecF* __restrict__ recf) {
+             const uint32_t* __restrict__ atom_struct, const StructDesc* __restrict__ descs, NsRec* __restrict__ rec,
+             NsRecF* __restrict__ recf) {
   const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
   if (a >= n) return;
   const uint32_t c = cell_of[a];
@@ -55,7 +58,8 @@ k_ns_scatter(const double* __restrict__ x, const double* __restrict__ y, const d
   r.perm = a;
   const uint32_t slot = cell_start[c] + rank_of[a];
   rec[slot] = r;
-  recf[slot] = NsRecF{(float)(r.x - ox), (float)(r.y - oy), (float)(r.z - oz), r.w};
+  const StructDesc& d = descs[atom_struct ? atom_struct[a] : 0u];
+  recf[slot] = NsRecF{(float)(r.x - d.ox), (float)(r.y - d.oy), (float)(r.z - d.oz), r.w};
 }
 
 // One lane per sorted slot (= per selected atom; cell_start[n_cells] is their number).  Every candidate of the 27-cell
@@ -66,12 +70,14 @@ k_ns_scatter(const double* __restrict__ x, const double* __restrict__ y, const d
 // is the reference's.  The sum is accumulated in f64 and rounded to f32 once (the reference adds f32 terms in the
 // R*-tree's iteration order, which is unspecified: any order of the same terms lies within n * 2^-24 * sum|w| of this).
 __global__ void __launch_bounds__(256)
-k_neighbor_sum(const NsRec* __restrict__ rec, const NsRecF* __restrict__ recf, const uint32_t* __restrict__ cell_start, const StructDesc d,
-               uint32_t n_cells, double inv_edge, double r2, float thr_cert, float thr_hit, float* __restrict__ out) {
+k_neighbor_sum(const NsRec* __restrict__ rec, const NsRecF* __restrict__ recf, const uint32_t* __restrict__ cell_start,
+               const uint32_t* __restrict__ atom_struct, const StructDesc* __restrict__ descs, uint32_t n_cells, double inv_edge, double r2,
+               float thr_cert, float thr_hit, float* __restrict__ out) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= cell_start[n_cells]) return;
   const NsRec me = rec[i];
   const NsRecF mf = recf[i];
+  const StructDesc d = descs[atom_struct ? atom_struct[me.perm] : 0u];  // the shell never leaves the structure's own cells
   const int ix = cell_coord(me.x, d.ox, inv_edge, d.nx), iy = cell_coord(me.y, d.oy, inv_edge, d.ny), iz = cell_coord(me.z, d.oz, inv_edge, d.nz);
   const int x0 = max(ix - 1, 0), x1 = min(ix + 1, d.nx - 1);
   double acc = 0.0;

@@ -197,11 +197,12 @@ int  arp_stage_stats(arp_ctx* ctx, arp_stats* out); /* synchronises the stream *
 
 /* ---- weighted neighbour sum over the resident atoms -----------------------------------------------
  *   arp_stage_neighbor_sum()  <->  the radius query of get_per_atom_sap_score            src/sap.rs:181-215
- * After arp_stage_upload of a single-structure job (no run needed): for every atom x with select[x] != 0
- *     out[x] = sum of weight[y] over the atoms y with select[y] != 0 and distance_2(x, y) <= (double)(radius * radius),
+ * After arp_stage_upload (no run needed): for every atom x with select[x] != 0
+ *     out[x] = sum of weight[y] over the atoms y OF THE SAME STRUCTURE with select[y] != 0 and
+ *              distance_2(x, y) <= (double)(radius * radius),
  * x itself included (sap.rs:193-194), the comparison inclusive (rstar locate_within_distance) and the squared radius
  * formed in f32 like sap.rs:184; out[x] = 0 where select[x] == 0.  weight / select / out have n_atoms entries in the
- * job's atom order and may be host or device memory.  In the SAP score select = h.is_sidechain() and
+ * job's atom order (a batch job: the structures' atoms one after the other) and may be host or device memory.  In the SAP score select = h.is_sidechain() and
  * weight = hydrophobicity(resn) * clamp(sasa / max_asa(resn), 0, 1) (sap.rs:199-210): computing the SASA is outside this
  * library.  The distance test is exact FP64 in the reference's operation order, so the neighbour SET is the reference's;
  * the sum is accumulated in f64 and rounded once (the reference adds f32 terms in the R*-tree's unspecified iteration

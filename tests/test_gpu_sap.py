@@ -70,9 +70,25 @@ def test_inclusive_tie_and_errors(ctx, ubq_path):
     assert got[:4].tolist() == want[:4].tolist() == [3.0, 7.0, 6.0, 8.0]
     with pytest.raises(A.ArpeggiaError):
         ctx.neighbor_sum(w, sel, -1.0)
-    ctx.upload([A.Packed(ubq, "/", flags=2), A.Packed(ubq, "/", flags=2)])
-    with pytest.raises(A.ArpeggiaError, match="single-structure"):
-        ctx.neighbor_sum(np.zeros(2 * len(ubq), dtype=np.float32), np.zeros(2 * len(ubq), dtype=bool), 5.0)
+
+
+def test_batch_job_sums_stay_inside_each_structure(ctx, ubq_path, bft_path):
+    """A batch job (arp_stage_upload of several structures): every structure has its own cell list, the sums are those of
+    the structures run one by one -- also for structures that overlap in space (two copies of 1ubq at the same place)."""
+    ubq, bft = sap.prepare_atoms(A.parse_pdb(ubq_path)), sap.prepare_atoms(A.parse_pdb(bft_path))
+    far = ubq.copy()
+    far["x"] += 1000.0
+    parts = [ubq, bft, ubq, far]
+    rng = np.random.default_rng(17)
+    ws = [rng.integers(-8, 9, size=len(p)).astype(np.float32) for p in parts]
+    sels = [sap.sidechain_mask(p) for p in parts]
+    sels[2] = np.ones(len(ubq), dtype=bool)
+    single = [run_both(ctx, p, w, s, 5.0) for p, w, s in zip(parts, ws, sels)]
+    for got, want in single:
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    ctx.upload([A.Packed(p, "/", flags=2) for p in parts])
+    got = ctx.neighbor_sum(np.concatenate(ws), np.concatenate(sels), 5.0)
+    assert np.array_equal(got.view(np.uint32), np.concatenate([g for g, _ in single]).view(np.uint32))
 
 
 def test_neighbor_sum_1m_atoms(ctx, bft_path):
