@@ -807,10 +807,8 @@ constexpr int SA_ROUND = SA_ROUND_N;  // trips between two looks at the lists (a
 #ifndef SA_DYNAMIC_TILES
 #define SA_DYNAMIC_TILES 0
 #endif
-// CTAs per SM: 3 (70 registers) and 4 (64) run the screen equally fast, but k_exact behind it gains 2 us from the shorter,
-// more local queue interleave of 444 instead of 592 CTAs (r1t: pair stage 0.1750 -> 0.1727 ms); 5 (48 registers) was slower
 #ifndef SA_MIN_BLOCKS
-#define SA_MIN_BLOCKS 3
+#define SA_MIN_BLOCKS 4
 #endif
 
 __device__ __forceinline__ unsigned long long sa_add2(unsigned long long a, unsigned long long b) {
