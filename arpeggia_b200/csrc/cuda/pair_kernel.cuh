@@ -807,6 +807,8 @@ constexpr int SA_ROUND = SA_ROUND_N;  // trips between two looks at the lists (a
 #ifndef SA_DYNAMIC_TILES
 #define SA_DYNAMIC_TILES 0
 #endif
+// CTAs per SM: 3 (70 registers) gains 2 us on config 3 (k_exact behind it reads a less interleaved queue) but loses 3-5 % at
+// 10 M / 100 M atoms (k_exact 5.4 -> 6.3 ms on config 5); 5 (48 registers) is slower everywhere (r1t measurements)
 #ifndef SA_MIN_BLOCKS
 #define SA_MIN_BLOCKS 4
 #endif
