@@ -62,6 +62,7 @@ class Structure(C.Structure):
         ("bbox_min", C.c_double * 3), ("bbox_max", C.c_double * 3), ("has_bbox", C.c_int32), ("reserved_", C.c_int32),
         ("res_chain_key", _U32P), ("res_res_ordinal", _U32P), ("res_atom_begin", _U32P),
         ("x_milli", _I32P), ("y_milli", _I32P), ("z_milli", _I32P),
+        ("atom_gid", _U32P), ("ring_gid", _U32P), ("res_tag", _U32P),
     ]
 
 
@@ -135,6 +136,23 @@ class Frame(C.Structure):
     )
 
 
+class CommId(C.Structure):
+    """arp_comm_id (an ncclUniqueId)"""
+    _fields_ = [("bytes", C.c_char * 128)]
+
+
+class SlabInfo(C.Structure):
+    """arp_slab_info"""
+    _fields_ = [
+        ("own_atoms", C.c_int64), ("own_residues", C.c_int64), ("own_rings", C.c_int64),
+        ("ghost_atoms", C.c_int64), ("ghost_residues", C.c_int64), ("ghost_rings", C.c_int64), ("ghost_h", C.c_int64),
+        ("sent_atoms", C.c_int64), ("sent_residues", C.c_int64), ("sent_rings", C.c_int64),
+        ("bytes_sent", C.c_int64), ("bytes_received", C.c_int64),
+        ("n_peers", C.c_int32), ("transport", C.c_int32),
+        ("ms_select", C.c_float), ("ms_transfer", C.c_float), ("ms_unpack", C.c_float), ("ms_total", C.c_float),
+    ]
+
+
 class ArpeggiaError(RuntimeError):
     """Raised for every non-zero arp_status; `.code` is the status (include/arpeggia_cuda.h)."""
 
@@ -168,6 +186,11 @@ SIGNATURES = {
     "arp_contacts_frame": (C.c_int, [_P, C.POINTER(Structure), C.POINTER(Params), C.POINTER(FrameTables),
                                      C.POINTER(C.POINTER(Frame))]),
     "arp_frame_free": (None, [_P, C.POINTER(Frame)]),
+    "arp_comm_get_id": (C.c_int, [C.POINTER(CommId)]),
+    "arp_ctx_comm_init": (C.c_int, [_P, C.POINTER(CommId), C.c_int, C.c_int]),
+    "arp_ctx_create_multi": (C.c_int, [C.POINTER(_P), C.POINTER(C.c_int), C.c_int]),
+    "arp_slab_exchange": (C.c_int, [_P, C.POINTER(Params), C.POINTER(SlabInfo)]),
+    "arp_slab_exchange_multi": (C.c_int, [C.POINTER(_P), C.c_int, C.POINTER(Params), C.POINTER(SlabInfo)]),
     "arp_host_alloc": (C.c_int, [C.POINTER(_P), C.c_int64]),
     "arp_host_free": (None, [_P]),
     # arpeggia_host.h
@@ -182,6 +205,10 @@ SIGNATURES = {
     "arph_packed_warning": (C.c_char_p, [_P, C.c_int64]),
     "arph_packed_free": (None, [_P]),
     "arph_packed_frame_tables": (C.c_int, [_P, C.POINTER(C.POINTER(FrameTables))]),
+    "arph_packed_n_chains": (C.c_int64, [_P]),
+    "arph_packed_chain_id": (C.c_char_p, [_P, C.c_int64]),
+    "arph_packed_remap_chain_ranks": (C.c_int, [_P, _U32P, C.c_int64]),
+    "arph_packed_set_global_ids": (C.c_int, [_P, _U32P, _U32P, _U32P]),
     "arph_table_from_frame": (C.c_int, [_P, C.POINTER(Frame), C.POINTER(C.POINTER(Table))]),
     "arph_build_table": (C.c_int, [_P, _P, C.c_int64, C.POINTER(C.POINTER(Table))]),
     "arph_table_free": (None, [C.POINTER(Table)]),

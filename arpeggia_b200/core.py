@@ -103,7 +103,32 @@ class Packed:
             out[k] = view(getattr(s, k), 3 * s.n_rings, np.float64).reshape(-1, 3)
         for k in ("ring_attr", "ring_chain_key", "ring_res_ordinal"):
             out[k] = view(getattr(s, k), s.n_rings, np.uint32)
+        out["res_tag"] = view(s.res_tag, s.n_residues, np.uint32) if s.res_tag else None
+        out["atom_gid"] = view(s.atom_gid, s.n_atoms, np.uint32) if s.atom_gid else None
+        out["ring_gid"] = view(s.ring_gid, s.n_rings, np.uint32) if s.ring_gid else None
         return out
+
+    # ---- this structure as one part of a larger one (slab jobs) ------------------------------------------------
+    def chain_ids(self) -> list[bytes]:
+        """Chain ids in byte order = the packer's local chain ranks (low 24 bits of chain_key)."""
+        L = lib()
+        return [L.arph_packed_chain_id(self._h, k) for k in range(L.arph_packed_n_chains(self._h))]
+
+    def remap_chain_ranks(self, new_rank) -> None:
+        """Replace the local chain ranks by the ranks of the same chains in the undivided structure (complex.rs:129)."""
+        m = np.ascontiguousarray(new_rank, dtype=np.uint32)
+        check(lib().arph_packed_remap_chain_ranks(self._h, m.ctypes.data_as(_lib._U32P), len(m)))
+
+    def set_global_ids(self, atom_gid, ring_gid, res_tag=None) -> None:
+        """Ids of the atoms / rings in the undivided structure (rows then carry them) and residue tags valid across parts."""
+        a = np.ascontiguousarray(atom_gid, dtype=np.uint32)
+        g = np.ascontiguousarray(ring_gid, dtype=np.uint32)
+        s = self.structure
+        assert len(a) == s.n_atoms and len(g) == s.n_rings
+        t = None if res_tag is None else np.ascontiguousarray(res_tag, dtype=np.uint32)
+        assert t is None or len(t) == s.n_residues
+        check(lib().arph_packed_set_global_ids(self._h, a.ctypes.data_as(_lib._U32P), g.ctypes.data_as(_lib._U32P),
+                                               t.ctypes.data_as(_lib._U32P) if t is not None else None))
 
     def atom_serials(self) -> np.ndarray:
         """Serial number of every packed atom (atoms_with_hierarchy() order can differ from the record order)."""
@@ -257,6 +282,18 @@ class Context:
         out["frame_stats"] = fs
         return out
 
+    # ---- slab jobs ----------------------------------------------------------------------------------------
+    def comm_init(self, comm_id: "_lib.CommId", rank: int, world: int) -> None:
+        """arp_ctx_comm_init: join the communicator whose id one rank made with comm_get_id() (one process per GPU)."""
+        check(lib().arp_ctx_comm_init(self._h, C.byref(comm_id), rank, world), self._h)
+
+    def slab_exchange(self, vdw_comp=0.1, dist_cutoff=6.5) -> dict:
+        """arp_slab_exchange: complete the uploaded (owned) part with halo copies from the other ranks."""
+        prm = Params(vdw_comp, dist_cutoff, 0, 0)
+        info = _lib.SlabInfo()
+        check(lib().arp_slab_exchange(self._h, C.byref(prm), C.byref(info)), self._h)
+        return {k: getattr(info, k) for k, _ in _lib.SlabInfo._fields_}
+
     def stats(self) -> dict:
         st = Stats()
         check(lib().arp_stage_stats(self._h, C.byref(st)), self._h)
@@ -309,6 +346,39 @@ def split_rows(result: dict) -> list[np.ndarray]:
             part[col] = np.where(ring, v | np.uint32(_lib.RING_FLAG), v)
         out.append(part)
     return out
+
+
+def comm_get_id() -> "_lib.CommId":
+    """arp_comm_get_id: a fresh communicator id (ncclUniqueId); distribute its 128 bytes to every rank."""
+    cid = _lib.CommId()
+    check(lib().arp_comm_get_id(C.byref(cid)))
+    return cid
+
+
+def create_multi(devices) -> list[Context]:
+    """arp_ctx_create_multi: one context per entry of `devices`, driven by this process.  Distinct devices talk over NCCL
+    (ncclCommInitAll); a repeated device makes the set use peer copies (the single-GPU test configuration)."""
+    n = len(devices)
+    hs = (C.c_void_p * n)()
+    dv = (C.c_int * n)(*devices)
+    check(lib().arp_ctx_create_multi(hs, dv, n))
+    out = []
+    for k in range(n):
+        cx = Context.__new__(Context)
+        cx._h = C.c_void_p(hs[k])
+        cx.device = devices[k]
+        out.append(cx)
+    return out
+
+
+def slab_exchange_multi(ctxs, vdw_comp=0.1, dist_cutoff=6.5) -> list[dict]:
+    """arp_slab_exchange_multi on every context of a create_multi() set."""
+    n = len(ctxs)
+    hs = (C.c_void_p * n)(*[cx._h for cx in ctxs])
+    prm = Params(vdw_comp, dist_cutoff, 0, 0)
+    info = (_lib.SlabInfo * n)()
+    check(lib().arp_slab_exchange_multi(hs, n, C.byref(prm), info), ctxs[0]._h)
+    return [{k: getattr(info[i], k) for k, _ in _lib.SlabInfo._fields_} for i in range(n)]
 
 
 _default = threading.local()

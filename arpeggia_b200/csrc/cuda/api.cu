@@ -14,6 +14,7 @@
 #include "ring_kernels.cuh"
 #include "frame_kernels.cuh"
 #include "nsum_kernels.cuh"
+#include "slab_kernels.cuh"
 
 using namespace arpd;
 
@@ -99,6 +100,38 @@ struct arp_ctx {
   bool have_hint = false;                // every structure of the job came with one
   bool ignore_hint = false;              // a hint turned out wrong: the job is re-run with the computed boxes
 
+  // global ids of the job's atoms / rings and per-residue tags (arp_structure.atom_gid / ring_gid / res_tag)
+  DBuf<uint32_t> atom_gid, ring_gid, res_tag, struct_res_begin;
+  DBuf<unsigned int> up_err;       // error word of the upload-time kernels
+  HBuf<unsigned int> h_up_err;
+  bool have_gid = false;           // every structure of the job came with ids: rows carry them
+  bool have_tag = false;           // every structure of the job came with tags (else they are derived on the device)
+  bool have_res_csr = false;       // res_atom_begin is resident (every structure came with it)
+  bool rows_global = false;        // the rows of the last run have been rewritten to global ids (arp_stage_download)
+
+  // slab jobs (arp_slab_exchange): communicator, the owned part of the resident job, exchange scratch
+  struct Slab {
+    void* comm = nullptr;          // ncclComm_t
+    int rank = 0, world = 1;
+    std::vector<arp_ctx*> clique;  // arp_ctx_create_multi: every context of the set, in rank order
+    bool copy_mode = false;        // a device appears twice in the set: messages move as peer copies
+    int64_t own_atoms = -1, own_res = 0, own_rings = 0, own_h = 0;  // -1: no exchange since the upload
+    bool have_extent = false;
+    std::vector<double> all_box;   // 7 per rank: min xyz, max xyz of the owned atoms, largest residue x-extent
+    std::vector<int> peers;        // ranks within reach, in the order of the per-peer arrays
+    uint32_t n_blocks = 0;
+    DBuf<unsigned long long> extent, gather, row;
+    HBuf<unsigned long long> h_gather, h_small;
+    DBuf<uint32_t> res_mask, ring_mask;
+    DBuf<Tri> block_tri;
+    DBuf<HaloCounts> counts;
+    DBuf<unsigned int> cursor;
+    DBuf<int> peer_rank;
+    DBuf<unsigned char> send[HALO_MAX_PEERS], recv[HALO_MAX_PEERS];
+    cudaEvent_t ev[5] = {};
+    int64_t ghost[4] = {0, 0, 0, 0}, sent[4] = {0, 0, 0, 0}, bytes_sent = 0, bytes_recv = 0;
+  } slab;
+
   // cell lists and sorted records
   DBuf<unsigned long long> bbox;
   DBuf<uint32_t> cell_of, rank_of, cell_start;
@@ -176,6 +209,8 @@ struct arp_ctx {
 
 namespace {
 
+void slab_release(arp_ctx* c);  // api_slab.inc
+
 int fail(arp_ctx* c, int code, const std::string& msg) {
   if (c) c->err = msg;
   arp::last_error() = msg;
@@ -233,6 +268,8 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
   if (n < 1) throw arp::Error{ARP_ERR_ARG, "a job needs at least one structure"};
   c->have_job = c->have_run = false;
   c->job_gen += 1;  // a new job: a captured run no longer applies
+  c->slab.own_atoms = -1;
+  c->slab.have_extent = false;
   c->atom_begin.assign(n + 1, 0);
   c->ring_begin.assign(n + 1, 0);
   std::vector<int64_t> res_begin(n + 1, 0), h_begin(n + 1, 0);
@@ -324,6 +361,7 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
   bool expand_res_id = c->n_res > 0;
   for (int64_t k = 0; k < n; ++k)
     if (!s[k]->res_atom_begin) expand_res_id = false;
+  c->have_res_csr = expand_res_id;
   if (expand_res_id) {
     // like res_h_begin below: every structure contributes its first n_residues offsets, the tail closes the CSR
     upload_concat(c, c->res_atom_begin, s, n, [](const arp_structure* t) { return t->res_atom_begin; }, nrs, 1, multi ? &atom_adj : nullptr, false);
@@ -351,6 +389,47 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
     c->h_words.p[16] = (uint32_t)c->n_h;  // its own page-locked slot, see above
     CK(cudaMemcpyAsync(c->res_h_begin.p + c->n_res, c->h_words.p + 16, 4, cudaMemcpyDefault, c->stream));
   }
+  // optional global ids: rows then carry them (arp_structure.atom_gid / ring_gid)
+  c->have_gid = true;
+  for (int64_t k = 0; k < n; ++k)
+    if ((s[k]->n_atoms > 0 && !s[k]->atom_gid) || (s[k]->n_rings > 0 && !s[k]->ring_gid)) c->have_gid = false;
+  if (c->have_gid) {
+    upload_concat(c, c->atom_gid, s, n, [](const arp_structure* t) { return t->atom_gid; }, nat, 0, nullptr, false);
+    upload_concat(c, c->ring_gid, s, n, [](const arp_structure* t) { return t->ring_gid; }, nrg, 0, nullptr, false);
+  }
+  // residue tags: the caller's, or derived from (chain key, ordinal) of neighbouring residues (hierarchy order assumed)
+  c->have_tag = c->n_res > 0;
+  for (int64_t k = 0; k < n; ++k)
+    if (s[k]->n_residues > 0 && !s[k]->res_tag) c->have_tag = false;
+  bool derive_tags = false;
+  if (c->have_tag) {
+    upload_concat(c, c->res_tag, s, n, [](const arp_structure* t) { return t->res_tag; }, nrs, 0, nullptr, false);
+  } else if (c->per_residue_keys && c->n_res > 0) {
+    derive_tags = true;
+    c->res_tag.need((size_t)c->n_res + 1);
+    c->struct_res_begin.need((size_t)n + 1);
+    c->up_err.need(1);
+    c->h_up_err.need(1);
+    CK(cudaMemsetAsync(c->up_err.p, 0, sizeof(unsigned int), c->stream));
+    {
+      std::vector<uint32_t> rb(res_begin.begin(), res_begin.end());
+      CK(cudaStreamSynchronize(c->stream));  // the staging buffer is reused
+      c->stage.need(rb.size() * sizeof(uint32_t));
+      std::memcpy(c->stage.p, rb.data(), rb.size() * sizeof(uint32_t));
+      CK(cudaMemcpyAsync(c->struct_res_begin.p, c->stage.p, rb.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+    }
+    k_res_tag_steps<<<(unsigned)((c->n_res + 255) / 256), 256, 0, c->stream>>>(c->res_chain_key.p, c->res_res_ordinal.p, c->struct_res_begin.p,
+                                                                              (uint32_t)n, (uint32_t)c->n_res, c->res_tag.p, c->up_err.p);
+    CK(cudaGetLastError());
+    {
+      const uint32_t tiles = ((uint32_t)c->n_res + SCAN_TILE - 1) / SCAN_TILE;
+      c->scan_status.need(tiles + 1);
+      CK(cudaMemsetAsync(c->scan_status.p, 0, (size_t)(tiles + 1) * sizeof(unsigned long long), c->stream));
+      k_scan_lookback<<<tiles, SCAN_THREADS, 0, c->stream>>>(c->res_tag.p, (uint32_t)c->n_res, c->scan_status.p, tiles, c->up_err.p);
+      CK(cudaGetLastError());
+    }
+    CK(cudaMemcpyAsync(c->h_up_err.p, c->up_err.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, c->stream));
+  }
   // structure descriptors (grids are filled in by the run, they depend on the cutoff)
   c->h_descs.assign(n, StructDesc{});
   for (int64_t k = 0; k < n; ++k) {
@@ -376,6 +455,10 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
   CK(cudaEventRecord(c->ev[1], c->stream));
   CK(cudaStreamSynchronize(c->stream));
   CK(cudaEventElapsedTime(&c->ms_h2d, c->ev[0], c->ev[1]));
+  if (derive_tags && *c->h_up_err.p) {
+    if (*c->h_up_err.p & 4u) throw arp::Error{ARP_ERR_CUDA, "residue-tag scan: look-back wait exceeded its bound"};
+    throw arp::Error{ARP_ERR_ARG, "residues are not in atoms_with_hierarchy() order (a chain's residue ordinals must increase): supply arp_structure.res_tag"};
+  }
   c->have_job = true;
 }
 
@@ -383,3 +466,4 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
 
 #include "api_run.inc"
 #include "api_nsum.inc"
+#include "api_slab.inc"

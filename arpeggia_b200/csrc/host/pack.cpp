@@ -303,7 +303,10 @@ void pack_records(const arp_atom_record* recs, int64_t n, const std::string& gro
   std::unordered_map<int32_t, uint32_t> chain_rank;  // lexicographic (byte order) rank, complex.rs:129
   {
     uint32_t rank = 0;
-    for (auto& id : all_chains) chain_rank[P.intern(id)] = rank++;
+    for (auto& id : all_chains) {
+      chain_rank[P.intern(id)] = rank++;
+      P.chain_by_rank.push_back(id);
+    }
     if (rank > (1u << 24)) throw Error{ARP_ERR_LIMIT, "more than 2^24 distinct chain ids"};
   }
   if (models.size() > 256) throw Error{ARP_ERR_LIMIT, "more than 256 models"};
@@ -554,6 +557,14 @@ void Packed::finish() {
   }
   t.res_chain_key = res_chain_key.data();
   t.res_res_ordinal = res_res_ordinal.data();
+  // residue tags (arp_structure.res_tag): the residues of a chain are contiguous and in ordinal order here, so a running
+  // count that steps by 1 inside a chain (consecutive ordinals) and by 2 otherwise has the required property
+  res_tag.assign(res_cb.size(), 0u);
+  for (size_t r = 1; r < res_cb.size(); ++r)
+    res_tag[r] = res_tag[r - 1] + ((res_chain_key[r] == res_chain_key[r - 1] && res_res_ordinal[r] == res_res_ordinal[r - 1] + 1u) ? 1u : 2u);
+  t.res_tag = res_tag.data();
+  t.atom_gid = atom_gid.empty() ? nullptr : atom_gid.data();
+  t.ring_gid = ring_gid.empty() ? nullptr : ring_gid.data();
   // atoms_with_hierarchy() order keeps the atoms of a residue together: res_id as a CSR (left out if it ever does not)
   t.res_atom_begin = nullptr;
   {
@@ -643,6 +654,50 @@ const arp_structure* arph_packed_structure(const arph_packed* p) { return &p->p.
 int64_t arph_packed_n_warnings(const arph_packed* p) { return (int64_t)p->p.warnings.size(); }
 const char* arph_packed_warning(const arph_packed* p, int64_t i) { return p->p.warnings[(size_t)i].c_str(); }
 void arph_packed_free(arph_packed* p) { delete p; }
+
+/* ---- a packed structure as one part of a larger one (slab jobs, arp_slab_exchange) -------------------------------------- */
+int64_t arph_packed_n_chains(const arph_packed* p) { return p ? (int64_t)p->p.chain_by_rank.size() : 0; }
+const char* arph_packed_chain_id(const arph_packed* p, int64_t rank) {
+  if (!p || rank < 0 || rank >= (int64_t)p->p.chain_by_rank.size()) return nullptr;
+  return p->p.chain_by_rank[(size_t)rank].c_str();
+}
+int arph_packed_remap_chain_ranks(arph_packed* p, const uint32_t* map, int64_t n) {
+  if (!p || !map || n != (int64_t)p->p.chain_by_rank.size()) {
+    arp::last_error() = "arph_packed_remap_chain_ranks: one new rank per chain of the packed structure";
+    return ARP_ERR_ARG;
+  }
+  for (int64_t k = 0; k < n; ++k)
+    if (map[k] >= (1u << 24)) {
+      arp::last_error() = "chain rank beyond 2^24";
+      return ARP_ERR_LIMIT;
+    }
+  auto fix = [&](std::vector<uint32_t>& v) {
+    for (auto& k : v) k = (k & 0xff000000u) | map[k & 0x00ffffffu];
+  };
+  fix(p->p.chain_key);
+  fix(p->p.res_chain_key);
+  fix(p->p.ring_chain_key);
+  return ARP_OK;
+}
+int arph_packed_set_global_ids(arph_packed* p, const uint32_t* atom_gid, const uint32_t* ring_gid, const uint32_t* res_tag) {
+  if (!p || !atom_gid || !ring_gid) {
+    arp::last_error() = "arph_packed_set_global_ids: null argument";
+    return ARP_ERR_ARG;
+  }
+  arp::Packed& P = p->p;
+  for (int64_t a = 0; a < P.s.n_atoms; ++a)
+    if (atom_gid[a] & ARP_RING_FLAG) {
+      arp::last_error() = "atom id beyond 2^31";
+      return ARP_ERR_LIMIT;
+    }
+  P.atom_gid.assign(atom_gid, atom_gid + P.s.n_atoms);
+  P.ring_gid.assign(ring_gid, ring_gid + P.s.n_rings);
+  if (res_tag) P.res_tag.assign(res_tag, res_tag + P.s.n_residues);
+  P.s.atom_gid = P.atom_gid.data();
+  P.s.ring_gid = P.ring_gid.data();
+  P.s.res_tag = P.res_tag.data();
+  return ARP_OK;
+}
 
 int arph_packed_frame_tables(arph_packed* p, const arp_frame_tables** out) {
   *out = nullptr;

@@ -17,6 +17,9 @@ struct Packed {
   std::vector<uint32_t> res_atom_begin;                  // CSR of the residues' atoms (compact form of res_id)
   std::vector<int32_t> res_cb, res_sg;
   std::vector<int32_t> x_milli, y_milli, z_milli;        // on-lattice form of x / y / z (empty when a coordinate is off the lattice)
+  std::vector<uint32_t> res_tag;                         // per residue: |tag difference| <= 1 <=> same chain, ordinals <= 1 apart
+  std::vector<uint32_t> atom_gid, ring_gid;              // ids in a larger structure (arph_packed_set_global_ids); empty = none
+  std::vector<std::string> chain_by_rank;                // chain ids in byte order = the low 24 bits of chain_key
   arp_structure s{};
 
   // decode side: one ResConf per (residue, conformer) = one ResidueId of the reference (residues.rs:7-21)

@@ -1,17 +1,19 @@
-"""Multi-GPU execution of the contacts path: one process per GPU, torch.distributed for the plumbing.
+"""Multi-GPU execution of the contacts path: one process per GPU, torch.distributed for the plumbing only.
 
 Two ways the path shards:
 
 * batches of independent structures  -> `shard_round_robin` + `run_batch_shard`: no collective on the data path,
   only an optional all-reduce of the workload counters for the report.
-* one giant assembly                  -> x-slabs with a halo (`SlabJob`): every rank owns the residues whose first
-  atom falls into its slab, ships the residues that reach into a neighbour's reach to that neighbour (NCCL send/recv
-  over NVLink when the tensors are CUDA tensors, gloo on the CPU for tests), marks what it receives as ghosts
-  (ARP_ATTR_GHOST) and runs the unchanged kernels: a row is emitted by the owner of its `from` atom / ring, so the
-  union of the ranks' rows is exactly the single-GPU row set.  Whole residues travel, so the hydrogen lists and
-  CB/SG slots the per-pair tests gather from (hbond.rs:38-42, vdw.rs:55-74) are complete on every rank.
+* one giant assembly                  -> x-slabs with a halo.  Every rank packs ONLY the residues it owns
+  (`pack_tiled_slab` for the synthetic tilings, `cut_slab` for a packed structure), uploads them and calls
+  `arp_slab_exchange` (include/arpeggia_cuda.h): select / pack / unpack run as CUDA kernels on the context's
+  stream, the messages move with ncclSend / ncclRecv over NVLink inside the library's own communicator -- no torch
+  op and no host-side selection between "owned slab on the device" and `arp_stage_run`.  A row is emitted by the
+  owner of its `from` atom / ring and carries global ids, so the union of the ranks' rows is exactly the
+  single-GPU row set.  `SlabRank` wraps the calls; torch.distributed only carries the 128-byte communicator id.
 
-A structure here is a dict of torch tensors ("SoA dict") mirroring arp_structure, plus global ids.
+The second half of this file (`soa_from_arrays` ... `exchange_halos`) is the same halo rule stated with torch
+tensors on the host: test infrastructure (gloo, CPU) that the device path is checked against, not a product path.
 """
 from __future__ import annotations
 
@@ -22,6 +24,7 @@ import torch
 import torch.distributed as dist
 
 from . import _lib
+from .core import Context, Packed, comm_get_id
 
 GHOST = 0x4000
 ATOM_KEYS = ("x", "y", "z", "attr", "chain_key", "res_ordinal", "res_id", "gid")
@@ -31,6 +34,152 @@ RING_KEYS = ("ring_c", "ring_n", "ring_attr", "ring_chain_key", "ring_res_ordina
 def shard_round_robin(n: int, rank: int, world: int) -> list[int]:
     """Structure k of a batch goes to GPU k mod world."""
     return list(range(rank, n, world))
+
+
+# ---- slab jobs through the C ABI ------------------------------------------------------------------------------------
+def slab_x_range(nx: int, rank: int, world: int) -> tuple[int, int]:
+    """x-indices of the tiling's copies that rank `rank` owns."""
+    return (nx * rank) // world, (nx * (rank + 1)) // world
+
+
+def tiled_chain_ranks(base_chains, n_copies: int) -> dict:
+    """Byte-order rank of every chain id "<id><5-digit copy number>" of a tiling (synth.tile): what complex.rs:129
+    compares.  Built from the id strings themselves, so it holds for any base ids."""
+    ids = sorted(ch + b"%05d" % c for ch in base_chains for c in range(n_copies)) if n_copies > 1 else sorted(base_chains)
+    return {cid: k for k, cid in enumerate(ids)}
+
+
+def pack_tiled_slab(base: np.ndarray, nx: int, ny: int, nz: int, rank: int, world: int, pitch=None, groups: str = "/") -> Packed:
+    """Rank `rank`'s x-slab of the tiling of `base` (synth.tile), packed on its own: the rank never sees the rest of the
+    assembly.  Chain ranks, atom / ring ids and residue tags are those of the undivided tiling, computed from the copy
+    numbers (every copy packs to the same layout; ids are copy-major like the packer's hierarchy order)."""
+    from . import synth
+
+    pitch = synth.PITCH_6BFT if pitch is None else pitch
+    xr = slab_x_range(nx, rank, world)
+    copies = np.asarray(synth.copy_numbers(nx, ny, nz, xr), dtype=np.int64)
+    n_copies = nx * ny * nz
+    atoms = synth.tile(base, nx, ny, nz, pitch, x_range=xr)
+    p = Packed(atoms, groups, flags=_lib.HOST_FLAG_SKIP_LOAD_FILTER)
+    st = p.structure
+    L = len(copies)
+    assert L > 0 and st.n_atoms % L == 0 and st.n_rings % L == 0 and st.n_residues % L == 0
+    na, ng, nr = st.n_atoms // L, st.n_rings // L, st.n_residues // L
+    # chain ranks in the whole tiling
+    ranks = tiled_chain_ranks(sorted(set(np.unique(base["chain"]).tolist())), n_copies)
+    p.remap_chain_ranks([ranks[cid] for cid in p.chain_ids()])
+    # ids: copy-major
+    atom_gid = (copies[:, None] * na + np.arange(na)[None, :]).reshape(-1)
+    ring_gid = (copies[:, None] * ng + np.arange(ng)[None, :]).reshape(-1)
+    # tags: the packer's running tags restart per copy with a gap of 2 in the whole tiling as well
+    tag = p.arrays()["res_tag"].astype(np.int64).reshape(L, nr)
+    tag = tag - tag[:, :1]
+    span = int(tag.max()) + 2
+    res_tag = (copies[:, None] * span + tag).reshape(-1)
+    assert atom_gid.max() < 2**31 and res_tag.max() < 2**32
+    p.set_global_ids(atom_gid, ring_gid, res_tag)
+    return p
+
+
+class ArrayStructure:
+    """arp_structure over numpy arrays in the compact per-residue form (kept alive here)."""
+
+    def __init__(self, a: dict):
+        st = _lib.Structure()
+        types = dict(_lib.Structure._fields_)
+        self.keep = {}
+
+        def put(name, v, dt):
+            v = np.ascontiguousarray(v, dtype=dt)
+            self.keep[name] = v
+            setattr(st, name, C.cast(C.c_void_p(v.ctypes.data if v.size else None), types[name]) if v.size else types[name]())
+
+        st.n_atoms, st.n_residues, st.n_rings, st.n_h = len(a["x"]), len(a["res_cb"]), len(a["ring_attr"]), len(a["h_x"])
+        for k in ("x", "y", "z", "h_x", "h_y", "h_z"):
+            put(k, a[k], np.float64)
+        put("ring_center", np.asarray(a["ring_center"]).reshape(-1), np.float64)
+        put("ring_normal", np.asarray(a["ring_normal"]).reshape(-1), np.float64)
+        for k in ("attr", "res_h_begin", "res_chain_key", "res_res_ordinal", "res_atom_begin", "ring_attr", "ring_chain_key",
+                  "ring_res_ordinal", "atom_gid", "ring_gid", "res_tag"):
+            put(k, a[k], np.uint32)
+        for k in ("res_cb", "res_sg"):
+            put(k, a[k], np.int32)
+        self.struct = st
+
+    @property
+    def structure_ptr(self):
+        return C.pointer(self.struct)
+
+
+def cut_slab(a: dict, rank: int, world: int) -> dict:
+    """The residues rank `rank` owns when the packed structure `a` (Packed.arrays()) is cut into x-slabs of equal residue
+    count (by the x of a residue's first atom), as compact arrays with the whole structure's ids, chain ranks and tags."""
+    rab = a["res_atom_begin"].astype(np.int64)
+    nres = len(rab) - 1
+    counts = np.diff(rab)
+    anchor = np.where(counts > 0, a["x"][np.minimum(rab[:-1], max(len(a["x"]) - 1, 0))], -np.inf) if len(a["x"]) else np.zeros(nres)
+    order = np.sort(anchor)
+    inner = [order[min(nres - 1, (nres * r) // world)] for r in range(1, world)]
+    bounds = [-np.inf] + inner + [np.inf]
+    sel = (anchor >= bounds[rank]) & (anchor < bounds[rank + 1]) if rank < world - 1 else anchor >= bounds[rank]
+    ridx = np.nonzero(sel)[0]
+    amask = np.repeat(sel, counts)
+    aidx = np.nonzero(amask)[0]
+    new_atom = np.cumsum(amask) - 1
+    out = {k: a[k][aidx] for k in ("x", "y", "z", "attr")}
+    out["atom_gid"] = aidx
+    out["res_atom_begin"] = np.concatenate([[0], np.cumsum(counts[ridx])])
+    for k in ("res_chain_key", "res_res_ordinal", "res_tag"):
+        out[k] = a[k][ridx]
+    for k in ("res_cb", "res_sg"):
+        v = a[k][ridx].astype(np.int64)
+        out[k] = np.where(v >= 0, new_atom[np.maximum(v, 0)], -1)
+    hb = a["res_h_begin"].astype(np.int64)
+    hcounts = np.diff(hb)
+    hidx = np.nonzero(np.repeat(sel, hcounts))[0]
+    for k in ("h_x", "h_y", "h_z"):
+        out[k] = a[k][hidx]
+    out["res_h_begin"] = np.concatenate([[0], np.cumsum(hcounts[ridx])])
+    # a ring belongs to the residue with its (chain key, ordinal)
+    rkey = (a["res_chain_key"].astype(np.int64) << 32) | a["res_res_ordinal"].astype(np.int64)
+    o = np.argsort(rkey)
+    want = (a["ring_chain_key"].astype(np.int64) << 32) | a["ring_res_ordinal"].astype(np.int64)
+    ring_res = o[np.searchsorted(rkey[o], want)] if len(want) else np.zeros(0, dtype=np.int64)
+    gidx = np.nonzero(sel[ring_res])[0] if len(want) else np.zeros(0, dtype=np.int64)
+    for k in ("ring_center", "ring_normal", "ring_attr", "ring_chain_key", "ring_res_ordinal"):
+        out[k] = a[k][gidx]
+    out["ring_gid"] = gidx
+    return out
+
+
+def broadcast_comm_id(rank: int, group=None) -> "_lib.CommId":
+    """One rank makes the communicator id, torch.distributed carries its 128 bytes to the others (any backend)."""
+    cid = comm_get_id() if rank == 0 else _lib.CommId()
+    box = [C.string_at(C.addressof(cid), 128) if rank == 0 else None]  # the raw 128 bytes, NULs included
+    dist.broadcast_object_list(box, src=0, group=group)
+    C.memmove(C.addressof(cid), box[0], 128)
+    return cid
+
+
+class SlabRank:
+    """One rank of a slab job: a context with its own NCCL communicator, the owned part resident on the device."""
+
+    def __init__(self, ctx: Context, rank: int, world: int, group=None):
+        self.ctx, self.rank, self.world = ctx, rank, world
+        if world > 1:
+            ctx.comm_init(broadcast_comm_id(rank, group), rank, world)
+
+    def upload(self, own):
+        """own: a Packed (pack_tiled_slab) or an ArrayStructure (cut_slab)."""
+        self.ctx.upload([own])
+
+    def exchange(self, vdw_comp=0.1, dist_cutoff=6.5) -> dict:
+        return self.ctx.slab_exchange(vdw_comp, dist_cutoff)
+
+    def run(self, vdw_comp=0.1, dist_cutoff=6.5, flags=0) -> dict:
+        """Kernels on owned + ghosts; rows come back with global ids."""
+        self.ctx.run(vdw_comp, dist_cutoff, flags)
+        return self.ctx.download()
 
 
 # ---- SoA dicts ------------------------------------------------------------------------------------------------
@@ -295,20 +444,6 @@ def globalize_rows(rows: np.ndarray, gid: torch.Tensor, ring_gid: torch.Tensor) 
         res[~ring] = g[idx[~ring]].astype(np.uint32)
         out[col] = res
     return out
-
-
-def run_slab(ctx, own: dict, vdw_comp=0.1, dist_cutoff=6.5, flags=0, group=None):
-    """One rank's share of a slab-decomposed job: halo exchange, kernels, rows with global ids."""
-    width = max(abs(dist_cutoff), 6.0) * (1.0 + 1e-6) + 1e-6  # ring-ring pairs reach 6.0 A regardless of dist_cutoff
-    combined, info = exchange_halos(own, width, group)
-    bound = BoundStructure(combined)
-    if combined["x"].is_cuda:
-        torch.cuda.current_stream(combined["x"].device).synchronize()  # the context runs on its own stream
-    res = ctx.contacts_rows([bound.ptr], vdw_comp, dist_cutoff, flags)
-    res["rows"] = globalize_rows(res["rows"], bound.gid, bound.ring_gid)
-    res["halo"] = info
-    res["n_local_atoms"] = int(combined["x"].numel())
-    return res
 
 
 def run_batch_shard(ctx, packs, rank: int, world: int, vdw_comp=0.1, dist_cutoff=6.5, flags=0):

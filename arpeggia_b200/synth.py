@@ -20,32 +20,43 @@ def _milli(v: np.ndarray) -> np.ndarray:
     return np.rint(v * 1000.0).astype(np.int64)
 
 
-def tile(atoms: np.ndarray, nx: int, ny: int, nz: int, pitch=PITCH_6BFT, serial_stride: int | None = None) -> np.ndarray:
+def copy_numbers(nx: int, ny: int, nz: int, x_range=None) -> list[int]:
+    """Copy numbers c = (k*ny + j)*nx + i of a tiling, in generation order, restricted to x-indices i in x_range."""
+    i0, i1 = (0, nx) if x_range is None else x_range
+    return [(k * ny + j) * nx + i for k in range(nz) for j in range(ny) for i in range(i0, i1)]
+
+
+def tile(atoms: np.ndarray, nx: int, ny: int, nz: int, pitch=PITCH_6BFT, serial_stride: int | None = None, x_range=None) -> np.ndarray:
     """nx*ny*nz translated copies of `atoms`; copy (i,j,k) is shifted by (i,j,k)*pitch and its chains are
-    renamed "<id><5-digit copy number>" so every chain id stays unique (model 0)."""
+    renamed "<id><5-digit copy number>" so every chain id stays unique (model 0).  x_range = (i0, i1) generates only
+    the copies with i0 <= i < i1 -- one x-slab of the assembly -- with the copy numbers, chain ids and serials they
+    have in the whole tiling (copy_numbers() lists them)."""
     atoms = np.ascontiguousarray(atoms, dtype=ATOM_DTYPE)
     n = len(atoms)
     copies = nx * ny * nz
+    i0, i1 = (0, nx) if x_range is None else x_range
     if serial_stride is None:
         serial_stride = int(atoms["serial"].max()) + 1
-    out = np.empty(n * copies, dtype=ATOM_DTYPE)
+    out = np.empty(n * (i1 - i0) * ny * nz, dtype=ATOM_DTYPE)
     mx, my, mz = _milli(atoms["x"]), _milli(atoms["y"]), _milli(atoms["z"])
     px, py, pz = (int(round(p * 1000)) for p in pitch)
     chains = np.unique(atoms["chain"])
-    c = 0
+    masks = [(ch, atoms["chain"] == ch) for ch in chains]
+    q = 0
     for k in range(nz):
         for j in range(ny):
-            for i in range(nx):
-                blk = out[c * n:(c + 1) * n]
+            for i in range(i0, i1):
+                c = (k * ny + j) * nx + i
+                blk = out[q * n:(q + 1) * n]
                 blk[:] = atoms
                 blk["x"] = (mx + i * px) / 1000.0
                 blk["y"] = (my + j * py) / 1000.0
                 blk["z"] = (mz + k * pz) / 1000.0
                 blk["serial"] = atoms["serial"] + c * serial_stride
                 if copies > 1:
-                    for ch in chains:
-                        blk["chain"][atoms["chain"] == ch] = ch + b"%05d" % c
-                c += 1
+                    for ch, m in masks:
+                        blk["chain"][m] = ch + b"%05d" % c
+                q += 1
     return out
 
 

@@ -17,6 +17,7 @@ pub const ARP_ERR_ARG: c_int = 8;
 pub const ARP_ERR_CUDA: c_int = 9;
 pub const ARP_ERR_OOM: c_int = 10;
 pub const ARP_ERR_LIMIT: c_int = 11;
+pub const ARP_ERR_NCCL: c_int = 12;
 
 pub const ARP_ATTR_ELEM_MASK: u32 = 0x0000_000F;
 pub const ARP_ATTR_LIGAND: u32 = 0x0000_0010;
@@ -71,6 +72,9 @@ pub struct arp_structure {
     pub x_milli: *const i32,
     pub y_milli: *const i32,
     pub z_milli: *const i32,
+    pub atom_gid: *const u32,
+    pub ring_gid: *const u32,
+    pub res_tag: *const u32,
 }
 
 #[repr(C)]
@@ -192,6 +196,36 @@ pub struct arp_frame {
     pub key_bits: i32,
 }
 
+/// An `ncclUniqueId`: made by one rank (`arp_comm_get_id`), carried to the others by the host's own means.
+#[repr(C)]
+#[derive(Clone, Copy)]
+pub struct arp_comm_id {
+    pub bytes: [c_char; 128],
+}
+
+#[repr(C)]
+#[derive(Clone, Copy, Default)]
+pub struct arp_slab_info {
+    pub own_atoms: i64,
+    pub own_residues: i64,
+    pub own_rings: i64,
+    pub ghost_atoms: i64,
+    pub ghost_residues: i64,
+    pub ghost_rings: i64,
+    pub ghost_h: i64,
+    pub sent_atoms: i64,
+    pub sent_residues: i64,
+    pub sent_rings: i64,
+    pub bytes_sent: i64,
+    pub bytes_received: i64,
+    pub n_peers: i32,
+    pub transport: i32,
+    pub ms_select: f32,
+    pub ms_transfer: f32,
+    pub ms_unpack: f32,
+    pub ms_total: f32,
+}
+
 /// Opaque context: one per (device, host thread).
 #[repr(C)]
 pub struct arp_ctx {
@@ -218,6 +252,11 @@ extern "C" {
     pub fn arp_stage_frame(ctx: *mut arp_ctx, t: *const arp_frame_tables, out: *mut *mut arp_frame) -> c_int;
     pub fn arp_contacts_frame(ctx: *mut arp_ctx, s: *const arp_structure, p: *const arp_params, t: *const arp_frame_tables, out: *mut *mut arp_frame) -> c_int;
     pub fn arp_frame_free(ctx: *mut arp_ctx, f: *mut arp_frame);
+    pub fn arp_comm_get_id(out: *mut arp_comm_id) -> c_int;
+    pub fn arp_ctx_comm_init(ctx: *mut arp_ctx, id: *const arp_comm_id, rank: c_int, world: c_int) -> c_int;
+    pub fn arp_ctx_create_multi(out: *mut *mut arp_ctx, devices: *const c_int, n_devices: c_int) -> c_int;
+    pub fn arp_slab_exchange(ctx: *mut arp_ctx, p: *const arp_params, info: *mut arp_slab_info) -> c_int;
+    pub fn arp_slab_exchange_multi(ctx: *const *mut arp_ctx, n: c_int, p: *const arp_params, info: *mut arp_slab_info) -> c_int;
     pub fn arp_host_alloc(out: *mut *mut c_void, bytes: i64) -> c_int;
     pub fn arp_host_free(p: *mut c_void);
 }

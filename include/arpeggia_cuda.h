@@ -42,7 +42,8 @@ typedef enum arp_status {
   ARP_ERR_ARG = 8,
   ARP_ERR_CUDA = 9,
   ARP_ERR_OOM = 10,
-  ARP_ERR_LIMIT = 11        /* > 2^31 atoms, > 2^32 cells, > 256 models, > 2^24 chains */
+  ARP_ERR_LIMIT = 11,       /* > 2^31 atoms, > 2^32 cells, > 256 models, > 2^24 chains */
+  ARP_ERR_NCCL = 12         /* NCCL not loadable, or a communicator call failed */
 } arp_status;
 
 /* Interaction labels: declaration order of `enum Interaction`, src/contacts/structs.rs:6-51. */
@@ -129,6 +130,21 @@ typedef struct arp_structure {
   const int32_t* x_milli;
   const int32_t* y_milli;
   const int32_t* z_milli;
+  /* Optional ids of the atoms / rings in a larger, undivided structure (n_atoms / n_rings entries, < 2^31).  When
+   * given, arp_row.from / .to carry these ids instead of job-local indices.  Required for slab jobs (arp_slab_exchange):
+   * halo copies arrive with the ids their owner gave them, so the union of the ranks' rows is the row set of the
+   * undivided structure. */
+  const uint32_t* atom_gid;
+  const uint32_t* ring_gid;
+  /* Optional per-residue tag (n_residues entries) with the property
+   *     |res_tag[a] - res_tag[b]| <= 1   <=>   a and b are in the same model and chain and their residue ordinals
+   *                                            differ by at most 1                          (complex.rs:108-120)
+   * e.g. (index of the residue in atoms_with_hierarchy() order) + 2 * (index of its chain).  The emit-radius screen
+   * decides the in-chain neighbour rule from it without gathering chain keys.  When NULL the device derives the tags
+   * from res_chain_key / res_res_ordinal, ASSUMING atoms_with_hierarchy() order: the residues of a chain are contiguous
+   * and in ordinal order (violations that are visible between neighbouring residues fail the job with ARP_ERR_ARG).
+   * Slab jobs (arp_slab_exchange) need tags that are valid across ranks, so there the caller must supply them. */
+  const uint32_t* res_tag;
 } arp_structure;
 
 #define ARP_FLAG_EMIT_RADIUS_SCREEN 0x1u /* screen atom pairs at min(dist_cutoff, largest distance at which any
@@ -270,6 +286,47 @@ int  arp_stage_frame(arp_ctx* ctx, const arp_frame_tables* t, arp_frame** out);
 /* One-shot: arp_stage_upload + arp_stage_run + arp_stage_frame. */
 int  arp_contacts_frame(arp_ctx* ctx, const arp_structure* s, const arp_params* p, const arp_frame_tables* t, arp_frame** out);
 void arp_frame_free(arp_ctx* ctx, arp_frame* f); /* ctx may be NULL; the memory returns to a process-wide pool */
+
+/* ---- one assembly cut into x-slabs over several GPUs (BASELINE config 5) -------------------------------
+ * Partitions the three search loops of complex.rs:197-213, 306-321, 356-370 by the owner of the row's `from` entity.
+ * Every rank (one context = one GPU) owns a set of WHOLE residues -- normally those of an x-slab -- and uploads them with
+ * arp_stage_upload (one structure, compact per-residue forms, atom_gid / ring_gid / res_tag given, chain keys and residue
+ * ordinals those of the undivided structure).  arp_slab_exchange then completes the job with read-only halo copies:
+ *   k_halo_mark      every owned residue with an atom whose x lies within `width` of a peer's owned x-range (and every
+ *                    ring whose centroid does) is marked for that peer; width = max(|dist_cutoff|, 6.0) (pi-pi reaches
+ *                    6.0 A whatever the cutoff, aromatic.rs:33-64) -- whole residues, so the hydrogen lists and CB / SG
+ *                    slots the per-pair tests gather from (hbond.rs:38-42, vdw.rs:55-74) are complete on the receiver
+ *   k_halo_count/_offsets   deterministic message offsets (block sums + one small scan), counts to the host (the one
+ *                    host synchronisation of the exchange: NCCL needs the byte counts)
+ *   k_halo_pack      residues, atoms, hydrogens, rings -> one contiguous message per peer
+ *   ncclSend/ncclRecv (grouped, on the context's stream; NVLink 5 / NVSwitch) -- or peer copies, see below
+ *   k_halo_unpack    appends the received records to the resident job, marks them ARP_ATTR_GHOST (they take part in
+ *                    every test but never start a row) and rebases their indices
+ * after which arp_stage_run / arp_stage_download work unchanged; rows carry global ids.  Ghosts of an earlier exchange
+ * are dropped first, so the call can be repeated.  There is no torch or host-side selection anywhere on this path.
+ *
+ * Communicators: one process per GPU -> arp_comm_get_id on one rank, the 128 bytes distributed by the host's own means
+ * (MPI, a socket, torch.distributed), arp_ctx_comm_init on every rank.  One process driving several GPUs ->
+ * arp_ctx_create_multi (ncclCommInitAll) and arp_slab_exchange_multi.  NCCL is loaded with dlopen("libnccl.so.2") on
+ * first use (the copy already in the process, if any), so the library itself has no NCCL link dependency.
+ * arp_ctx_create_multi accepts a device more than once (NCCL does not): such a set moves its messages with
+ * cudaMemcpyPeerAsync instead -- the same kernels and byte layout, used to test the path on a single GPU. */
+typedef struct arp_comm_id { char bytes[128]; } arp_comm_id; /* ncclUniqueId */
+int  arp_comm_get_id(arp_comm_id* out);
+int  arp_ctx_comm_init(arp_ctx* ctx, const arp_comm_id* id, int rank, int world);
+int  arp_ctx_create_multi(arp_ctx** out /* [n_devices] */, const int* devices, int n_devices);
+
+typedef struct arp_slab_info {
+  int64_t own_atoms, own_residues, own_rings;
+  int64_t ghost_atoms, ghost_residues, ghost_rings, ghost_h;
+  int64_t sent_atoms, sent_residues, sent_rings;
+  int64_t bytes_sent, bytes_received;
+  int32_t n_peers;       /* ranks this one exchanged a (possibly empty) message with */
+  int32_t transport;     /* 1 = NCCL send/recv, 2 = peer copies (duplicate devices in one process) */
+  float ms_select, ms_transfer, ms_unpack, ms_total; /* CUDA events on the context's stream; ms_total includes the host wait */
+} arp_slab_info;
+int  arp_slab_exchange(arp_ctx* ctx, const arp_params* p, arp_slab_info* info /* may be NULL */);
+int  arp_slab_exchange_multi(arp_ctx* const* ctx, int n, const arp_params* p, arp_slab_info* info /* [n] or NULL */);
 
 /* Page-locked host memory for callers that want true asynchronous H2D/D2H (optional). */
 int  arp_host_alloc(void** out, int64_t bytes);

@@ -86,6 +86,14 @@ const arp_structure* arph_packed_structure(const arph_packed* p);
 int64_t arph_packed_n_warnings(const arph_packed* p);           /* ring residues with < 3 ring atoms (mod.rs:64-68) */
 const char* arph_packed_warning(const arph_packed* p, int64_t i);
 void arph_packed_free(arph_packed* p);
+/* A packed structure as one PART of a larger one (one rank's slab of an assembly, arp_slab_exchange): the packer ranks
+ * chain ids among the chains IT sees (complex.rs:129 compares the id strings), so a host that packs only its part
+ * replaces those ranks by the ranks in the undivided structure, and attaches the atoms' / rings' ids there plus residue
+ * tags that are valid across parts (arp_structure.atom_gid / ring_gid / res_tag; res_tag NULL keeps the local tags). */
+int64_t arph_packed_n_chains(const arph_packed* p);
+const char* arph_packed_chain_id(const arph_packed* p, int64_t rank);  /* chain ids in byte order = local rank order */
+int  arph_packed_remap_chain_ranks(arph_packed* p, const uint32_t* new_rank, int64_t n_chains);
+int  arph_packed_set_global_ids(arph_packed* p, const uint32_t* atom_gid, const uint32_t* ring_gid, const uint32_t* res_tag);
 /* The integer side tables arp_stage_frame / arp_contacts_frame need (dense sort ranks of the string keys, per-entity
  * and per-residue columns).  Built on first use, owned by the packed structure, valid until arph_packed_free. */
 int  arph_packed_frame_tables(arph_packed* p, const arp_frame_tables** out);

@@ -33,7 +33,8 @@ def test_every_declared_symbol_is_exported_and_bound():
 
 def test_struct_sizes_match_the_headers():
     assert C.sizeof(_lib.Params) == 24 and _lib.ROW_DTYPE.itemsize == 16 and _lib.ATOM_DTYPE.itemsize == 96
-    assert C.sizeof(_lib.Structure) == 4 * 8 + 18 * 8 + 6 * 8 + 2 * 4 + 3 * 8 + 3 * 8  # counts, pointers, bbox hint, compact forms, lattice form
+    assert C.sizeof(_lib.Structure) == 4 * 8 + 18 * 8 + 6 * 8 + 2 * 4 + 3 * 8 + 3 * 8 + 3 * 8  # counts, pointers, bbox hint, compact forms, lattice form, ids + tags
+    assert C.sizeof(_lib.SlabInfo) == 12 * 8 + 2 * 4 + 4 * 4 and C.sizeof(_lib.CommId) == 128
     assert C.sizeof(_lib.Result) == 8 * 8
 
 
@@ -75,7 +76,7 @@ def test_rust_bindings_declare_the_device_abi():
         assert re.search(rf"pub fn {name}\(", text), f"{name} missing from the Rust bindings"
     for struct, ctype in (("arp_structure", _lib.Structure), ("arp_params", _lib.Params), ("arp_result", _lib.Result),
                           ("arp_stats", _lib.Stats), ("arp_frame_side", _lib.FrameSide), ("arp_frame_tables", _lib.FrameTables),
-                          ("arp_frame", _lib.Frame)):
+                          ("arp_frame", _lib.Frame), ("arp_slab_info", _lib.SlabInfo)):
         body = re.search(rf"pub struct {struct} \{{(.*?)\n\}}", text, re.S).group(1)
         rust_fields = re.findall(r"pub (\w+):", body)
         assert rust_fields == [f for f, _ in ctype._fields_], struct
