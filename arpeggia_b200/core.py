@@ -206,7 +206,7 @@ class Context:
         L = lib()
         if isinstance(structures, Packed):
             structures = [structures]
-        ptrs = (C.POINTER(Structure) * len(structures))(*[s.structure_ptr if isinstance(s, Packed) else s for s in structures])
+        ptrs = (C.POINTER(Structure) * len(structures))(*[s.structure_ptr if hasattr(s, "structure_ptr") else s for s in structures])
         prm = Params(vdw_comp, dist_cutoff, flags, 0)
         rp = C.POINTER(Result)()
         check(L.arp_contacts_batch(self._h, ptrs, len(structures), C.byref(prm), C.byref(rp)), self._h)
@@ -233,7 +233,7 @@ class Context:
         if isinstance(structures, Packed):
             structures = [structures]
         self._keep = structures  # host arrays must stay alive during the call only, but keep refs anyway
-        ptrs = (C.POINTER(Structure) * len(structures))(*[s.structure_ptr if isinstance(s, Packed) else s for s in structures])
+        ptrs = (C.POINTER(Structure) * len(structures))(*[s.structure_ptr if hasattr(s, "structure_ptr") else s for s in structures])
         check(lib().arp_stage_upload(self._h, ptrs, len(structures)), self._h)
 
     def run(self, vdw_comp=0.1, dist_cutoff=6.5, flags=0):
