@@ -31,6 +31,12 @@ import threading
 import time
 from pathlib import Path
 
+# torchrun exports OMP_NUM_THREADS=1; the host packer (OpenMP) should use this rank's share of the cores instead.
+# Must happen before any library that carries libgomp is loaded.
+_WORLD = int(os.environ.get("WORLD_SIZE", "1"))
+if _WORLD > 1 or "OMP_NUM_THREADS" not in os.environ:
+    os.environ["OMP_NUM_THREADS"] = str(max(1, (os.cpu_count() or 1) // _WORLD))
+
 import numpy as np
 
 ROOT = Path(__file__).resolve().parent
@@ -161,6 +167,133 @@ def pinned_structure(A, packed):
     return dst, keep, total
 
 
+# single-GPU totals of the two multi-GPU configurations (profiles/r1t_big100m.json, r1t_batch.json): what the union of
+# the ranks' results must equal
+SLAB_EXPECT = {(16, 32, 24): {"rows": 88_915_968, "pairs_in_cutoff": 4_871_872_512, "atoms": 100_515_840, "ms_one_gpu": 23.49}}
+BATCH_EXPECT = {10000: {"rows": 42_379_378, "pairs_in_cutoff": 2_332_010_892, "atoms": 48_780_000, "ms_one_gpu": 10.45}}
+
+
+def bench_slab(ctx_device: int, rank: int, world: int, tiling, reps: int = 3):
+    """BASELINE config 5: the 6bft tiling cut into `world` x-slabs.  Every rank tiles and packs ONLY its own slab,
+    uploads it, and the halo exchange runs on the device behind the C ABI (arp_slab_exchange: CUDA select / pack /
+    unpack kernels + ncclSend / ncclRecv on the context's stream).  Returns this rank's numbers; reduced by the caller."""
+    import torch
+    import torch.distributed as dist
+
+    import arpeggia_b200 as A
+    from arpeggia_b200 import distributed as D
+
+    nx, ny, nz = tiling
+    base = A.parse_pdb(ROOT / "tests" / "data" / "6bft.pdb")
+    t0 = time.perf_counter()
+    own = D.pack_tiled_slab(base, nx, ny, nz, rank, world)
+    s_pack = time.perf_counter() - t0
+    ctx = A.Context(ctx_device)
+    sr = D.SlabRank(ctx, rank, world)
+    t0 = time.perf_counter()
+    sr.upload(own)
+    s_upload = time.perf_counter() - t0
+    halo_wall, info = [], None
+    for it in range(reps + 1):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        info = sr.exchange(0.1, 6.5)
+        halo_wall.append(1e3 * (time.perf_counter() - t0))
+    halo_wall = halo_wall[1:]  # the first call sizes the buffers
+    ms_run = []
+    for it in range(reps + 2):
+        ctx.run(0.1, 6.5, 1)
+        st = ctx.stats()
+        ms_run.append(st["ms_run"])
+    st1 = ctx.stats()
+    rows = int(st1["n_rows"])
+    ctx.run(0.1, 6.5, 0)  # the workload constant: in-cutoff pairs, every one counted by exactly one owner
+    r0 = ctx.download()
+    st0 = ctx.stats()
+    assert len(r0["rows"]) == rows, (len(r0["rows"]), rows)
+    out = {"rows": rows, "pairs_in_cutoff": int(r0["pairs_in_cutoff"]), "own_atoms": int(info["own_atoms"]), "ghost_atoms": int(info["ghost_atoms"]),
+           "ghost_rings": int(info["ghost_rings"]), "halo_bytes": int(info["bytes_sent"]), "n_peers": int(info["n_peers"]),
+           "ms_halo_wall": float(np.median(halo_wall)), "ms_halo_device": float(info["ms_total"]), "ms_halo_select": float(info["ms_select"]),
+           "ms_halo_transfer": float(info["ms_transfer"]), "ms_halo_unpack": float(info["ms_unpack"]),
+           "ms_device": float(np.median(ms_run[2:])), "ms_device_counting": float(st0["ms_run"]),
+           "ms_grid": float(st1["ms_grid"]), "ms_pairs": float(st1["ms_pairs"]), "s_pack": s_pack, "s_upload": s_upload,
+           "transport": int(info["transport"]), "local_atoms": int(st1["n_atoms"])}
+    ctx.close()
+    del own
+    return out
+
+
+def bench_batch(ctx_device: int, rank: int, world: int, n_structures: int, reps: int = 3):
+    """BASELINE config 4: complex k of the batch goes to rank k mod world (distributed.run_batch_shard ->
+    arp_contacts_batch); no collective on the data path."""
+    import arpeggia_b200 as A
+    from arpeggia_b200 import distributed as D, synth
+
+    base = A.parse_pdb(ROOT / "tests" / "data" / "6bft.pdb")
+    mine = D.shard_round_robin(n_structures, rank, world)
+    t0 = time.perf_counter()
+    packs = [A.Packed(synth.jittered_complex(base, k), "/", flags=2) for k in mine]
+    s_pack = time.perf_counter() - t0
+    ctx = A.Context(ctx_device)
+    t0 = time.perf_counter()
+    res = ctx.contacts_rows(packs, 0.1, 6.5, 0)  # one-shot through the C ABI: upload, kernels, rows back
+    s_call = time.perf_counter() - t0
+    rows, pairs = len(res["rows"]), int(res["pairs_in_cutoff"])
+    del res
+    ctx.upload(packs)
+    ms = []
+    for it in range(reps + 2):
+        ctx.run(0.1, 6.5, 1)
+        ms.append(ctx.stats()["ms_run"])
+    st = ctx.stats()
+    assert int(st["n_rows"]) == rows
+    out = {"structures": len(mine), "atoms": int(st["n_atoms"]), "rows": rows, "pairs_in_cutoff": pairs, "ms_device": float(np.median(ms[2:])),
+           "ms_grid": float(st["ms_grid"]), "ms_pairs": float(st["ms_pairs"]), "s_pack": s_pack, "s_one_shot_call": s_call}
+    ctx.close()
+    return out
+
+
+def all_ranks_ok(err, world: int, device):
+    """Every rank reports whether its leg succeeded before any rank reduces numbers (a failed rank must not leave the
+    others inside a collective); returns the first error text, or None."""
+    import torch
+    import torch.distributed as dist
+
+    if world == 1:
+        return err
+    box = [None] * world
+    dist.all_gather_object(box, err)
+    for r, e in enumerate(box):
+        if e:
+            return f"rank {r}: {e}"
+    return None
+
+
+def guarded_leg(fn, *a):
+    try:
+        return fn(*a), None
+    except Exception as e:  # noqa: BLE001 -- reported in the bench line
+        return None, f"{type(e).__name__}: {e}"[:400]
+
+
+def reduce_records(rec: dict, world: int, device):
+    """sum / max of every numeric field over the ranks (NCCL all-gather of one small tensor)."""
+    import torch
+    import torch.distributed as dist
+
+    keys = sorted(rec)
+    t = torch.tensor([float(rec[k]) for k in keys], dtype=torch.float64, device=device)
+    if world > 1:
+        parts = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(parts, t)
+        m = torch.stack(parts).cpu().numpy()
+    else:
+        m = t.cpu().numpy()[None, :]
+    return {k: m[:, i] for i, k in enumerate(keys)}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -171,6 +304,10 @@ def main():
     ap.add_argument("--flags", type=int, default=1, help="arp_params.flags (1 = emit-radius screen, the drop-in's path; 0 = counting mode)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-counting", action="store_true", help="skip the counting-mode (flags 0) side measurement")
+    ap.add_argument("--multi", default="auto", choices=["auto", "on", "off"],
+                    help="configs 4 and 5 over the ranks (\"batch\" and \"slab\" records); auto = when world > 1")
+    ap.add_argument("--slab-tiling", default="16,32,24", help="config 5 = 6bft tiled nx,ny,nz, cut into world x-slabs")
+    ap.add_argument("--batch-structures", type=int, default=10000, help="config 4 = this many jittered complexes over the ranks")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
@@ -393,6 +530,81 @@ def main():
             sap_info["cpu_cores"] = os.cpu_count() or 1
             sap_info["equals_oracle"] = bool(np.array_equal(got.view(np.uint32), want.view(np.uint32)))
 
+    # ---- BASELINE configs 4 and 5 over the ranks (every rank takes part; rank 0 reports) --------------------------------
+    slab_rec = batch_rec = None
+    if args.multi == "on" or (args.multi == "auto" and world > 1):
+        dev = f"cuda:{local}"
+        ctx.close()  # the config-3 buffers are not needed any more
+        del flush
+        torch.cuda.empty_cache()
+        tiling = tuple(int(v) for v in args.slab_tiling.split(","))
+        try:
+            t0 = time.perf_counter()
+            mine, err = guarded_leg(bench_slab, local, rank, world, tiling)
+            err = all_ranks_ok(err, world, dev)
+            if err:
+                raise RuntimeError(err)
+            m = reduce_records(mine, world, dev)
+            exp = SLAB_EXPECT.get(tiling)
+            slab_rec = {
+                "workload": f"6bft tiled {tiling[0]}x{tiling[1]}x{tiling[2]} (BASELINE.json configs[4]) cut into {world} x-slabs; every rank tiles and packs only its own slab",
+                "atoms": int(m["own_atoms"].sum()), "rows_union": int(m["rows"].sum()), "pairs_in_cutoff_sum": int(m["pairs_in_cutoff"].sum()),
+                "ms_device_max": float(m["ms_device"].max()), "ms_device_counting_max": float(m["ms_device_counting"].max()),
+                "ms_halo": float(m["ms_halo_wall"].max()), "ms_halo_device_max": float(m["ms_halo_device"].max()),
+                "ms_halo_select_max": float(m["ms_halo_select"].max()), "ms_halo_transfer_max": float(m["ms_halo_transfer"].max()),
+                "ms_halo_unpack_max": float(m["ms_halo_unpack"].max()),
+                "halo_bytes": [int(v) for v in m["halo_bytes"]], "ghost_atoms": [int(v) for v in m["ghost_atoms"]],
+                "ghost_rings": [int(v) for v in m["ghost_rings"]], "own_atoms": [int(v) for v in m["own_atoms"]],
+                "n_peers": [int(v) for v in m["n_peers"]], "transport": {0: "none", 1: "nccl send/recv", 2: "peer copies"}[int(m["transport"].max())],
+                "ms_grid_max": float(m["ms_grid"].max()), "ms_pairs_max": float(m["ms_pairs"].max()),
+                "s_tile_and_pack_max": float(m["s_pack"].max()), "s_upload_max": float(m["s_upload"].max()),
+                "pairs_per_s": float(m["pairs_in_cutoff"].sum() / (m["ms_device"].max() * 1e-3)),
+                "pairs_per_s_incl_halo": float(m["pairs_in_cutoff"].sum() / ((m["ms_device"].max() + m["ms_halo_wall"].max()) * 1e-3)),
+                "api": "arp_stage_upload (owned slab) -> arp_slab_exchange (CUDA select/pack/unpack + ncclSend/ncclRecv) -> arp_stage_run (flags 1)",
+                "s_total": time.perf_counter() - t0,
+            }
+            if exp:
+                slab_rec["expected"] = {"rows": exp["rows"], "pairs_in_cutoff": exp["pairs_in_cutoff"], "source": "profiles/r1t_big100m.json (one GPU)"}
+                slab_rec["verified"] = bool(slab_rec["rows_union"] == exp["rows"] and slab_rec["pairs_in_cutoff_sum"] == exp["pairs_in_cutoff"]
+                                            and slab_rec["atoms"] == exp["atoms"])
+                slab_rec["speedup_vs_one_gpu"] = exp["ms_one_gpu"] / slab_rec["ms_device_max"]
+                slab_rec["one_gpu_ms"] = exp["ms_one_gpu"]
+                assert slab_rec["verified"], ("slab totals differ from the single-GPU run", slab_rec["rows_union"], slab_rec["pairs_in_cutoff_sum"])
+        except Exception as e:  # keep the headline line even if this leg fails; the failure is in the record
+            slab_rec = {**(slab_rec or {}), "error": f"{type(e).__name__}: {e}"[:400]}
+            if world > 1:
+                print(f"[bench] slab leg failed on rank {rank}: {slab_rec['error']}", file=sys.stderr)
+        torch.cuda.empty_cache()
+        try:
+            t0 = time.perf_counter()
+            mine, err = guarded_leg(bench_batch, local, rank, world, args.batch_structures)
+            err = all_ranks_ok(err, world, dev)
+            if err:
+                raise RuntimeError(err)
+            m = reduce_records(mine, world, dev)
+            exp = BATCH_EXPECT.get(args.batch_structures)
+            batch_rec = {
+                "workload": f"{args.batch_structures} jittered ~5k-atom complexes (BASELINE.json configs[3]), complex k on rank k mod {world}",
+                "structures": int(m["structures"].sum()), "atoms": int(m["atoms"].sum()), "rows": int(m["rows"].sum()),
+                "pairs_in_cutoff": int(m["pairs_in_cutoff"].sum()), "ms_device_max": float(m["ms_device"].max()),
+                "structures_per_s": float(m["structures"].sum() / (m["ms_device"].max() * 1e-3)),
+                "pairs_per_s": float(m["pairs_in_cutoff"].sum() / (m["ms_device"].max() * 1e-3)),
+                "s_pack_max": float(m["s_pack"].max()), "s_one_shot_call_max": float(m["s_one_shot_call"].max()),
+                "structures_per_s_one_shot_call": float(m["structures"].sum() / m["s_one_shot_call"].max()),
+                "api": "distributed.run_batch_shard -> arp_contacts_batch per rank (no data-path collective); ms_device = arp_stage_run, flags 1",
+                "s_total": time.perf_counter() - t0,
+            }
+            if exp:
+                batch_rec["expected"] = {"rows": exp["rows"], "pairs_in_cutoff": exp["pairs_in_cutoff"], "source": "profiles/r1t_batch.json (one GPU)"}
+                batch_rec["verified"] = bool(batch_rec["rows"] == exp["rows"] and batch_rec["pairs_in_cutoff"] == exp["pairs_in_cutoff"]
+                                             and batch_rec["atoms"] == exp["atoms"])
+                batch_rec["speedup_vs_one_gpu"] = exp["ms_one_gpu"] / batch_rec["ms_device_max"]
+                assert batch_rec["verified"], ("batch totals differ from the single-GPU run", batch_rec["rows"], batch_rec["pairs_in_cutoff"])
+        except Exception as e:
+            batch_rec = {**(batch_rec or {}), "error": f"{type(e).__name__}: {e}"[:400]}
+            if world > 1:
+                print(f"[bench] batch leg failed on rank {rank}: {batch_rec['error']}", file=sys.stderr)
+
     if rank == 0:
         peaks = {}
         pk = ROOT / "MEASURED_PEAKS.json"
@@ -442,6 +654,8 @@ def main():
             "frame": frame_info,
             "counting_mode": counting,
             "sap_neighbor_sum": sap_info,
+            "slab": slab_rec,
+            "batch": batch_rec,
             "gpu_launches": int(st0["kernel_launches"]) * args.steps,
             "clocks": clocks,
             "contacts_per_s": world * n_rows / (ms_max * 1e-3),
