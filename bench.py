@@ -36,6 +36,33 @@ from pathlib import Path
 _WORLD = int(os.environ.get("WORLD_SIZE", "1"))
 if _WORLD > 1 or "OMP_NUM_THREADS" not in os.environ:
     os.environ["OMP_NUM_THREADS"] = str(max(1, (os.cpu_count() or 1) // _WORLD))
+os.environ.setdefault("OMP_WAIT_POLICY", "PASSIVE")  # idle OpenMP workers sleep instead of spinning next to the launching thread
+
+
+def bind_to_gpu_cores(local_rank: int, world: int):
+    """Pin this rank to the cores of the NUMA node its GPU hangs off (sysfs local_cpulist), split among the ranks that
+    share the node: pinned host buffers are then allocated next to the GPU and the launching thread stays there.
+    Returns a description for the bench line, or None when the topology cannot be read."""
+    try:
+        out = subprocess.run(["nvidia-smi", "--query-gpu=pci.bus_id", "--format=csv,noheader", "-i", str(local_rank)],
+                             capture_output=True, text=True, timeout=20).stdout.strip().lower()
+        bus = out[-12:] if len(out) >= 12 else out  # 00000000:1b:00.0 -> 0000:1b:00.0
+        cpus = Path(f"/sys/bus/pci/devices/{bus}/local_cpulist").read_text().strip()
+        node = Path(f"/sys/bus/pci/devices/{bus}/numa_node").read_text().strip()
+        ids = []
+        for part in cpus.split(","):
+            a, _, b = part.partition("-")
+            ids += list(range(int(a), int(b or a) + 1))
+        ids = sorted(set(ids) & set(os.sched_getaffinity(0)))
+        if not ids:
+            return None
+        per = max(1, (os.cpu_count() or 1) // max(world, 1))
+        k = (local_rank * per) % max(len(ids), 1)
+        mine = (ids[k:] + ids[:k])[:per] if world > 1 else ids
+        os.sched_setaffinity(0, mine)
+        return {"numa_node": int(node), "cores": len(mine), "first_core": mine[0]}
+    except Exception:
+        return None
 
 import numpy as np
 
@@ -250,6 +277,7 @@ def bench_batch(ctx_device: int, rank: int, world: int, n_structures: int, reps:
     st = ctx.stats()
     assert int(st["n_rows"]) == rows
     out = {"structures": len(mine), "atoms": int(st["n_atoms"]), "rows": rows, "pairs_in_cutoff": pairs, "ms_device": float(np.median(ms[2:])),
+           "ms_device_first": float(ms[0]), "retries": int(st["pair_kernel_retries"]), "cells": int(st["n_cells"]),
            "ms_grid": float(st["ms_grid"]), "ms_pairs": float(st["ms_pairs"]), "s_pack": s_pack, "s_one_shot_call": s_call}
     ctx.close()
     return out
@@ -324,6 +352,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
     torch.cuda.set_device(local)
+    binding = bind_to_gpu_cores(local, world) if world > 1 else None
     if world > 1:
         # NCCL announces its version on stdout when the communicator comes up; the contract is ONE json line there
         sys.stdout.flush()
@@ -437,7 +466,7 @@ def main():
         n_rows_e2e = one_call()
     barrier()
     t0 = time.perf_counter()
-    e2e_steps = max(3, min(args.steps, 10))
+    e2e_steps = max(3, args.steps)
     for _ in range(e2e_steps):
         n_rows_e2e = one_call()
     torch.cuda.synchronize()
@@ -550,6 +579,7 @@ def main():
                 "workload": f"6bft tiled {tiling[0]}x{tiling[1]}x{tiling[2]} (BASELINE.json configs[4]) cut into {world} x-slabs; every rank tiles and packs only its own slab",
                 "atoms": int(m["own_atoms"].sum()), "rows_union": int(m["rows"].sum()), "pairs_in_cutoff_sum": int(m["pairs_in_cutoff"].sum()),
                 "ms_device_max": float(m["ms_device"].max()), "ms_device_counting_max": float(m["ms_device_counting"].max()),
+                "ms_device_each": [round(float(v), 4) for v in m["ms_device"]],
                 "ms_halo": float(m["ms_halo_wall"].max()), "ms_halo_device_max": float(m["ms_halo_device"].max()),
                 "ms_halo_select_max": float(m["ms_halo_select"].max()), "ms_halo_transfer_max": float(m["ms_halo_transfer"].max()),
                 "ms_halo_unpack_max": float(m["ms_halo_unpack"].max()),
@@ -587,6 +617,9 @@ def main():
                 "workload": f"{args.batch_structures} jittered ~5k-atom complexes (BASELINE.json configs[3]), complex k on rank k mod {world}",
                 "structures": int(m["structures"].sum()), "atoms": int(m["atoms"].sum()), "rows": int(m["rows"].sum()),
                 "pairs_in_cutoff": int(m["pairs_in_cutoff"].sum()), "ms_device_max": float(m["ms_device"].max()),
+                "ms_device_each": [round(float(v), 4) for v in m["ms_device"]], "ms_device_first_each": [round(float(v), 4) for v in m["ms_device_first"]],
+                "ms_grid_each": [round(float(v), 4) for v in m["ms_grid"]], "ms_pairs_each": [round(float(v), 4) for v in m["ms_pairs"]],
+                "cells_each": [int(v) for v in m["cells"]], "retries_each": [int(v) for v in m["retries"]],
                 "structures_per_s": float(m["structures"].sum() / (m["ms_device"].max() * 1e-3)),
                 "pairs_per_s": float(m["pairs_in_cutoff"].sum() / (m["ms_device"].max() * 1e-3)),
                 "s_pack_max": float(m["s_pack"].max()), "s_one_shot_call_max": float(m["s_one_shot_call"].max()),
@@ -649,6 +682,7 @@ def main():
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "ms_per_step": float(e2e_t.item()), "ms_h2d": st["ms_h2d"], "ms_run": st["ms_run"], "ms_d2h": st["ms_d2h"],
+                    "ms_host_other_rank0": e2e_ms - st["ms_h2d"] - st["ms_run"] - st["ms_d2h"], "calls": e2e_steps, "cpu_binding": binding,
                     "api": "arp_contacts (C ABI, pinned host SoA in, host rows out)"},
             "e2e_concurrent": e2e_conc,
             "frame": frame_info,
