@@ -31,6 +31,7 @@ ROW_DTYPE = np.dtype([("from", "<u4"), ("to", "<u4"), ("label", "<u4"), ("distan
 RING_FLAG = 0x80000000
 FLAG_EMIT_RADIUS_SCREEN = 1
 FLAG_COUNT_CLASSIFIED = 2
+STATIC_MAX_ATOMS = 131072  # ARP_STATIC_MAX_ATOMS
 HOST_FLAG_NO_MULTIMODEL_QUIRK = 1
 HOST_FLAG_SKIP_LOAD_FILTER = 2
 HOST_FLAG_NO_COUNTERS = 4
@@ -191,6 +192,7 @@ SIGNATURES = {
     "arp_ctx_create_multi": (C.c_int, [C.POINTER(_P), C.POINTER(C.c_int), C.c_int]),
     "arp_slab_exchange": (C.c_int, [_P, C.POINTER(Params), C.POINTER(SlabInfo)]),
     "arp_slab_exchange_multi": (C.c_int, [C.POINTER(_P), C.c_int, C.POINTER(Params), C.POINTER(SlabInfo)]),
+    "arp_neighbor_sum_static": (C.c_int, [C.c_int, _P, _P, _P, _P, _P, _P, C.c_int64, C.c_float, _P]),
     "arp_host_alloc": (C.c_int, [C.POINTER(_P), C.c_int64]),
     "arp_host_free": (None, [_P]),
     # arpeggia_host.h

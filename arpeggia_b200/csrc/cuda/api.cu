@@ -467,3 +467,4 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
 #include "api_run.inc"
 #include "api_nsum.inc"
 #include "api_slab.inc"
+#include "api_static.inc"

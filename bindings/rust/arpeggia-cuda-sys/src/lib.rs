@@ -37,6 +37,8 @@ pub const ARP_FLAG_EMIT_RADIUS_SCREEN: u32 = 0x1;
 pub const ARP_FLAG_COUNT_CLASSIFIED: u32 = 0x2;
 /// `Interaction` (structs.rs:6-51) in declaration order: `label as usize` indexes the enum.
 pub const ARP_N_LABELS: usize = 19;
+pub const ARP_STATIC_MAX_ATOMS: i64 = 131072;
+pub const ARP_STATIC_MAX_CELLS: i64 = 262144;
 
 #[repr(C)]
 pub struct arp_structure {
@@ -257,6 +259,7 @@ extern "C" {
     pub fn arp_ctx_create_multi(out: *mut *mut arp_ctx, devices: *const c_int, n_devices: c_int) -> c_int;
     pub fn arp_slab_exchange(ctx: *mut arp_ctx, p: *const arp_params, info: *mut arp_slab_info) -> c_int;
     pub fn arp_slab_exchange_multi(ctx: *const *mut arp_ctx, n: c_int, p: *const arp_params, info: *mut arp_slab_info) -> c_int;
+    pub fn arp_neighbor_sum_static(device: c_int, stream: *mut c_void, x: *const f64, y: *const f64, z: *const f64, weight: *const f32, select: *const u8, n_atoms: i64, radius: f32, out: *mut f32) -> c_int;
     pub fn arp_host_alloc(out: *mut *mut c_void, bytes: i64) -> c_int;
     pub fn arp_host_free(p: *mut c_void);
 }

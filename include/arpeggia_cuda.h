@@ -328,6 +328,24 @@ typedef struct arp_slab_info {
 int  arp_slab_exchange(arp_ctx* ctx, const arp_params* p, arp_slab_info* info /* may be NULL */);
 int  arp_slab_exchange_multi(arp_ctx* const* ctx, int n, const arp_params* p, arp_slab_info* info /* [n] or NULL */);
 
+/* ---- the neighbour sum for callers that cannot allocate -----------------------------------------------------------------
+ * No counterpart in the reference: added for callers that must not call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same computation as
+ * arp_stage_neighbor_sum -- the same kernels -- on caller-owned DEVICE arrays of one structure:
+ *     out[i] = select[i] ? sum of weight[j] over j with select[j] and distance_2(i, j) <= (double)(radius * radius) : 0
+ * with every byte of scratch (bounding box, cell list, scan status, sorted records) in one file-scope __device__ array
+ * of fixed size: ARP_STATIC_MAX_ATOMS atoms at most (more fails with ARP_ERR_LIMIT; the cell grid is coarsened to fit
+ * ARP_STATIC_MAX_CELLS).  Every GPU that loads the library holds that array (8.4 MB) until the process exits.
+ * The call allocates nothing -- no cudaMalloc / cudaFree / cudaMallocHost, no context, no library routine that does --
+ * launches on `stream` (a cudaStream_t; NULL = the default stream) of `device` and returns after synchronising that
+ * stream.  x / y / z / weight / select / out are device pointers of n_atoms entries.  ALL calls on a device share the
+ * one array (it is re-initialised by every call): calls that overlap on the GPU -- from two host threads or two
+ * streams -- race and give wrong sums; serialise them.  Errors: arp_last_error(NULL). */
+#define ARP_STATIC_MAX_ATOMS 131072
+#define ARP_STATIC_MAX_CELLS 262144
+int  arp_neighbor_sum_static(int device, void* stream, const double* x, const double* y, const double* z, const float* weight,
+                             const unsigned char* select, int64_t n_atoms, float radius, float* out);
+
 /* Page-locked host memory for callers that want true asynchronous H2D/D2H (optional). */
 int  arp_host_alloc(void** out, int64_t bytes);
 void arp_host_free(void* p);
