@@ -41,8 +41,13 @@ def contacts(input_file: str, groups: str = "/", vdw_comp: float = 0.1, dist_cut
         no ring residue at all, element without a van der Waals radius, ...), or when no CUDA device exists.
     """
     del num_threads
-    atoms = load_atoms(input_file)
-    # the reference's DataFrame carries no workload counters: let the device screen at the emit radius (same rows)
-    table = default_context(device).contacts_table(atoms, groups, float(vdw_comp), float(dist_cutoff), bool(ignore_zero_occupancy),
-                                                   flags=FLAG_NO_COUNTERS)
-    return to_frame(table)
+    # one C call, file -> sorted frame (arph_contacts_file: reader, packer, device search + classification, frame built on
+    # the device); the reference's DataFrame carries no workload counters, so the device screens at the emit radius (same
+    # rows).  The columns reach Arrow without a Python list (core.table_to_arrow).
+    at, _ = default_context(device).contacts_file_arrow(input_file, groups, float(vdw_comp), float(dist_cutoff), bool(ignore_zero_occupancy),
+                                                        flags=FLAG_NO_COUNTERS)
+    try:
+        import polars as pl
+    except ImportError:
+        return at
+    return pl.from_arrow(at)

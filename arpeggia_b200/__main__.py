@@ -42,7 +42,8 @@ def main(argv=None) -> int:
     n_clash = sum(1 for v in inter if v == "StericClash")
     if n_clash:  # cli/contacts.rs:116-132
         log.warning("Found %d steric %s", n_clash, "clash" if n_clash == 1 else "clashes")
-    path = os.path.join(out_dir, a.filename + "." + a.output_format)
+    # Path::with_extension (cli/contacts.rs:111-113): an extension already in the name is REPLACED, not appended to
+    path = os.path.join(out_dir, os.path.splitext(a.filename)[0] + "." + a.output_format)
     write_table(df, path, a.output_format)
     log.info("Results saved to %s", path)
     return 0

@@ -199,6 +199,7 @@ SIGNATURES = {
     "arph_last_error": (C.c_char_p, []),
     "arph_parse_pdb": (C.c_int, [C.c_char_p, C.POINTER(_P), C.POINTER(C.c_int64)]),
     "arph_parse_cif": (C.c_int, [C.c_char_p, C.POINTER(_P), C.POINTER(C.c_int64)]),
+    "arph_parse_cif_ids": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(_P), C.POINTER(C.c_int64)]),
     "arph_parse_file": (C.c_int, [C.c_char_p, C.POINTER(_P), C.POINTER(C.c_int64)]),
     "arph_free": (None, [_P]),
     "arph_pack": (C.c_int, [_P, C.c_int64, C.c_char_p, C.c_int, C.c_uint32, C.POINTER(_P)]),

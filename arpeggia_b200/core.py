@@ -24,11 +24,11 @@ COLUMNS = (
 )
 
 
-def _parse_with(fn_name: str, path) -> np.ndarray:
+def _parse_with(fn_name: str, path, *extra) -> np.ndarray:
     L = lib()
     p = C.c_void_p()
     n = C.c_int64()
-    check(getattr(L, fn_name)(os.fspath(path).encode(), C.byref(p), C.byref(n)))
+    check(getattr(L, fn_name)(os.fspath(path).encode(), *extra, C.byref(p), C.byref(n)))
     try:
         if n.value == 0:
             return np.zeros(0, dtype=ATOM_DTYPE)
@@ -43,9 +43,10 @@ def parse_pdb(path) -> np.ndarray:
     return _parse_with("arph_parse_pdb", path)
 
 
-def parse_cif(path) -> np.ndarray:
-    """The _atom_site loop of an mmCIF file as a structured array (ATOM_DTYPE)."""
-    return _parse_with("arph_parse_cif", path)
+def parse_cif(path, auth_ids: bool = False) -> np.ndarray:
+    """The _atom_site loop of an mmCIF file as a structured array (ATOM_DTYPE).  Chain ids / residue numbers are the label
+    identifiers (pdbtbx's choice as far as it is known); auth_ids=True takes the author identifiers instead."""
+    return _parse_with("arph_parse_cif_ids", path, int(bool(auth_ids)))
 
 
 def load_atoms(path) -> np.ndarray:
@@ -186,6 +187,68 @@ def read_table(t: Table) -> dict:
     return out
 
 
+class _TableOwner:
+    """Keeps an arph_table alive for the Arrow buffers that point into it; frees it when the last of them is gone."""
+
+    def __init__(self, tp):
+        self.tp = tp
+
+    def __del__(self):
+        try:
+            lib().arph_table_free(self.tp)
+        except Exception:  # interpreter teardown
+            pass
+
+
+def table_to_arrow(tp, strings: str = "string"):
+    """POINTER(arph_table) -> pyarrow.Table with the reference's schema (src/contacts/mod.rs:140-214).  TAKES OWNERSHIP of
+    the table.  No Python list and no copy of a column: every numeric column is an Arrow array over the table's own
+    (page-locked) memory, and the int32 id columns are the INDEX buffers of Arrow dictionary arrays over the table's string
+    dictionary.  strings="dictionary" leaves those columns dictionary-encoded (polars: Categorical); "string" decodes them
+    to large_utf8 in Arrow's C++ (polars: String, the reference's dtype)."""
+    import pyarrow as pa
+
+    t = tp.contents
+    n = int(t.n_rows)
+    owner = _TableOwner(tp)
+    dic = pa.array([t.strings[i].decode() for i in range(t.n_strings)], type=pa.large_string())  # a few thousand entries
+    lab = pa.array(LABELS, type=pa.large_string())
+
+    def wrap(ptr, typ, width, validity=None, nulls=0):
+        if n == 0:
+            return pa.array([], type=typ)
+        buf = pa.foreign_buffer(C.addressof(ptr.contents), n * width, base=owner)
+        return pa.Array.from_buffers(typ, n, [validity, buf], null_count=nulls)
+
+    def text(idx, d):
+        if n == 0:
+            return pa.array([], type=pa.large_string()) if strings != "dictionary" else pa.DictionaryArray.from_arrays(pa.array([], type=pa.int32()), d)
+        a = pa.DictionaryArray.from_arrays(idx, d)  # checks the indices against the dictionary
+        return a if strings == "dictionary" else a.dictionary_decode()
+
+    bitmap, n_null = None, 0
+    if n:
+        valid = np.ctypeslib.as_array(t.sc_valid, shape=(n,)) != 0
+        n_null = int(n - np.count_nonzero(valid))
+        bitmap = pa.py_buffer(np.packbits(valid, bitorder="little").tobytes())
+    cols = []
+    for name in COLUMNS:
+        if name == "model":
+            a = wrap(t.model, pa.uint32(), 4)
+        elif name == "interaction":
+            a = text(wrap(t.interaction, pa.uint8(), 1), lab)
+        elif name == "distance":
+            a = wrap(t.distance, pa.float32(), 4)
+        elif name.startswith("sc_"):
+            a = wrap(getattr(t, name), pa.float32(), 4, bitmap, n_null)
+        elif name.split("_", 1)[-1] in STRING_COLS:
+            a = text(wrap(getattr(t, name), pa.int32(), 4), dic)
+        else:
+            a = wrap(getattr(t, name), pa.int32(), 4)
+        cols.append(a)
+    return pa.table(cols, names=list(COLUMNS))
+
+
 class Context:
     """arp_ctx: one per (device, host thread).  Creating it without a CUDA device raises ArpeggiaError."""
 
@@ -228,6 +291,17 @@ class Context:
         finally:
             L.arph_table_free(tp)
 
+    def contacts_file_arrow(self, path, groups="/", vdw_comp=0.1, dist_cutoff=6.5, ignore_zero_occupancy=False, flags=0,
+                            strings: str = "string"):
+        """arph_contacts_file: file -> (parse, pack, device, frame) -> pyarrow.Table, plus the host-side timings."""
+        L = lib()
+        tp = C.POINTER(Table)()
+        check(L.arph_contacts_file(self._h, os.fspath(path).encode(), groups.encode(), vdw_comp, dist_cutoff, int(ignore_zero_occupancy),
+                                   flags, C.byref(tp)))
+        t = tp.contents
+        info = {k: getattr(t, k) for k in ("n_rows", "n_atoms", "t_setup_s", "t_classify_s", "t_table_s")}
+        return table_to_arrow(tp, strings), info  # the Arrow table owns the arph_table from here on
+
     # ---- staged -------------------------------------------------------------------------------------
     def upload(self, structures):
         if isinstance(structures, Packed):
@@ -264,7 +338,7 @@ class Context:
         finally:
             L.arp_result_free(self._h, rp)
 
-    def frame(self, packed: "Packed") -> dict:
+    def frame(self, packed: "Packed", arrow: str | None = None):
         """arp_stage_frame after run(): sort + decode + sc join on the device -> the table of get_contacts, plus the
         device timings of the frame stage under "frame_stats"."""
         L = lib()
@@ -275,6 +349,8 @@ class Context:
         fs = {k: getattr(fp.contents, k) for k in ("ms_sort", "ms_columns", "ms_d2h", "sort_passes", "key_bits")}
         tb = C.POINTER(Table)()
         check(L.arph_table_from_frame(packed._h, fp, C.byref(tb)))  # owns the frame from here on
+        if arrow:
+            return table_to_arrow(tb, arrow), fs  # owns the table (and the frame's page-locked columns under it)
         try:
             out = read_table(tb.contents)
         finally:

@@ -175,7 +175,7 @@ struct arp_ctx {
   HBuf<unsigned long long> h_bbox;
   HBuf<Counters> h_ctr;
   HBuf<unsigned char> stage;  // concatenation buffer for batch uploads
-  HBuf<arp_row> h_rows;       // result rows (library-owned, reused by the next download)
+  std::vector<HBuf<arp_row>> row_pool;  // page-locked row buffers of freed results (every arp_result owns its rows)
 
   // A whole run as a CUDA graph: captured when the same job is run again with the same parameters and buffer sizes
   // (parameter studies on a resident structure, the timed loop of bench.py), replayed from then on -- one graph launch

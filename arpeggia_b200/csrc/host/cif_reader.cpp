@@ -1,9 +1,12 @@
 // mmCIF reader for the host side: the `_atom_site` loop of the first data block that has one, as atom records.
 // The reference reads PDB or mmCIF by file extension through pdbtbx (src/utils.rs:51-57,
 // ReadOptions{only_atomic_coords: true, level: Loose}); pdbtbx's source is not under /root/reference, so the column
-// choice below is this repo's statement of it and is UNPINNED: author identifiers where the file
-// has them (auth_asym_id, auth_seq_id -- what the PDB-format file of the same entry carries, so both formats give the
-// same frame), label identifiers otherwise.
+// choice below is this repo's statement of it and is UNPINNED.  As far as pdbtbx 0.12's _atom_site parser is
+// remembered it REQUIRES label_asym_id / label_seq_id / label_comp_id / label_atom_id and builds chain ids and residue
+// numbers from them, so the default here is the label identifiers (auth_* only where a label value is absent or null,
+// e.g. label_seq_id "." of waters).  Entries whose author and label ids differ (6bft: auth chains A,B,C,G,H,L are label
+// chains A..F) then give different chain / resi columns than their PDB-format file: that is the reference's behaviour
+// too.  arph_parse_cif_ids(path, 1, ...) selects the author identifiers instead (what the PDB-format file carries).
 // One pass over a whole-file buffer; tokens are string views into it; numbers via std::from_chars.
 #include <charconv>
 #include <cstdio>
@@ -117,7 +120,7 @@ bool is_loop_end(std::string_view tok) {  // an unquoted keyword or tag where a 
 }
 
 // one _atom_site row -> one record; false when a coordinate does not parse
-bool row_to_record(const std::string_view* row, const int* where, arp_atom_record& r) {
+bool row_to_record(const std::string_view* row, const int* where, bool auth_ids, arp_atom_record& r) {
   auto get = [&](int c) -> std::string_view {
     if (where[c] < 0) return {};
     const std::string_view v = row[where[c]];
@@ -133,10 +136,10 @@ bool row_to_record(const std::string_view* row, const int* where, arp_atom_recor
   number(get(MODEL), r.model);
   store(r.name, sizeof r.name, first_of(LABEL_ATOM, AUTH_ATOM));
   store(r.resn, sizeof r.resn, first_of(LABEL_COMP, AUTH_COMP));
-  store(r.chain, sizeof r.chain, first_of(AUTH_ASYM, LABEL_ASYM));
+  store(r.chain, sizeof r.chain, auth_ids ? first_of(AUTH_ASYM, LABEL_ASYM) : first_of(LABEL_ASYM, AUTH_ASYM));
   store(r.altloc, sizeof r.altloc, get(ALT));
   store(r.icode, sizeof r.icode, get(INS));
-  number(first_of(AUTH_SEQ, LABEL_SEQ), r.resi);
+  number(auth_ids ? first_of(AUTH_SEQ, LABEL_SEQ) : first_of(LABEL_SEQ, AUTH_SEQ), r.resi);
   if (!number(get(X), r.x) || !number(get(Y), r.y) || !number(get(Z), r.z)) return false;
   r.occupancy = 1.0;
   number(get(OCC), r.occupancy);
@@ -163,7 +166,7 @@ struct CifPiece {
   int64_t bad_row = -1;  // piece-local index of a row with an unreadable coordinate
 };
 
-void parse_piece(std::string_view text, size_t width, const int* where, CifPiece& P) {
+void parse_piece(std::string_view text, size_t width, const int* where, bool auth_ids, CifPiece& P) {
   std::vector<std::string_view> row(width);
   P.recs.reserve(text.size() / 80 + 1);
   size_t pos = 0;
@@ -196,7 +199,7 @@ void parse_piece(std::string_view text, size_t width, const int* where, CifPiece
       return;
     }
     arp_atom_record r;
-    if (!row_to_record(row.data(), where, r)) {
+    if (!row_to_record(row.data(), where, auth_ids, r)) {
       P.bad_row = (int64_t)P.recs.size();
       return;
     }
@@ -208,7 +211,8 @@ void parse_piece(std::string_view text, size_t width, const int* where, CifPiece
 
 extern "C" {
 
-int arph_parse_cif(const char* path, arp_atom_record** out, int64_t* n) {
+int arph_parse_cif_ids(const char* path, int use_auth_ids, arp_atom_record** out, int64_t* n) {
+  const bool auth_ids = use_auth_ids != 0;
   *out = nullptr;
   *n = 0;
   FILE* f = std::fopen(path, "rb");
@@ -280,7 +284,7 @@ int arph_parse_cif(const char* path, arp_atom_record** out, int64_t* n) {
       }
       std::vector<CifPiece> pieces((size_t)NT);
 #pragma omp parallel for schedule(static, 1) num_threads(NT)
-      for (int t = 0; t < NT; ++t) parse_piece(body.substr(cut[(size_t)t], cut[(size_t)t + 1] - cut[(size_t)t]), width, where, pieces[(size_t)t]);
+      for (int t = 0; t < NT; ++t) parse_piece(body.substr(cut[(size_t)t], cut[(size_t)t + 1] - cut[(size_t)t]), width, where, auth_ids, pieces[(size_t)t]);
       bool regular = true;
       size_t total = 0;
       int last = NT - 1;
@@ -326,7 +330,7 @@ int arph_parse_cif(const char* path, arp_atom_record** out, int64_t* n) {
       }
       if (k < width) break;  // truncated last row (Loose: dropped)
       arp_atom_record r;
-      if (!row_to_record(row.data(), where, r)) {
+      if (!row_to_record(row.data(), where, auth_ids, r)) {
         arp::last_error() = "mmCIF _atom_site row " + std::to_string(recs.size() + 1) + ": unreadable coordinate";
         return ARP_ERR_IO;
       }
@@ -343,6 +347,8 @@ int arph_parse_cif(const char* path, arp_atom_record** out, int64_t* n) {
   if (!recs.empty()) std::memcpy(*out, recs.data(), recs.size() * sizeof(arp_atom_record));
   return ARP_OK;
 }
+
+int arph_parse_cif(const char* path, arp_atom_record** out, int64_t* n) { return arph_parse_cif_ids(path, 0, out, n); }
 
 // pdbtbx dispatches on the extension (src/utils.rs:51-57): .cif / .mmcif -> mmCIF, everything else -> PDB
 int arph_parse_file(const char* path, arp_atom_record** out, int64_t* n) {

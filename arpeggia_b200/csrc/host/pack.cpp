@@ -482,7 +482,7 @@ void pack_records(const arp_atom_record* recs, int64_t n, const std::string& gro
             if (last_el_class < 0) {
               const std::string el = fixed_field(a.element, 4);
               throw Error{ARP_ERR_ELEMENT, el.empty() ? "atom " + std::to_string(a.serial) + " has no element"
-                                                      : "element '" + el + "' has no van der Waals radius"};
+                                                      : "unsupported element '" + el + "' (not one of the element classes this path knows; pdbtbx would need a van der Waals radius for it, vdw.rs:28)"};
             }
             const uint32_t by_res = bits_res[k];                      // residue().name(): hydrophobic.rs:16, aromatic.rs:18, vdw.rs:50
             const uint32_t by_conf = c.name == resn_id ? by_res : bits_of(c.name, last_name_id);  // conformer().name(): ionic.rs:45-46, hbond.rs:120-121

@@ -88,6 +88,7 @@ int arph_parse_pdb(const char* path, arp_atom_record** out, int64_t* n) {
   struct Chunk {
     std::vector<arp_atom_record> recs;
     std::vector<std::pair<size_t, int64_t>> marks;  // (records of this chunk before the MODEL line, its serial)
+    size_t bad_pos = std::string::npos;             // byte offset of the first line with an unreadable field
   };
   int T = 1;
 #ifdef _OPENMP
@@ -130,17 +131,30 @@ int arph_parse_pdb(const char* path, arp_atom_record** out, int64_t* n) {
       store(r.altloc, sizeof r.altloc, field(line, 17, 17));
       store(r.resn, sizeof r.resn, field(line, 18, 20));
       store(r.chain, sizeof r.chain, field(line, 22, 22));
-      number(field(line, 23, 26), r.resi);
+      // a residue number or coordinate that does not parse ("****", a truncated line) is an error in pdbtbx even at the
+      // Loose level: fail with the line number instead of placing the atom at the origin / in residue 0
+      bool ok = number(field(line, 23, 26), r.resi);
       store(r.icode, sizeof r.icode, field(line, 27, 27));
-      number(field(line, 31, 38), r.x);
-      number(field(line, 39, 46), r.y);
-      number(field(line, 47, 54), r.z);
+      ok = number(field(line, 31, 38), r.x) && ok;
+      ok = number(field(line, 39, 46), r.y) && ok;
+      ok = number(field(line, 47, 54), r.z) && ok;
+      if (!ok) {
+        C.bad_pos = (size_t)(line.data() - text.data());
+        break;
+      }
       r.occupancy = 1.0;
       number(field(line, 55, 60), r.occupancy);
       element_of(line, r.element);
       C.recs.push_back(r);
     }
   }
+  for (int t = 0; t < T; ++t)
+    if (chunks[(size_t)t].bad_pos != std::string::npos) {
+      const size_t at = chunks[(size_t)t].bad_pos;
+      const size_t line_no = (size_t)std::count(text.begin(), text.begin() + (std::ptrdiff_t)at, '\n') + 1;
+      arp::last_error() = std::string(path) + ":" + std::to_string(line_no) + ": residue number or coordinate field does not parse";
+      return ARP_ERR_IO;
+    }
   size_t total = 0;
   std::vector<size_t> first((size_t)T + 1, 0);
   std::vector<int64_t> model_in((size_t)T, 0);  // MODEL serial in force where the chunk starts

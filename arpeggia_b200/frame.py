@@ -45,9 +45,15 @@ def write_table(frame, path, file_type: str = "csv"):
 
     at = frame if isinstance(frame, pa.Table) else frame.to_arrow()
     if file_type == "csv":
-        import pyarrow.csv as pacsv
+        # the reference writes through polars' CsvWriter (utils.rs:121-144): fields quoted only when they need it
+        try:
+            import polars as pl
 
-        pacsv.write_csv(at, path)
+            (frame if not isinstance(frame, pa.Table) else pl.from_arrow(frame)).write_csv(path)
+        except ImportError:
+            import pyarrow.csv as pacsv
+
+            pacsv.write_csv(at, path, write_options=pacsv.WriteOptions(quoting_style="needed"))
     elif file_type == "parquet":
         import pyarrow.parquet as pq
 

@@ -78,3 +78,28 @@ def jittered_complex(base: np.ndarray, k: int, chains=(b"A", b"B", b"C", b"G"), 
     for ax in ("x", "y", "z"):
         sub[ax] = (_milli(sub[ax]) + rng.integers(-amplitude_milli, amplitude_milli + 1, size=len(sub))) / 1000.0
     return sub
+
+
+def write_cif(atoms: np.ndarray, path) -> None:
+    """Atom records -> a minimal PDBx/mmCIF file (one _atom_site row per line, label ids = author ids).  The tiled
+    assemblies carry 6-character chain ids, which the one-column chain field of the PDB format cannot hold."""
+    cols = ["group_PDB", "id", "type_symbol", "label_atom_id", "label_alt_id", "label_comp_id", "label_asym_id", "label_seq_id",
+            "pdbx_PDB_ins_code", "Cartn_x", "Cartn_y", "Cartn_z", "occupancy", "auth_seq_id", "auth_asym_id", "pdbx_PDB_model_num"]
+
+    def txt(field, blank="."):
+        out = []
+        for b in atoms[field].tolist():
+            v = b.decode().strip()
+            out.append(blank if not v else (f'"{v}"' if ("'" in v or " " in v) else v))
+        return out
+
+    het = ["HETATM" if h else "ATOM" for h in atoms["hetero"].tolist()]
+    el, name, alt, resn, chain, ic = txt("element", "?"), txt("name"), txt("altloc"), txt("resn"), txt("chain"), txt("icode", "?")
+    ser, resi, mod = atoms["serial"].tolist(), atoms["resi"].tolist(), np.maximum(atoms["model"], 1).tolist()
+    x, y, z, occ = atoms["x"].tolist(), atoms["y"].tolist(), atoms["z"].tolist(), atoms["occupancy"].tolist()
+    line = [f"{het[i]} {ser[i]} {el[i]} {name[i]} {alt[i]} {resn[i]} {chain[i]} {resi[i]} {ic[i]} {x[i]:.3f} {y[i]:.3f} {z[i]:.3f} "
+            f"{occ[i]:.2f} {resi[i]} {chain[i]} {mod[i]}" for i in range(len(atoms))]
+    with open(path, "w") as f:
+        f.write("data_SYNTH\n#\nloop_\n" + "".join(f"_atom_site.{c}\n" for c in cols))
+        f.write("\n".join(line))
+        f.write("\n#\n")

@@ -519,6 +519,14 @@ def main():
         t0 = time.perf_counter()
         fr = ctx.frame(packed)
         t_dev_wall = 1e3 * (time.perf_counter() - t0)
+        walls = {}
+        for mode in ("dictionary", "string"):  # the same frame straight into Arrow (no Python list): dictionary-encoded / String columns
+            ctx.frame(packed, arrow=mode)
+            t0 = time.perf_counter()
+            at, _ = ctx.frame(packed, arrow=mode)
+            walls[mode] = 1e3 * (time.perf_counter() - t0)
+            assert at.num_rows == fr["n_rows"]
+        del at
         t0 = time.perf_counter()
         host_tab = packed.build_table(rows_host)
         t_host = 1e3 * (time.perf_counter() - t0)
@@ -526,9 +534,44 @@ def main():
         frame_info = {"rows": int(fr["n_rows"]), "ms_sort": fr["frame_stats"]["ms_sort"], "ms_columns": fr["frame_stats"]["ms_columns"],
                       "ms_d2h": fr["frame_stats"]["ms_d2h"], "sort_passes": fr["frame_stats"]["sort_passes"],
                       "key_bits": fr["frame_stats"]["key_bits"], "ms_wall_incl_numpy_copy": t_dev_wall,
+                      "ms_wall_to_arrow_dictionary_columns": walls["dictionary"], "ms_wall_to_arrow_string_columns": walls["string"],
                       "host_table_ms_incl_numpy_copy": t_host, "equals_host_table": bool(same),
                       "api": "arp_stage_frame (keys + radix sort + decode + sc join on the device, columns D2H)"}
     d2h_bytes = int(n_rows_e2e * 16)
+
+    # ---- the real drop-in call: file -> sorted frame (arph_contacts_file / arpeggia_b200.contacts), configs 2 and 3 ------------
+    dropin = None
+    if rank == 0 and world == 1 and not args.no_counting:
+        import tempfile
+
+        from arpeggia_b200 import synth
+
+        dropin = {}
+        with tempfile.TemporaryDirectory() as td:
+            cif3 = os.path.join(td, "config3.cif")  # 6-character chain ids do not fit the PDB format's one-column chain field
+            t0 = time.perf_counter()
+            synth.write_cif(atoms, cif3)
+            dropin["s_write_config3_cif_python"] = time.perf_counter() - t0
+            dropin["config3_file_bytes"] = os.path.getsize(cif3)
+            for name, path in (("config2_6bft_pdb", str(ROOT / "tests" / "data" / "6bft.pdb")), ("config3_1m_cif", cif3)):
+                best = None
+                for _ in range(3):
+                    t0 = time.perf_counter()
+                    at, info = ctx.contacts_file_arrow(path, flags=A.FLAG_NO_COUNTERS, strings="dictionary")
+                    w_dict = time.perf_counter() - t0
+                    rec = {"s_wall_file_to_arrow": w_dict, "rows": int(info["n_rows"]), "atoms": int(info["n_atoms"]),
+                           "s_pack_and_side_tables": info["t_setup_s"], "s_device_upload_run_frame": info["t_classify_s"],
+                           "s_table_wrap": info["t_table_s"]}
+                    if best is None or w_dict < best["s_wall_file_to_arrow"]:
+                        best = rec
+                    del at
+                t0 = time.perf_counter()
+                df = A.contacts(path)
+                best["s_wall_python_contacts_string_columns"] = time.perf_counter() - t0
+                del df
+                dropin[name] = best
+        dropin["api"] = ("arph_contacts_file (reader + packer + device + frame, one C call) -> Arrow with dictionary-encoded string "
+                         "columns; arpeggia_b200.contacts() = the same + Arrow String columns (the reference's dtype)")
 
     # ---- the SAP radius query (src/sap.rs:181-215) on the same assembly, beside the oracle ---------
     sap_info = None
@@ -687,12 +730,14 @@ def main():
             "e2e_concurrent": e2e_conc,
             "frame": frame_info,
             "counting_mode": counting,
+            "dropin_e2e": dropin,
             "sap_neighbor_sum": sap_info,
             "slab": slab_rec,
             "batch": batch_rec,
             "gpu_launches": int(st0["kernel_launches"]) * args.steps,
             "clocks": clocks,
             "contacts_per_s": world * n_rows / (ms_max * 1e-3),
+            "pairs_in_cutoff_per_s": value,  # what `value` is: the workload's in-cutoff pairs (a constant, see config.screen) / step time
             "candidate_tests_per_s": world * res["pairs_screened"] / (ms_max * 1e-3),
             "atoms_per_s": world * n_atoms / (ms_max * 1e-3),
             "stage_ms": {"grid": t_grid / args.steps, "pairs": ms_pairs, "rings_overlapped": t_rings / args.steps},
@@ -702,6 +747,21 @@ def main():
             c = cpu_reference(atoms, 125, threads)
             line["cpu_baseline"] = {"value": c["pairs"] / c["hot_s"], "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": c["sample"], "seconds": c["hot_s"]}
+            # the reference's own shape (shape A): serial neighbour search + classification at the default -j 1
+            # (cli/contacts.rs:46-47, complex.rs:197-213), on a bounded sample
+            c1 = cpu_reference(atoms, 25, 1)
+            line["cpu_baseline_ref_shaped"] = {"value": c1["pairs"] / c1["hot_s"], "unit": UNIT, "cores": 1, "kind": "port",
+                                               "sample": c1["sample"], "seconds": c1["hot_s"],
+                                               "shape": "serial neighbour search, 1 thread (the reference's default num_threads = 1)"}
+            # the whole get_contacts on the CPU: hierarchy + index build, search, classification, ring loops, frame (join + sort)
+            from oracle import oracle as O
+            t0 = time.perf_counter()
+            full = O.contacts(atoms.view(O.ATOM_DTYPE), "/", 0.1, 6.5, flags=O.FLAG_SKIP_LOAD_FILTER, num_threads=threads)
+            line["cpu_full"] = {"s_wall": time.perf_counter() - t0, "cores": threads, "kind": "port", "rows": int(full["n_rows"]),
+                                "s_setup": full["t_setup_s"], "s_search": full["t_search_s"], "s_classify": full["t_classify_s"],
+                                "s_rings": full["t_rings_s"], "s_table": full["t_table_s"],
+                                "what": "oracle get_contacts on atom records of config 3 (no file parsing), all host threads"}
+            del full
         else:
             line["cpu_baseline"] = None
         print(json.dumps(line))

@@ -170,7 +170,8 @@ typedef struct arp_row {
 
 typedef struct arp_result {
   int64_t n_rows;
-  const arp_row* rows;            /* host memory, UNSORTED (order is not deterministic) */
+  const arp_row* rows;            /* page-locked host memory owned by THIS result (valid until arp_result_free, whatever
+                                     else is called on the context meanwhile); UNSORTED (order is not deterministic) */
   int64_t n_structures;
   const int64_t* atom_begin;      /* n_structures+1: offsets of each structure's atoms in the job */
   const int64_t* ring_begin;      /* n_structures+1 */
@@ -202,7 +203,9 @@ void* arp_ctx_stream(arp_ctx* ctx);             /* the cudaStream_t every kernel
 int  arp_contacts(arp_ctx* ctx, const arp_structure* s, const arp_params* p, arp_result** out);
 /* Many independent structures in one job; no pair ever spans two structures. */
 int  arp_contacts_batch(arp_ctx* ctx, const arp_structure* const* s, int64_t n, const arp_params* p, arp_result** out);
-void arp_result_free(arp_ctx* ctx, arp_result* r);
+void arp_result_free(arp_ctx* ctx, arp_result* r); /* ctx: the (live) context the result came from -- its row buffer is kept
+                                                       for that context's next download -- or NULL (e.g. the context is
+                                                       already destroyed): the buffer is released */
 
 /* Staged form of the same job, for pipelines that keep inputs resident in HBM:
  * upload once, run any number of times (asynchronous on the stream), download the last run's rows. */

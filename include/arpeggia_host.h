@@ -71,9 +71,12 @@ const char* arph_last_error(void);
 
 /* Fixed-column PDB reader (ATOM / HETATM / MODEL). *out is malloc'd; release with arph_free. */
 int  arph_parse_pdb(const char* path, arp_atom_record** out, int64_t* n);
-/* mmCIF: the _atom_site loop (author chain / residue numbers where present).  pdbtbx's own column choice is not
- * under /root/reference: parity unpinned. */
+/* mmCIF: the _atom_site loop.  Chain ids and residue numbers come from the LABEL identifiers (label_asym_id,
+ * label_seq_id; auth_* only where the label value is absent or null) -- pdbtbx 0.12's column choice as far as it can be
+ * established without its source (not under /root/reference: parity unpinned).  arph_parse_cif_ids with
+ * use_auth_ids != 0 takes the author identifiers instead (what the PDB-format file of the same entry carries). */
 int  arph_parse_cif(const char* path, arp_atom_record** out, int64_t* n);
+int  arph_parse_cif_ids(const char* path, int use_auth_ids, arp_atom_record** out, int64_t* n);
 /* Dispatch on the extension like pdbtbx (src/utils.rs:51-57): .cif / .mmcif -> mmCIF, anything else -> PDB. */
 int  arph_parse_file(const char* path, arp_atom_record** out, int64_t* n);
 void arph_free(void* p);

@@ -8,7 +8,6 @@ if str(ROOT) not in sys.path:
     sys.path.insert(0, str(ROOT))
 
 DATA = ROOT / "tests" / "data"
-GOLDEN = ROOT / "tests" / "golden"
 
 
 def pytest_configure(config):

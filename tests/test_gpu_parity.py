@@ -102,6 +102,43 @@ def test_python_dropin_surface(ubq_path):
     assert (df2.height if hasattr(df2, "height") else df2.num_rows) == 532
 
 
+def test_python_dropin_frame_equals_the_oracle_table(bft_path, tmp_path):
+    """arpeggia.contacts(file): the Arrow columns (built from the table's id columns as dictionary indices, no Python
+    list) carry exactly the oracle's table -- values, nulls, dtypes of mod.rs:140-214 -- for a PDB and an mmCIF file."""
+    import pyarrow as pa
+
+    from arpeggia_b200 import synth
+
+    bft = A.parse_pdb(bft_path)
+    want = O.contacts(bft.view(O.ATOM_DTYPE), "/", 0.1, 6.5, num_threads=0)
+    cif = tmp_path / "s.cif"
+    synth.write_cif(bft, cif)
+    for path in (bft_path, str(cif)):
+        df = A.contacts(path)
+        at = df if isinstance(df, pa.Table) else df.to_arrow()
+        assert at.num_rows == want["n_rows"] and at.column_names == A.COLUMNS
+        for c in A.COLUMNS:
+            col = at[c].combine_chunks()
+            if c == "model":
+                assert col.type == pa.uint32()
+                assert np.array_equal(col.to_numpy(), want[c] if path == bft_path else np.ones_like(want[c]))  # the cif carries model 1
+            elif c.startswith("sc_"):
+                assert col.type == pa.float32() and col.null_count == int((~want["sc_valid"]).sum())
+                v = col.to_numpy(zero_copy_only=False)
+                assert np.array_equal(np.isnan(v), ~want["sc_valid"] | np.isnan(want[c]))
+                m = want["sc_valid"]
+                assert np.array_equal(v[m].view(np.uint32), want[c][m].view(np.uint32))
+            elif c == "distance":
+                assert col.type == pa.float32() and np.array_equal(col.to_numpy().view(np.uint32), want[c].view(np.uint32))
+            elif want[c].dtype == object:
+                assert col.type in (pa.large_string(), pa.string()) and col.to_pylist() == want[c].tolist(), c
+            else:
+                assert col.type == pa.int32() and np.array_equal(col.to_numpy(), want[c]), c
+    # dictionary-encoded form of the same frame
+    at2, _ = A.default_context(0).contacts_file_arrow(bft_path, flags=A.FLAG_NO_COUNTERS, strings="dictionary")
+    assert pa.types.is_dictionary(at2["from_chain"].type) and at2["from_chain"].to_pylist() == want["from_chain"].tolist()
+
+
 def test_config3_1m_atoms_bit_exact(ctx, bft):
     """BASELINE config 3 at full size: 6bft tiled 5x5x5 = 1 022 500 atoms, table identical to the oracle's."""
     from arpeggia_b200 import synth
@@ -431,3 +468,46 @@ def test_contexts_on_several_host_threads_same_rows(ubq, bft):
     for t in th:
         t.join()
     assert not errors, errors
+
+
+@pytest.mark.parametrize("k", [0, 1, 499, 4242, 9999])
+def test_config4_complexes_equal_the_oracle(ctx, bft, k):
+    """BASELINE config 4: complex k of the batch (chains A, B, C, G of 6bft, jittered: other ties and labels than 6bft)
+    against the ORACLE, full sorted 20-column table, both screen modes -- and its rows inside a batch job are the rows the
+    oracle-checked table was built from."""
+    from arpeggia_b200 import synth
+
+    atoms = synth.jittered_complex(bft, k)
+    want = O.contacts(atoms.view(O.ATOM_DTYPE), "/", 0.1, 6.5, flags=O.FLAG_SKIP_LOAD_FILTER, num_threads=0)
+    assert want["n_rows"] > 3000
+    for flags in (2, 2 | 4):  # counting mode / emit-radius screen
+        assert_tables_equal(ctx.contacts_table(atoms, "/", 0.1, 6.5, flags=flags), want, f"complex {k} flags {flags}")
+    # the same complex as one structure of a batch job: its rows, decoded and sorted by the host table, are the oracle's table
+    others = [A.Packed(synth.jittered_complex(bft, j), "/", flags=2) for j in (k + 1, k + 2)]
+    mine = A.Packed(atoms, "/", flags=2)
+    res = ctx.contacts_rows([others[0], mine, others[1]], 0.1, 6.5, 1)
+    assert_tables_equal(mine.build_table(A.split_rows(res)[1]), want, f"complex {k} inside a batch")
+
+
+def test_results_own_their_rows(ctx, bft, ubq):
+    """an arp_result keeps its rows while later calls run on the same context (each result owns its page-locked
+    buffer; freed buffers are pooled for the next download)."""
+    import ctypes as C
+
+    from arpeggia_b200 import _lib as AL
+
+    L = AL.lib()
+    prm = AL.Params(0.1, 6.5, 0, 0)
+    held = []
+    for atoms in (bft, ubq, bft):
+        p = A.Packed(atoms)
+        rp = C.POINTER(AL.Result)()
+        AL.check(L.arp_contacts(ctx._h, p.structure_ptr, C.byref(prm), C.byref(rp)), ctx._h)
+        held.append(rp)
+    views = [np.frombuffer((C.c_char * (r.contents.n_rows * 16)).from_address(r.contents.rows), dtype=A.ROW_DTYPE) for r in held]
+    assert [len(v) for v in views] == [7236, 532, 7236] and len({r.contents.rows for r in held}) == 3
+    key = ["from", "to", "label", "distance"]
+    assert np.array_equal(np.sort(views[0], order=key), np.sort(views[2], order=key))
+    assert views[1]["from"].max() < 660  # still the 1ubq rows, not overwritten by the third call
+    for r in held:
+        L.arp_result_free(ctx._h, r)

@@ -202,6 +202,19 @@ CIF_COLS = ["group_PDB", "id", "type_symbol", "label_atom_id", "label_alt_id", "
             "auth_seq_id", "auth_comp_id", "auth_asym_id", "auth_atom_id", "pdbx_PDB_model_num"]
 
 
+def label_seq_ids(atoms):
+    """label_seq_id the way the archive numbers it: 1, 2, 3 ... along each chain, whatever the author numbers are."""
+    out, seq, last = np.zeros(len(atoms), dtype=np.int64), 0, None
+    for k, a in enumerate(atoms):
+        key = (a["model"], a["chain"], a["resi"], a["icode"])
+        if last is None or key[:2] != last[:2]:
+            seq = 1
+        elif key != last:
+            seq += 1
+        out[k], last = seq, key
+    return out
+
+
 def write_cif(atoms, path, model=1):
     """A PDBx/mmCIF file the way the PDB writes them: label_* and auth_* identifiers differ (waters get their own label
     chain and no label_seq_id), a quoted value and a text field precede the _atom_site loop."""
@@ -212,12 +225,13 @@ def write_cif(atoms, path, model=1):
     out = ["data_TEST", "#", "_entry.id TEST", "_struct.title 'a title with loop_ and _atom_site.fake inside quotes'", "#",
            "loop_", "_citation.id", "_citation.title", "primary", ";A multi-line", "text field with loop_ at its start", ";", "#",
            "loop_"] + [f"_atom_site.{c}" for c in CIF_COLS]
+    seqs = label_seq_ids(atoms)
     for k, a in enumerate(atoms):
         hoh = a["resn"] == b"HOH"
         label_asym = "W" if hoh else {"A": "A"}.get(a["chain"].decode(), "L" + a["chain"].decode())
         out.append(" ".join([
             "HETATM" if a["hetero"] else "ATOM", str(int(a["serial"])), q(a["element"]).title() if a["element"] else "?", q(a["name"]),
-            q(a["altloc"]), q(a["resn"]), label_asym, "1", "." if hoh else str(k // 7 + 1), q(a["icode"]).replace(".", "?"),
+            q(a["altloc"]), q(a["resn"]), label_asym, "1", "." if hoh else str(int(seqs[k])), q(a["icode"]).replace(".", "?"),
             f"{a['x']:.3f}", f"{a['y']:.3f}", f"{a['z']:.3f}", f"{a['occupancy']:.2f}", "10.00", "?", str(int(a["resi"])), q(a["resn"]),
             q(a["chain"]), q(a["name"]), str(model)]))
     out.append("#")
@@ -236,12 +250,12 @@ def test_mmcif_reader_gives_the_pdb_readers_records(which, ubq, bft, tmp_path):
         atoms = F.all_cases(ubq.view(O.ATOM_DTYPE))[which].view(A.ATOM_DTYPE)
     p = tmp_path / "s.cif"
     write_cif(atoms, p)
-    got = A.parse_cif(p)
+    got = A.parse_cif(p, auth_ids=True)  # the author identifiers are what the PDB-format file carries
     assert len(got) == len(atoms)
     for f in ("x", "y", "z", "occupancy", "serial", "resi", "chain", "resn", "name", "element", "altloc", "icode", "hetero"):
         assert np.array_equal(got[f], atoms[f]), f
     assert (got["model"] == 1).all()
-    assert np.array_equal(A.load_atoms(p), got)  # dispatch on the extension
+    assert np.array_equal(A.load_atoms(p), A.parse_cif(p))  # dispatch on the extension; label identifiers by default
     q = tmp_path / "s.pdb1"
     q.write_bytes(open(os.path.join(os.path.dirname(__file__), "data", "1ubq.pdb"), "rb").read())
     assert len(A.load_atoms(q)) == 660  # anything else is read as PDB
@@ -249,6 +263,37 @@ def test_mmcif_reader_gives_the_pdb_readers_records(which, ubq, bft, tmp_path):
     a, b = A.Packed(atoms).arrays(), A.Packed(got).arrays()
     for k in ("x", "attr", "chain_key", "res_ordinal", "res_id", "ring_center", "ring_normal"):
         assert np.array_equal(a[k], b[k]), k
+
+
+def test_mmcif_label_identifiers_are_the_default(bft, tmp_path):
+    """pdbtbx builds chain ids and residue numbers from label_asym_id / label_seq_id (as far as its parser is
+    known; unpinned), so an entry whose author and label ids differ -- every 6bft chain but A here, all residue numbers,
+    the waters' own label chain -- gives other chain / resi columns, another `groups` selection and another chain-rank
+    order than its PDB-format file.  The author ids stay available behind an explicit flag."""
+    p = tmp_path / "s.cif"
+    write_cif(bft, p)
+    lab, auth = A.parse_cif(p), A.parse_cif(p, auth_ids=True)
+    assert np.array_equal(auth["chain"], bft["chain"]) and np.array_equal(auth["resi"], bft["resi"])
+    hoh = bft["resn"] == b"HOH"
+    want_chain = np.array([b"W" if h else (b"A" if c == b"A" else b"L" + c) for c, h in zip(bft["chain"], hoh)], dtype="S8")
+    assert np.array_equal(lab["chain"], want_chain)
+    assert np.array_equal(lab["resi"], np.where(hoh, bft["resi"], label_seq_ids(bft)))  # label_seq_id "." -> auth_seq_id
+    assert (lab["resi"] != bft["resi"]).any()
+    for f in ("x", "y", "z", "serial", "resn", "name", "element", "altloc", "icode"):
+        assert np.array_equal(lab[f], auth[f]), f
+    # group selection works on the label chain ids: "LB" exists, "B" does not
+    import ctypes as C
+    lig, rec = C.create_string_buffer(256), C.create_string_buffer(256)
+    chains = ",".join(sorted({c.decode() for c in lab["chain"]}))
+    assert _lib.lib().arph_parse_groups(chains.encode(), b"LB,LC/A", lig, rec, 256) == 0
+    assert lig.value == b"LB,LC" and rec.value == b"A"
+    sel = A.Packed(lab, "LB,LC/A").arrays()
+    lig_bit, rec_bit = 0x10, 0x20
+    assert int(((sel["attr"] & lig_bit) != 0).sum()) == int(np.isin(lab["chain"], [b"LB", b"LC"]).sum())
+    assert int(((sel["attr"] & rec_bit) != 0).sum()) == int((lab["chain"] == b"A").sum())
+    # "B" names no chain under the label ids: nothing is selected as ligand, whereas the author ids select chain B
+    assert int(((A.Packed(lab, "B/A").arrays()["attr"] & lig_bit) != 0).sum()) == 0
+    assert int(((A.Packed(auth, "B/A").arrays()["attr"] & lig_bit) != 0).sum()) == int((bft["chain"] == b"B").sum())
 
 
 def test_mmcif_tokenizer_edge_cases(tmp_path):
