@@ -106,6 +106,7 @@ struct arp_ctx {
   HBuf<unsigned int> h_up_err;
   bool have_gid = false;           // every structure of the job came with ids: rows carry them
   bool have_tag = false;           // every structure of the job came with tags (else they are derived on the device)
+  bool tags_ok = false;            // res_tag is resident and valid: the emit-radius screen can run
   bool have_res_csr = false;       // res_atom_begin is resident (every structure came with it)
   bool rows_global = false;        // the rows of the last run have been rewritten to global ids (arp_stage_download)
 
@@ -137,15 +138,17 @@ struct arp_ctx {
   DBuf<uint32_t> cell_of, rank_of, cell_start;
   DBuf<unsigned long long> scan_status, rscan_status;
   DBuf<uint32_t> rcell_of, rrank_of, rcell_start, rperm, cations;
-  DBuf<float> pos2;          // sorted positions interleaved per slot pair (k_screen_atoms)
-  DBuf<uint2> skey;          // (chain key, residue ordinal) per sorted slot (k_screen_atoms)
-  DBuf<RecA> recA;
+  DBuf<float> pos2;          // sorted positions + residue tags interleaved per slot pair (k_screen_atoms)
+  DBuf<SlotCell> slot_cell;  // cell and boundary bits per sorted slot (k_screen_atoms)
+  DBuf<RecA> recA;           // counting mode
   DBuf<RecB> recB;
+  DBuf<RecK> recK;
   DBuf<Item> items;
   DBuf<Counters> ctr;
   DBuf<arp_row> rows;
   uint64_t row_cap = 0;
-  DBuf<uint2> pairq, pairq2;  // pairs between k_screen -> k_filter -> k_exact
+  DBuf<uint2> pairq;          // pairs between k_screen -> k_filter
+  DBuf<uint4> pairq2;         // pairs for k_exact (with the input indices of both atoms)
   uint64_t pairq_cap = 0, pairq2_cap = 0;
   int64_t n_cells = 0, n_rcells = 0;
 
@@ -404,8 +407,17 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
   bool derive_tags = false;
   if (c->have_tag) {
     upload_concat(c, c->res_tag, s, n, [](const arp_structure* t) { return t->res_tag; }, nrs, 0, nullptr, false);
-  } else if (c->per_residue_keys && c->n_res > 0) {
+  } else if (c->n_res > 0) {
     derive_tags = true;
+    if (!c->per_residue_keys) {  // per-atom keys only: the residues' keys first (every atom of a residue carries the same pair)
+      c->res_chain_key.need((size_t)c->n_res);
+      c->res_res_ordinal.need((size_t)c->n_res);
+      if (c->n_atoms > 0) {
+        k_res_keys_from_atoms<<<(unsigned)((c->n_atoms + 255) / 256), 256, 0, c->stream>>>(c->chain_key.p, c->res_ordinal.p, c->res_id.p, (uint32_t)c->n_atoms,
+                                                                                         c->res_chain_key.p, c->res_res_ordinal.p);
+        CK(cudaGetLastError());
+      }
+    }
     c->res_tag.need((size_t)c->n_res + 1);
     c->struct_res_begin.need((size_t)n + 1);
     c->up_err.need(1);
@@ -455,9 +467,12 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
   CK(cudaEventRecord(c->ev[1], c->stream));
   CK(cudaStreamSynchronize(c->stream));
   CK(cudaEventElapsedTime(&c->ms_h2d, c->ev[0], c->ev[1]));
+  c->tags_ok = c->n_res > 0;
   if (derive_tags && *c->h_up_err.p) {
     if (*c->h_up_err.p & 4u) throw arp::Error{ARP_ERR_CUDA, "residue-tag scan: look-back wait exceeded its bound"};
-    throw arp::Error{ARP_ERR_ARG, "residues are not in atoms_with_hierarchy() order (a chain's residue ordinals must increase): supply arp_structure.res_tag"};
+    // residues are not in atoms_with_hierarchy() order (a chain's ordinals do not increase) and the caller gave no
+    // res_tag: the emit-radius screen, which needs the tags, is not used for this job (rows are the same either way)
+    c->tags_ok = false;
   }
   c->have_job = true;
 }

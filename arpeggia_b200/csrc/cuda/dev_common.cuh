@@ -21,7 +21,9 @@ struct StructDesc {
 // Sorted (by cell) atom records, 32 bytes = one sector each.
 // RecA: everything the f32 stages need about an atom.  The screen reads the first 16 bytes (origin-relative f32 position +
 //       attribute word: one 16-byte cp.async per candidate), the pair filter reads the whole sector in one gather.
-// RecB: what the exact stage reads: f64 position (+ chain key and residue ordinal for the ring kernels).
+// RecB: everything the exact stage reads about an atom, ONE sector: f64 position, attribute word, residue id.
+// RecK: what the pair filter of the emit-radius mode and the ring kernel read: attribute word, chain key, residue ordinal,
+//       input index.  (The f32 positions of that mode live in the pair-interleaved array pos2, see k_screen_atoms.)
 struct __align__(32) RecA {
   float x, y, z;
   uint32_t attr;         // ARP_ATTR_* | bit 31: may start a row (k_scatter_atoms)
@@ -32,8 +34,20 @@ struct __align__(32) RecA {
 };
 struct __align__(32) RecB {
   double x, y, z;
+  uint32_t attr;         // as RecA.attr
+  uint32_t res_id;       // job-global residue id (H lists, CB / SG slots)
+};
+struct __align__(16) RecK {
+  uint32_t attr;         // as RecA.attr
   uint32_t chain_key;
   uint32_t res_ordinal;
+  uint32_t perm;         // job-global atom index in input order (output rows)
+};
+// emit-radius mode: the cell of a sorted slot and which of its neighbours exist
+//   bits: 1 = ix > 0, 2 = ix + 1 < nx, 4 = iy > 0, 8 = iy + 1 < ny, 16 = iz + 1 < nz
+struct __align__(8) SlotCell {
+  uint32_t cell;         // job-wide cell id
+  uint32_t bits;
 };
 
 // Work item of the pair kernel: one non-empty cell and its half shell (the cell plus its 13 forward neighbours),
@@ -97,8 +111,11 @@ struct Counters {
 };
 
 struct PairArgs {
-  const RecA* recA;
+  const RecA* recA;            // counting mode
   const RecB* recB;
+  const RecK* recK;
+  const SlotCell* slot_cell;   // emit-radius mode
+  const uint32_t* atom_struct; // input-order atom -> structure; nullptr when the job has one structure
   const uint32_t* cell_start;  // n_cells + 1
   const Item* items;           // non-empty cells
   const StructDesc* descs;
@@ -114,7 +131,7 @@ struct PairArgs {
   const double* hz;
   uint2* pairq;                // k_screen -> k_filter: (from slot, candidate slot)
   unsigned long long pairq_cap;
-  uint2* pairq2;               // k_filter -> k_exact: the same with flags in the top bits
+  uint4* pairq2;               // k_filter / k_screen_atoms -> k_exact: (slot a | flags, slot b | flags, input index a, input index b)
   unsigned long long pairq2_cap;
   arp_row* rows;
   unsigned long long row_cap;
@@ -135,7 +152,7 @@ struct RingArgs {
   // cation list: sorted slots of the atoms with ARP_ATTR_POS_RES (k_scatter_atoms)
   const uint32_t* cations;
   const uint32_t* atom_struct;  // input-order atom -> structure; nullptr when the job has one structure
-  const RecA* recA;
+  const RecK* recK;
   const RecB* recB;
   const StructDesc* descs;
   arp_row* rows;

@@ -301,7 +301,8 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
                 const uint32_t* __restrict__ res_id, const uint32_t* __restrict__ res_chain_key, const uint32_t* __restrict__ res_res_ordinal,
                 const uint32_t* __restrict__ atom_struct, const StructDesc* __restrict__ descs, const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of, const uint32_t* __restrict__ cell_start,
                 uint32_t n, double edge, double inv_edge, RecA* __restrict__ recA, RecB* __restrict__ recB, Item* __restrict__ items,
-                uint32_t* __restrict__ cations, Counters* __restrict__ ctr, float* __restrict__ pos2, uint2* __restrict__ skey) {
+                uint32_t* __restrict__ cations, Counters* __restrict__ ctr, RecK* __restrict__ recK, float* __restrict__ pos2,
+                SlotCell* __restrict__ slot_cell, const uint32_t* __restrict__ res_tag) {
   // slots in `items` / `cations` are reserved per BLOCK (shared-memory counters, one global atomicAdd each): the 110 000
   // same-address atomics of a one-per-cell reservation were 40 % of this kernel's stall samples
   __shared__ uint32_t s_items, s_cat, s_items_base, s_cat_base;
@@ -334,19 +335,24 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
   ra.chain_key = res_chain_key ? res_chain_key[ra.res_id] : chain_key[a];
   ra.res_ordinal = res_chain_key ? res_res_ordinal[ra.res_id] : res_ordinal[a];
   ra.perm = a;
-  recA[slot] = ra;
   RecB rb;
   rb.x = px;
   rb.y = py;
   rb.z = pz;
-  rb.chain_key = ra.chain_key;
-  rb.res_ordinal = ra.res_ordinal;
+  rb.attr = ra.attr;
+  rb.res_id = ra.res_id;
   recB[slot] = rb;
-  if (pos2) {  // what k_screen_atoms reads: positions interleaved per slot PAIR (x0 x1 | y0 y1 | z0 z1 | c0 c1: 32 bytes), keys per slot
+  recK[slot] = RecK{ra.attr, ra.chain_key, ra.res_ordinal, a};
+  if (pos2) {
+    // emit-radius mode, what k_screen_atoms reads: positions and residue tags interleaved per slot PAIR
+    // (x0 x1 | y0 y1 | z0 z1 | t0 t1: 32 bytes), and the slot's cell with its boundary bits
     float* q = pos2 + 8u * (size_t)(slot >> 1) + (slot & 1u);
     q[0] = ra.x, q[2] = ra.y, q[4] = ra.z;
-    q[6] = __uint_as_float(slot - r);  // the cell's first slot = where its work item sits (below)
-    skey[slot] = make_uint2(ra.chain_key, ra.res_ordinal);
+    q[6] = __uint_as_float(res_tag[ra.res_id]);
+    const int ix = cell_coord(px, d.ox, inv_edge, d.nx), iy = cell_coord(py, d.oy, inv_edge, d.ny), iz = cell_coord(pz, d.oz, inv_edge, d.nz);
+    slot_cell[slot] = SlotCell{c, (ix > 0 ? 1u : 0u) | (ix + 1 < d.nx ? 2u : 0u) | (iy > 0 ? 4u : 0u) | (iy + 1 < d.ny ? 8u : 0u) | (iz + 1 < d.nz ? 16u : 0u)};
+  } else {
+    recA[slot] = ra;
   }
   }
   // the few atoms that can make a cation-pi contact (aromatic.rs:18) are listed for the ring kernel; the first arrival
@@ -363,7 +369,7 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
     my_cat = __shfl_sync(0xffffffffu, wc, 0) + __popc(bc & lt);
     my_item = __shfl_sync(0xffffffffu, wi, 0) + __popc(bi & lt);
   }
-  if (first) s_fc[my_item] = c, s_fs[my_item] = s, s_fp[0][my_item] = px, s_fp[1][my_item] = py, s_fp[2][my_item] = pz;
+  if (first && !pos2) s_fc[my_item] = c, s_fs[my_item] = s, s_fp[0][my_item] = px, s_fp[1][my_item] = py, s_fp[2][my_item] = pz;
   __syncthreads();
   if (threadIdx.x == 0) {
     s_cat_base = s_cat ? atomicAdd(&ctr->n_cations, s_cat) : 0u;
@@ -373,7 +379,8 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
   if (is_cat) cations[s_cat_base + my_cat] = slot;
   // the cells' half shells as 5 runs of sorted slots, one THREAD per first arrival of the block (one atom in four starts a
   // cell at the emit-radius edge: built in place, three quarters of every warp idled through these 150 instructions)
-  for (uint32_t i = threadIdx.x; i < s_items; i += blockDim.x) {
+  const uint32_t n_build = pos2 ? 0u : s_items;  // the emit-radius screen finds its runs through slot_cell + cell_start: no work items
+  for (uint32_t i = threadIdx.x; i < n_build; i += blockDim.x) {
     const uint32_t fc = s_fc[i], fs = s_fs[i];
     const StructDesc& d = descs[fs];
     const int nx = d.nx, ny = d.ny, nz = d.nz;
@@ -405,9 +412,8 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
     it.cy = (float)(((double)iy + 0.5) * edge);
     it.cz = (float)(((double)iz + 0.5) * edge);
     it.pad = 0;
-    // counting mode: a compact list (k_screen hands the items out to warps); emit-radius mode: the item sits at the cell's
-    // first slot, which every atom of the cell knows (slot - rank) and leaves in its position record for k_screen_atoms
-    items[pos2 ? it.cb : s_items_base + i] = it;
+    // a compact list: k_screen hands the items out to warps
+    items[s_items_base + i] = it;
   }
 }
 

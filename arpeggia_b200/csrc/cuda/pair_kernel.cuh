@@ -123,30 +123,23 @@ __device__ __forceinline__ void flush_rows(const PairArgs& G, PendingRows& R) {
   }
   R.m = 0u;
 }
-// the records of one queue entry: everything the exact stage reads, gathered in ONE round (both 32-byte RecB sectors,
-// attr and the second half of both RecA sectors: residue id for the disulfide / hydrogen tests, perm for the row)
+// the records of one queue entry: ONE 32-byte sector per atom (f64 position, attribute word, residue id); the input
+// indices the rows carry ride in the queue entry itself
 struct ExactOperands {
   RecB a, b;
-  uint32_t wa, wb;
-  uint4 ta, tb;  // chain_key, res_ordinal, res_id, perm
 };
-__device__ __forceinline__ void exact_gather(const PairArgs& G, const uint2 e, bool have, ExactOperands& X) {
+__device__ __forceinline__ void exact_gather(const PairArgs& G, const uint4 e, bool have, ExactOperands& X) {
   if (!have) return;
-  const uint32_t sa = e.x & SLOT_MASK, sb = e.y & SLOT_MASK;
-  X.a = G.recB[sa];
-  X.b = G.recB[sb];
-  X.wa = G.recA[sa].attr;
-  X.wb = G.recA[sb].attr;
-  X.ta = *(reinterpret_cast<const uint4*>(G.recA + sa) + 1);
-  X.tb = *(reinterpret_cast<const uint4*>(G.recA + sb) + 1);
+  X.a = G.recB[e.x & SLOT_MASK];
+  X.b = G.recB[e.y & SLOT_MASK];
 }
-__device__ __forceinline__ void exact_batch(const PairArgs& G, const DevParams& P, const uint2 e, bool have, const ExactOperands& X, int lane,
+__device__ __forceinline__ void exact_batch(const PairArgs& G, const DevParams& P, const uint4 e, bool have, const ExactOperands& X, int lane,
                                             PairCounts& K, PendingRows& R) {
   uint32_t m = 0, ip = 0, iq = 0;
   double dist = 0.0;
   if (have) {
     const RecB &a = X.a, &b = X.b;
-    const uint32_t wa = X.wa, wb = X.wb;
+    const uint32_t wa = a.attr, wb = b.attr;
     // rstar distance_2 / pdbtbx Atom::distance: ((dx*dx + dy*dy) + dz*dz), every operation rounded once
     const double dx = dsub(b.x, a.x), dy = dsub(b.y, a.y), dz = dsub(b.z, a.z);
     const double d2 = dadd(dadd(dmul(dx, dx), dmul(dy, dy)), dmul(dz, dz));
@@ -158,15 +151,15 @@ __device__ __forceinline__ void exact_batch(const PairArgs& G, const DevParams& 
       if ((e.x & QF_B) && (e.y & QF_B) && d2 <= P.emit_d2_max) {
         dist = __dsqrt_rn(d2);
         const bool swap = (e.y & QF_A) != 0u;
-        ip = swap ? X.tb.w : X.ta.w;
-        iq = swap ? X.ta.w : X.tb.w;
+        ip = swap ? e.w : e.z;
+        iq = swap ? e.z : e.w;
         // one instance of the ladder (instruction-cache footprint): operands selected, not two inlined calls
         RecB p, r;
         p.x = swap ? b.x : a.x, p.y = swap ? b.y : a.y, p.z = swap ? b.z : a.z;
         r.x = swap ? a.x : b.x, r.y = swap ? a.y : b.y, r.z = swap ? a.z : b.z;
-        p.chain_key = r.chain_key = 0u;      // classify_pair reads positions only
-        p.res_ordinal = r.res_ordinal = 0u;
-        m = classify_pair(G, P, p, swap ? wb : wa, swap ? X.tb.z : X.ta.z, r, swap ? wa : wb, swap ? X.ta.z : X.tb.z, dist);
+        p.attr = r.attr = 0u;  // classify_pair reads positions only
+        p.res_id = r.res_id = 0u;
+        m = classify_pair(G, P, p, swap ? wb : wa, swap ? b.res_id : a.res_id, r, swap ? wa : wb, swap ? a.res_id : b.res_id, dist);
       }
     }
   }
@@ -204,11 +197,11 @@ __device__ __forceinline__ float label_limit2(const DevParams& P, const float* l
 //                             on to the second queue, 32 at a time.
 struct FilterOut {
   bool go;
-  uint2 out;
+  uint4 out;
 };
 __device__ __forceinline__ FilterOut filter_phase2(const PairArgs& G, const DevParams& P, const float* lim2, uint2 e, bool have,
                                                    uint32_t& n_cls32) {
-  FilterOut r{false, make_uint2(0u, 0u)};
+  FilterOut r{false, make_uint4(0u, 0u, 0u, 0u)};
   if (have) {
     const uint4* pa = reinterpret_cast<const uint4*>(G.recA + e.x);
     const uint4* pb = reinterpret_cast<const uint4*>(G.recA + e.y);
@@ -225,6 +218,8 @@ __device__ __forceinline__ FilterOut filter_phase2(const PairArgs& G, const DevP
     r.go = amb || (pot && valid);
     r.out.x = e.x | (amb ? QF_A : 0u) | (valid ? QF_B : 0u);
     r.out.y = e.y | (dir == 2 ? QF_A : 0u) | (pot ? QF_B : 0u);
+    r.out.z = a1.w;  // input indices of the two atoms: the exact stage writes them into the rows
+    r.out.w = b1.w;
   }
   return r;
 }
@@ -247,12 +242,12 @@ __device__ __forceinline__ void filter_gather(const PairArgs& G, const uint2 e, 
 __global__ void __launch_bounds__(CLS_THREADS, 4) k_filter(const PairArgs G, const DevParams P) {
   __shared__ float lim2[256];  // per element-class pair: (max(cov sum, vdW sum) + |comp|)^2 + g, rounded up
   __shared__ uint2 stash1[CLS_WARPS][64];  // phase-1 survivors waiting for a full warp (carry-over < 32 + one trip)
-  __shared__ uint2 stash2[CLS_WARPS][64];  // phase-2 survivors waiting for a full 32-entry flush
+  __shared__ uint4 stash2[CLS_WARPS][64];  // phase-2 survivors waiting for a full 32-entry flush
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   for (int k = threadIdx.x; k < 256; k += CLS_THREADS) lim2[k] = class_pair_limit2(P, k >> 4, k & 15);
   __syncthreads();
   uint2* s1 = stash1[wid];
-  uint2* s2 = stash2[wid];
+  uint4* s2 = stash2[wid];
   int n1 = 0, n2 = 0;
   uint32_t n_in32 = 0, n_cls32 = 0;
   const unsigned long long n_pairs = min(G.ctr->q_len, G.pairq_cap);
@@ -347,11 +342,33 @@ __global__ void __launch_bounds__(CLS_THREADS, EXACT_MIN_BLOCKS) k_exact(const P
   const unsigned long long n_pairs = min(G.ctr->q2_len, G.pairq2_cap);
   const unsigned long long stride = (unsigned long long)gridDim.x * CLS_WARPS * 32ull;
   unsigned long long base = ((unsigned long long)blockIdx.x * CLS_WARPS + wid) * 32ull;
-  uint2 e_next = make_uint2(0u, 0u);  // read one trip ahead
-  if (base + lane < n_pairs) e_next = __ldcs(G.pairq2 + base + lane);
+#ifndef EXACT_PREFETCH
+#define EXACT_PREFETCH 0  // r2b: 0.035 -> 0.038 ms with it (80 registers spill; 120 registers at 2 CTAs / SM: 0.039): off.  1: the records of trip t + 1 are gathered before trip t computes (entries read two trips ahead)
+#endif
   PendingRows R{0ull, 0u, 0u, 0u, 0u, 0.f};
+#if EXACT_PREFETCH
+  const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+  uint4 e = zero, e_next = zero;
+  if (base + lane < n_pairs) e = __ldcs(G.pairq2 + base + lane);
+  if (base + stride + lane < n_pairs) e_next = __ldcs(G.pairq2 + base + stride + lane);
+  ExactOperands X;
+  exact_gather(G, e, base + lane < n_pairs, X);
   for (; base < n_pairs; base += stride) {
-    const uint2 e = e_next;
+    const bool have = base + lane < n_pairs, have_n = base + stride + lane < n_pairs;
+    const uint4 e_cur = e;
+    const ExactOperands X_cur = X;
+    e = e_next;
+    e_next = zero;
+    if (base + 2ull * stride + lane < n_pairs) e_next = __ldcs(G.pairq2 + base + 2ull * stride + lane);
+    exact_gather(G, e, have_n, X);                              // the next trip's records fly ...
+    if (__any_sync(0xffffffffu, R.m != 0u)) flush_rows(G, R);  // ... under the previous trip's rows
+    exact_batch(G, P, e_cur, have, X_cur, lane, K, R);          // ... and this trip's ladder
+  }
+#else
+  uint4 e_next = make_uint4(0u, 0u, 0u, 0u);  // read one trip ahead
+  if (base + lane < n_pairs) e_next = __ldcs(G.pairq2 + base + lane);
+  for (; base < n_pairs; base += stride) {
+    const uint4 e = e_next;
     const bool have = base + lane < n_pairs;
     if (base + stride + lane < n_pairs) e_next = __ldcs(G.pairq2 + base + stride + lane);
     ExactOperands X;
@@ -359,6 +376,7 @@ __global__ void __launch_bounds__(CLS_THREADS, EXACT_MIN_BLOCKS) k_exact(const P
     if (__any_sync(0xffffffffu, R.m != 0u)) flush_rows(G, R);  // the previous trip's rows, while the gathers fly
     exact_batch(G, P, e, have, X, lane, K, R);
   }
+#endif
   if (__any_sync(0xffffffffu, R.m != 0u)) flush_rows(G, R);
   unsigned long long n_in = K.n_in, n_cls = K.n_cls;
 #pragma unroll
@@ -780,37 +798,40 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_screen(const 
 // ---- k_screen_atoms: the screen at the emit radius (ARP_FLAG_EMIT_RADIUS_SCREEN), one LANE per from-atom -------------------
 // With cells at r_emit = 4.5 A instead of dist_cutoff a half shell holds ~40 candidates and a cell ~4 atoms: the
 // warp-per-cell screen above then spends nine tenths of its instructions on per-cell bookkeeping (measured: 0.195 ms for
-// 47 M tests against 0.155 ms for 119 M at dist_cutoff).  Here nothing is staged: a warp takes 32 consecutive sorted slots
-// (atoms of 6-9 neighbouring cells), each lane walks the five runs of ITS cell's half shell -- run 0 from its own slot + 1,
-// so every unordered pair is tested once.  Candidates are read two at a time from the pair-interleaved position array
-// (x0 x1 | y0 y1 | z0 z1 | pad, 32 bytes per slot pair, written by k_scatter_atoms): a 16- and an 8-byte load through L1 (lanes of a cell read the
-// same addresses: broadcasts) feed packed f32x2 arithmetic -- 3 add, 1 mul, 2 fma for TWO tests, the same operations in the
-// same order as k_filter's difference form, so the same value -- and one compare each against the from-atom's own largest
-// label limit (no in-cutoff counting in this mode).  A hit appends the candidate's slot to a per-lane list in shared
-// memory (a predicated store and add: no vote, no atomic in the loop).  Every SA_ROUND trips the warp checks the lists;
-// a flush drops the pairs no orientation of should_compare_entities can pass (same chain, ordinals <= 1 apart,
-// complex.rs:112-113: two hits in three), and writes the rest to the pair queue through a per-warp window (warp prefix
-// sum, one atomicAdd per SA_WINDOW entries).
+// 47 M tests against 0.155 ms for 119 M at dist_cutoff).  Here a warp takes 32 consecutive sorted slots (atoms of 6-9
+// neighbouring cells), each lane walks the five runs of ITS cell's half shell -- run 0 from its own slot + 1, so every
+// unordered pair is tested once.  A lane finds its runs through its slot's cell id and boundary bits (SlotCell) and the
+// cell table itself; no per-cell work item is built or read in this mode.
+// Candidates are read two at a time from the pair-interleaved array pos2 (x0 x1 | y0 y1 | z0 z1 | t0 t1, 32 bytes per slot
+// pair, written by k_scatter_atoms; t = residue tag): two 16-byte loads through L1 (lanes of a cell read the same
+// addresses: broadcasts) feed packed f32x2 arithmetic -- 3 add, 1 mul, 2 fma for TWO tests, the same operations in the same
+// order as k_filter's difference form, so the same value -- one compare each against the from-atom's own largest label
+// limit, and the in-chain neighbour rule of complex.rs:112-113 decided right there from the tags (|tag difference| <= 1
+// <=> same chain, residue ordinals at most 1 apart: no orientation of should_compare_entities can pass; two hits in
+// three end here, with no gather).  A hit appends (candidate slot, d2) to a per-lane list in shared memory (a predicated
+// store and add: no vote, no atomic in the loop).  Every SA_ROUND trips the warp looks at the lists; a flush runs stage
+// B1 on them -- per-pair label limit, both orientations of the pair filter (one 16-byte gather per hit) -- and sends the
+// survivors, with the input indices the rows will carry, to the queue of k_exact 32 at a time (one atomicAdd per 32).
 constexpr int SA_THREADS = 256;
 constexpr int SA_WARPS = SA_THREADS / 32;
 constexpr uint32_t SA_WINDOW = 512;
 #ifndef SA_BUF_N
-#define SA_BUF_N 16
+#define SA_BUF_N 12
 #endif
 #ifndef SA_ROUND_N
 #define SA_ROUND_N 4
 #endif
 constexpr int SA_BUF = SA_BUF_N;      // entries of a lane's hit list
 constexpr int SA_ROUND = SA_ROUND_N;  // trips between two looks at the lists (a trip appends at most 2)
-// tiles handed out through the work cursor instead of a static stride: measured (r1t) k_screen_atoms 0.128 -> 0.126 ms, but
-// k_exact behind it 0.045 -> 0.050 ms (its queue comes out less local) -- off
-#ifndef SA_DYNAMIC_TILES
-#define SA_DYNAMIC_TILES 0
-#endif
-// CTAs per SM: 3 (70 registers) gains 2 us on config 3 (k_exact behind it reads a less interleaved queue) but loses 3-5 % at
-// 10 M / 100 M atoms (k_exact 5.4 -> 6.3 ms on config 5); 5 (48 registers) is slower everywhere (r1t measurements)
+static_assert(SA_BUF > 2 * SA_ROUND, "a round must fit the list");
 #ifndef SA_MIN_BLOCKS
 #define SA_MIN_BLOCKS 4
+#endif
+#ifndef SA_TAG_IN_TRIP
+#define SA_TAG_IN_TRIP 1  // 1: the in-chain rule is decided in the trip (tags ride in the position records: 32 bytes per trip);
+#endif                    // 0: in the flush, with one 4-byte gather per hit (24 bytes per trip, three times as many hits)
+#ifndef SA_FLUSH_DEPTH
+#define SA_FLUSH_DEPTH 2  // hit-list rows (= gathers per lane) in flight in a flush
 #endif
 
 __device__ __forceinline__ unsigned long long sa_add2(unsigned long long a, unsigned long long b) {
@@ -834,213 +855,261 @@ __device__ __forceinline__ unsigned long long sa_dup(float a) {
   return r;
 }
 
-constexpr int SA_RUNS = 6;      // rows of a thread's run table: up to 5 non-empty runs + the closing row
-constexpr int SA_STASH1 = 160;  // a warp's residue-filter survivors: carry-over < 32 + four rows of up to 32
+constexpr int SA_RUNS = 6;  // rows of a thread's run table: up to 5 non-empty runs + the closing row
 struct SaSmem {
   float lim1[16];
   float lim2[256];                                                   // per element-class pair: see k_filter
   uint32_t run_b[SA_RUNS][SA_THREADS], run_e[SA_RUNS][SA_THREADS];  // every thread's non-empty runs, then the closing row
-  uint32_t hits[SA_BUF][SA_THREADS];                                // per-lane hit lists (candidate slots)
-  uint2 stash1[SA_WARPS][SA_STASH1];                                // (from slot, candidate slot) waiting for a full warp
-  unsigned int* cursor[32];  // &ctr->work, one copy per lane (see draw_cursor)
-  uint2 stash2[SA_WARPS][64];                                       // pairs for k_exact waiting for a full 32-entry flush
+  uint2 hits[SA_BUF][SA_THREADS];                                   // per-lane hit lists: (candidate slot, d2 bits)
+  uint4 stash2[SA_WARPS][64];                                       // pairs for k_exact waiting for a full 32-entry flush
 };
 // a warp's carry-over between flushes, tiles and the final drain
 struct SaCarry {
-  int n1, n2;
-  unsigned long long n_q;  // pairs that passed the residue filter (statistics: arp_stats.n_screened_pairs)
+  int n2;
+  unsigned long long n_q;  // hits that passed the in-chain rule (statistics: arp_stats.n_screened_pairs)
 };
 
-// Stage B1 on a warp's stash, exactly k_filter's phase 2 (per-pair label limit, both orientations of the pair filter),
-// 32 pairs at a time; survivors go to the queue of k_exact, one atomicAdd per 32.  drain: also the incomplete last batches.
-__device__ __forceinline__ void sa_filter(const PairArgs& G, const DevParams& P, SaSmem& S, int wid, int lane, SaCarry& K, bool drain) {
-  uint2* s1 = S.stash1[wid];
-  uint2* s2 = S.stash2[wid];
-  const uint32_t lt = (1u << lane) - 1u;
-  uint32_t unused = 0;
-  while (K.n1 >= 32 || (drain && K.n1 > 0)) {
-    const int m = min(K.n1, 32);
-    K.n1 -= m;
-    const FilterOut r = filter_phase2(G, P, S.lim2, s1[K.n1 + (lane < m ? lane : 0)], lane < m, unused);
-    const uint32_t b2 = __ballot_sync(0xffffffffu, r.go);
-    if (r.go) s2[K.n2 + __popc(b2 & lt)] = r.out;
-    K.n2 += __popc(b2);
-    __syncwarp();
-    if (K.n2 >= 32 || (drain && K.n1 == 0 && K.n2 > 0)) {
-      const int k = min(K.n2, 32);
-      unsigned long long w = 0;
-      if (lane == 0) w = atomicAdd(&G.ctr->q2_len, (unsigned long long)k);
-      w = __shfl_sync(0xffffffffu, w, 0) + lane;
-      K.n2 -= k;
-      if (lane < k && w < G.pairq2_cap) __stcs(G.pairq2 + w, s2[K.n2 + lane]);
-      __syncwarp();
-    }
-  }
-  if (drain && K.n2 > 0) {  // nothing was left in the first stash: the loop above did not run
+// the warp's second stash -> the queue of k_exact, 32 entries per atomicAdd (drain: whatever is left)
+__device__ __forceinline__ void sa_emit(const PairArgs& G, SaSmem& S, int wid, int lane, SaCarry& K, bool drain) {
+  uint4* s2 = S.stash2[wid];
+  while (K.n2 >= 32 || (drain && K.n2 > 0)) {
+    const int k = min(K.n2, 32);
     unsigned long long w = 0;
-    if (lane == 0) w = atomicAdd(&G.ctr->q2_len, (unsigned long long)K.n2);
+    if (lane == 0) w = atomicAdd(&G.ctr->q2_len, (unsigned long long)k);
     w = __shfl_sync(0xffffffffu, w, 0) + lane;
-    if (lane < K.n2 && w < G.pairq2_cap) __stcs(G.pairq2 + w, s2[lane]);
-    K.n2 = 0;
+    K.n2 -= k;
+    if (lane < k && w < G.pairq2_cap) __stcs(G.pairq2 + w, s2[K.n2 + lane]);
+    __syncwarp();
   }
 }
 
-// the hit lists of a warp -> in-chain neighbour filter -> the warp's stash -> sa_filter.  key = (chain key, residue
-// ordinal) per sorted slot.  Entry j of every lane at a time: the survivors of a row are ranked by a ballot.
-__device__ __forceinline__ void sa_flush(const PairArgs& G, const DevParams& P, const uint2* __restrict__ key, SaSmem& S, int tid, int lane,
-                                         uint32_t slot, uint2 mine, uint32_t cnt, SaCarry& K) {
+// Stage B1 on the hit lists of a warp, entry j of every lane at a time (SA_FLUSH_DEPTH gathers in flight): per-pair label
+// limit (no label of complex.rs:217-296 fires beyond it), both orientations of should_compare_entities
+// (complex.rs:76-131); the survivors of a row are ranked by a ballot into the warp's stash.  `mine` = the lane's own RecK.
+__device__ __forceinline__ void sa_flush(const PairArgs& G, const DevParams& P, SaSmem& S, const unsigned long long* __restrict__ pos2, int tid,
+                                         int lane, uint32_t slot, const RecK mine, uint32_t tf1, uint32_t cnt, SaCarry& K) {
   const uint32_t maxc = __reduce_max_sync(0xffffffffu, cnt);
   const uint32_t lt = (1u << lane) - 1u;
-  uint2* s1 = S.stash1[tid >> 5];
-  for (uint32_t j0 = 0; j0 < maxc; j0 += 4u) {  // four gathers in flight
-    uint32_t c[4];
-    uint2 b[4];
+  const int wid = tid >> 5;
+  uint4* s2 = S.stash2[wid];
+#if SA_TAG_IN_TRIP
+  K.n_q += cnt;
+#endif
+  for (uint32_t j0 = 0; j0 < maxc; j0 += SA_FLUSH_DEPTH) {
+    uint2 h[SA_FLUSH_DEPTH];
+    uint4 kb[SA_FLUSH_DEPTH];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      c[u] = 0u, b[u] = mine;  // "same residue": dropped
+    for (int u = 0; u < SA_FLUSH_DEPTH; ++u) {
+      h[u] = make_uint2(0u, 0x7f800000u);  // no hit: d2 = +inf fails every limit
+      kb[u] = make_uint4(0u, 0u, 0u, 0u);
       if (j0 + u < cnt) {
-        c[u] = S.hits[j0 + u][tid];
-        b[u] = key[c[u]];
+        h[u] = S.hits[j0 + u][tid];
+        kb[u] = *reinterpret_cast<const uint4*>(G.recK + h[u].x);
+#if !SA_TAG_IN_TRIP
+        const uint32_t tc = reinterpret_cast<const uint32_t*>(pos2)[8u * (size_t)(h[u].x >> 1) + 6u + (h[u].x & 1u)];
+        if (tc - tf1 <= 2u) h[u].y = 0x7f800000u;  // same chain, residue ordinals at most 1 apart: no orientation can pass
+        else K.n_q += 1u;
+#endif
       }
     }
-    int n1 = K.n1;
+    int n2 = K.n2;
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const bool keep = !(mine.x == b[u].x && (mine.y - b[u].y + 1u) <= 2u);  // not: same chain, |ordinal difference| <= 1
-      const uint32_t m = __ballot_sync(0xffffffffu, keep);
-      if (keep) s1[n1 + __popc(m & lt)] = make_uint2(slot, c[u]);
-      n1 += __popc(m);
+    for (int u = 0; u < SA_FLUSH_DEPTH; ++u) {
+      if (j0 + u >= maxc) break;  // warp-uniform
+      const float d2 = __uint_as_float(h[u].y);
+      const bool pot = d2 <= label_limit2(P, S.lim2, mine.attr, kb[u].x);
+      const int dir = pot ? pair_direction(mine.attr, mine.chain_key, mine.res_ordinal, kb[u].x, kb[u].y, kb[u].z) : 0;
+      const bool go = dir != 0;
+      const uint32_t m = __ballot_sync(0xffffffffu, go);
+      if (go) s2[n2 + __popc(m & lt)] = make_uint4(slot | QF_B, h[u].x | (dir == 2 ? QF_A : 0u) | QF_B, mine.perm, kb[u].w);
+      n2 += __popc(m);
+      __syncwarp();
+      if (n2 >= 32) {  // the stash holds 64: never more than 31 + 32 before this point
+        K.n2 = n2;
+        sa_emit(G, S, wid, lane, K, false);
+        n2 = K.n2;
+      }
     }
-    K.n_q += (unsigned long long)(n1 - K.n1);
-    K.n1 = n1;
-    __syncwarp();
-    sa_filter(G, P, S, tid >> 5, lane, K, false);
+    K.n2 = n2;
   }
+}
+
+// The trips of one tile.  A lane is active while s < re.  The trips are branch-free (a lane that has finished keeps
+// computing on slot pair 0 and appends nothing), so a round of SA_ROUND trips is straight-line code; the candidates of
+// trip t + 1 are loaded before trip t computes.  Candidates come straight from pos2 through L1 (r2b: staging the union of
+// the warp's five candidate spans in shared memory first -- cp.async, 4 KB per warp, trips on ld.shared -- was built and
+// measured: 0.185 ms against 0.138 ms; the kernel is bound by issue slots, not by L1, and the staging adds instructions).
+__device__ __forceinline__ void sa_trips(const PairArgs& G, const DevParams& P, SaSmem& S, const unsigned long long* __restrict__ pos2,
+                                         int tid, int lane, uint32_t slot, const RecK mine, unsigned long long nax, unsigned long long nay,
+                                         unsigned long long naz, float tlim, uint32_t tf1, uint32_t s, uint32_t rb, uint32_t re, uint32_t rp,
+                                         SaCarry& K) {
+  constexpr uint32_t ROW = 4u * SA_THREADS, B_TO_E = 4u * SA_THREADS * SA_RUNS;  // byte strides of the run tables
+  constexpr uint32_t HROW = 8u * SA_THREADS;                                      // byte stride of the hit lists
+  const uint32_t hp0 = (uint32_t)__cvta_generic_to_shared(&S.hits[0][tid]);
+  auto load = [&](uint32_t ld, ulonglong2& XY, ulonglong2& ZT) {
+    // slot pair (ld, ld + 1): 32 bytes as two 16-byte loads: (x0 x1 | y0 y1) and (z0 z1 | t0 t1)
+    XY = *reinterpret_cast<const ulonglong2*>(pos2 + 2u * ld);
+#if SA_TAG_IN_TRIP
+    ZT = *reinterpret_cast<const ulonglong2*>(pos2 + 2u * ld + 2u);
+#else
+    ZT.x = pos2[2u * ld + 2u];
+    ZT.y = 0ull;
+#endif
+  };
+  uint32_t ld = s < re ? s : 0u;
+  ulonglong2 XY, ZT;
+  load(ld, XY, ZT);
+  uint32_t hp = hp0;  // shared-memory address of the next free entry of this lane's hit list
+  while (__any_sync(0xffffffffu, s < re)) {
+#pragma unroll
+    for (int trip = 0; trip < SA_ROUND; ++trip) {
+      // where the next trip reads: two slots on, or the start of the next run
+      uint32_t sn = s + 2u, rbn = rb, ren = re;
+      asm volatile("{\n\t.reg .pred p, q;\n\t"
+                   "setp.lt.u32 q, %6, %2;\n\t"
+                   "setp.ge.and.u32 p, %0, %2, q;\n\t"
+                   "@p ld.shared.u32 %1, [%3];\n\t"
+                   "@p ld.shared.u32 %2, [%3+%4];\n\t"
+                   "@p add.u32 %3, %3, %5;\n\t"
+                   "@p and.b32 %0, %1, 0xfffffffe;\n\t}"
+                   : "+r"(sn), "+r"(rbn), "+r"(ren), "+r"(rp) : "n"(B_TO_E), "n"(ROW), "r"(s) : "memory");
+      ld = sn < ren ? sn : 0u;
+      ulonglong2 XYn, ZTn;
+      load(ld, XYn, ZTn);
+      const unsigned long long dx = sa_add2(XY.x, nax), dy = sa_add2(XY.y, nay), dz = sa_add2(ZT.x, naz);
+      const unsigned long long d2 = sa_fma2(dz, dz, sa_fma2(dy, dy, sa_mul2(dx, dx)));
+      uint32_t d0, d1, t0, t1;
+      asm("mov.b64 {%0, %1}, %2;" : "=r"(d0), "=r"(d1) : "l"(d2));
+      asm("mov.b64 {%0, %1}, %2;" : "=r"(t0), "=r"(t1) : "l"(ZT.y));
+      const uint32_t s1 = s + 1u;
+      // predicated store + add (written in PTX: the compiler otherwise keeps a count and rebuilds the address).
+      // hit = within the from-atom's label limit, inside the run, and NOT (same chain, residue ordinals <= 1 apart)
+#if SA_TAG_IN_TRIP
+      asm volatile("{\n\t.reg .pred p;\n\t.reg .u32 t;\n\t"
+                   "setp.le.f32 p, %1, %2;\n\t"
+                   "setp.ge.and.u32 p, %3, %4, p;\n\t"
+                   "sub.u32 t, %6, %7;\n\t"
+                   "setp.gt.and.u32 p, t, 2, p;\n\t"
+                   "@p st.shared.v2.u32 [%0], {%3, %8};\n\t"
+                   "@p add.u32 %0, %0, %5;\n\t}"
+                   : "+r"(hp) : "f"(__uint_as_float(d0)), "f"(tlim), "r"(s), "r"(rb), "n"(HROW), "r"(t0), "r"(tf1), "r"(d0) : "memory");
+      asm volatile("{\n\t.reg .pred p;\n\t.reg .u32 t;\n\t"
+                   "setp.le.f32 p, %1, %2;\n\t"
+                   "setp.lt.and.u32 p, %3, %4, p;\n\t"
+                   "sub.u32 t, %6, %7;\n\t"
+                   "setp.gt.and.u32 p, t, 2, p;\n\t"
+                   "@p st.shared.v2.u32 [%0], {%3, %8};\n\t"
+                   "@p add.u32 %0, %0, %5;\n\t}"
+                   : "+r"(hp) : "f"(__uint_as_float(d1)), "f"(tlim), "r"(s1), "r"(re), "n"(HROW), "r"(t1), "r"(tf1), "r"(d1) : "memory");
+#else
+      asm volatile("{\n\t.reg .pred p;\n\t"
+                   "setp.le.f32 p, %1, %2;\n\t"
+                   "setp.ge.and.u32 p, %3, %4, p;\n\t"
+                   "@p st.shared.v2.u32 [%0], {%3, %6};\n\t"
+                   "@p add.u32 %0, %0, %5;\n\t}"
+                   : "+r"(hp) : "f"(__uint_as_float(d0)), "f"(tlim), "r"(s), "r"(rb), "n"(HROW), "r"(d0) : "memory");
+      asm volatile("{\n\t.reg .pred p;\n\t"
+                   "setp.le.f32 p, %1, %2;\n\t"
+                   "setp.lt.and.u32 p, %3, %4, p;\n\t"
+                   "@p st.shared.v2.u32 [%0], {%3, %6};\n\t"
+                   "@p add.u32 %0, %0, %5;\n\t}"
+                   : "+r"(hp) : "f"(__uint_as_float(d1)), "f"(tlim), "r"(s1), "r"(re), "n"(HROW), "r"(d1) : "memory");
+      (void)t0, (void)t1;
+#endif
+      s = sn, rb = rbn, re = ren, XY = XYn, ZT = ZTn;
+    }
+    if (__any_sync(0xffffffffu, hp > hp0 + (uint32_t)(SA_BUF - 2 * SA_ROUND) * HROW)) {
+      sa_flush(G, P, S, pos2, tid, lane, slot, mine, tf1, (hp - hp0) / HROW, K);
+      hp = hp0;
+    }
+  }
+  if (__any_sync(0xffffffffu, hp != hp0)) sa_flush(G, P, S, pos2, tid, lane, slot, mine, tf1, (hp - hp0) / HROW, K);
 }
 
 __global__ void __launch_bounds__(SA_THREADS, SA_MIN_BLOCKS) k_screen_atoms(const PairArgs G, const DevParams P,
-                                                                            const unsigned long long* __restrict__ pos2, const uint2* __restrict__ key,
-                                                                            uint32_t n_atoms) {
+                                                                            const unsigned long long* __restrict__ pos2, uint32_t n_atoms) {
   __shared__ SaSmem S;
-  const int lane = threadIdx.x & 31, tid = threadIdx.x;
+  const int lane = threadIdx.x & 31, tid = threadIdx.x, wid = threadIdx.x >> 5;
   if (tid < 16) {
     float m = 0.f;
     for (int eb = 0; eb < 16; ++eb) m = fmaxf(m, class_pair_limit2(P, tid, eb));
     S.lim1[tid] = m;
   }
   for (int k = tid; k < 256; k += SA_THREADS) S.lim2[k] = class_pair_limit2(P, k >> 4, k & 15);
-  if (tid < 32) S.cursor[tid] = &G.ctr->work;
   __syncthreads();
   const uint32_t n_tiles = (n_atoms + 31u) >> 5;
-#if !SA_DYNAMIC_TILES
   const uint32_t n_warps = gridDim.x * SA_WARPS;
-#endif
-  SaCarry K{0, 0, 0ull};
+  // single-structure jobs: the grid's row pitches are the same for every lane
+  uint32_t nx0 = 0, nxny0 = 0;
+  if (!G.atom_struct) {
+    const StructDesc& d = G.descs[0];
+    nx0 = (uint32_t)d.nx, nxny0 = (uint32_t)d.nx * (uint32_t)d.ny;
+  }
+  SaCarry K{0, 0ull};
   unsigned long long n_tests = 0;
-  const uint32_t hp0 = (uint32_t)__cvta_generic_to_shared(&S.hits[0][tid]);
   const uint32_t rp0 = (uint32_t)__cvta_generic_to_shared(&S.run_b[0][tid]);
-  constexpr uint32_t ROW = 4u * SA_THREADS, B_TO_E = 4u * SA_THREADS * SA_RUNS;  // byte strides of the two tables
-#if SA_DYNAMIC_TILES
-  // tiles are handed out through the work cursor (free in this mode: k_screen is not launched): their cost varies with
-  // the local density, a static stride leaves the last wave ragged.  The next ticket is requested before the tile is
-  // processed, so its round trip is hidden.
-  uint32_t tile = __shfl_sync(0xffffffffu, draw_cursor(S.cursor[lane], lane), 0);
-  while (tile < n_tiles) {
-    const uint32_t next_tile = draw_cursor(S.cursor[lane], lane);
-#else
-  for (uint32_t tile = blockIdx.x * SA_WARPS + (tid >> 5); tile < n_tiles; tile += n_warps) {
-#endif
+  constexpr uint32_t ROW = 4u * SA_THREADS;
+  const uint32_t* __restrict__ cs = G.cell_start;
+  for (uint32_t tile = blockIdx.x * SA_WARPS + wid; tile < n_tiles; tile += n_warps) {
     const uint32_t slot = (tile << 5) + lane;
-    uint32_t s = 0, rb = 0, re = 0, rp = rp0;
-    uint2 mine = make_uint2(0u, 0u);
+    uint32_t tf1 = 0;
+    RecK mine{0u, 0u, 0u, 0u};
     unsigned long long nax = 0, nay = 0, naz = 0;  // (-x, -x), (-y, -y), (-z, -z) of the from-atom
     float tlim = -1.f;
+    // the five runs of this lane's half shell as sorted slots [b, e): rows (dy, dz) = (+1,0) (-1,+1) (0,+1) (+1,+1) with x
+    // from ix-1 to ix+1, then the rest of the own cell and its +x neighbour from the lane's own slot + 1
+    uint32_t b5[5], e5[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) b5[k] = 0xffffffffu, e5[k] = 0u;
     if (slot < n_atoms) {
-      const uint4 a0 = *reinterpret_cast<const uint4*>(G.recA + slot);
-      mine = key[slot];
-      // the pair record's fourth word pair holds the cells' first slots (k_scatter_atoms): the work item sits there
-      const uint4* ip = reinterpret_cast<const uint4*>(G.items + reinterpret_cast<const uint32_t*>(pos2)[8u * (slot >> 1) + 6u + (slot & 1u)]);
-      const uint4 i0 = ip[0], off = ip[1], dl = ip[2];  // (cb, n_own, total, sid), off[4], delta[4]
-      nax = sa_dup(-__uint_as_float(a0.x)), nay = sa_dup(-__uint_as_float(a0.y)), naz = sa_dup(-__uint_as_float(a0.z));
-      tlim = fminf(P.thr_near, atom_limit2(P, S.lim1, a0.w));  // no label can fire for this atom beyond its own limit
-      // runs 1..4 first: the lanes of a cell walk them in step (same addresses: one wavefront); run 0 -- the rest of the
-      // own cell and its +x neighbour, from the lane's own slot + 1 -- differs per lane and goes last
-      const uint32_t b5[5] = {off.x + dl.x, off.y + dl.y, off.z + dl.z, off.w + dl.w, slot + 1u};
-      const uint32_t e5[5] = {off.y + dl.x, off.z + dl.y, off.w + dl.z, i0.z + dl.w, i0.x + off.x};
-      uint32_t n = 0;
+      mine = G.recK[slot];
+      const SlotCell sc = G.slot_cell[slot];
+      const float* q = reinterpret_cast<const float*>(pos2) + 8u * (size_t)(slot >> 1) + (slot & 1u);
+      nax = sa_dup(-q[0]), nay = sa_dup(-q[2]), naz = sa_dup(-q[4]);
+      tf1 = __float_as_uint(q[6]) - 1u;  // |tag - own tag| <= 1  <=>  tag - (own tag - 1) <= 2 (unsigned)
+      tlim = fminf(P.thr_near, atom_limit2(P, S.lim1, mine.attr));  // no label can fire for this atom beyond its own limit
+      uint32_t nx = nx0, nxny = nxny0;
+      if (G.atom_struct) {  // batch jobs: every structure has its own grid
+        const StructDesc& d = G.descs[G.atom_struct[mine.perm]];
+        nx = (uint32_t)d.nx, nxny = (uint32_t)d.nx * (uint32_t)d.ny;
+      }
+      const uint32_t c = sc.cell, xl = sc.bits & 1u, xh = (sc.bits >> 1) & 1u;
+      const bool yl = sc.bits & 4u, yh = sc.bits & 8u, zh = sc.bits & 16u;
+      const uint32_t rc4[4] = {c + nx, c - nx + nxny, c + nxny, c + nx + nxny};
+      const bool ok4[4] = {yh, yl && zh, zh, yh && zh};
 #pragma unroll
-      for (int k = 0; k < 5; ++k) {
-        if (b5[k] < e5[k]) {
-          S.run_b[n][tid] = b5[k], S.run_e[n][tid] = e5[k];
-          ++n;
-          n_tests += e5[k] - b5[k];
+      for (int k = 0; k < 4; ++k)
+        if (ok4[k]) {
+          const uint32_t b = cs[rc4[k] - xl], e = cs[rc4[k] + xh + 1u];
+          if (b < e) b5[k] = b, e5[k] = e;
         }
+      {
+        const uint32_t e = cs[c + 1u + xh];
+        if (slot + 1u < e) b5[4] = slot + 1u, e5[4] = e;
       }
-      S.run_b[n][tid] = 0xffffffffu, S.run_e[n][tid] = 0u;  // the closing row: no s reaches rb or stays below re (s keeps stepping)
-      rb = S.run_b[0][tid], re = S.run_e[0][tid];
-      rp = rp0 + ROW;
-      s = rb & ~1u;
-    } else {
-      rb = 0xffffffffu;
     }
-    // A lane is active while s < re.  The trips are branch-free (a lane that has finished keeps computing on slot pair 0
-    // and appends nothing), so a round of SA_ROUND trips is straight-line code; the candidates of trip t + 1 are loaded
-    // before trip t computes.
-    uint32_t ld = s < re ? s : 0u;
-    // slot pair (s, s + 1): 32 bytes, as a 16- and an 8-byte load (one 32-byte LDG.256 was measured: 0.127 -> 0.133 ms)
-    ulonglong2 XY = *reinterpret_cast<const ulonglong2*>(pos2 + 2u * ld);
-    unsigned long long Z = pos2[2u * ld + 2u];
-    uint32_t hp = hp0;  // shared-memory address of the next free entry of this lane's hit list
-    while (__any_sync(0xffffffffu, s < re)) {
+    // ---- this lane's run table: rows 0..3 first (the lanes of a cell walk them in step), the own row last -----------------
+    uint32_t n = 0;
 #pragma unroll
-      for (int trip = 0; trip < SA_ROUND; ++trip) {
-        // where the next trip reads: two slots on, or the start of the next run
-        uint32_t sn = s + 2u, rbn = rb, ren = re;
-        asm volatile("{\n\t.reg .pred p, q;\n\t"
-                     "setp.lt.u32 q, %6, %2;\n\t"
-                     "setp.ge.and.u32 p, %0, %2, q;\n\t"
-                     "@p ld.shared.u32 %1, [%3];\n\t"
-                     "@p ld.shared.u32 %2, [%3+%4];\n\t"
-                     "@p add.u32 %3, %3, %5;\n\t"
-                     "@p and.b32 %0, %1, 0xfffffffe;\n\t}"
-                     : "+r"(sn), "+r"(rbn), "+r"(ren), "+r"(rp) : "n"(B_TO_E), "n"(ROW), "r"(s) : "memory");
-        ld = sn < ren ? sn : 0u;
-        const ulonglong2 XYn = *reinterpret_cast<const ulonglong2*>(pos2 + 2u * ld);
-        const unsigned long long Zn = pos2[2u * ld + 2u];
-        const unsigned long long dx = sa_add2(XY.x, nax), dy = sa_add2(XY.y, nay), dz = sa_add2(Z, naz);
-        const unsigned long long d2 = sa_fma2(dz, dz, sa_fma2(dy, dy, sa_mul2(dx, dx)));
-        float d0, d1;
-        asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(d2));
-        const uint32_t s1 = s + 1u;
-        // predicated store + add (written in PTX: the compiler otherwise keeps a count and rebuilds the address)
-        asm volatile("{\n\t.reg .pred p;\n\t"
-                     "setp.le.f32 p, %1, %2;\n\t"
-                     "setp.ge.and.u32 p, %3, %4, p;\n\t"
-                     "@p st.shared.u32 [%0], %3;\n\t"
-                     "@p add.u32 %0, %0, %5;\n\t}"
-                     : "+r"(hp) : "f"(d0), "f"(tlim), "r"(s), "r"(rb), "n"(ROW) : "memory");
-        asm volatile("{\n\t.reg .pred p;\n\t"
-                     "setp.le.f32 p, %1, %2;\n\t"
-                     "setp.lt.and.u32 p, %3, %4, p;\n\t"
-                     "@p st.shared.u32 [%0], %3;\n\t"
-                     "@p add.u32 %0, %0, %5;\n\t}"
-                     : "+r"(hp) : "f"(d1), "f"(tlim), "r"(s1), "r"(re), "n"(ROW) : "memory");
-        s = sn, rb = rbn, re = ren, XY = XYn, Z = Zn;
-      }
-      if (__any_sync(0xffffffffu, hp > hp0 + (uint32_t)(SA_BUF - 2 * SA_ROUND) * ROW)) {
-        sa_flush(G, P, key, S, tid, lane, slot, mine, (hp - hp0) / ROW, K);
-        hp = hp0;
+    for (int k = 0; k < 5; ++k) {
+      if (b5[k] < e5[k]) {
+        S.run_b[n][tid] = b5[k], S.run_e[n][tid] = e5[k];
+        ++n;
+        n_tests += e5[k] - b5[k];
       }
     }
-    if (__any_sync(0xffffffffu, hp != hp0)) sa_flush(G, P, key, S, tid, lane, slot, mine, (hp - hp0) / ROW, K);
-#if SA_DYNAMIC_TILES
-    tile = __shfl_sync(0xffffffffu, next_tile, 0);
-#endif
+    S.run_b[n][tid] = 0xffffffffu, S.run_e[n][tid] = 0u;  // the closing row: no s reaches rb or stays below re (s keeps stepping)
+    uint32_t rb = 0xffffffffu, re = 0u, s = 0u;
+    if (n) rb = S.run_b[0][tid], re = S.run_e[0][tid], s = rb & ~1u;
+    sa_trips(G, P, S, pos2, tid, lane, slot, mine, nax, nay, naz, tlim, tf1, s, rb, re, rp0 + ROW, K);
   }
-  sa_filter(G, P, S, tid >> 5, lane, K, true);
-  if (lane == 0 && K.n_q) atomicAdd(&G.ctr->q_len, K.n_q);
+  sa_emit(G, S, wid, lane, K, true);
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) n_tests += __shfl_xor_sync(0xffffffffu, n_tests, o);
+  for (int o = 16; o > 0; o >>= 1) {
+    n_tests += __shfl_xor_sync(0xffffffffu, n_tests, o);
+    K.n_q += __shfl_xor_sync(0xffffffffu, K.n_q, o);
+  }
+  if (lane == 0 && K.n_q) atomicAdd(&G.ctr->q_len, K.n_q);
   if (lane == 0 && n_tests) atomicAdd(&G.ctr->screened, n_tests);
 }
 

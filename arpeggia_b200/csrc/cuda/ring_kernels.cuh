@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(256) k_rings(const RingArgs R, const DevParams
       sid = R.ring_struct ? R.ring_struct[q] : 0u;
     } else {
       const uint32_t t = R.cations[q - R.n_rings];
-      const RecA a = R.recA[t];
+      const RecK a = R.recK[t];
       const RecB b = R.recB[t];
       id1 = a.perm;
       w1 = a.attr, k1 = a.chain_key, o1 = a.res_ordinal;

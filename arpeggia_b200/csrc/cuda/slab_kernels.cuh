@@ -324,6 +324,17 @@ __global__ void __launch_bounds__(256) k_res_tag_steps(const uint32_t* __restric
   step[r] = s;
 }
 
+// per-residue (chain key, ordinal) from the per-atom arrays: every atom of a residue carries the same pair (benign race)
+__global__ void __launch_bounds__(256) k_res_keys_from_atoms(const uint32_t* __restrict__ chain_key, const uint32_t* __restrict__ res_ordinal,
+                                                             const uint32_t* __restrict__ res_id, uint32_t n_atoms,
+                                                             uint32_t* __restrict__ res_chain_key, uint32_t* __restrict__ res_res_ordinal) {
+  const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= n_atoms) return;
+  const uint32_t r = res_id[a];
+  res_chain_key[r] = chain_key[a];
+  res_res_ordinal[r] = res_ordinal[a];
+}
+
 // one row of the count matrix: what this rank sends to every rank (4 counts each), from the per-peer counters
 __global__ void k_halo_row(const HaloCounts* __restrict__ counts, const int* __restrict__ peer_rank, int n_peers, int world,
                            unsigned long long* __restrict__ row /* [world * 4] */) {
