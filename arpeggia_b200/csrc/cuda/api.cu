@@ -267,6 +267,7 @@ void upload_concat(arp_ctx* c, DBuf<T>& dst, const arp_structure* const* s, int6
 }
 
 void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
+  arp::NvtxRange nvtx_("arp:upload");
   CK(cudaSetDevice(c->device));
   if (n < 1) throw arp::Error{ARP_ERR_ARG, "a job needs at least one structure"};
   c->have_job = c->have_run = false;

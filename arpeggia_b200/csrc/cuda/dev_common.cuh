@@ -110,6 +110,19 @@ struct Counters {
   unsigned long long q2_len;      uint64_t padr[15];   // pairs pushed by k_filter (likewise)
 };
 
+// Checked build (-DARP_CHECKED=1, scratch/checked.sh): the index arithmetic the kernels rely on is verified on the device
+// -- slots below the atom count, cells inside the cell table, per-lane list and stash positions inside their arrays,
+// queue entries decoded to valid slots -- and a violated check sets bit (16 + id) of Counters.error, which fails the job
+// on the host with the check's number.  compute-sanitizer is closed on this pool; this is the stand-in (profiles/).
+#ifndef ARP_CHECKED
+#define ARP_CHECKED 0
+#endif
+#if ARP_CHECKED
+#define ARP_CHK(ctr, cond, id) do { if (!(cond)) atomicOr(&(ctr)->error, 0x10000u << (id)); } while (0)
+#else
+#define ARP_CHK(ctr, cond, id) do { } while (0)
+#endif
+
 struct PairArgs {
   const RecA* recA;            // counting mode
   const RecB* recB;
@@ -117,6 +130,7 @@ struct PairArgs {
   const SlotCell* slot_cell;   // emit-radius mode
   const uint32_t* atom_struct; // input-order atom -> structure; nullptr when the job has one structure
   const uint32_t* cell_start;  // n_cells + 1
+  uint32_t n_atoms, n_cells;   // sizes of the sorted arrays / the cell table (checked build)
   const Item* items;           // non-empty cells
   const StructDesc* descs;
   // original-order arrays (gathers for disulfide / hydrogen lists)

@@ -322,6 +322,7 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
   const StructDesc& d = descs[s];
   c = cell_of[a], r = rank_of[a];
   slot = cell_start[c] + r;
+  ARP_CHK(ctr, slot < n && slot < cell_start[c + 1], 10);  // the atom's place lies inside its cell's slot range
   px = x[a], py = y[a], pz = z[a];
   RecA ra;
   ra.x = (float)(px - d.ox);

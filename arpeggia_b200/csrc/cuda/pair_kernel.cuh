@@ -130,6 +130,7 @@ struct ExactOperands {
 };
 __device__ __forceinline__ void exact_gather(const PairArgs& G, const uint4 e, bool have, ExactOperands& X) {
   if (!have) return;
+  ARP_CHK(G.ctr, (e.x & SLOT_MASK) < G.n_atoms && (e.y & SLOT_MASK) < G.n_atoms, 0);  // queue entries decode to sorted slots
   X.a = G.recB[e.x & SLOT_MASK];
   X.b = G.recB[e.y & SLOT_MASK];
 }
@@ -878,6 +879,7 @@ __device__ __forceinline__ void sa_emit(const PairArgs& G, SaSmem& S, int wid, i
     if (lane == 0) w = atomicAdd(&G.ctr->q2_len, (unsigned long long)k);
     w = __shfl_sync(0xffffffffu, w, 0) + lane;
     K.n2 -= k;
+    ARP_CHK(G.ctr, K.n2 >= 0 && K.n2 + k <= 64, 1);  // the stash holds 64 entries
     if (lane < k && w < G.pairq2_cap) __stcs(G.pairq2 + w, s2[K.n2 + lane]);
     __syncwarp();
   }
@@ -903,7 +905,9 @@ __device__ __forceinline__ void sa_flush(const PairArgs& G, const DevParams& P, 
       h[u] = make_uint2(0u, 0x7f800000u);  // no hit: d2 = +inf fails every limit
       kb[u] = make_uint4(0u, 0u, 0u, 0u);
       if (j0 + u < cnt) {
+        ARP_CHK(G.ctr, j0 + u < (uint32_t)SA_BUF, 2);  // a lane's list never outgrows its SA_BUF entries
         h[u] = S.hits[j0 + u][tid];
+        ARP_CHK(G.ctr, h[u].x < G.n_atoms && h[u].x != slot, 3);  // a hit is another atom's sorted slot
         kb[u] = *reinterpret_cast<const uint4*>(G.recK + h[u].x);
 #if !SA_TAG_IN_TRIP
         const uint32_t tc = reinterpret_cast<const uint32_t*>(pos2)[8u * (size_t)(h[u].x >> 1) + 6u + (h[u].x & 1u)];
@@ -921,6 +925,7 @@ __device__ __forceinline__ void sa_flush(const PairArgs& G, const DevParams& P, 
       const int dir = pot ? pair_direction(mine.attr, mine.chain_key, mine.res_ordinal, kb[u].x, kb[u].y, kb[u].z) : 0;
       const bool go = dir != 0;
       const uint32_t m = __ballot_sync(0xffffffffu, go);
+      ARP_CHK(G.ctr, n2 + __popc(m) <= 64, 4);
       if (go) s2[n2 + __popc(m & lt)] = make_uint4(slot | QF_B, h[u].x | (dir == 2 ? QF_A : 0u) | QF_B, mine.perm, kb[u].w);
       n2 += __popc(m);
       __syncwarp();
@@ -1018,6 +1023,7 @@ __device__ __forceinline__ void sa_trips(const PairArgs& G, const DevParams& P, 
 #endif
       s = sn, rb = rbn, re = ren, XY = XYn, ZT = ZTn;
     }
+    ARP_CHK(G.ctr, hp <= hp0 + (uint32_t)SA_BUF * HROW, 9);  // a round appends at most 2 * SA_ROUND entries to a list that had room for them
     if (__any_sync(0xffffffffu, hp > hp0 + (uint32_t)(SA_BUF - 2 * SA_ROUND) * HROW)) {
       sa_flush(G, P, S, pos2, tid, lane, slot, mine, tf1, (hp - hp0) / HROW, K);
       hp = hp0;
@@ -1077,10 +1083,13 @@ __global__ void __launch_bounds__(SA_THREADS, SA_MIN_BLOCKS) k_screen_atoms(cons
       const bool yl = sc.bits & 4u, yh = sc.bits & 8u, zh = sc.bits & 16u;
       const uint32_t rc4[4] = {c + nx, c - nx + nxny, c + nxny, c + nx + nxny};
       const bool ok4[4] = {yh, yl && zh, zh, yh && zh};
+      ARP_CHK(G.ctr, c < G.n_cells && c + 1u + xh <= G.n_cells, 5);  // the slot's cell lies in the cell table
 #pragma unroll
       for (int k = 0; k < 4; ++k)
         if (ok4[k]) {
+          ARP_CHK(G.ctr, rc4[k] >= xl && rc4[k] + xh + 1u <= G.n_cells, 6);  // and so do the rows of its half shell
           const uint32_t b = cs[rc4[k] - xl], e = cs[rc4[k] + xh + 1u];
+          ARP_CHK(G.ctr, b <= e && e <= n_atoms, 7);  // runs are slot ranges
           if (b < e) b5[k] = b, e5[k] = e;
         }
       {
@@ -1098,6 +1107,11 @@ __global__ void __launch_bounds__(SA_THREADS, SA_MIN_BLOCKS) k_screen_atoms(cons
         n_tests += e5[k] - b5[k];
       }
     }
+#ifdef ARP_CHECK_SELFTEST  // negative control of the checked build: a bound that real inputs violate must fail the job
+    ARP_CHK(G.ctr, n < 3u, 8);
+#else
+    ARP_CHK(G.ctr, n < (uint32_t)SA_RUNS, 8);  // five runs at most, then the closing row
+#endif
     S.run_b[n][tid] = 0xffffffffu, S.run_e[n][tid] = 0u;  // the closing row: no s reaches rb or stays below re (s keeps stepping)
     uint32_t rb = 0xffffffffu, re = 0u, s = 0u;
     if (n) rb = S.run_b[0][tid], re = S.run_e[0][tid], s = rb & ~1u;

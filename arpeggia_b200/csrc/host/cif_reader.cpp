@@ -212,6 +212,7 @@ void parse_piece(std::string_view text, size_t width, const int* where, bool aut
 extern "C" {
 
 int arph_parse_cif_ids(const char* path, int use_auth_ids, arp_atom_record** out, int64_t* n) {
+  arp::NvtxRange nvtx_("arph:parse_cif");
   const bool auth_ids = use_auth_ids != 0;
   *out = nullptr;
   *n = 0;

@@ -7,7 +7,23 @@
 #include "arpeggia_cuda.h"
 #include "arpeggia_host.h"
 
+// Tracing: NVTX ranges around every phase of the path (header-only NVTX v3: no link dependency, a no-op unless a
+// tool -- nsys, ncu --nvtx -- is attached).  Ranges are named "arp:<phase>" (device path) / "arph:<phase>" (host side).
+#include <nvtx3/nvToolsExt.h>
+
 namespace arp {
+
+struct NvtxRange {
+  bool open = true;
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  void end() {
+    if (open) nvtxRangePop();
+    open = false;
+  }
+  ~NvtxRange() { end(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 struct Error {
   int code;

@@ -635,6 +635,7 @@ extern "C" {
 int arph_pack(const arp_atom_record* atoms, int64_t n, const char* groups, int ignore_zero_occupancy, uint32_t flags,
               arph_packed** out) {
   *out = nullptr;
+  arp::NvtxRange nvtx_("arph:pack");
   auto* h = new arph_packed();
   try {
     arp::pack_records(atoms, n, groups ? groups : "/", ignore_zero_occupancy != 0, flags, h->p);

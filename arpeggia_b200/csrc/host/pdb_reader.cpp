@@ -58,6 +58,7 @@ extern "C" {
 void arph_free(void* p) { std::free(p); }
 
 int arph_parse_pdb(const char* path, arp_atom_record** out, int64_t* n) {
+  arp::NvtxRange nvtx_("arph:parse_pdb");
   *out = nullptr;
   *n = 0;
   FILE* f = std::fopen(path, "rb");

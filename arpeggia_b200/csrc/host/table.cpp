@@ -53,6 +53,7 @@ void label_ranks(int32_t* lrank) {  // the interaction column is a string: sort 
 // rings; ent_rank orders (resi, altloc, atomi) = sort keys 4-6 / 7-9 of mod.rs:123-134, ent_tie breaks the ties the
 // reference leaves open by entity order -- build_table below uses the same order, so both paths give the same frame.
 void build_frame_tables(const Packed& P, FrameTables& T) {
+  NvtxRange nvtx_("arph:frame_tables");
   const std::vector<int32_t> srank = string_ranks(P);
   const size_t n_sides = P.resconfs.size(), n_atoms = P.x.size(), n_rings = P.ring_rc.size(), E = n_atoms + n_rings;
   T.sides.assign(n_sides, arp_frame_side{});
@@ -342,6 +343,7 @@ arph_table* table_from_frame(const Packed& P, arp_frame* f) {
 
 extern "C" {
 int arph_build_table(const arph_packed* p, const arp_row* rows, int64_t n_rows, arph_table** out) {
+  arp::NvtxRange nvtx_("arph:build_table");
   *out = nullptr;
   try {
     *out = arp::build_table(arph_packed_ref(p), rows, n_rows);
@@ -355,6 +357,7 @@ int arph_build_table(const arph_packed* p, const arp_row* rows, int64_t n_rows, 
   }
 }
 int arph_table_from_frame(const arph_packed* p, arp_frame* f, arph_table** out) {
+  arp::NvtxRange nvtx_("arph:table_from_frame");
   *out = nullptr;
   if (!p || !f) {
     if (f) arp_frame_free(nullptr, f);
