@@ -9,7 +9,7 @@ C ABI in include/arpeggia_cuda.h; there is no CPU fallback.
 from __future__ import annotations
 
 from ._lib import ArpeggiaError, ATOM_DTYPE, HOST_FLAG_NO_COUNTERS as FLAG_NO_COUNTERS, LABELS, ROW_DTYPE
-from .core import COLUMNS, Context, Packed, default_context, load_atoms, parse_cif, parse_pdb, read_table, split_rows
+from .core import COLUMNS, Context, Packed, default_context, load_atoms, pack_many, parse_cif, parse_pdb, read_table, split_rows
 from .frame import to_arrow, to_frame
 from . import sap  # noqa: F401  (the neighbour sum of the SAP score)
 

@@ -203,6 +203,7 @@ SIGNATURES = {
     "arph_parse_file": (C.c_int, [C.c_char_p, C.POINTER(_P), C.POINTER(C.c_int64)]),
     "arph_free": (None, [_P]),
     "arph_pack": (C.c_int, [_P, C.c_int64, C.c_char_p, C.c_int, C.c_uint32, C.POINTER(_P)]),
+    "arph_pack_many": (C.c_int, [C.POINTER(_P), C.POINTER(C.c_int64), C.c_int64, C.c_char_p, C.c_int, C.c_uint32, C.POINTER(_P)]),
     "arph_packed_structure": (C.POINTER(Structure), [_P]),
     "arph_packed_n_warnings": (C.c_int64, [_P]),
     "arph_packed_warning": (C.c_char_p, [_P, C.c_int64]),

@@ -162,6 +162,23 @@ class Packed:
     __del__ = close
 
 
+def pack_many(atom_arrays, groups: str = "/", ignore_zero_occupancy: bool = False, flags: int = 0) -> list:
+    """arph_pack_many: a list of atom-record arrays -> a list of Packed, packed on all host threads (one structure each)."""
+    L = lib()
+    arrs = [np.ascontiguousarray(a, dtype=ATOM_DTYPE) for a in atom_arrays]
+    count = len(arrs)
+    ptrs = (C.c_void_p * count)(*[a.ctypes.data for a in arrs])
+    ns = (C.c_int64 * count)(*[len(a) for a in arrs])
+    out = (C.c_void_p * count)()
+    check(L.arph_pack_many(ptrs, ns, count, groups.encode(), int(ignore_zero_occupancy), flags, out))
+    packs = []
+    for k in range(count):
+        p = Packed.__new__(Packed)
+        p._atoms, p._h = arrs[k], C.c_void_p(out[k])
+        packs.append(p)
+    return packs
+
+
 def read_table(t: Table) -> dict:
     """Copy an arph_table into numpy arrays (string columns as object arrays)."""
     n = t.n_rows
@@ -223,7 +240,7 @@ def table_to_arrow(tp, strings: str = "string"):
     def text(idx, d):
         if n == 0:
             return pa.array([], type=pa.large_string()) if strings != "dictionary" else pa.DictionaryArray.from_arrays(pa.array([], type=pa.int32()), d)
-        a = pa.DictionaryArray.from_arrays(idx, d)  # checks the indices against the dictionary
+        a = pa.DictionaryArray.from_arrays(idx, d, safe=False)  # the library only ever writes ids of its own dictionary
         return a if strings == "dictionary" else a.dictionary_decode()
 
     bitmap, n_null = None, 0

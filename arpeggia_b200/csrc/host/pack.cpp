@@ -651,6 +651,38 @@ int arph_pack(const arp_atom_record* atoms, int64_t n, const char* groups, int i
   *out = h;
   return ARP_OK;
 }
+/* Many independent structures at once (BASELINE config 4: 10 000 complexes): one structure per host thread, each packed
+ * exactly like arph_pack does it (the parallel regions inside a pack run serially here: no nested teams). */
+int arph_pack_many(const arp_atom_record* const* atoms, const int64_t* n, int64_t count, const char* groups, int ignore_zero_occupancy,
+                   uint32_t flags, arph_packed** out) {
+  arp::NvtxRange nvtx_("arph:pack_many");
+  if (count < 0 || (count > 0 && (!atoms || !n || !out))) {
+    arp::last_error() = "arph_pack_many: null argument";
+    return ARP_ERR_ARG;
+  }
+  for (int64_t k = 0; k < count; ++k) out[k] = nullptr;
+  int first_rc = ARP_OK;
+  int64_t first_bad = -1;
+  std::string first_msg;
+#pragma omp parallel for schedule(dynamic, 4)
+  for (int64_t k = 0; k < count; ++k) {
+    arph_packed* h = nullptr;
+    const int rc = arph_pack(atoms[k], n[k], groups, ignore_zero_occupancy, flags, &h);
+    out[k] = h;
+    if (rc != ARP_OK) {
+#pragma omp critical(arph_pack_many_error)
+      if (first_bad < 0 || k < first_bad) first_bad = k, first_rc = rc, first_msg = arp::last_error();  // this thread's message
+    }
+  }
+  if (first_rc != ARP_OK) {
+    for (int64_t k = 0; k < count; ++k) {
+      delete out[k];
+      out[k] = nullptr;
+    }
+    arp::last_error() = "structure " + std::to_string(first_bad) + ": " + first_msg;
+  }
+  return first_rc;
+}
 const arp_structure* arph_packed_structure(const arph_packed* p) { return &p->p.s; }
 int64_t arph_packed_n_warnings(const arph_packed* p) { return (int64_t)p->p.warnings.size(); }
 const char* arph_packed_warning(const arph_packed* p, int64_t i) { return p->p.warnings[(size_t)i].c_str(); }

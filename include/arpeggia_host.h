@@ -85,6 +85,10 @@ void arph_free(void* p);
 typedef struct arph_packed arph_packed;
 int  arph_pack(const arp_atom_record* atoms, int64_t n, const char* groups, int ignore_zero_occupancy,
                uint32_t flags, arph_packed** out);
+/* count independent structures, one per host thread (BASELINE config 4); out[count].  On failure every out[k] is NULL and
+ * the message names the first structure that failed. */
+int  arph_pack_many(const arp_atom_record* const* atoms, const int64_t* n, int64_t count, const char* groups,
+                    int ignore_zero_occupancy, uint32_t flags, arph_packed** out);
 const arp_structure* arph_packed_structure(const arph_packed* p);
 int64_t arph_packed_n_warnings(const arph_packed* p);           /* ring residues with < 3 ring atoms (mod.rs:64-68) */
 const char* arph_packed_warning(const arph_packed* p, int64_t i);
