@@ -90,6 +90,7 @@ class Stats(C.Structure):
         ("ms_h2d", C.c_float), ("ms_grid", C.c_float), ("ms_pairs", C.c_float), ("ms_rings", C.c_float),
         ("ms_d2h", C.c_float), ("ms_run", C.c_float),
         ("ms_screen", C.c_float), ("ms_filter", C.c_float), ("ms_exact", C.c_float), ("reserved2_", C.c_float),
+        ("ms_wall_upload", C.c_float), ("ms_wall_run", C.c_float), ("ms_wall_download", C.c_float), ("ms_wall_call", C.c_float),
     ]
 
 

@@ -1,6 +1,7 @@
 // C ABI of the device path (include/arpeggia_cuda.h): context, staged upload / run / download, one-shot calls.
 // sm_100a only; every kernel of the job is launched on the context's own stream.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -197,6 +198,7 @@ struct arp_ctx {
 
   // bookkeeping of the last run
   bool have_job = false, have_run = false;
+  bool settled = false;  // the last run has been waited for and its counters checked (settle_run)
   arp_params last_params{};
   DevParams dp{};
   cudaEvent_t ev[13] = {};  // timing marks (recorded as external event nodes inside a capture: still readable after a replay)
@@ -208,6 +210,7 @@ struct arp_ctx {
   int64_t launches = 0;
   int retries = 0;
   float ms_h2d = 0.f, ms_d2h = 0.f;
+  float ms_wall[4] = {0.f, 0.f, 0.f, 0.f};  // one-shot call: upload, run, download, whole call (host wall clock)
 };
 
 namespace {

@@ -357,7 +357,8 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
     torch.cuda.set_device(local)
-    binding = bind_to_gpu_cores(local, world) if world > 1 else None
+    # pinning the ranks to cores next to their GPU made no difference on these boxes (one NUMA node; profiles/r2b_e2e_phases_*): opt-in
+    binding = bind_to_gpu_cores(local, world) if world > 1 and os.environ.get("ARP_BENCH_BIND") else None
     if world > 1:
         # NCCL announces its version on stdout when the communicator comes up; the contract is ONE json line there
         sys.stdout.flush()
@@ -482,6 +483,9 @@ def main():
     e2e_value = world * pairs / (float(e2e_t.item()) * 1e-3)
 
     st = ctx.stats()  # of the last end-to-end call
+    # every rank's phases of that call: host wall clock (arp_stats.ms_wall_*) beside the device times inside them
+    e2e_keys = ("ms_wall_call", "ms_wall_upload", "ms_h2d", "ms_wall_run", "ms_run", "ms_wall_download", "ms_d2h")
+    e2e_ranks = reduce_records({k: st[k] for k in e2e_keys}, world, f"cuda:{local}")
 
     # ---- the same call from several host threads, one context (= one stream) each: job i+1's upload, job i's kernels and
     # job i-1's row download run on the copy engines and the SMs at the same time (a side figure; `e2e` is the serial call)
@@ -732,6 +736,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "ms_per_step": float(e2e_t.item()), "ms_h2d": st["ms_h2d"], "ms_run": st["ms_run"], "ms_d2h": st["ms_d2h"],
                     "ms_host_other_rank0": e2e_ms - st["ms_h2d"] - st["ms_run"] - st["ms_d2h"], "calls": e2e_steps, "cpu_binding": binding,
+                    "last_call_per_rank": {k: [round(float(v), 4) for v in e2e_ranks[k]] for k in e2e_keys},
                     "api": "arp_contacts (C ABI, pinned host SoA in, host rows out)"},
             "e2e_concurrent": e2e_conc,
             "frame": frame_info,

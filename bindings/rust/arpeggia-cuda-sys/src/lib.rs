@@ -130,6 +130,10 @@ pub struct arp_stats {
     pub ms_filter: f32,
     pub ms_exact: f32,
     pub reserved2_: f32,
+    pub ms_wall_upload: f32,
+    pub ms_wall_run: f32,
+    pub ms_wall_download: f32,
+    pub ms_wall_call: f32,
 }
 
 #[repr(C)]

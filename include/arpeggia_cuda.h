@@ -190,6 +190,10 @@ typedef struct arp_stats {
   int64_t n_filtered_pairs;       /* entries of the second pair queue (k_filter -> k_exact) */
   float ms_h2d, ms_grid, ms_pairs, ms_rings, ms_d2h, ms_run; /* ms_run = the whole job; ms_rings overlaps ms_pairs (side stream) */
   float ms_screen, ms_filter, ms_exact, reserved2_;          /* the three kernels of ms_pairs */
+  /* host wall clock of the phases of the last one-shot call (arp_contacts / arp_contacts_batch), each from its first API
+   * call to the return of its last synchronisation: upload, run (enqueue + wait for the counters), download.  Their sum
+   * minus ms_h2d + ms_run + ms_d2h is host overhead (submission, wake-ups after a synchronisation). */
+  float ms_wall_upload, ms_wall_run, ms_wall_download, ms_wall_call;
 } arp_stats;
 
 typedef struct arp_ctx arp_ctx;

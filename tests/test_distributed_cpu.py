@@ -108,3 +108,107 @@ def test_slab_bounds_balance():
     b = D.slab_bounds(x, 4)
     counts = [int(((x >= b[r]) & (x < b[r + 1])).sum()) for r in range(4)]
     assert sum(counts) == 1001 and max(counts) - min(counts) <= 1
+
+
+# ---- the slab path that runs behind the C ABI: what every rank hands to arp_stage_upload (host logic, no GPU) ----------
+def _tag_property_holds(a):
+    """|tag difference| <= 1  <=>  same chain and residue ordinals at most 1 apart, checked on neighbouring residues and on
+    a sample of random residue pairs."""
+    t = a["res_tag"].astype(np.int64)
+    ck, ro = a["res_chain_key"].astype(np.int64), a["res_res_ordinal"].astype(np.int64)
+    rng = np.random.default_rng(0)
+    i = np.concatenate([np.arange(len(t) - 1), rng.integers(0, len(t), 4000)])
+    j = np.concatenate([np.arange(1, len(t)), rng.integers(0, len(t), 4000)])
+    close = (ck[i] == ck[j]) & (np.abs(ro[i] - ro[j]) <= 1)
+    return np.array_equal(np.abs(t[i] - t[j]) <= 1, close)
+
+
+def test_tiled_slab_packed_alone_matches_the_whole_tiling():
+    """pack_tiled_slab: a rank tiles and packs ONLY its x-slab; chain ranks, global ids and residue tags are those the whole
+    tiling gets when it is packed in one piece."""
+    from arpeggia_b200 import synth
+
+    bft = A.parse_pdb(os.path.join(ROOT, "tests", "data", "6bft.pdb"))
+    nx, ny, nz, world = 4, 1, 2, 3  # uneven split of the x-indices: 1 + 1 + 2
+    whole = A.Packed(synth.tile(bft, nx, ny, nz), "/", flags=2).arrays()
+    assert _tag_property_holds(whole)
+    seen_atoms, seen_rings = [], []
+    for rank in range(world):
+        a = D.pack_tiled_slab(bft, nx, ny, nz, rank, world).arrays()
+        g, rg = a["atom_gid"], a["ring_gid"]
+        for k in ("x", "y", "z", "attr", "chain_key", "res_ordinal"):
+            assert np.array_equal(a[k], whole[k][g]), (rank, k)
+        for k in ("ring_center", "ring_normal", "ring_attr", "ring_chain_key", "ring_res_ordinal"):
+            assert np.array_equal(a[k], whole[k][rg]), (rank, k)
+        # the tags are the whole tiling's up to one constant per copy, which keeps the property across ranks
+        assert _tag_property_holds(a)
+        first_res = a["res_id"][np.searchsorted(g, g)]  # identity; residues of a slab keep their order
+        assert np.array_equal(first_res, a["res_id"])
+        seen_atoms.append(g)
+        seen_rings.append(rg)
+    assert np.array_equal(np.sort(np.concatenate(seen_atoms)), np.arange(whole["n_atoms"]))
+    assert np.array_equal(np.sort(np.concatenate(seen_rings)), np.arange(whole["n_rings"]))
+    # tags of different ranks never collide into a false neighbourhood: compare across two slabs
+    a0, a1 = D.pack_tiled_slab(bft, nx, ny, nz, 0, world).arrays(), D.pack_tiled_slab(bft, nx, ny, nz, 2, world).arrays()
+    d = np.abs(a0["res_tag"].astype(np.int64)[:, None][:200] - a1["res_tag"].astype(np.int64)[None, :200])
+    assert d.min() > 1
+
+
+def test_cut_slab_partitions_a_packed_structure():
+    """cut_slab: whole residues, every atom / ring owned by exactly one rank, indices rebased, ids and tags global."""
+    bft = A.parse_pdb(os.path.join(ROOT, "tests", "data", "6bft.pdb"))
+    whole = A.Packed(bft).arrays()
+    for world in (1, 2, 5):
+        atoms, rings = [], []
+        for rank in range(world):
+            o = D.cut_slab(whole, rank, world)
+            g = np.asarray(o["atom_gid"])
+            assert np.array_equal(o["x"], whole["x"][g]) and np.array_equal(o["attr"], whole["attr"][g])
+            rab = np.asarray(o["res_atom_begin"])
+            assert rab[0] == 0 and rab[-1] == len(g) and (np.diff(rab) >= 0).all()
+            rid = np.repeat(np.arange(len(rab) - 1), np.diff(rab))
+            assert np.array_equal(np.asarray(o["res_tag"])[rid], whole["res_tag"][whole["res_id"][g]])  # residues stay whole
+            for k in ("res_cb", "res_sg"):
+                v = np.asarray(o[k])
+                ok = v >= 0
+                assert (rid[v[ok]] == np.nonzero(ok)[0]).all()  # the CB / SG of a residue is one of its own atoms
+            hb = np.asarray(o["res_h_begin"])
+            assert hb[0] == 0 and hb[-1] == len(o["h_x"])
+            S = D.ArrayStructure(o)  # the arp_structure handed to arp_stage_upload
+            assert (S.struct.n_atoms, S.struct.n_rings) == (len(g), len(o["ring_gid"])) and bool(S.struct.res_tag) and bool(S.struct.atom_gid)
+            atoms.append(g)
+            rings.append(np.asarray(o["ring_gid"]))
+        assert np.array_equal(np.sort(np.concatenate(atoms)), np.arange(whole["n_atoms"]))
+        assert np.array_equal(np.sort(np.concatenate(rings)), np.arange(whole["n_rings"]))
+
+
+def _comm_id_worker(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import ctypes as C
+
+        from arpeggia_b200 import _lib
+
+        # what SlabRank does before arp_ctx_comm_init: rank 0's 128 bytes reach every rank (here a stand-in id: making a
+        # real one needs NCCL and a GPU)
+        cid = _lib.CommId()
+        if rank == 0:
+            C.memmove(C.addressof(cid), bytes(range(128)), 128)
+        box = [C.string_at(C.addressof(cid), 128) if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        C.memmove(C.addressof(cid), box[0], 128)
+        np.save(os.path.join(out_dir, f"id_{rank}.npy"), np.frombuffer(C.string_at(C.addressof(cid), 128), dtype=np.uint8))
+        xr = D.slab_x_range(16, rank, world)
+        np.save(os.path.join(out_dir, f"xr_{rank}.npy"), np.array(xr))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_comm_id_broadcast_and_x_ranges_gloo(tmp_path):
+    world = 2
+    mp.spawn(_comm_id_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    ids = [np.load(tmp_path / f"id_{r}.npy") for r in range(world)]
+    assert np.array_equal(ids[0], np.arange(128, dtype=np.uint8)) and np.array_equal(ids[0], ids[1])  # NUL bytes survive
+    xr = [np.load(tmp_path / f"xr_{r}.npy") for r in range(world)]
+    assert xr[0][0] == 0 and xr[0][1] == xr[1][0] and xr[1][1] == 16

@@ -160,6 +160,14 @@ def test_tiled_slab_packed_alone_equals_the_whole_assembly():
     rows = np.concatenate(rows)
     assert np.array_equal(np.sort(rows, order=KEY), np.sort(single["rows"], order=KEY))
     assert [i["n_peers"] for i in infos] == [1, 2, 2, 1]
+    # ... and against the ORACLE: the union of the ranks' rows (global ids = indices of the whole packed tiling), decoded and
+    # sorted by the host table, is the oracle's table of the whole assembly
+    from oracle import oracle as O
+    from tests.util import assert_tables_equal
+
+    atoms = synth.tile(bft, nx, ny, nz)
+    want = O.contacts(atoms.view(O.ATOM_DTYPE), "/", 0.1, 6.5, flags=O.FLAG_SKIP_LOAD_FILTER, num_threads=0)
+    assert_tables_equal(whole.build_table(rows), want, "4 slabs vs oracle")
     for cx in ctxs:
         cx.close()
 
