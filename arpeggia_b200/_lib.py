@@ -35,6 +35,7 @@ STATIC_MAX_ATOMS = 131072  # ARP_STATIC_MAX_ATOMS
 HOST_FLAG_NO_MULTIMODEL_QUIRK = 1
 HOST_FLAG_SKIP_LOAD_FILTER = 2
 HOST_FLAG_NO_COUNTERS = 4
+HOST_FLAG_DEVICE_COLUMNS = 8
 
 LABELS = [
     "StericClash", "CovalentBond", "Disulfide", "VanDerWaalsContact", "IonicBond", "HydrogenBond",
@@ -104,7 +105,8 @@ class Table(C.Structure):
            ("sc_valid", C.POINTER(C.c_uint8)), ("n_strings", C.c_int32), ("strings", C.POINTER(C.c_char_p)),
            ("n_atoms", C.c_int64), ("pairs_in_cutoff", C.c_int64), ("pairs_classified", C.c_int64),
            ("t_setup_s", C.c_double), ("t_search_s", C.c_double), ("t_classify_s", C.c_double),
-           ("t_rings_s", C.c_double), ("t_table_s", C.c_double)]
+           ("t_rings_s", C.c_double), ("t_table_s", C.c_double),
+           ("sc_validity", C.POINTER(C.c_uint8)), ("sc_null_count", C.c_int64)]
     )
 
 
@@ -185,6 +187,9 @@ SIGNATURES = {
     "arp_stage_neighbor_sum": (C.c_int, [_P, _P, _P, C.c_float, _P]),
     "arp_neighbor_sum_stats": (C.c_int, [_P, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_int64)]),
     "arp_stage_frame": (C.c_int, [_P, C.POINTER(FrameTables), C.POINTER(C.POINTER(Frame))]),
+    "arp_stage_frame_compact": (C.c_int, [_P, C.POINTER(FrameTables), C.POINTER(C.POINTER(Frame))]),
+    "arp_contacts_frame_compact": (C.c_int, [_P, C.POINTER(Structure), C.POINTER(Params), C.POINTER(FrameTables),
+                                             C.POINTER(C.POINTER(Frame))]),
     "arp_contacts_frame": (C.c_int, [_P, C.POINTER(Structure), C.POINTER(Params), C.POINTER(FrameTables),
                                      C.POINTER(C.POINTER(Frame))]),
     "arp_frame_free": (None, [_P, C.POINTER(Frame)]),

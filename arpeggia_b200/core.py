@@ -197,6 +197,8 @@ def read_table(t: Table) -> dict:
             v = arr(getattr(t, f"{side}_{c}"), np.int32)
             out[f"{side}_{c}"] = strings[v] if c in STRING_COLS else v
     out["sc_valid"] = arr(t.sc_valid, np.uint8).astype(bool)
+    out["sc_validity_bits"] = np.ctypeslib.as_array(t.sc_validity, shape=((n + 7) // 8,)).copy() if n else np.zeros(0, dtype=np.uint8)
+    out["sc_null_count"] = int(t.sc_null_count)
     for c in ("sc_centroid_dist", "sc_dihedral", "sc_centroid_angle"):
         out[c] = arr(getattr(t, c), np.float32)
     for c in ("n_atoms", "pairs_in_cutoff", "pairs_classified", "t_setup_s", "t_classify_s", "t_table_s"):
@@ -244,10 +246,9 @@ def table_to_arrow(tp, strings: str = "string"):
         return a if strings == "dictionary" else a.dictionary_decode()
 
     bitmap, n_null = None, 0
-    if n:
-        valid = np.ctypeslib.as_array(t.sc_valid, shape=(n,)) != 0
-        n_null = int(n - np.count_nonzero(valid))
-        bitmap = pa.py_buffer(np.packbits(valid, bitorder="little").tobytes())
+    if n:  # the library hands the validity of the sc_* columns over in Arrow's own layout
+        n_null = int(t.sc_null_count)
+        bitmap = pa.foreign_buffer(C.addressof(t.sc_validity.contents), (n + 7) // 8, base=owner)
     cols = []
     for name in COLUMNS:
         if name == "model":
@@ -355,14 +356,16 @@ class Context:
         finally:
             L.arp_result_free(self._h, rp)
 
-    def frame(self, packed: "Packed", arrow: str | None = None):
-        """arp_stage_frame after run(): sort + decode + sc join on the device -> the table of get_contacts, plus the
-        device timings of the frame stage under "frame_stats"."""
+    def frame(self, packed: "Packed", arrow: str | None = None, device_columns: bool = False):
+        """arp_stage_frame_compact after run(): sort + sc join on the device, 26 bytes per row back, the per-entity columns
+        gathered by arph_table_from_frame on the host's threads -> the table of get_contacts, plus the device timings of
+        the frame stage under "frame_stats".  device_columns=True: arp_stage_frame (every column decoded on the device,
+        86 bytes per row back)."""
         L = lib()
         tp = C.POINTER(FrameTables)()
         check(L.arph_packed_frame_tables(packed._h, C.byref(tp)))
         fp = C.POINTER(Frame)()
-        check(L.arp_stage_frame(self._h, tp, C.byref(fp)), self._h)
+        check((L.arp_stage_frame if device_columns else L.arp_stage_frame_compact)(self._h, tp, C.byref(fp)), self._h)
         fs = {k: getattr(fp.contents, k) for k in ("ms_sort", "ms_columns", "ms_d2h", "sort_passes", "key_bits")}
         tb = C.POINTER(Table)()
         check(L.arph_table_from_frame(packed._h, fp, C.byref(tb)))  # owns the frame from here on

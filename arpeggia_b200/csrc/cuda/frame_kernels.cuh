@@ -39,7 +39,7 @@ struct FrameArgs {
 };
 
 struct FrameOut {  // device pointers into one block, same layout as the pinned host block
-  uint32_t* model;
+  uint32_t* model;  // NULL (with col[]) in the compact frame: the fifteen per-entity columns stay on the host's side
   uint8_t* interaction;
   float* distance;
   int32_t* col[14];
@@ -202,15 +202,17 @@ __global__ void __launch_bounds__(256) k_frame_columns(const FrameArgs A, const 
     const uint4 a = p[0], b = p[1];
     S[s].chain = (int32_t)a.x, S[s].resn = (int32_t)a.y, S[s].resi = (int32_t)a.z, S[s].icode = (int32_t)a.w;
     S[s].altloc = (int32_t)b.x, S[s].model = b.y, S[s].chain_rank = b.z, S[s].has_sc = b.w;
-    O.col[7 * s + 0][k] = S[s].chain;
-    O.col[7 * s + 1][k] = S[s].resn;
-    O.col[7 * s + 2][k] = S[s].resi;
-    O.col[7 * s + 3][k] = S[s].icode;
-    O.col[7 * s + 4][k] = S[s].altloc;
-    O.col[7 * s + 5][k] = A.ent_atomn[e2[s]];
-    O.col[7 * s + 6][k] = A.ent_atomi[e2[s]];
+    if (O.model) {
+      O.col[7 * s + 0][k] = S[s].chain;
+      O.col[7 * s + 1][k] = S[s].resn;
+      O.col[7 * s + 2][k] = S[s].resi;
+      O.col[7 * s + 3][k] = S[s].icode;
+      O.col[7 * s + 4][k] = S[s].altloc;
+      O.col[7 * s + 5][k] = A.ent_atomn[e2[s]];
+      O.col[7 * s + 6][k] = A.ent_atomi[e2[s]];
+    }
   }
-  O.model[k] = S[0].model;
+  if (O.model) O.model[k] = S[0].model;
   // complex.rs:152-161: statistics exist iff both residues have a side-chain plane
   const float qnan = __int_as_float(0x7fc00000);
   float scd = qnan, sch = qnan, sca = qnan;

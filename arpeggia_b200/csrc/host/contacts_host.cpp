@@ -27,21 +27,23 @@ int arph_contacts(arp_ctx* ctx, const arp_atom_record* atoms, int64_t n, const c
   prm.dist_cutoff = dist_cutoff;
   // the table reports both workload counters, unless the caller only wants the frame the reference returns
   prm.flags = (flags & ARPH_FLAG_NO_COUNTERS) ? ARP_FLAG_EMIT_RADIUS_SCREEN : ARP_FLAG_COUNT_CLASSIFIED;
-  // rows stay on the device: sorted, decoded and joined there (arp_stage_frame), only the columns come back
+  // rows stay on the device: sorted and joined there (arp_stage_frame_compact); 26 bytes per row come back and the
+  // per-entity columns are gathered from the side tables on the host's threads (ARPH_FLAG_DEVICE_COLUMNS: on the device)
   arp::FrameTables ft;
   arp_frame* frame = nullptr;
   double t2 = t1, t3 = t1;
   try {
     arp::build_frame_tables(arph_packed_ref(pk), ft);
     t2 = now_s();
-    rc = arp_contacts_frame(ctx, arph_packed_structure(pk), &prm, &ft.t, &frame);
+    rc = (flags & ARPH_FLAG_DEVICE_COLUMNS) ? arp_contacts_frame(ctx, arph_packed_structure(pk), &prm, &ft.t, &frame)
+                                            : arp_contacts_frame_compact(ctx, arph_packed_structure(pk), &prm, &ft.t, &frame);
     if (rc != ARP_OK) {
       arp::last_error() = arp_last_error(ctx);
       arph_packed_free(pk);
       return rc;
     }
     t3 = now_s();
-    *out = arp::table_from_frame(arph_packed_ref(pk), frame);
+    *out = arp::table_from_frame(arph_packed_ref(pk), frame, &ft.t);
     frame = nullptr;
     (*out)->t_setup_s = t2 - t0;
     (*out)->t_classify_s = t3 - t2;

@@ -782,3 +782,4 @@ int arph_parse_groups(const char* chains_csv, const char* groups, char* ligand_o
 }
 
 const arp::Packed& arph_packed_ref(const arph_packed* p) { return p->p; }
+const arp_frame_tables* arph_packed_cached_frame_tables(const arph_packed* p) { return p->have_frame_tables ? &p->frame_tables.t : nullptr; }

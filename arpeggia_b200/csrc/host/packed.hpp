@@ -61,9 +61,12 @@ struct FrameTables {
   std::vector<int32_t> ent_atomn, ent_atomi;
 };
 void build_frame_tables(const Packed& p, FrameTables& out);
-arph_table* table_from_frame(const Packed& p, arp_frame* f);  // takes ownership of f (released by arph_table_free)
+// takes ownership of f (released by arph_table_free); t = the frame tables of p if the caller has them (a compact frame's
+// per-entity columns are gathered through them; built here when NULL)
+arph_table* table_from_frame(const Packed& p, arp_frame* f, const arp_frame_tables* t = nullptr);
 
 }  // namespace arp
 
 struct arph_packed;
 const arp::Packed& arph_packed_ref(const arph_packed* p);
+const arp_frame_tables* arph_packed_cached_frame_tables(const arph_packed* p);  // NULL until arph_packed_frame_tables built them

@@ -6,7 +6,9 @@
 // integer ranks of the dictionary strings, so no string is compared or materialised per row.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <numeric>
 #include <vector>
 
@@ -14,9 +16,52 @@
 
 namespace arp {
 
+// Process-wide pool of column blocks for tables gathered on the host (table_from_frame on a compact frame): a fresh
+// 50 MB allocation pays its page faults on every call, a block that went round once does not.
+struct ColumnBlock {
+  unsigned char* p = nullptr;
+  size_t cap = 0;
+};
+namespace {
+std::mutex g_block_mu;
+std::vector<ColumnBlock> g_blocks;
+ColumnBlock block_acquire(size_t bytes) {
+  {
+    std::lock_guard<std::mutex> g(g_block_mu);
+    int best = -1;
+    for (int k = 0; k < (int)g_blocks.size(); ++k)
+      if (g_blocks[k].cap >= bytes && (best < 0 || g_blocks[k].cap < g_blocks[best].cap)) best = k;
+    if (best >= 0) {
+      ColumnBlock b = g_blocks[best];
+      g_blocks.erase(g_blocks.begin() + best);
+      return b;
+    }
+  }
+  ColumnBlock b;
+  b.cap = bytes + bytes / 8 + 4096;
+  b.p = static_cast<unsigned char*>(std::aligned_alloc(256, (b.cap + 255) / 256 * 256));
+  if (!b.p) throw Error{ARP_ERR_OOM, "out of host memory for the table's columns"};
+  return b;
+}
+void block_release(ColumnBlock b) {
+  if (!b.p) return;
+  {
+    std::lock_guard<std::mutex> g(g_block_mu);
+    if (g_blocks.size() < 2) {
+      g_blocks.push_back(b);
+      return;
+    }
+  }
+  std::free(b.p);
+}
+}  // namespace
+
 struct TableStore {
   arph_table t{};  // must stay the first member (arph_table_free casts back)
   arp_frame* frame = nullptr;  // device-built tables borrow the frame's page-locked columns
+  ColumnBlock block;           // ... and hold the columns gathered on the host (compact frames) + the validity bitmap
+  std::vector<uint8_t> validity;
+  ~TableStore() { block_release(block); }
   std::vector<uint32_t> model;
   std::vector<uint8_t> interaction, sc_valid;
   std::vector<float> distance, scd, sch, sca;
@@ -282,6 +327,12 @@ arph_table* build_table(const Packed& P, const arp_row* rows, int64_t n) {
   t.sc_dihedral = T->sch.data();
   t.sc_centroid_angle = T->sca.data();
   t.sc_valid = T->sc_valid.data();
+  T->validity.assign((size_t)(n + 7) / 8, 0);
+  for (int64_t k = 0; k < n; ++k) {
+    if (T->sc_valid[k]) T->validity[k >> 3] |= (uint8_t)(1u << (k & 7));
+    else t.sc_null_count += 1;
+  }
+  t.sc_validity = T->validity.data();
   for (auto& s : T->strings) T->cstrs.push_back(s.c_str());
   t.n_strings = (int32_t)T->cstrs.size();
   t.strings = T->cstrs.data();
@@ -292,40 +343,108 @@ arph_table* build_table(const Packed& P, const arp_row* rows, int64_t n) {
 // A frame built on the device becomes the host table without copying a column: the table borrows the frame's
 // page-locked arrays.  Rows the device marked sc_valid = 2 (an angle too close to an f32 rounding boundary for the
 // device's acos, or NaN) are recomputed with the host libm, so the sc_* columns carry the same bits as build_table's.
-arph_table* table_from_frame(const Packed& P, arp_frame* f) {
+// A COMPACT frame (arp_stage_frame_compact: no model / from_* / to_* columns) gets those fifteen columns here: pure
+// gathers entity -> side -> field through the frame tables, rows split over the host's threads (mod.rs:140-181 builds
+// the same columns from its row structs).  One pass does all of it, plus the Arrow validity bitmap of the sc_* columns.
+arph_table* table_from_frame(const Packed& P, arp_frame* f, const arp_frame_tables* ft) {
   auto* T = new TableStore();
   try {
     T->strings = P.strings;
-    const int64_t n = f->n_rows, n_atoms = (int64_t)P.x.size();
-    for (int64_t k = 0; k < n; ++k) {
-      if (f->sc_valid[k] != 2) continue;
-      auto rc_of = [&](uint32_t v) { return (v & ARP_RING_FLAG) ? P.ring_rc[v & ~ARP_RING_FLAG] : P.atom_rc[v]; };
-      if (((f->from[k] & ARP_RING_FLAG) ? (int64_t)(f->from[k] & ~ARP_RING_FLAG) >= (int64_t)P.ring_rc.size() : (int64_t)f->from[k] >= n_atoms) ||
-          ((f->to[k] & ARP_RING_FLAG) ? (int64_t)(f->to[k] & ~ARP_RING_FLAG) >= (int64_t)P.ring_rc.size() : (int64_t)f->to[k] >= n_atoms))
-        throw Error{ARP_ERR_ARG, "frame row references an entity outside the structure"};
-      const Packed::ResConf& a = P.resconfs[rc_of(f->from[k])];
-      const Packed::ResConf& b = P.resconfs[rc_of(f->to[k])];
-      f->sc_dihedral[k] = (float)plane_dihedral(a.sc.n, b.sc.n);
-      f->sc_centroid_angle[k] = (float)plane_point_angle(a.sc, b.sc.c);
-      f->sc_valid[k] = 1;
+    const int64_t n = f->n_rows, n_atoms = (int64_t)P.x.size(), n_rings = (int64_t)P.ring_rc.size();
+    const bool compact = !f->from_chain;
+    FrameTables local;
+    if (compact && n > 0 && !ft) {
+      build_frame_tables(P, local);
+      ft = &local.t;
     }
-    // null statistics carry the same quiet-NaN bits as build_table's (the validity column says they are null)
-    for (int64_t k = 0; k < n; ++k)
-      if (!f->sc_valid[k]) f->sc_centroid_dist[k] = f->sc_dihedral[k] = f->sc_centroid_angle[k] = std::nanf("");
+    if (compact && n > 0 && (ft->n_atoms != n_atoms || ft->n_rings != n_rings || !ft->ent_atomn || !ft->ent_atomi))
+      throw Error{ARP_ERR_ARG, "frame tables do not describe this structure"};
+    // one block: [15 gathered columns] + validity bitmap, every section 256-byte aligned
+    const size_t col_bytes = ((size_t)n * 4 + 255) / 256 * 256, map_bytes = ((size_t)(n + 7) / 8 + 255) / 256 * 256;
+    T->block = block_acquire((compact ? 15 * col_bytes : 0) + map_bytes + 256);
+    unsigned char* base = T->block.p;
+    uint32_t* model = f->model;
+    int32_t* col[14] = {f->from_chain, f->from_resn, f->from_resi, f->from_insertion, f->from_altloc, f->from_atomn, f->from_atomi,
+                        f->to_chain,   f->to_resn,   f->to_resi,   f->to_insertion,   f->to_altloc,   f->to_atomn,   f->to_atomi};
+    if (compact) {
+      model = reinterpret_cast<uint32_t*>(base);
+      for (int k = 0; k < 14; ++k) col[k] = reinterpret_cast<int32_t*>(base + (size_t)(k + 1) * col_bytes);
+      base += 15 * col_bytes;
+    }
+    uint8_t* bitmap = base;
+    constexpr int64_t kChunk = 8192;  // a multiple of 8: every chunk owns whole bitmap bytes
+    const int64_t n_chunks = (n + kChunk - 1) / kChunk;
+    int64_t nulls = 0;
+    int bad = 0;
+#pragma omp parallel for schedule(static) reduction(+ : nulls) reduction(| : bad) if (n > 4 * kChunk)
+    for (int64_t c = 0; c < n_chunks; ++c) {
+      const int64_t k0 = c * kChunk, k1 = std::min(n, k0 + kChunk);
+      for (int64_t k = k0; k < k1; ++k) {
+        const uint32_t v2[2] = {f->from[k], f->to[k]};
+        uint32_t rc[2];
+        bool ok = true;
+        for (int s = 0; s < 2; ++s) {
+          const uint32_t v = v2[s], i = v & ~ARP_RING_FLAG;
+          const bool ring = (v & ARP_RING_FLAG) != 0;
+          if (ring ? (int64_t)i >= n_rings : (int64_t)v >= n_atoms) {
+            ok = false;
+            break;
+          }
+          rc[s] = ring ? P.ring_rc[i] : P.atom_rc[v];
+          if (compact) {
+            const int64_t e = ring ? n_atoms + (int64_t)i : (int64_t)v;
+            const arp_frame_side& sd = ft->sides[rc[s]];
+            col[7 * s + 0][k] = sd.chain;
+            col[7 * s + 1][k] = sd.resn;
+            col[7 * s + 2][k] = sd.resi;
+            col[7 * s + 3][k] = sd.icode;
+            col[7 * s + 4][k] = sd.altloc;
+            col[7 * s + 5][k] = ft->ent_atomn[e];
+            col[7 * s + 6][k] = ft->ent_atomi[e];
+            if (s == 0) model[k] = sd.model;
+          }
+        }
+        if (!ok) {
+          bad |= 1;
+          continue;
+        }
+        if (f->sc_valid[k] == 2) {
+          const Packed::ResConf& a = P.resconfs[rc[0]];
+          const Packed::ResConf& b = P.resconfs[rc[1]];
+          f->sc_dihedral[k] = (float)plane_dihedral(a.sc.n, b.sc.n);
+          f->sc_centroid_angle[k] = (float)plane_point_angle(a.sc, b.sc.c);
+          f->sc_valid[k] = 1;
+        }
+        // null statistics carry the same quiet-NaN bits as build_table's (the validity column says they are null)
+        if (!f->sc_valid[k]) {
+          f->sc_centroid_dist[k] = f->sc_dihedral[k] = f->sc_centroid_angle[k] = std::nanf("");
+          nulls += 1;
+        }
+      }
+      for (int64_t k = k0; k < k1; k += 8) {
+        uint8_t byte = 0;
+        for (int64_t j = k; j < std::min(k1, k + 8); ++j) byte |= (uint8_t)((f->sc_valid[j] ? 1u : 0u) << (j - k));
+        bitmap[k >> 3] = byte;
+      }
+    }
+    if (bad) throw Error{ARP_ERR_ARG, "frame row references an entity outside the structure"};
+    arph_table& t = T->t;
+    t.n_rows = n;
+    t.model = model;
+    t.from_chain = col[0], t.from_resn = col[1], t.from_resi = col[2], t.from_insertion = col[3];
+    t.from_altloc = col[4], t.from_atomn = col[5], t.from_atomi = col[6];
+    t.to_chain = col[7], t.to_resn = col[8], t.to_resi = col[9], t.to_insertion = col[10];
+    t.to_altloc = col[11], t.to_atomn = col[12], t.to_atomi = col[13];
+    t.sc_validity = bitmap;
+    t.sc_null_count = nulls;
   } catch (...) {
     delete T;
     throw;
   }
   T->frame = f;
   arph_table& t = T->t;
-  t.n_rows = f->n_rows;
-  t.model = f->model;
   t.interaction = f->interaction;
   t.distance = f->distance;
-  t.from_chain = f->from_chain, t.from_resn = f->from_resn, t.from_resi = f->from_resi, t.from_insertion = f->from_insertion;
-  t.from_altloc = f->from_altloc, t.from_atomn = f->from_atomn, t.from_atomi = f->from_atomi;
-  t.to_chain = f->to_chain, t.to_resn = f->to_resn, t.to_resi = f->to_resi, t.to_insertion = f->to_insertion;
-  t.to_altloc = f->to_altloc, t.to_atomn = f->to_atomn, t.to_atomi = f->to_atomi;
   t.sc_centroid_dist = f->sc_centroid_dist;
   t.sc_dihedral = f->sc_dihedral;
   t.sc_centroid_angle = f->sc_centroid_angle;
@@ -365,7 +484,7 @@ int arph_table_from_frame(const arph_packed* p, arp_frame* f, arph_table** out) 
     return ARP_ERR_ARG;
   }
   try {
-    *out = arp::table_from_frame(arph_packed_ref(p), f);
+    *out = arp::table_from_frame(arph_packed_ref(p), f, arph_packed_cached_frame_tables(p));
     return ARP_OK;
   } catch (const arp::Error& e) {
     arp_frame_free(nullptr, f);

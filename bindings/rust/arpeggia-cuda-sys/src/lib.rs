@@ -257,6 +257,8 @@ extern "C" {
     pub fn arp_neighbor_sum_stats(ctx: *mut arp_ctx, ms_grid: *mut f32, ms_sum: *mut f32, n_cells: *mut i64) -> c_int;
     pub fn arp_stage_frame(ctx: *mut arp_ctx, t: *const arp_frame_tables, out: *mut *mut arp_frame) -> c_int;
     pub fn arp_contacts_frame(ctx: *mut arp_ctx, s: *const arp_structure, p: *const arp_params, t: *const arp_frame_tables, out: *mut *mut arp_frame) -> c_int;
+    pub fn arp_stage_frame_compact(ctx: *mut arp_ctx, t: *const arp_frame_tables, out: *mut *mut arp_frame) -> c_int;
+    pub fn arp_contacts_frame_compact(ctx: *mut arp_ctx, s: *const arp_structure, p: *const arp_params, t: *const arp_frame_tables, out: *mut *mut arp_frame) -> c_int;
     pub fn arp_frame_free(ctx: *mut arp_ctx, f: *mut arp_frame);
     pub fn arp_comm_get_id(out: *mut arp_comm_id) -> c_int;
     pub fn arp_ctx_comm_init(ctx: *mut arp_ctx, id: *const arp_comm_id, rank: c_int, world: c_int) -> c_int;

@@ -292,6 +292,13 @@ typedef struct arp_frame {
 int  arp_stage_frame(arp_ctx* ctx, const arp_frame_tables* t, arp_frame** out);
 /* One-shot: arp_stage_upload + arp_stage_run + arp_stage_frame. */
 int  arp_contacts_frame(arp_ctx* ctx, const arp_structure* s, const arp_params* p, const arp_frame_tables* t, arp_frame** out);
+/* The compact frame: the same sort, the same rows in the same order, but the fifteen per-entity columns (`model` and the
+ * fourteen from_ / to_ columns) are NULL and never leave the device -- they are pure gathers through `from` / `to`
+ * (entity -> side -> field) the host can do from the tables it built (arph_table_from_frame does, on the host's threads).
+ * What crosses PCIe is from, to, interaction, distance, the three sc_* and sc_valid: 26 bytes per row instead of 86;
+ * t->ent_atomn / t->ent_atomi may be NULL and are not uploaded.  Errors (narrowing, rows outside the tables) as above. */
+int  arp_stage_frame_compact(arp_ctx* ctx, const arp_frame_tables* t, arp_frame** out);
+int  arp_contacts_frame_compact(arp_ctx* ctx, const arp_structure* s, const arp_params* p, const arp_frame_tables* t, arp_frame** out);
 void arp_frame_free(arp_ctx* ctx, arp_frame* f); /* ctx may be NULL; the memory returns to a process-wide pool */
 
 /* ---- one assembly cut into x-slabs over several GPUs (BASELINE config 5) -------------------------------

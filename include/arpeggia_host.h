@@ -59,6 +59,8 @@ typedef struct arph_table {
   int64_t pairs_in_cutoff;
   int64_t pairs_classified;
   double  t_setup_s, t_search_s, t_classify_s, t_rings_s, t_table_s; /* pack, -, device run, -, table */
+  const uint8_t* sc_validity;      /* the same as sc_valid != 0, as a bitmap (bit k & 7 of byte k >> 3: Arrow's layout) */
+  int64_t sc_null_count;           /* rows with sc_valid == 0 */
 } arph_table;
 
 #define ARPH_FLAG_NO_MULTIMODEL_QUIRK 1u /* do NOT reproduce complex.rs:447-449 (planes of every model = last model's) */
@@ -66,6 +68,11 @@ typedef struct arph_table {
 #define ARPH_FLAG_NO_COUNTERS          4u /* arph_contacts: the caller only wants the frame (what get_contacts returns).  The
                                             device then screens at the emit radius (ARP_FLAG_EMIT_RADIUS_SCREEN) and the
                                             table's pairs_in_cutoff / pairs_classified are -1.  Rows are identical. */
+
+#define ARPH_FLAG_DEVICE_COLUMNS        8u /* arph_contacts: decode the fifteen per-entity columns on the device
+                                            (arp_contacts_frame, 86 bytes per row over PCIe) instead of gathering them on
+                                            the host from a compact frame (arp_contacts_frame_compact, 26 bytes per row).
+                                            The table is the same either way. */
 
 const char* arph_last_error(void);
 
@@ -104,7 +111,8 @@ int  arph_packed_set_global_ids(arph_packed* p, const uint32_t* atom_gid, const 
 /* The integer side tables arp_stage_frame / arp_contacts_frame need (dense sort ranks of the string keys, per-entity
  * and per-residue columns).  Built on first use, owned by the packed structure, valid until arph_packed_free. */
 int  arph_packed_frame_tables(arph_packed* p, const arp_frame_tables** out);
-/* Wrap a device-built frame as the host table (no column is copied; takes ownership of f, also on failure). */
+/* Wrap a device-built frame as the host table (no column is copied; takes ownership of f, also on failure).  A compact
+ * frame's model / from_* / to_* columns are gathered here (entity -> side -> field), rows split over the host's threads. */
 int  arph_table_from_frame(const arph_packed* p, arp_frame* f, arph_table** out);
 
 /* rows (structure-local atom / ring indices) -> sorted 20-column table. */

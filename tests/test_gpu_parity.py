@@ -228,26 +228,28 @@ def test_bounding_box_hint_is_verified(ctx, bft):
 
 
 # ---- the frame built on the device (arp_stage_frame) ------------------------------------------------
-def _staged_tables(ctx, atoms, flags=0, groups="/"):
+def _staged_tables(ctx, atoms, flags=0, groups="/", device_columns=False):
     """(frame built on the device, table built on the host from the same run's rows)"""
     p = A.Packed(atoms, groups, flags=flags)
     ctx.upload(p)
     ctx.run(0.1, 6.5, flags=2)
     host = p.build_table(ctx.download()["rows"])
-    dev = ctx.frame(p)
+    dev = ctx.frame(p, device_columns=device_columns)
     return dev, host, p
 
 
+@pytest.mark.parametrize("columns", ["host", "device"])
 @pytest.mark.parametrize("case", ["1ubq", "6bft", "altloc", "insertion", "two_models", "protonated"])
-def test_device_frame_equals_host_table(ctx, ubq, bft, case):
+def test_device_frame_equals_host_table(ctx, ubq, bft, case, columns):
     """Sort + decode + side-chain join on the device give the very frame results_to_df / collect_sc_stats / sort give on
-    the host (mod.rs:61-214): same order, same dictionary ids, same f32 bits."""
+    the host (mod.rs:61-214): same order, same dictionary ids, same f32 bits -- with the fifteen per-entity columns
+    decoded on the device (arp_stage_frame) or gathered by the host from the compact frame (arp_stage_frame_compact)."""
     from tests import fixtures as F
 
     atoms = {"1ubq": ubq, "6bft": bft}.get(case)
     if atoms is None:
         atoms = F.all_cases(ubq.view(O.ATOM_DTYPE))[case].view(A.ATOM_DTYPE)
-    dev, host, _ = _staged_tables(ctx, atoms)
+    dev, host, _ = _staged_tables(ctx, atoms, device_columns=columns == "device")
     assert_tables_equal(dev, host, case)
     assert np.array_equal(dev["interaction_code"], host["interaction_code"]) and np.array_equal(dev["model"], host["model"])
     fs = dev["frame_stats"]
@@ -284,9 +286,18 @@ def test_device_frame_1m_rows_sorted(ctx, bft):
     """Config 3 at full size: 0.9 M rows sorted on the device equal the host's comparator sort of the same rows."""
     from arpeggia_b200 import synth
 
-    dev, host, _ = _staged_tables(ctx, synth.assembly_1m(bft), flags=2)
+    dev, host, p = _staged_tables(ctx, synth.assembly_1m(bft), flags=2)
     assert dev["n_rows"] == host["n_rows"] > 900000
     assert_tables_equal(dev, host, "1M frame")
+    # the same rows with every column decoded on the device, and straight into Arrow (validity bitmap from the library)
+    full = ctx.frame(p, device_columns=True)
+    assert_tables_equal(full, host, "1M frame, device columns")
+    assert full["frame_stats"]["ms_d2h"] > dev["frame_stats"]["ms_d2h"]  # 86 vs 26 bytes per row
+    at, _ = ctx.frame(p, arrow="dictionary")
+    assert at.num_rows == host["n_rows"] and at["sc_dihedral"].null_count == int((~host["sc_valid"]).sum())
+    assert np.array_equal(at["from_atomi"].to_numpy(), host["from_atomi"]) and np.array_equal(at["to_resi"].to_numpy(), host["to_resi"])
+    valid = np.asarray(at["sc_centroid_dist"].is_valid())
+    assert np.array_equal(valid, host["sc_valid"])
 
 
 def test_frame_narrowing_error(ctx, ubq):

@@ -144,6 +144,9 @@ def test_table_builder_equals_oracle(which, ubq, bft):
     rows = rows_from_oracle_table(atoms, p, want)
     rng = np.random.default_rng(7)
     got = p.build_table(rows[rng.permutation(len(rows))])  # device rows arrive in arbitrary order
+    # the validity of the sc_* columns also comes as a bitmap in Arrow's layout
+    bits = np.unpackbits(got["sc_validity_bits"], bitorder="little")[: got["n_rows"]].astype(bool)
+    assert np.array_equal(bits, got["sc_valid"]) and got["sc_null_count"] == int((~got["sc_valid"]).sum())
     assert_tables_equal(got, want, which)
     at = A.to_arrow(got)
     assert at.column_names == A.COLUMNS and at.num_rows == want["n_rows"]
