@@ -86,7 +86,7 @@ class Stats(C.Structure):
     """arp_stats"""
     _fields_ = [
         ("n_atoms", C.c_int64), ("n_rings", C.c_int64), ("n_cells", C.c_int64), ("n_nonempty_cells", C.c_int64),
-        ("n_rows", C.c_int64), ("kernel_launches", C.c_int64), ("pair_kernel_retries", C.c_int32), ("reserved_", C.c_int32),
+        ("n_rows", C.c_int64), ("kernel_launches", C.c_int64), ("pair_kernel_retries", C.c_int32), ("upload_copies", C.c_int32),
         ("n_screened_pairs", C.c_int64), ("n_filtered_pairs", C.c_int64),
         ("ms_h2d", C.c_float), ("ms_grid", C.c_float), ("ms_pairs", C.c_float), ("ms_rings", C.c_float),
         ("ms_d2h", C.c_float), ("ms_run", C.c_float),

@@ -5,6 +5,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <functional>
 #include <string>
 #include <type_traits>
 #include <vector>
@@ -72,6 +73,14 @@ struct HBuf {
     p = nullptr;
     cap = 0;
   }
+};
+
+// one array of an upload that goes straight from the caller's memory to its device buffer
+struct UpItem {
+  const unsigned char* h;
+  unsigned char* d;
+  size_t bytes;
+  int after;  // 0 = nothing; 1 / 2: a kernel of the upload waits for this array (see flush_uploads)
 };
 
 }  // namespace
@@ -203,6 +212,11 @@ struct arp_ctx {
   DevParams dp{};
   cudaEvent_t ev[13] = {};  // timing marks (recorded as external event nodes inside a capture: still readable after a replay)
   cudaEvent_t udep[3] = {};  // upload: fork / join edges to the side stream (the expand kernels run beside the copies)
+  std::vector<UpItem> up_items;  // an upload's direct copies, issued by flush_uploads (neighbours in host memory travel as one copy)
+  DBuf<unsigned char> up_arena;  // landing area of such merged copies; k_scatter_segments moves the arrays to their buffers
+  int up_copies = 0;             // H2D copies the last upload issued for its arrays (after merging)
+  std::function<void(int)> up_after;  // the running upload's kernels that wait for a marked array
+  bool h2d_pending = false;      // a one-shot call left the upload's end un-waited: ms_h2d is read once the run has settled
   HBuf<uint32_t> h_words;   // page-locked single words of an upload (CSR closing entries)
   HBuf<StructDesc> h_descs_up;  // page-locked source of the upload's descriptor copy
   cudaEvent_t dep[3] = {};  // fork / join edges between the main and the side stream (plain records: captured as dependencies)
@@ -237,6 +251,129 @@ int guarded(arp_ctx* c, F&& f) {
   }
 }
 
+// Issue the queued direct copies of an upload.  Arrays that follow one another in the caller's memory (less than a page
+// apart: the arrays of one arena) travel as ONE copy into c->up_arena and are moved to their buffers by one kernel --
+// on this pool's boxes a 20 MB copy runs at 54 GB/s, the same bytes as five copies at 35-43 GB/s
+// (profiles/r2c_pcie_copy_rates.json).  The bytes between two such arrays are read too: they lie in pages that hold
+// the arrays' own first / last bytes, so they are mapped.  Copies go out in host-address order; `after(k)` is called
+// once the stream holds EVERY array marked k (the upload's expand kernels wait for exactly those).
+// Which allocation a host pointer belongs to, as far as a merged copy must know: pageable memory (the driver stages it
+// anyway), or page-locked memory with the extent of its allocation (one copy must not cross from one page-locked
+// allocation into the next: cudaMemcpyAsync refuses that).  Anything else -- device or managed memory, a failed query --
+// is `other` and never merged.
+struct HostSpan {
+  enum Kind { pageable, pinned, other } kind = other;
+  uintptr_t base = 0;
+  size_t size = 0;
+};
+HostSpan host_span_of(const void* p) {
+  HostSpan r;
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return r;
+  }
+  if (a.type == cudaMemoryTypeUnregistered) {
+    r.kind = HostSpan::pageable;
+    return r;
+  }
+  if (a.type != cudaMemoryTypeHost) return r;
+  using Query = int (*)(void*, int, unsigned long long);  // cuPointerGetAttribute
+  static Query query = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult st{};
+    if (cudaGetDriverEntryPoint("cuPointerGetAttribute", &f, cudaEnableDefault, &st) != cudaSuccess || st != cudaDriverEntryPointSuccess) {
+      cudaGetLastError();
+      f = nullptr;
+    }
+    return reinterpret_cast<Query>(f);
+  }();
+  if (!query) return r;
+  unsigned long long base = 0;
+  size_t size = 0;
+  const unsigned long long q = reinterpret_cast<uintptr_t>(p);
+  if (query(&base, 11 /* CU_POINTER_ATTRIBUTE_RANGE_START_ADDR */, q) != 0 || query(&size, 12 /* CU_POINTER_ATTRIBUTE_RANGE_SIZE */, q) != 0 || !size) return r;
+  r.kind = HostSpan::pinned;
+  r.base = (uintptr_t)base;
+  r.size = size;
+  return r;
+}
+
+template <class After>
+void flush_uploads_impl(arp_ctx* c, After&& after) {
+  std::vector<UpItem>& it = c->up_items;
+  if (it.empty()) return;
+  constexpr size_t kGap = 4096;
+  std::stable_sort(it.begin(), it.end(), [](const UpItem& a, const UpItem& b) { return a.h < b.h; });
+  int waiting[3] = {0, 0, 0};  // arrays a marked kernel still waits for
+  for (const UpItem& u : it) waiting[u.after] += 1;
+  // runs of neighbours, by host address
+  struct Run {
+    size_t first, last, span;
+  };
+  std::vector<Run> runs;
+  size_t arena = 0;
+  const auto words = [](const UpItem& u) { return (reinterpret_cast<uintptr_t>(u.h) & 3u) == 0 && (u.bytes & 3u) == 0; };  // k_scatter_segments moves 4-byte words
+  for (size_t k = 0; k < it.size();) {
+    size_t j = k;
+    HostSpan run_span;
+    bool have_span = false;
+    while (j + 1 < it.size() && j + 1 - k < (size_t)SEG_MAX && words(it[j]) && words(it[j + 1]) && it[j + 1].h >= it[j].h + it[j].bytes &&
+           (size_t)(it[j + 1].h - (it[j].h + it[j].bytes)) < kGap) {
+      if (!have_span) {
+        run_span = host_span_of(it[k].h);
+        have_span = true;
+      }
+      if (run_span.kind == HostSpan::other) break;
+      const uintptr_t next_end = reinterpret_cast<uintptr_t>(it[j + 1].h) + it[j + 1].bytes;
+      if (run_span.kind == HostSpan::pinned) {  // the next array must lie in the same page-locked allocation
+        if (next_end > run_span.base + run_span.size) break;
+      } else {  // pageable so far: the next one must be pageable too
+        if (host_span_of(it[j + 1].h).kind != HostSpan::pageable || host_span_of(reinterpret_cast<const void*>(next_end - 1)).kind != HostSpan::pageable) break;
+      }
+      ++j;
+    }
+    const size_t span = (size_t)(it[j].h + it[j].bytes - it[k].h);
+    runs.push_back(Run{k, j, span});
+    if (j > k) arena += (span + 255) / 256 * 256;
+    k = j + 1;
+  }
+  c->up_arena.need(std::max<size_t>(arena, 1));  // (grows between uploads only: a free here would wait for the device)
+  size_t at = 0;
+  for (const Run& r : runs) {
+    if (r.first == r.last) {
+      const UpItem& u = it[r.first];
+      CK(cudaMemcpyAsync(u.d, u.h, u.bytes, cudaMemcpyDefault, c->stream));
+    } else {
+      unsigned char* land = c->up_arena.p + at;
+      at += (r.span + 255) / 256 * 256;
+      CK(cudaMemcpyAsync(land, it[r.first].h, r.span, cudaMemcpyDefault, c->stream));
+      Segments S{};
+      size_t most = 0;
+      for (size_t k = r.first; k <= r.last; ++k) {
+        const UpItem& u = it[k];
+        S.src[S.n] = land + (u.h - it[r.first].h);
+        S.dst[S.n] = u.d;
+        S.bytes[S.n] = u.bytes;
+        most = std::max(most, u.bytes);
+        S.n += 1;
+      }
+      const unsigned bx = (unsigned)std::min<size_t>((most / 16 + 255) / 256 + 1, 4 * (size_t)c->sm_count);
+      k_scatter_segments<<<dim3(bx, (unsigned)S.n), 256, 0, c->stream>>>(S);
+      CK(cudaGetLastError());
+    }
+    c->up_copies += 1;
+    for (size_t k = r.first; k <= r.last; ++k)
+      if (it[k].after && --waiting[it[k].after] == 0) after(it[k].after);  // the last array that kernel waits for is on the stream
+  }
+  it.clear();
+}
+void flush_uploads(arp_ctx* c) {
+  flush_uploads_impl(c, [c](int k) {
+    if (c->up_after) c->up_after(k);
+  });
+}
+
 // Concatenate one array of every structure into device memory.  `adjust(s)` is added to every element of
 // structure s (index arrays that point into the concatenated job).  n == 1: straight from the caller's memory.
 template <class T, class GetPtr, class GetLen>
@@ -246,10 +383,12 @@ void upload_concat(arp_ctx* c, DBuf<T>& dst, const arp_structure* const* s, int6
   for (int64_t k = 0; k < n; ++k) total += (size_t)len(s[k]);
   dst.need(std::max<size_t>(total, 1));
   if (total == 0) return;
-  if (n == 1 && !adjust) {
-    if (len(s[0])) CK(cudaMemcpyAsync(dst.p, ptr(s[0]), (size_t)len(s[0]) * sizeof(T), cudaMemcpyDefault, c->stream));
+  if (n == 1 && !adjust) {  // queued: flush_uploads issues it, merged with its neighbours in host memory where it has any
+    if (len(s[0]))
+      c->up_items.push_back(UpItem{reinterpret_cast<const unsigned char*>(ptr(s[0])), reinterpret_cast<unsigned char*>(dst.p), (size_t)len(s[0]) * sizeof(T), 0});
     return;
   }
+  flush_uploads(c);  // the staged path below copies on the stream itself: keep the order
   // the staging buffer is reused by the next array: wait until the previous copy has left it
   CK(cudaStreamSynchronize(c->stream));
   c->stage.need(total * sizeof(T));
@@ -269,7 +408,7 @@ void upload_concat(arp_ctx* c, DBuf<T>& dst, const arp_structure* const* s, int6
   CK(cudaMemcpyAsync(dst.p, h, off * sizeof(T), cudaMemcpyDefault, c->stream));
 }
 
-void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
+void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n, bool one_shot = false) {
   arp::NvtxRange nvtx_("arp:upload");
   CK(cudaSetDevice(c->device));
   if (n < 1) throw arp::Error{ARP_ERR_ARG, "a job needs at least one structure"};
@@ -311,6 +450,30 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
   CK(cudaEventRecord(c->ev[0], c->stream));
   c->h_words.need(32);
   bool side_used = false;
+  c->up_items.clear();
+  c->up_copies = 0;
+  c->h2d_pending = false;
+  // the two expand kernels run on the side stream as soon as their input has arrived, beside the remaining copies
+  c->up_after = [&](int which) {
+    if (which == 1) {
+      CK(cudaEventRecord(c->udep[0], c->stream));
+      CK(cudaStreamWaitEvent(c->side, c->udep[0], 0));
+      k_expand_milli<<<(unsigned)((c->n_atoms + 255) / 256), 256, 0, c->side>>>(c->xm.p, c->ym.p, c->zm.p, (uint32_t)c->n_atoms, c->x.p, c->y.p, c->z.p);
+    } else {
+      CK(cudaEventRecord(c->udep[1], c->stream));
+      CK(cudaStreamWaitEvent(c->side, c->udep[1], 0));
+      k_expand_res_id<<<(unsigned)((c->n_atoms + 255) / 256), 256, 0, c->side>>>(c->res_atom_begin.p, (uint32_t)c->n_res, (uint32_t)c->n_atoms, c->res_id.p);
+    }
+    CK(cudaGetLastError());
+    side_used = true;
+  };
+  // a kernel that needs the array queued last: marked for flush_uploads, or launched now if the copy is already on the stream
+  const auto then_kernel = [&](size_t queued_before, int which) {
+    if (c->up_items.size() > queued_before)
+      for (size_t k = queued_before; k < c->up_items.size(); ++k) c->up_items[k].after = which;
+    else
+      c->up_after(which);
+  };
   auto nat = [](const arp_structure* t) { return t->n_atoms; };
   auto nrs = [](const arp_structure* t) { return t->n_residues; };
   auto nrg = [](const arp_structure* t) { return t->n_rings; };
@@ -321,17 +484,14 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
   for (int64_t k = 0; k < n; ++k)
     if (!s[k]->x_milli || !s[k]->y_milli || !s[k]->z_milli) milli = false;
   if (milli) {  // on-lattice coordinates: half the bytes over PCIe, f64 rebuilt here
-    UP(xm, x_milli, nat);
-    UP(ym, y_milli, nat);
-    UP(zm, z_milli, nat);
     c->x.need(c->n_atoms);
     c->y.need(c->n_atoms);
     c->z.need(c->n_atoms);
-    CK(cudaEventRecord(c->udep[0], c->stream));  // on the side stream: the next copies do not wait for the kernel
-    CK(cudaStreamWaitEvent(c->side, c->udep[0], 0));
-    k_expand_milli<<<(unsigned)((c->n_atoms + 255) / 256), 256, 0, c->side>>>(c->xm.p, c->ym.p, c->zm.p, (uint32_t)c->n_atoms, c->x.p, c->y.p, c->z.p);
-    CK(cudaGetLastError());
-    side_used = true;
+    const size_t q = c->up_items.size();
+    UP(xm, x_milli, nat);
+    UP(ym, y_milli, nat);
+    UP(zm, z_milli, nat);
+    then_kernel(q, 1);  // on the side stream: the next copies do not wait for the kernel
   } else {
     for (int64_t k = 0; k < n; ++k)
       if (s[k]->n_atoms > 0 && (!s[k]->x || !s[k]->y || !s[k]->z)) throw arp::Error{ARP_ERR_ARG, "structure has neither x / y / z nor x_milli / y_milli / z_milli"};
@@ -371,18 +531,13 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
   c->have_res_csr = expand_res_id;
   if (expand_res_id) {
     // like res_h_begin below: every structure contributes its first n_residues offsets, the tail closes the CSR
+    const size_t q = c->up_items.size();
     upload_concat(c, c->res_atom_begin, s, n, [](const arp_structure* t) { return t->res_atom_begin; }, nrs, 1, multi ? &atom_adj : nullptr, false);
     // the closing word comes from a page-locked slot of its own (nothing else writes it during this upload: no wait)
     c->h_words.p[0] = (uint32_t)c->n_atoms;
     CK(cudaMemcpyAsync(c->res_atom_begin.p + c->n_res, c->h_words.p, 4, cudaMemcpyDefault, c->stream));
     c->res_id.need(std::max<int64_t>(c->n_atoms, 1));
-    if (c->n_atoms > 0) {  // on the side stream: the copy engine keeps going underneath
-      CK(cudaEventRecord(c->udep[1], c->stream));
-      CK(cudaStreamWaitEvent(c->side, c->udep[1], 0));
-      k_expand_res_id<<<(unsigned)((c->n_atoms + 255) / 256), 256, 0, c->side>>>(c->res_atom_begin.p, (uint32_t)c->n_res, (uint32_t)c->n_atoms, c->res_id.p);
-      CK(cudaGetLastError());
-      side_used = true;
-    }
+    if (c->n_atoms > 0) then_kernel(q, 2);  // on the side stream: the copy engine keeps going underneath
   } else {
     for (int64_t k = 0; k < n; ++k)
       if (s[k]->n_atoms > 0 && !s[k]->res_id) throw arp::Error{ARP_ERR_ARG, "structure has neither res_id nor res_atom_begin"};
@@ -409,9 +564,9 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
   for (int64_t k = 0; k < n; ++k)
     if (s[k]->n_residues > 0 && !s[k]->res_tag) c->have_tag = false;
   bool derive_tags = false;
-  if (c->have_tag) {
-    upload_concat(c, c->res_tag, s, n, [](const arp_structure* t) { return t->res_tag; }, nrs, 0, nullptr, false);
-  } else if (c->n_res > 0) {
+  if (c->have_tag) upload_concat(c, c->res_tag, s, n, [](const arp_structure* t) { return t->res_tag; }, nrs, 0, nullptr, false);
+  flush_uploads(c);  // every array of the job is on the stream from here on
+  if (!c->have_tag && c->n_res > 0) {
     derive_tags = true;
     if (!c->per_residue_keys) {  // per-atom keys only: the residues' keys first (every atom of a residue carries the same pair)
       c->res_chain_key.need((size_t)c->n_res);
@@ -469,8 +624,15 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n) {
     CK(cudaGetLastError());
   }
   CK(cudaEventRecord(c->ev[1], c->stream));
-  CK(cudaStreamSynchronize(c->stream));
-  CK(cudaEventElapsedTime(&c->ms_h2d, c->ev[0], c->ev[1]));
+  c->up_after = nullptr;
+  if (one_shot && !derive_tags) {
+    // arp_contacts*: the caller's arrays stay valid until the call returns, and it returns after the download -- the
+    // run is queued behind the copies without a host round trip in between
+    c->h2d_pending = true;
+  } else {
+    CK(cudaStreamSynchronize(c->stream));  // arp_stage_upload: the caller may reuse its arrays once this returns
+    CK(cudaEventElapsedTime(&c->ms_h2d, c->ev[0], c->ev[1]));
+  }
   c->tags_ok = c->n_res > 0;
   if (derive_tags && *c->h_up_err.p) {
     if (*c->h_up_err.p & 4u) throw arp::Error{ARP_ERR_CUDA, "residue-tag scan: look-back wait exceeded its bound"};

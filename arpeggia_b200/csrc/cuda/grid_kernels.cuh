@@ -281,6 +281,28 @@ __global__ void __launch_bounds__(256) k_expand_res_id(const uint32_t* __restric
   res_id[a] = lo;
 }
 
+// ---- upload: the arrays of one merged host->device copy go to their own buffers ---------------------------------------
+constexpr int SEG_MAX = 24;
+struct Segments {
+  const unsigned char* src[SEG_MAX];
+  unsigned char* dst[SEG_MAX];
+  size_t bytes[SEG_MAX];  // multiples of 4; src and dst 4-byte aligned
+  int n;
+};
+__global__ void __launch_bounds__(256) k_scatter_segments(const Segments S) {
+  const int s = blockIdx.y;
+  const unsigned char* __restrict__ src = S.src[s];
+  unsigned char* __restrict__ dst = S.dst[s];
+  const size_t bytes = S.bytes[s], tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, step = (size_t)gridDim.x * blockDim.x;
+  size_t done = 0;
+  if (((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15u) == 0) {
+    const size_t n16 = bytes / 16;
+    for (size_t i = tid; i < n16; i += step) reinterpret_cast<uint4*>(dst)[i] = reinterpret_cast<const uint4*>(src)[i];
+    done = n16 * 16;
+  }
+  for (size_t i = done / 4 + tid; i < bytes / 4; i += step) reinterpret_cast<uint32_t*>(dst)[i] = reinterpret_cast<const uint32_t*>(src)[i];
+}
+
 // f64 coordinates from the on-lattice form (arp_structure.x_milli): one IEEE division per coordinate, the correctly
 // rounded double of the decimal v/1000 -- what the packer verified against the parsed value bit for bit
 __global__ void __launch_bounds__(256) k_expand_milli(const int32_t* __restrict__ xm, const int32_t* __restrict__ ym,

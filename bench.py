@@ -162,8 +162,10 @@ def run_reference_arm(args):
     return 0
 
 
-def pinned_structure(A, packed):
-    """Copy the packed SoA into page-locked memory (arp_host_alloc) and return (Structure, keepalive, bytes)."""
+def pinned_structure(A, packed, arena=True):
+    """Copy the packed SoA into page-locked memory (arp_host_alloc) and return (Structure, keepalive, bytes).  arena: one
+    allocation, the arrays one after the other (256-byte aligned) -- the library then moves them with one copy
+    (arp_stats.upload_copies); otherwise one allocation per array."""
     from arpeggia_b200 import _lib
 
     L = _lib.lib()
@@ -183,10 +185,21 @@ def pinned_structure(A, packed):
     lens = {**{k: n * s for k, s in sizes.items()}, "res_chain_key": 4 * nr, "res_res_ordinal": 4 * nr, "res_atom_begin": 4 * (nr + 1), "res_h_begin": 4 * (nr + 1), "h_x": 8 * nh, "h_y": 8 * nh, "h_z": 8 * nh,
             "res_cb": 4 * nr, "res_sg": 4 * nr, "ring_center": 24 * ng, "ring_normal": 24 * ng, "ring_attr": 4 * ng,
             "ring_chain_key": 4 * ng, "ring_res_ordinal": 4 * ng}
+    if src.res_tag:
+        lens["res_tag"] = 4 * nr  # the packer's residue tags: without them the library derives them on the device
+    block, at = None, 0
+    if arena:
+        block = C.c_void_p()
+        _lib.check(L.arp_host_alloc(C.byref(block), sum((b + 255) // 256 * 256 for b in lens.values()) + 256))
+        keep.append(block)
     for name, nbytes in lens.items():
-        p = C.c_void_p()
-        _lib.check(L.arp_host_alloc(C.byref(p), max(nbytes, 1)))
-        keep.append(p)
+        if arena:
+            p = C.c_void_p(block.value + at)
+            at += (nbytes + 255) // 256 * 256
+        else:
+            p = C.c_void_p()
+            _lib.check(L.arp_host_alloc(C.byref(p), max(nbytes, 1)))
+            keep.append(p)
         if nbytes:
             C.memmove(p, C.cast(getattr(src, name), C.c_void_p), nbytes)
         setattr(dst, name, C.cast(p, dict(_lib.Structure._fields_)[name]))
@@ -483,6 +496,20 @@ def main():
     e2e_value = world * pairs / (float(e2e_t.item()) * 1e-3)
 
     st = ctx.stats()  # of the last end-to-end call
+    # the same call with every array in a page-locked allocation of its own: one copy per array (a side figure)
+    e2e_sep = None
+    if world == 1:
+        hs2, keep2, _ = pinned_structure(A, packed, arena=False)
+        ptrs_arena, ptrs = ptrs, (C.POINTER(AL.Structure) * 1)(C.pointer(hs2))
+        for _ in range(2):
+            one_call()
+        n_sep = max(3, min(args.steps, 200))
+        t0 = time.perf_counter()
+        for _ in range(n_sep):
+            one_call()
+        st2 = ctx.stats()
+        e2e_sep = {"ms_per_step": 1e3 * (time.perf_counter() - t0) / n_sep, "ms_h2d": st2["ms_h2d"], "upload_copies": st2["upload_copies"], "calls": n_sep}
+        ptrs = ptrs_arena
     # every rank's phases of that call: host wall clock (arp_stats.ms_wall_*) beside the device times inside them
     e2e_keys = ("ms_wall_call", "ms_wall_upload", "ms_h2d", "ms_wall_run", "ms_run", "ms_wall_download", "ms_d2h")
     e2e_ranks = reduce_records({k: st[k] for k in e2e_keys}, world, f"cuda:{local}")
@@ -746,6 +773,8 @@ def main():
                     "ms_per_step": float(e2e_t.item()), "ms_h2d": st["ms_h2d"], "ms_run": st["ms_run"], "ms_d2h": st["ms_d2h"],
                     "ms_host_other_rank0": e2e_ms - st["ms_h2d"] - st["ms_run"] - st["ms_d2h"], "calls": e2e_steps, "cpu_binding": binding,
                     "last_call_per_rank": {k: [round(float(v), 4) for v in e2e_ranks[k]] for k in e2e_keys},
+                    "host_layout": "one page-locked arena, arrays 256-byte aligned one after the other", "upload_copies": st["upload_copies"],
+                    "separate_allocations": e2e_sep,
                     "api": "arp_contacts (C ABI, pinned host SoA in, host rows out)"},
             "e2e_concurrent": e2e_conc,
             "frame": frame_info,

@@ -117,7 +117,7 @@ pub struct arp_stats {
     pub n_rows: i64,
     pub kernel_launches: i64,
     pub pair_kernel_retries: i32,
-    pub reserved_: i32,
+    pub upload_copies: i32,
     pub n_screened_pairs: i64,
     pub n_filtered_pairs: i64,
     pub ms_h2d: f32,

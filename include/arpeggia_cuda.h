@@ -185,14 +185,15 @@ typedef struct arp_stats {
   int64_t n_atoms, n_rings, n_cells, n_nonempty_cells, n_rows;
   int64_t kernel_launches;        /* kernels of this library launched by the last run */
   int32_t pair_kernel_retries;    /* re-runs because the row buffer or a pair queue was too small */
-  int32_t reserved_;
+  int32_t upload_copies;          /* host->device copies the last upload issued for the job's arrays (neighbours in host memory travel as one) */
   int64_t n_screened_pairs;       /* entries of the first pair queue (k_screen -> k_filter), unused window tails included */
   int64_t n_filtered_pairs;       /* entries of the second pair queue (k_filter -> k_exact) */
   float ms_h2d, ms_grid, ms_pairs, ms_rings, ms_d2h, ms_run; /* ms_run = the whole job; ms_rings overlaps ms_pairs (side stream) */
   float ms_screen, ms_filter, ms_exact, reserved2_;          /* the three kernels of ms_pairs */
   /* host wall clock of the phases of the last one-shot call (arp_contacts / arp_contacts_batch), each from its first API
-   * call to the return of its last synchronisation: upload, run (enqueue + wait for the counters), download.  Their sum
-   * minus ms_h2d + ms_run + ms_d2h is host overhead (submission, wake-ups after a synchronisation). */
+   * call to the return of its last synchronisation: upload (enqueueing the copies: a one-shot call does not wait for
+   * them), run (enqueue + wait for copies, kernels and counters), download.  Their sum minus ms_h2d + ms_run + ms_d2h
+   * is host overhead (submission, wake-ups after a synchronisation). */
   float ms_wall_upload, ms_wall_run, ms_wall_download, ms_wall_call;
 } arp_stats;
 

@@ -522,3 +522,58 @@ def test_results_own_their_rows(ctx, bft, ubq):
     assert views[1]["from"].max() < 660  # still the 1ubq rows, not overwritten by the third call
     for r in held:
         L.arp_result_free(ctx._h, r)
+
+
+def test_arrays_of_one_host_arena_travel_as_one_copy(ctx, bft, ubq):
+    """The upload merges arrays that follow one another in the caller's memory into one host->device copy
+    (arp_stats.upload_copies) and moves them to their buffers on the device: the rows are those of the separate copies,
+    whatever the order and the padding of the arrays in the arena, with and without the on-lattice coordinates."""
+    import ctypes as C
+
+    from arpeggia_b200 import _lib as AL
+
+    L = AL.lib()
+    prm = AL.Params(0.1, 6.5, 0, 0)
+    key = ["from", "to", "label", "distance"]
+    n_of = {"n_atoms": 1, "n_residues": 1, "n_rings": 1, "n_h": 1}
+
+    def rows_of(sp):
+        rp = C.POINTER(AL.Result)()
+        AL.check(L.arp_contacts(ctx._h, sp, C.byref(prm), C.byref(rp)), ctx._h)
+        v = np.frombuffer((C.c_char * (rp.contents.n_rows * 16)).from_address(rp.contents.rows), dtype=A.ROW_DTYPE).copy()
+        L.arp_result_free(ctx._h, rp)
+        return np.sort(v, order=key), ctx.stats()["upload_copies"]
+
+    for atoms, milli in ((bft, True), (ubq, True), (bft, False)):
+        p = A.Packed(atoms)
+        src = p.structure
+        n, nr, ng, nh = src.n_atoms, src.n_residues, src.n_rings, src.n_h
+        want, copies_plain = rows_of(p.structure_ptr)
+        lens = {"attr": 4 * n, "res_chain_key": 4 * nr, "res_res_ordinal": 4 * nr, "res_atom_begin": 4 * (nr + 1), "res_h_begin": 4 * (nr + 1),
+                "h_x": 8 * nh, "h_y": 8 * nh, "h_z": 8 * nh, "res_cb": 4 * nr, "res_sg": 4 * nr, "ring_center": 24 * ng, "ring_normal": 24 * ng,
+                "ring_attr": 4 * ng, "ring_chain_key": 4 * ng, "ring_res_ordinal": 4 * ng, "res_tag": 4 * nr}
+        lens.update({"x_milli": 4 * n, "y_milli": 4 * n, "z_milli": 4 * n} if milli else {"x": 8 * n, "y": 8 * n, "z": 8 * n})
+        assert bool(src.x_milli) and bool(src.res_tag)
+        names = list(lens)
+        np.random.default_rng(5).shuffle(names)  # the arena's order is not the library's upload order
+        pads = [4, 16, 256, 1000, 0]
+        block = C.c_void_p()
+        AL.check(L.arp_host_alloc(C.byref(block), sum(lens.values()) + 1024 * len(lens) + 64))
+        try:
+            dst = AL.Structure()
+            for name, _ in AL.Structure._fields_:
+                if name.startswith("n_") or name.startswith("bbox_") or name == "has_bbox":
+                    setattr(dst, name, getattr(src, name))
+            at = 0
+            for k, name in enumerate(names):
+                ptr = C.c_void_p(block.value + at)
+                if lens[name]:
+                    C.memmove(ptr, C.cast(getattr(src, name), C.c_void_p), lens[name])
+                setattr(dst, name, C.cast(ptr, dict(AL.Structure._fields_)[name]))
+                at += lens[name] + pads[k % len(pads)]
+                at = (at + 7) // 8 * 8  # f64 arrays stay 8-byte aligned
+            got, copies = rows_of(C.pointer(dst))
+            assert np.array_equal(got, want), (milli, len(got), len(want))
+            assert copies == 1 and copies_plain >= 1, (copies, copies_plain)  # (the packer's own vectors may happen to be neighbours too)
+        finally:
+            L.arp_host_free(block)
