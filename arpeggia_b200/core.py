@@ -199,6 +199,7 @@ def read_table(t: Table) -> dict:
     out["sc_valid"] = arr(t.sc_valid, np.uint8).astype(bool)
     out["sc_validity_bits"] = np.ctypeslib.as_array(t.sc_validity, shape=((n + 7) // 8,)).copy() if n else np.zeros(0, dtype=np.uint8)
     out["sc_null_count"] = int(t.sc_null_count)
+    out["strings"] = [str(v) for v in strings[:-1]]  # the table's string dictionary (ids of the string columns index it)
     for c in ("sc_centroid_dist", "sc_dihedral", "sc_centroid_angle"):
         out[c] = arr(getattr(t, c), np.float32)
     for c in ("n_atoms", "pairs_in_cutoff", "pairs_classified", "t_setup_s", "t_classify_s", "t_table_s"):

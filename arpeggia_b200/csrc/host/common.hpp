@@ -1,8 +1,14 @@
 // Shared internals of the host side (not part of the ABI).
 #pragma once
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstdint>
 #include <cstring>
+#include <memory>
 #include <string>
+#include <utility>
+#include <vector>
 
 #include "arpeggia_cuda.h"
 #include "arpeggia_host.h"
@@ -67,5 +73,41 @@ struct AngleBounds {
   double f_lt_60_pos, f_lt_60_neg;
 };
 const AngleBounds& angle_bounds();
+
+// std::vector whose resize() leaves new elements uninitialised (trivial types only): the big per-atom arrays are resized
+// once and then written by every host thread, so the pages are first touched -- and faulted in -- by the threads that
+// fill them instead of by one thread zero-filling 100 MB.
+template <class T>
+struct NoInitAlloc : std::allocator<T> {
+  template <class U>
+  struct rebind {
+    using other = NoInitAlloc<U>;
+  };
+  NoInitAlloc() = default;
+  template <class U>
+  NoInitAlloc(const NoInitAlloc<U>&) {}
+  template <class U>
+  void construct(U* p) noexcept {
+    ::new (static_cast<void*>(p)) U;
+  }
+  template <class U, class... Args>
+  void construct(U* p, Args&&... args) {
+    ::new (static_cast<void*>(p)) U(std::forward<Args>(args)...);
+  }
+};
+template <class T>
+using RawVec = std::vector<T, NoInitAlloc<T>>;
+
+// ARPH_TIMING=1: the phases of the packer and of the side-table builder on stderr (a development aid)
+struct PhaseClock {
+  bool on = std::getenv("ARPH_TIMING") != nullptr;
+  std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+  void mark(const char* what) {
+    if (!on) return;
+    const auto now = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "[arph] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t).count());
+    t = now;
+  }
+};
 
 }  // namespace arp

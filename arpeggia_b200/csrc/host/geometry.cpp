@@ -33,7 +33,14 @@ bool fit_plane(const double* pts, int64_t n, Plane& out) {
   double c[3] = {0.0, 0.0, 0.0};
   for (int64_t i = 0; i < n; ++i)
     for (int k = 0; k < 3; ++k) c[k] = c[k] + w * pts[3 * i + k];
-  std::vector<double> m((size_t)(3 * n));  // m[k*n + i]
+  // m[k*n + i]; residues have a dozen atoms at most: no heap traffic for them (this runs once or twice per residue)
+  double m_small[3 * 32];
+  std::vector<double> m_big;
+  double* m = m_small;
+  if (n > 32) {
+    m_big.resize((size_t)(3 * n));
+    m = m_big.data();
+  }
   for (int k = 0; k < 3; ++k)
     for (int64_t i = 0; i < n; ++i) m[(size_t)(k * n + i)] = pts[3 * i + k] - c[k];
   double u[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};

@@ -15,6 +15,11 @@
 // SURVEY.md 8.2) is rebuilt with interned strings and flat index vectors.
 #include <algorithm>
 #include <cmath>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <omp.h>
+
 #include <array>
 #include <map>
 #include <set>
@@ -115,6 +120,7 @@ struct ChainT {
   int32_t id;
   std::vector<ResT> residues;
   std::unordered_map<std::pair<int64_t, int32_t>, size_t, ResKeyHash> lookup;
+  int owner = 0;  // the block (= thread) of phase 1 that created the chain
 };
 struct ModelT {
   int64_t serial;
@@ -169,99 +175,244 @@ void parse_groups(const std::set<std::string>& all, const std::string& groups, s
 
 static bool is_ring_residue_name(const std::string& s) { return s == "HIS" || s == "PHE" || s == "TYR" || s == "TRP"; }
 
+namespace {
+
+// A string table of one thread's block of records (phase 1 below); ids are in first-appearance order.
+struct LocalStrings {
+  std::vector<std::string> strings;
+  std::unordered_map<std::string, int32_t> ids;
+  int32_t intern(const std::string& s) {
+    auto it = ids.find(s);
+    if (it != ids.end()) return it->second;
+    const int32_t id = (int32_t)strings.size();
+    strings.push_back(s);
+    ids.emplace(s, id);
+    return id;
+  }
+};
+
+// Records [lo, hi) -> models / chains / residues / conformers in first-appearance order, records in file order
+// (pdbtbx: chain by id within a model, residue by (resi, icode) within a chain, conformer by (name, altloc) within a
+// residue).  Strings go through `S.intern`; name_id[k] = id of record k's atom name.
+template <class Strings>
+void group_records(const arp_atom_record* recs, int64_t lo, int64_t hi, Strings& S, std::vector<ModelT>& models, int32_t* name_id) {
+  struct NameSlot {
+    uint64_t raw;
+    int32_t id;
+  };
+  NameSlot name_cache[64];
+  for (auto& e : name_cache) e = NameSlot{0, -1};
+  int64_t mi = -1, ci = -1, ri = -1;
+  // one-entry caches so that runs of equal fields cost no hashing
+  char last_chain[8] = {1}, last_resn[8] = {1}, last_alt[2] = {1}, last_ic[2] = {1};
+  int32_t chain_id = -1, resn_id = -1, alt_id = -1, ic_id = -1;
+  for (int64_t k = lo; k < hi; ++k) {
+    const arp_atom_record& r = recs[k];
+    if (std::memcmp(last_chain, r.chain, 8) != 0 || chain_id < 0) {
+      std::memcpy(last_chain, r.chain, 8);
+      chain_id = S.intern(fixed_field(r.chain, 8));
+    }
+    if (std::memcmp(last_resn, r.resn, 8) != 0 || resn_id < 0) {
+      std::memcpy(last_resn, r.resn, 8);
+      resn_id = S.intern(fixed_field(r.resn, 8));
+    }
+    if (std::memcmp(last_alt, r.altloc, 2) != 0 || alt_id < 0) {
+      std::memcpy(last_alt, r.altloc, 2);
+      alt_id = S.intern(fixed_field(r.altloc, 2));
+    }
+    if (std::memcmp(last_ic, r.icode, 2) != 0 || ic_id < 0) {
+      std::memcpy(last_ic, r.icode, 2);
+      ic_id = S.intern(fixed_field(r.icode, 2));
+    }
+    if (mi < 0 || models[mi].serial != r.model) {
+      mi = -1;
+      for (size_t m = 0; m < models.size(); ++m)
+        if (models[m].serial == r.model) mi = (int64_t)m;
+      if (mi < 0) {
+        models.push_back(ModelT{r.model, {}, {}});
+        mi = (int64_t)models.size() - 1;
+      }
+      ci = ri = -1;
+    }
+    ModelT& M = models[mi];
+    if (ci < 0 || M.chains[ci].id != chain_id) {
+      auto it = M.lookup.find(chain_id);
+      if (it == M.lookup.end()) {
+        M.lookup.emplace(chain_id, M.chains.size());
+        M.chains.push_back(ChainT{chain_id, {}, {}, 0});
+        ci = (int64_t)M.chains.size() - 1;
+      } else {
+        ci = (int64_t)it->second;
+      }
+      ri = -1;
+    }
+    ChainT& Cn = M.chains[ci];
+    if (ri < 0 || Cn.residues[ri].resi != r.resi || Cn.residues[ri].icode != ic_id) {
+      const auto key = std::make_pair((int64_t)r.resi, ic_id);
+      auto it = Cn.lookup.find(key);
+      if (it == Cn.lookup.end()) {
+        Cn.lookup.emplace(key, Cn.residues.size());
+        Cn.residues.push_back(ResT{r.resi, ic_id, {}});
+        ri = (int64_t)Cn.residues.size() - 1;
+      } else {
+        ri = (int64_t)it->second;
+      }
+    }
+    ResT& R = Cn.residues[ri];
+    ConfT* cf = nullptr;
+    for (auto& c : R.confs)
+      if (c.name == resn_id && c.altloc == alt_id) cf = &c;
+    if (!cf) {
+      R.confs.push_back(ConfT{resn_id, alt_id, {}});
+      cf = &R.confs.back();
+    }
+    cf->recs.push_back(k);
+    // atom-name id of the record: a direct-mapped cache on the 8 raw bytes in front of the string table
+    uint64_t raw;
+    std::memcpy(&raw, r.name, 8);
+    NameSlot& ns = name_cache[(raw * 0x9E3779B97F4A7C15ull) >> 58];
+    if (ns.id < 0 || ns.raw != raw) {
+      ns.raw = raw;
+      ns.id = S.intern(fixed_field(r.name, 8));
+    }
+    name_id[k] = ns.id;
+  }
+}
+
+// Phase 1 on every host thread: the records are cut into blocks (at places where the residue changes), every block is
+// grouped on its own with a string table of its own, then the blocks are joined in file order.  A string's global id is
+// assigned in (block, local id) order = the order of first appearance in the file, and chains / residues / conformers
+// are appended in block order, so the result is the one the single pass over all records gives.
+void group_records_parallel(const arp_atom_record* recs, int64_t n, Packed& P, std::vector<ModelT>& models, int32_t* name_id, int blocks) {
+  std::vector<int64_t> cut((size_t)blocks + 1, n);
+  cut[0] = 0;
+  for (int b = 1; b < blocks; ++b) {
+    int64_t k = std::max(cut[b - 1], n * b / blocks);
+    const auto same_residue = [&](int64_t i) {
+      const arp_atom_record &u = recs[i - 1], &v = recs[i];
+      return u.model == v.model && u.resi == v.resi && std::memcmp(u.chain, v.chain, 8) == 0 && std::memcmp(u.icode, v.icode, 2) == 0;
+    };
+    while (k > 0 && k < n && same_residue(k)) ++k;
+    cut[b] = k;
+  }
+  std::vector<LocalStrings> ls((size_t)blocks);
+  std::vector<std::vector<ModelT>> lm((size_t)blocks);
+#pragma omp parallel for schedule(static, 1) num_threads(blocks)
+  for (int b = 0; b < blocks; ++b) group_records(recs, cut[b], cut[b + 1], ls[b], lm[b], name_id);
+  // global string ids, in order of first appearance
+  std::vector<std::vector<int32_t>> to_global((size_t)blocks);
+  for (int b = 0; b < blocks; ++b) {
+    to_global[b].resize(ls[b].strings.size());
+    for (size_t i = 0; i < ls[b].strings.size(); ++i) to_global[b][i] = P.intern(ls[b].strings[i]);
+  }
+#pragma omp parallel for schedule(static, 1) num_threads(blocks)
+  for (int b = 0; b < blocks; ++b) {
+    const std::vector<int32_t>& g = to_global[b];
+    for (int64_t k = cut[b]; k < cut[b + 1]; ++k) name_id[k] = g[name_id[k]];
+    for (auto& M : lm[b]) {
+      M.lookup.clear();
+      for (auto& Cn : M.chains) {
+        Cn.id = g[Cn.id];
+        Cn.owner = b;
+        Cn.lookup.clear();  // keyed by local ids; rebuilt below for the (rare) chain that continues in a later block
+        for (auto& R : Cn.residues) {
+          R.icode = g[R.icode];
+          for (auto& c : R.confs) c.name = g[c.name], c.altloc = g[c.altloc];
+        }
+      }
+    }
+  }
+  for (int b = 0; b < blocks; ++b)
+    for (auto& LM : lm[b]) {
+      int64_t mi = -1;
+      for (size_t m = 0; m < models.size(); ++m)
+        if (models[m].serial == LM.serial) mi = (int64_t)m;
+      if (mi < 0) {
+        models.push_back(ModelT{LM.serial, {}, {}});
+        mi = (int64_t)models.size() - 1;
+      }
+      ModelT& M = models[mi];
+      for (auto& LC : LM.chains) {
+        auto it = M.lookup.find(LC.id);
+        if (it == M.lookup.end()) {
+          M.lookup.emplace(LC.id, M.chains.size());
+          M.chains.push_back(std::move(LC));
+          continue;
+        }
+        ChainT& G = M.chains[it->second];  // the chain goes on: residue by residue, as the single pass would
+        if (G.lookup.size() != G.residues.size()) {
+          G.lookup.clear();
+          for (size_t r = 0; r < G.residues.size(); ++r) G.lookup.emplace(std::make_pair(G.residues[r].resi, G.residues[r].icode), r);
+        }
+        for (auto& LR : LC.residues) {
+          const auto key = std::make_pair(LR.resi, LR.icode);
+          auto ir = G.lookup.find(key);
+          if (ir == G.lookup.end()) {
+            G.lookup.emplace(key, G.residues.size());
+            G.residues.push_back(std::move(LR));
+            continue;
+          }
+          ResT& GR = G.residues[ir->second];
+          for (auto& lc : LR.confs) {
+            ConfT* cf = nullptr;
+            for (auto& c : GR.confs)
+              if (c.name == lc.name && c.altloc == lc.altloc) cf = &c;
+            if (!cf)
+              GR.confs.push_back(std::move(lc));
+            else
+              cf->recs.insert(cf->recs.end(), lc.recs.begin(), lc.recs.end());
+          }
+        }
+      }
+    }
+}
+
+}  // namespace
+
 void pack_records(const arp_atom_record* recs, int64_t n, const std::string& groups, bool ignore_zero_occupancy, uint32_t flags,
                   Packed& P) {
   if (n >= (int64_t)1 << 31) throw Error{ARP_ERR_LIMIT, "more than 2^31 atom records"};
+  PhaseClock clk;
+  // every phase below that walks the records or the residues runs on all host threads (one thread when the caller is
+  // itself a parallel region: arph_pack_many packs one structure per thread)
+  const int host_threads = omp_in_parallel() ? 1 : omp_get_max_threads();
   // ---- 1. group records into the hierarchy --------------------------------------------------------
   std::vector<ModelT> models;
   std::vector<int32_t> name_id((size_t)n);
   {
-    struct NameSlot {
-      uint64_t raw;
-      int32_t id;
-    };
-    NameSlot name_cache[64];
-    for (auto& e : name_cache) e = NameSlot{0, -1};
-    int64_t mi = -1, ci = -1, ri = -1;
-    // one-entry caches so that runs of equal fields cost no hashing
-    char last_chain[8] = {1}, last_resn[8] = {1}, last_alt[2] = {1}, last_ic[2] = {1};
-    int32_t chain_id = -1, resn_id = -1, alt_id = -1, ic_id = -1;
-    for (int64_t k = 0; k < n; ++k) {
-      const arp_atom_record& r = recs[k];
-      if (std::memcmp(last_chain, r.chain, 8) != 0 || chain_id < 0) {
-        std::memcpy(last_chain, r.chain, 8);
-        chain_id = P.intern(fixed_field(r.chain, 8));
-      }
-      if (std::memcmp(last_resn, r.resn, 8) != 0 || resn_id < 0) {
-        std::memcpy(last_resn, r.resn, 8);
-        resn_id = P.intern(fixed_field(r.resn, 8));
-      }
-      if (std::memcmp(last_alt, r.altloc, 2) != 0 || alt_id < 0) {
-        std::memcpy(last_alt, r.altloc, 2);
-        alt_id = P.intern(fixed_field(r.altloc, 2));
-      }
-      if (std::memcmp(last_ic, r.icode, 2) != 0 || ic_id < 0) {
-        std::memcpy(last_ic, r.icode, 2);
-        ic_id = P.intern(fixed_field(r.icode, 2));
-      }
-      if (mi < 0 || models[mi].serial != r.model) {
-        mi = -1;
-        for (size_t m = 0; m < models.size(); ++m)
-          if (models[m].serial == r.model) mi = (int64_t)m;
-        if (mi < 0) {
-          models.push_back(ModelT{r.model, {}, {}});
-          mi = (int64_t)models.size() - 1;
-        }
-        ci = ri = -1;
-      }
-      ModelT& M = models[mi];
-      if (ci < 0 || M.chains[ci].id != chain_id) {
-        auto it = M.lookup.find(chain_id);
-        if (it == M.lookup.end()) {
-          M.lookup.emplace(chain_id, M.chains.size());
-          M.chains.push_back(ChainT{chain_id, {}, {}});
-          ci = (int64_t)M.chains.size() - 1;
-        } else {
-          ci = (int64_t)it->second;
-        }
-        ri = -1;
-      }
-      ChainT& Cn = M.chains[ci];
-      if (ri < 0 || Cn.residues[ri].resi != r.resi || Cn.residues[ri].icode != ic_id) {
-        const auto key = std::make_pair((int64_t)r.resi, ic_id);
-        auto it = Cn.lookup.find(key);
-        if (it == Cn.lookup.end()) {
-          Cn.lookup.emplace(key, Cn.residues.size());
-          Cn.residues.push_back(ResT{r.resi, ic_id, {}});
-          ri = (int64_t)Cn.residues.size() - 1;
-        } else {
-          ri = (int64_t)it->second;
-        }
-      }
-      ResT& R = Cn.residues[ri];
-      ConfT* cf = nullptr;
-      for (auto& c : R.confs)
-        if (c.name == resn_id && c.altloc == alt_id) cf = &c;
-      if (!cf) {
-        R.confs.push_back(ConfT{resn_id, alt_id, {}});
-        cf = &R.confs.back();
-      }
-      cf->recs.push_back(k);
-      // atom-name id of the record: a direct-mapped cache on the 8 raw bytes in front of the string table
-      uint64_t raw;
-      std::memcpy(&raw, r.name, 8);
-      NameSlot& ns = name_cache[(raw * 0x9E3779B97F4A7C15ull) >> 58];
-      if (ns.id < 0 || ns.raw != raw) {
-        ns.raw = raw;
-        ns.id = P.intern(fixed_field(r.name, 8));
-      }
-      name_id[k] = ns.id;
-    }
+    int blocks = (int)std::min<int64_t>(host_threads, n / 8192);
+    if (const char* ev = std::getenv("ARPH_PACK_BLOCKS")) blocks = (int)std::min<int64_t>(std::max(1, std::atoi(ev)), std::max<int64_t>(n, 1));  // tests: any input, any cut
+    if (blocks > 1)
+      group_records_parallel(recs, n, P, models, name_id.data(), blocks);
+    else
+      group_records(recs, 0, n, P, models, name_id.data());
   }
+  clk.mark("1 hierarchy");
   const int32_t blank = P.intern("");
+  // every chain of every model, in hierarchy order
+  struct ChainRef {
+    size_t mi;
+    ChainT* c;
+  };
+  std::vector<ChainRef> chains;
+  for (size_t mi = 0; mi < models.size(); ++mi)
+    for (auto& Cn : models[mi].chains) chains.push_back(ChainRef{mi, &Cn});
+  const int64_t n_chains_all = (int64_t)chains.size();
+  auto uniform_name = [](const ResT& R) -> int32_t {  // pdbtbx Residue::name()
+    if (R.confs.empty()) return -1;
+    for (auto& c : R.confs)
+      if (c.name != R.confs[0].name) return -1;
+    return R.confs[0].name;
+  };
   // ---- 2. blank-altloc conformer joins every other conformer (pdbtbx reader post-pass) ----------------
-  for (auto& M : models)
-    for (auto& Cn : M.chains)
+  // ---- 3. load_model filter + zero occupancy ---------------------------------------------------------
+  {
+    std::vector<char> known(P.strings.size(), 0);
+    for (size_t i = 0; i < P.strings.size(); ++i) known[i] = ((flags & ARPH_FLAG_SKIP_LOAD_FILTER) || known_residue(P.strings[i])) ? 1 : 0;
+    std::vector<char> bad_name((size_t)n_chains_all, 0);
+#pragma omp parallel for schedule(dynamic, 4) num_threads(host_threads) if (n > 65536)
+    for (int64_t ci = 0; ci < n_chains_all; ++ci) {
+      ChainT& Cn = *chains[ci].c;
       for (auto& R : Cn.residues) {
         if (R.confs.size() < 2) continue;
         int which = -1;
@@ -272,22 +423,17 @@ void pack_records(const arp_atom_record* recs, int64_t n, const std::string& gro
         R.confs.erase(R.confs.begin() + which);
         for (auto& c : R.confs) c.recs.insert(c.recs.end(), shared.begin(), shared.end());
       }
-  // ---- 3. load_model filter + zero occupancy ---------------------------------------------------------
-  auto uniform_name = [&](const ResT& R) -> int32_t {  // pdbtbx Residue::name()
-    if (R.confs.empty()) return -1;
-    for (auto& c : R.confs)
-      if (c.name != R.confs[0].name) return -1;
-    return R.confs[0].name;
-  };
-  for (auto& M : models)
-    for (auto& Cn : M.chains) {
       std::vector<ResT> kept;
       kept.reserve(Cn.residues.size());
       for (auto& R : Cn.residues) {
         const int32_t nm = uniform_name(R);
-        if (nm < 0) throw Error{ARP_ERR_RESIDUE_NAME, "residue has conformers with different names (Residue::name() is None)"};
-        if ((flags & ARPH_FLAG_SKIP_LOAD_FILTER) || known_residue(P.strings[nm])) kept.push_back(std::move(R));
+        if (nm < 0) {
+          bad_name[ci] = 1;
+          break;
+        }
+        if (known[nm]) kept.push_back(std::move(R));
       }
+      if (bad_name[ci]) continue;
       Cn.residues.swap(kept);
       Cn.lookup.clear();
       if (ignore_zero_occupancy)
@@ -295,6 +441,10 @@ void pack_records(const arp_atom_record* recs, int64_t n, const std::string& gro
           for (auto& c : R.confs)
             c.recs.erase(std::remove_if(c.recs.begin(), c.recs.end(), [&](int64_t k) { return recs[k].occupancy == 0.0; }), c.recs.end());
     }
+    for (int64_t ci = 0; ci < n_chains_all; ++ci)
+      if (bad_name[ci]) throw Error{ARP_ERR_RESIDUE_NAME, "residue has conformers with different names (Residue::name() is None)"};
+  }
+  clk.mark("2-3 conformers, filters");
   // ---- 4. chain groups ------------------------------------------------------------------------------
   std::set<std::string> all_chains, ligand, receptor;
   for (auto& M : models)
@@ -313,215 +463,278 @@ void pack_records(const arp_atom_record* recs, int64_t n, const std::string& gro
 
   // ---- 5. planes (complex.rs:442-514), including the multi-model key overwrite (ledger item 12) ------
   const bool quirk = models.size() > 1 && !(flags & ARPH_FLAG_NO_MULTIMODEL_QUIRK);
-  // table bits of every record by RESIDUE name (residue().name(): planes, hydrophobic.rs:16, aromatic.rs:18, vdw.rs:50),
-  // looked up once per (residue name, atom name) pair and shared by the plane fits and the attribute words below
-  std::unordered_map<uint64_t, uint32_t> bits_cache;
-  auto bits_of = [&](int32_t resn_id, int32_t atom_id) {
-    const uint64_t key = ((uint64_t)(uint32_t)resn_id << 32) | (uint32_t)atom_id;
-    auto it = bits_cache.find(key);
-    if (it != bits_cache.end()) return it->second;
-    const uint32_t b = table_bits(P.strings[resn_id], P.strings[atom_id]);
-    bits_cache.emplace(key, b);
-    return b;
+  // every residue, models / chains / residues in order
+  struct ResRef {
+    const ResT* r;
+    uint32_t chain;    // index into chains[]
+    uint32_t ordinal;  // position within its chain
   };
+  std::vector<ResRef> all_res;
+  for (int64_t ci = 0; ci < n_chains_all; ++ci) {
+    const ChainT& Cn = *chains[ci].c;
+    for (size_t o = 0; o < Cn.residues.size(); ++o) all_res.push_back(ResRef{&Cn.residues[o], (uint32_t)ci, (uint32_t)o});
+  }
+  const int64_t n_res = (int64_t)all_res.size();
+  // table bits of every record by RESIDUE name (residue().name(): planes, hydrophobic.rs:16, aromatic.rs:18, vdw.rs:50)
+  // -- the conformers of a residue all carry that name (phase 3), so conformer().name() (ionic.rs:45-46, hbond.rs:120-121)
+  // reads the same bits -- and the element class of every record; then the plane fits (one small SVD per residue, two
+  // for ring residues).  All per residue, independent: every host thread, each with its own (residue name, atom name) cache.
   std::vector<uint32_t> bits_res((size_t)n, 0u);
-  std::vector<const ResT*> all_res;  // every residue, models / chains / residues in order
-  for (auto& M : models)
-    for (auto& Cn : M.chains)
-      for (auto& R : Cn.residues) {
-        all_res.push_back(&R);
-        const int32_t nm = uniform_name(R);
-        int32_t last_atom = -1;
-        uint32_t last_bits = 0;
-        for (auto& c : R.confs)
-          for (int64_t k : c.recs) {
-            if (name_id[k] != last_atom) {
-              last_atom = name_id[k];
-              last_bits = bits_of(nm, last_atom);
-            }
-            bits_res[k] = last_bits;
-          }
-      }
-  auto residue_plane = [&](const ResT& R, uint32_t want, Plane& out) {  // thread-safe: reads only
-    std::vector<double> pts;
-    for (auto& c : R.confs)
-      for (int64_t k : c.recs)
-        if (bits_res[k] & want) {
-          pts.push_back(recs[k].x);
-          pts.push_back(recs[k].y);
-          pts.push_back(recs[k].z);
-        }
-    return fit_plane(pts.data(), (int64_t)pts.size() / 3, out);
-  };
-  // the plane fits (one small SVD per residue, two for ring residues) are independent: all host threads
+  std::vector<int8_t> el_class((size_t)n, 0);
   struct ResPlanes {
     Plane ring, sc;
     bool ok_ring, ok_sc, ring_res;
   };
-  std::vector<ResPlanes> planes(all_res.size());
+  std::vector<ResPlanes> planes((size_t)n_res);
+  std::vector<uint32_t> res_atoms((size_t)n_res + 1, 0u), res_h((size_t)n_res + 1, 0u);  // counts, then offsets
+  auto residue_plane = [&](const ResT& R, uint32_t want, Plane& out) {  // thread-safe: reads only
+    double small[3 * 32] = {};  // a residue's ring / side-chain atoms: a dozen at most (the vector is for the odd giant)
+    std::vector<double> big;
+    int64_t np = 0;
+    for (auto& c : R.confs)
+      for (int64_t k : c.recs)
+        if (bits_res[k] & want) {
+          if (np < 32 && big.empty()) {
+            small[3 * np] = recs[k].x, small[3 * np + 1] = recs[k].y, small[3 * np + 2] = recs[k].z;
+          } else {
+            if (big.empty()) big.assign(small, small + 3 * np);
+            big.push_back(recs[k].x);
+            big.push_back(recs[k].y);
+            big.push_back(recs[k].z);
+          }
+          ++np;
+        }
+    return fit_plane(big.empty() ? small : big.data(), np, out);
+  };
   {
     std::vector<char> ring_name_flag(P.strings.size(), 0);
     for (size_t i = 0; i < P.strings.size(); ++i) ring_name_flag[i] = is_ring_residue_name(P.strings[i]) ? 1 : 0;
-    const int64_t nres_all = (int64_t)all_res.size();
-#pragma omp parallel for schedule(static, 32) if (nres_all > 256)  // ~1 us per plane fit: worth the fork from a few hundred residues on
-    for (int64_t i = 0; i < nres_all; ++i) {
-      const ResT& R = *all_res[i];
-      ResPlanes& o = planes[i];
-      o.ring_res = ring_name_flag[uniform_name(R)] != 0;
-      o.ok_ring = o.ring_res && residue_plane(R, T_RING, o.ring);
-      o.ok_sc = residue_plane(R, T_SCP, o.sc);
-    }
-  }
-  using PKey = std::array<int64_t, 5>;  // chain, resi, icode, altloc, resn
-  std::map<PKey, Plane> last_ring, last_sc;
-  if (quirk) {
-    size_t ri_all = 0;
-    for (auto& M : models)
-      for (auto& Cn : M.chains)
-        for (auto& R : Cn.residues) {
-          const int32_t nm = uniform_name(R);
-          const ResPlanes& pl = planes[ri_all++];
-          for (auto& c : R.confs) {
-            const PKey key{Cn.id, R.resi, R.icode, c.altloc, nm};
-            if (pl.ok_ring) last_ring[key] = pl.ring;
-            if (pl.ok_sc) last_sc[key] = pl.sc;
-          }
-        }
-  }
-
-  // ---- 6. flatten in atoms_with_hierarchy() order ------------------------------------------------------
-  int64_t n_atoms = 0, n_res = 0;
-  for (auto& M : models)
-    for (auto& Cn : M.chains) {
-      n_res += (int64_t)Cn.residues.size();
-      for (auto& R : Cn.residues)
-        for (auto& c : R.confs) n_atoms += (int64_t)c.recs.size();
-    }
-  P.x.reserve(n_atoms);
-  P.y.reserve(n_atoms);
-  P.z.reserve(n_atoms);
-  P.attr.reserve(n_atoms);
-  P.chain_key.reserve(n_atoms);
-  P.res_ordinal.reserve(n_atoms);
-  P.res_id.reserve(n_atoms);
-  P.atom_rc.reserve(n_atoms);
-  P.atom_name.reserve(n_atoms);
-  P.atom_serial.reserve(n_atoms);
-  P.res_h_begin.reserve(n_res + 1);
-  P.res_cb.reserve(n_res);
-  P.res_sg.reserve(n_res);
-
-  const int32_t id_CB = P.intern("CB"), id_SG = P.intern("SG"), id_C = P.intern("C"), id_CYS = P.intern("CYS");
-  char last_el[4] = {1};
-  int last_el_class = -2;
-  size_t res_all = 0;  // index into planes[]
-
-  for (size_t mi = 0; mi < models.size(); ++mi) {
-    const ModelT& M = models[mi];
-    for (auto& Cn : M.chains) {
-      const std::string chain_str = P.strings[Cn.id];  // by value: intern() below may reallocate P.strings
-      const uint32_t group_bits = (ligand.count(chain_str) ? ARP_ATTR_LIGAND : 0u) | (receptor.count(chain_str) ? ARP_ATTR_RECEPTOR : 0u);
-      const uint32_t ckey = ((uint32_t)mi << 24) | chain_rank[Cn.id];
-      for (size_t ordinal = 0; ordinal < Cn.residues.size(); ++ordinal) {
-        const ResT& R = Cn.residues[ordinal];
-        const int32_t resn_id = uniform_name(R);
-        const std::string resn = P.strings[resn_id];
-        const uint32_t rid = (uint32_t)P.res_cb.size();
-        P.res_cb.push_back(-1);
-        P.res_sg.push_back(-1);
-        P.res_h_begin.push_back((uint32_t)P.hx.size());
-        const ResPlanes& pl = planes[res_all++];
-        Plane pr{}, ps{};
-        bool okr = false, oks = false;
-        const bool ring_res = pl.ring_res;
-        if (!quirk) {
-          okr = pl.ok_ring, oks = pl.ok_sc;
-          pr = pl.ring, ps = pl.sc;
-        }
-        for (auto& c : R.confs) {
-          if (quirk) {
-            const PKey key{Cn.id, R.resi, R.icode, c.altloc, resn_id};
-            auto ir = last_ring.find(key);
-            okr = ir != last_ring.end();
-            if (okr) pr = ir->second;
-            auto is = last_sc.find(key);
-            oks = is != last_sc.end();
-            if (oks) ps = is->second;
-          }
-          const uint32_t rc = (uint32_t)P.resconfs.size();
-          Packed::ResConf rcx;
-          rcx.chain = Cn.id;
-          rcx.resn = resn_id;
-          rcx.icode = R.icode;
-          rcx.altloc = c.altloc;
-          rcx.resi = R.resi;
-          rcx.model_serial = M.serial;
-          rcx.has_sc = oks;
-          rcx.sc = ps;
-          P.resconfs.push_back(rcx);
-          if (okr) {
-            for (int k = 0; k < 3; ++k) {
-              P.ring_c.push_back(pr.c[k]);
-              P.ring_n.push_back(pr.n[k]);
-            }
-            P.ring_attr.push_back(group_bits);
-            P.ring_chain_key.push_back(ckey);
-            P.ring_res_ordinal.push_back((uint32_t)ordinal);
-            P.ring_rc.push_back(rc);
-          } else if (ring_res && (!quirk || mi == 0)) {
-            P.warnings.push_back("Failed to calculate ring position for chain " + chain_str + " residue " + resn + " " +
-                                 std::to_string(R.resi) + P.strings[R.icode]);
-          }
+#pragma omp parallel num_threads(host_threads) if (n_res > 256)  // ~1 us per plane fit: worth the fork from a few hundred residues on
+    {
+      std::unordered_map<uint64_t, uint32_t> bits_cache;
+      char last_el[4] = {1};
+      int last_el_class = -2;
+#pragma omp for schedule(static, 64)
+      for (int64_t i = 0; i < n_res; ++i) {
+        const ResT& R = *all_res[i].r;
+        const int32_t nm = uniform_name(R);
+        int32_t last_atom = -1;
+        uint32_t last_bits = 0, na = 0, nhyd = 0;
+        for (auto& c : R.confs)
           for (int64_t k : c.recs) {
+            if (name_id[k] != last_atom) {
+              last_atom = name_id[k];
+              const uint64_t key = ((uint64_t)(uint32_t)nm << 32) | (uint32_t)last_atom;
+              auto it = bits_cache.find(key);
+              if (it == bits_cache.end()) it = bits_cache.emplace(key, table_bits(P.strings[nm], P.strings[last_atom])).first;
+              last_bits = it->second;
+            }
+            bits_res[k] = last_bits;
             const arp_atom_record& a = recs[k];
-            const int32_t last_name_id = name_id[k];
             if (std::memcmp(last_el, a.element, 4) != 0 || last_el_class == -2) {
               std::memcpy(last_el, a.element, 4);
               last_el_class = arp_element_class(fixed_field(a.element, 4).c_str());
             }
-            if (last_el_class < 0) {
-              const std::string el = fixed_field(a.element, 4);
-              throw Error{ARP_ERR_ELEMENT, el.empty() ? "atom " + std::to_string(a.serial) + " has no element"
-                                                      : "unsupported element '" + el + "' (not one of the element classes this path knows; pdbtbx would need a van der Waals radius for it, vdw.rs:28)"};
-            }
-            const uint32_t by_res = bits_res[k];                      // residue().name(): hydrophobic.rs:16, aromatic.rs:18, vdw.rs:50
-            const uint32_t by_conf = c.name == resn_id ? by_res : bits_of(c.name, last_name_id);  // conformer().name(): ionic.rs:45-46, hbond.rs:120-121
-            uint32_t w = (uint32_t)last_el_class | group_bits;
-            if (by_conf & T_POS) w |= ARP_ATTR_POS_CONF;
-            if (by_conf & T_NEG) w |= ARP_ATTR_NEG_CONF;
-            if (by_conf & T_DON) w |= ARP_ATTR_DONOR;
-            if (by_conf & T_ACC) w |= ARP_ATTR_ACCEPTOR;
-            if (by_res & T_POS) w |= ARP_ATTR_POS_RES;
-            if (by_res & T_HYD) w |= ARP_ATTR_HYDROPHOBIC;
-            if (last_el_class == 1 && last_name_id != id_C) w |= ARP_ATTR_WEAK_DONOR;  // hbond.rs:204-207 (class 1 = carbon)
-            if (resn_id == id_CYS && last_name_id == id_SG) w |= ARP_ATTR_CYS_SG;
-            const int32_t idx = (int32_t)P.x.size();
-            if (last_el_class == 0) {  // hydrogen: joins the residue's H list (hbond.rs:38-42)
-              P.hx.push_back(a.x);
-              P.hy.push_back(a.y);
-              P.hz.push_back(a.z);
-            }
-            if (last_name_id == id_CB && P.res_cb[rid] < 0) P.res_cb[rid] = idx;  // vdw.rs:55-74 `.find()` = first match
-            if (last_name_id == id_SG && P.res_sg[rid] < 0) P.res_sg[rid] = idx;
-            P.x.push_back(a.x);
-            P.y.push_back(a.y);
-            P.z.push_back(a.z);
-            P.attr.push_back(w);
-            P.chain_key.push_back(ckey);
-            P.res_ordinal.push_back((uint32_t)ordinal);
-            P.res_id.push_back(rid);
-            P.atom_rc.push_back(rc);
-            P.atom_name.push_back(last_name_id);
-            P.atom_serial.push_back(a.serial);
+            el_class[k] = (int8_t)last_el_class;  // < 0: unknown element, reported in phase 6 for the first such atom
+            na += 1;
+            nhyd += last_el_class == 0 ? 1u : 0u;
           }
-        }
+        res_atoms[i] = na;
+        res_h[i] = nhyd;
+        ResPlanes& o = planes[i];
+        o.ring_res = ring_name_flag[nm] != 0;
+        o.ok_ring = o.ring_res && residue_plane(R, T_RING, o.ring);
+        o.ok_sc = residue_plane(R, T_SCP, o.sc);
       }
     }
   }
-  P.res_h_begin.push_back((uint32_t)P.hx.size());
+  clk.mark("4-5 groups, bits, plane fits");
+  using PKey = std::array<int64_t, 5>;  // chain, resi, icode, altloc, resn
+  std::map<PKey, Plane> last_ring, last_sc;
+  if (quirk) {
+    for (int64_t i = 0; i < n_res; ++i) {
+      const ResT& R = *all_res[i].r;
+      const ChainT& Cn = *chains[all_res[i].chain].c;
+      const int32_t nm = uniform_name(R);
+      const ResPlanes& pl = planes[i];
+      for (auto& c : R.confs) {
+        const PKey key{Cn.id, R.resi, R.icode, c.altloc, nm};
+        if (pl.ok_ring) last_ring[key] = pl.ring;
+        if (pl.ok_sc) last_sc[key] = pl.sc;
+      }
+    }
+  }
+
+  // ---- 6. flatten in atoms_with_hierarchy() order ------------------------------------------------------
+  // Where every residue's atoms, hydrogens, conformers and rings start in the flat arrays: counts per residue (the atom
+  // and hydrogen counts come from phase 5), one prefix sum, then every residue writes its own ranges -- on all host threads.
+  std::vector<uint32_t> res_rc((size_t)n_res + 1, 0u), res_ring((size_t)n_res + 1, 0u);
+  std::vector<uint8_t> conf_ring;  // per conformer (filled below): bit 0 = has a ring plane, bit 1 = has a side-chain plane
+  {
+    for (int64_t i = 0; i < n_res; ++i) res_rc[i] = (uint32_t)all_res[i].r->confs.size();
+    uint32_t at = 0;
+    for (int64_t i = 0; i <= n_res; ++i) {
+      const uint32_t c = i < n_res ? res_rc[i] : 0u;
+      res_rc[i] = at;
+      at += c;
+    }
+    conf_ring.assign(at, 0);
+  }
+  const int64_t n_rc = res_rc[n_res];
+  std::vector<const Plane*> conf_pr((size_t)n_rc, nullptr), conf_ps((size_t)n_rc, nullptr);
+#pragma omp parallel for schedule(static, 256) num_threads(host_threads) if (n_res > 4096)
+  for (int64_t i = 0; i < n_res; ++i) {
+    const ResT& R = *all_res[i].r;
+    const ResPlanes& pl = planes[i];
+    uint32_t rings = 0;
+    for (size_t ck = 0; ck < R.confs.size(); ++ck) {
+      const size_t rc = res_rc[i] + ck;
+      const Plane *pr = nullptr, *ps = nullptr;
+      if (!quirk) {
+        pr = pl.ok_ring ? &pl.ring : nullptr;
+        ps = pl.ok_sc ? &pl.sc : nullptr;
+      } else {  // the maps hold what the LAST model left under this key (complex.rs:447-449)
+        const PKey key{chains[all_res[i].chain].c->id, R.resi, R.icode, R.confs[ck].altloc, uniform_name(R)};
+        auto ir = last_ring.find(key);
+        if (ir != last_ring.end()) pr = &ir->second;
+        auto is = last_sc.find(key);
+        if (is != last_sc.end()) ps = &is->second;
+      }
+      conf_pr[rc] = pr, conf_ps[rc] = ps;
+      conf_ring[rc] = (uint8_t)((pr ? 1 : 0) | (ps ? 2 : 0));
+      rings += pr ? 1u : 0u;
+    }
+    res_ring[i] = rings;
+  }
+  {
+    uint32_t a = 0, h = 0, g = 0;
+    for (int64_t i = 0; i <= n_res; ++i) {
+      const uint32_t ca = i < n_res ? res_atoms[i] : 0u, ch = i < n_res ? res_h[i] : 0u, cg = i < n_res ? res_ring[i] : 0u;
+      res_atoms[i] = a, res_h[i] = h, res_ring[i] = g;
+      a += ca, h += ch, g += cg;
+    }
+  }
+  const int64_t n_atoms = res_atoms[n_res], n_h = res_h[n_res], n_rings = res_ring[n_res];
+  P.x.resize(n_atoms), P.y.resize(n_atoms), P.z.resize(n_atoms);
+  P.attr.resize(n_atoms), P.chain_key.resize(n_atoms), P.res_ordinal.resize(n_atoms), P.res_id.resize(n_atoms);
+  P.atom_rc.resize(n_atoms), P.atom_name.resize(n_atoms), P.atom_serial.resize(n_atoms);
+  P.hx.resize(n_h), P.hy.resize(n_h), P.hz.resize(n_h);
+  P.res_h_begin.assign(res_h.begin(), res_h.end());  // n_res + 1 entries, the last one closes the CSR
+  P.res_cb.assign((size_t)n_res, -1), P.res_sg.assign((size_t)n_res, -1);
+  P.resconfs.resize((size_t)n_rc);
+  P.ring_c.resize(3 * n_rings), P.ring_n.resize(3 * n_rings);
+  P.ring_attr.resize(n_rings), P.ring_chain_key.resize(n_rings), P.ring_res_ordinal.resize(n_rings), P.ring_rc.resize(n_rings);
+
+  const int32_t id_CB = P.intern("CB"), id_SG = P.intern("SG"), id_C = P.intern("C"), id_CYS = P.intern("CYS");
+  // per chain: group bits and key
+  std::vector<uint32_t> chain_bits((size_t)n_chains_all), chain_ckey((size_t)n_chains_all);
+  for (int64_t ci = 0; ci < n_chains_all; ++ci) {
+    const std::string& chain_str = P.strings[chains[ci].c->id];
+    chain_bits[ci] = (ligand.count(chain_str) ? ARP_ATTR_LIGAND : 0u) | (receptor.count(chain_str) ? ARP_ATTR_RECEPTOR : 0u);
+    chain_ckey[ci] = ((uint32_t)chains[ci].mi << 24) | chain_rank[chains[ci].c->id];
+  }
+  int64_t first_bad_atom = INT64_MAX;  // flat index of the first atom with an element this path does not know
+#pragma omp parallel for schedule(static, 256) num_threads(host_threads) reduction(min : first_bad_atom) if (n_res > 4096)
+  for (int64_t i = 0; i < n_res; ++i) {
+    const ResT& R = *all_res[i].r;
+    const uint32_t ci = all_res[i].chain, ordinal = all_res[i].ordinal;
+    const ChainT& Cn = *chains[ci].c;
+    const int64_t model_serial = models[chains[ci].mi].serial;
+    const int32_t resn_id = uniform_name(R);
+    const uint32_t group_bits = chain_bits[ci], ckey = chain_ckey[ci], rid = (uint32_t)i;
+    int64_t at = res_atoms[i], ah = res_h[i], ag = res_ring[i];
+    for (size_t ck = 0; ck < R.confs.size(); ++ck) {
+      const ConfT& c = R.confs[ck];
+      const uint32_t rc = res_rc[i] + (uint32_t)ck;
+      Packed::ResConf& rcx = P.resconfs[rc];
+      rcx.chain = Cn.id;
+      rcx.resn = resn_id;
+      rcx.icode = R.icode;
+      rcx.altloc = c.altloc;
+      rcx.resi = R.resi;
+      rcx.model_serial = model_serial;
+      rcx.has_sc = conf_ps[rc] != nullptr;
+      rcx.sc = conf_ps[rc] ? *conf_ps[rc] : Plane{};
+      if (conf_pr[rc]) {
+        for (int k = 0; k < 3; ++k) {
+          P.ring_c[3 * ag + k] = conf_pr[rc]->c[k];
+          P.ring_n[3 * ag + k] = conf_pr[rc]->n[k];
+        }
+        P.ring_attr[ag] = group_bits;
+        P.ring_chain_key[ag] = ckey;
+        P.ring_res_ordinal[ag] = ordinal;
+        P.ring_rc[ag] = rc;
+        ++ag;
+      }
+      for (int64_t k : c.recs) {
+        const arp_atom_record& a = recs[k];
+        const int32_t atom_name = name_id[k];
+        const int cls = el_class[k];
+        if (cls < 0) first_bad_atom = std::min(first_bad_atom, at);
+        const uint32_t by_res = bits_res[k], by_conf = by_res;  // see phase 5: the conformer's name is the residue's
+        uint32_t w = (uint32_t)(cls < 0 ? 0 : cls) | group_bits;
+        if (by_conf & T_POS) w |= ARP_ATTR_POS_CONF;
+        if (by_conf & T_NEG) w |= ARP_ATTR_NEG_CONF;
+        if (by_conf & T_DON) w |= ARP_ATTR_DONOR;
+        if (by_conf & T_ACC) w |= ARP_ATTR_ACCEPTOR;
+        if (by_res & T_POS) w |= ARP_ATTR_POS_RES;
+        if (by_res & T_HYD) w |= ARP_ATTR_HYDROPHOBIC;
+        if (cls == 1 && atom_name != id_C) w |= ARP_ATTR_WEAK_DONOR;  // hbond.rs:204-207 (class 1 = carbon)
+        if (resn_id == id_CYS && atom_name == id_SG) w |= ARP_ATTR_CYS_SG;
+        if (cls == 0) {  // hydrogen: joins the residue's H list (hbond.rs:38-42)
+          P.hx[ah] = a.x, P.hy[ah] = a.y, P.hz[ah] = a.z;
+          ++ah;
+        }
+        if (atom_name == id_CB && P.res_cb[rid] < 0) P.res_cb[rid] = (int32_t)at;  // vdw.rs:55-74 `.find()` = first match
+        if (atom_name == id_SG && P.res_sg[rid] < 0) P.res_sg[rid] = (int32_t)at;
+        P.x[at] = a.x, P.y[at] = a.y, P.z[at] = a.z;
+        P.attr[at] = w;
+        P.chain_key[at] = ckey;
+        P.res_ordinal[at] = ordinal;
+        P.res_id[at] = rid;
+        P.atom_rc[at] = rc;
+        P.atom_name[at] = atom_name;
+        P.atom_serial[at] = a.serial;
+        ++at;
+      }
+    }
+  }
+  if (first_bad_atom != INT64_MAX) {
+    // the record behind that flat index: walk its residue once more
+    int64_t i = (int64_t)(std::upper_bound(res_atoms.begin(), res_atoms.end(), (uint32_t)first_bad_atom) - res_atoms.begin()) - 1;
+    int64_t at = res_atoms[i];
+    for (auto& c : all_res[i].r->confs)
+      for (int64_t k : c.recs)
+        if (at++ == first_bad_atom) {
+          const std::string el = fixed_field(recs[k].element, 4);
+          throw Error{ARP_ERR_ELEMENT, el.empty() ? "atom " + std::to_string(recs[k].serial) + " has no element"
+                                                  : "unsupported element '" + el + "' (not one of the element classes this path knows; pdbtbx would need a van der Waals radius for it, vdw.rs:28)"};
+        }
+  }
+  // ring residues without a ring plane (mod.rs:64-68 logs them), in hierarchy order
+  for (int64_t i = 0; i < n_res; ++i) {
+    if (!planes[i].ring_res) continue;
+    const ResT& R = *all_res[i].r;
+    const ChainRef& cr = chains[all_res[i].chain];
+    for (size_t ck = 0; ck < R.confs.size(); ++ck)
+      if (!(conf_ring[res_rc[i] + ck] & 1) && (!quirk || cr.mi == 0))
+        P.warnings.push_back("Failed to calculate ring position for chain " + P.strings[cr.c->id] + " residue " + P.strings[uniform_name(R)] + " " +
+                             std::to_string(R.resi) + P.strings[R.icode]);
+  }
   if (P.ring_rc.empty()) throw Error{ARP_ERR_NO_RINGS, "Error building ring positions"};  // complex.rs:50
   P.ring_name = P.intern("Ring");
+  clk.mark("6 flatten");
   P.finish();
+  clk.mark("7 finish");
+  // the hierarchy is a few hundred thousand small vectors: freed on all threads rather than by one destructor at the
+  // end, every chain by the thread that allocated most of it in phase 1 (its own malloc arena: no lock traffic)
+#pragma omp parallel num_threads(host_threads) if (n > 65536)
+  {
+    const int me = omp_get_thread_num(), team = omp_get_num_threads();
+    for (int64_t ci = 0; ci < n_chains_all; ++ci)
+      if (chains[ci].c->owner % team == me) std::vector<ResT>().swap(chains[ci].c->residues);
+  }
+  clk.mark("8 release");
 }
 
 void Packed::finish() {
@@ -548,53 +761,81 @@ void Packed::finish() {
   t.ring_attr = ring_attr.data();
   t.ring_chain_key = ring_chain_key.data();
   t.ring_res_ordinal = ring_res_ordinal.data();
+  const int64_t na = (int64_t)res_id.size(), nr = (int64_t)res_cb.size();
+  const bool big = na > 65536 && !omp_in_parallel();  // the loops over the atoms run on every host thread
+  // atoms_with_hierarchy() order keeps the atoms of a residue together: res_id as a CSR (left out if it ever does not)
+  t.res_atom_begin = nullptr;
+  {
+    int grouped = 1;
+#pragma omp parallel for schedule(static) reduction(& : grouped) if (big)
+    for (int64_t a = 1; a < na; ++a) grouped &= (res_id[a] == res_id[a - 1] || res_id[a] == res_id[a - 1] + 1) ? 1 : 0;
+    if (grouped && (res_id.empty() || (res_id.front() == 0 && (int64_t)res_id.back() + 1 == nr))) {
+      res_atom_begin.assign((size_t)nr + 1, 0u);
+#pragma omp parallel for schedule(static) if (big)
+      for (int64_t a = 0; a < na; ++a)
+        if (a == 0 || res_id[a] != res_id[a - 1]) res_atom_begin[res_id[a]] = (uint32_t)a;  // every residue id occurs (grouped, 0 .. nr-1)
+      res_atom_begin[nr] = (uint32_t)na;
+      t.res_atom_begin = res_atom_begin.data();
+    }
+  }
   // compact per-residue form of chain_key / res_ordinal (what the device path uploads when it is present)
-  res_chain_key.assign(res_cb.size(), 0u);
-  res_res_ordinal.assign(res_cb.size(), 0u);
-  for (size_t a = 0; a < res_id.size(); ++a) {
-    res_chain_key[res_id[a]] = chain_key[a];
-    res_res_ordinal[res_id[a]] = res_ordinal[a];
+  res_chain_key.assign((size_t)nr, 0u);
+  res_res_ordinal.assign((size_t)nr, 0u);
+  if (t.res_atom_begin) {
+#pragma omp parallel for schedule(static) if (big)
+    for (int64_t r = 0; r < nr; ++r) {
+      const uint32_t a = res_atom_begin[r];
+      res_chain_key[r] = chain_key[a];
+      res_res_ordinal[r] = res_ordinal[a];
+    }
+  } else {
+    for (size_t a = 0; a < res_id.size(); ++a) {
+      res_chain_key[res_id[a]] = chain_key[a];
+      res_res_ordinal[res_id[a]] = res_ordinal[a];
+    }
   }
   t.res_chain_key = res_chain_key.data();
   t.res_res_ordinal = res_res_ordinal.data();
   // residue tags (arp_structure.res_tag): the residues of a chain are contiguous and in ordinal order here, so a running
   // count that steps by 1 inside a chain (consecutive ordinals) and by 2 otherwise has the required property
-  res_tag.assign(res_cb.size(), 0u);
-  for (size_t r = 1; r < res_cb.size(); ++r)
+  res_tag.assign((size_t)nr, 0u);
+  for (int64_t r = 1; r < nr; ++r)
     res_tag[r] = res_tag[r - 1] + ((res_chain_key[r] == res_chain_key[r - 1] && res_res_ordinal[r] == res_res_ordinal[r - 1] + 1u) ? 1u : 2u);
   t.res_tag = res_tag.data();
   t.atom_gid = atom_gid.empty() ? nullptr : atom_gid.data();
   t.ring_gid = ring_gid.empty() ? nullptr : ring_gid.data();
-  // atoms_with_hierarchy() order keeps the atoms of a residue together: res_id as a CSR (left out if it ever does not)
-  t.res_atom_begin = nullptr;
-  {
-    bool grouped = true;
-    for (size_t a = 1; a < res_id.size() && grouped; ++a) grouped = res_id[a] == res_id[a - 1] || res_id[a] == res_id[a - 1] + 1;
-    if (grouped && (res_id.empty() || (res_id.front() == 0 && (size_t)res_id.back() + 1 == res_cb.size()))) {
-      res_atom_begin.assign(res_cb.size() + 1, 0u);
-      for (uint32_t r : res_id) res_atom_begin[r + 1] += 1;
-      for (size_t r = 0; r < res_cb.size(); ++r) res_atom_begin[r + 1] += res_atom_begin[r];
-      t.res_atom_begin = res_atom_begin.data();
-    }
-  }
   // on-lattice form of the coordinates (arp_structure.x_milli): offered only when EVERY coordinate is bit for bit the
   // double (double)v / 1000.0 of a 32-bit v -- true for anything read from PDB fixed columns -- so the device rebuilds the
-  // same f64 values from half the bytes
+  // same f64 values from half the bytes.  The bounding-box hint for the cell-grid layout (verified on the device) comes
+  // out of the same pass.
   t.x_milli = t.y_milli = t.z_milli = nullptr;
-  {
-    bool lattice = !x.empty();
-    for (int a = 0; a < 3 && lattice; ++a) {
-      const std::vector<double>& v = a == 0 ? x : (a == 1 ? y : z);
-      std::vector<int32_t>& m = a == 0 ? x_milli : (a == 1 ? y_milli : z_milli);
-      m.resize(v.size());
-      for (size_t k = 0; k < v.size(); ++k) {
-        const double q = v[k] * 1000.0;
-        if (!(q > -2147483000.0 && q < 2147483000.0)) { lattice = false; break; }
-        const int32_t r = (int32_t)std::llrint(q);
-        if ((double)r / 1000.0 != v[k] || (r == 0 && std::signbit(v[k]))) { lattice = false; break; }
+  t.has_bbox = 0;
+  if (na > 0) {
+    x_milli.resize((size_t)na), y_milli.resize((size_t)na), z_milli.resize((size_t)na);
+    int lattice = 1, finite = 1;
+    for (int axis = 0; axis < 3; ++axis) {
+      const double* v = axis == 0 ? x.data() : (axis == 1 ? y.data() : z.data());
+      int32_t* m = axis == 0 ? x_milli.data() : (axis == 1 ? y_milli.data() : z_milli.data());
+      double lo = v[0], hi = v[0];
+#pragma omp parallel for schedule(static) reduction(& : lattice, finite) reduction(min : lo) reduction(max : hi) if (big)
+      for (int64_t k = 0; k < na; ++k) {
+        const double c = v[k], q = c * 1000.0;
+        if (!(c == c) || c - c != 0.0) finite = 0;
+        lo = c < lo ? c : lo;
+        hi = c > hi ? c : hi;
+        int32_t r = 0;
+        bool ok = q > -2147483000.0 && q < 2147483000.0;
+        if (ok) {
+          r = (int32_t)std::llrint(q);
+          ok = (double)r / 1000.0 == c && !(r == 0 && std::signbit(c));
+        }
+        if (!ok) lattice = 0;
         m[k] = r;
       }
+      t.bbox_min[axis] = lo;
+      t.bbox_max[axis] = hi;
     }
+    t.has_bbox = finite ? 1 : 0;
     if (lattice) {
       t.x_milli = x_milli.data();
       t.y_milli = y_milli.data();
@@ -602,23 +843,6 @@ void Packed::finish() {
     } else {
       x_milli.clear(), y_milli.clear(), z_milli.clear();
     }
-  }
-  // bounding-box hint for the cell-grid layout (verified on the device)
-  t.has_bbox = 0;
-  if (!x.empty()) {
-    bool finite = true;
-    for (int a = 0; a < 3; ++a) {
-      const std::vector<double>& v = a == 0 ? x : (a == 1 ? y : z);
-      double lo = v[0], hi = v[0];
-      for (double q : v) {
-        if (!(q == q) || q - q != 0.0) finite = false;
-        lo = q < lo ? q : lo;
-        hi = q > hi ? q : hi;
-      }
-      t.bbox_min[a] = lo;
-      t.bbox_max[a] = hi;
-    }
-    t.has_bbox = finite ? 1 : 0;
   }
 }
 
@@ -704,7 +928,7 @@ int arph_packed_remap_chain_ranks(arph_packed* p, const uint32_t* map, int64_t n
       arp::last_error() = "chain rank beyond 2^24";
       return ARP_ERR_LIMIT;
     }
-  auto fix = [&](std::vector<uint32_t>& v) {
+  auto fix = [&](auto& v) {
     for (auto& k : v) k = (k & 0xff000000u) | map[k & 0x00ffffffu];
   };
   fix(p->p.chain_key);

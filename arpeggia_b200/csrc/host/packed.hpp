@@ -11,12 +11,14 @@ namespace arp {
 
 struct Packed {
   // device SoA (arp_structure points into these)
-  std::vector<double> x, y, z, hx, hy, hz, ring_c, ring_n;
-  std::vector<uint32_t> attr, chain_key, res_ordinal, res_id, res_h_begin, ring_attr, ring_chain_key, ring_res_ordinal;
+  RawVec<double> x, y, z;  // (the per-atom arrays: resized once, filled by every host thread -- RawVec, common.hpp)
+  std::vector<double> hx, hy, hz, ring_c, ring_n;
+  RawVec<uint32_t> attr, chain_key, res_ordinal, res_id;
+  std::vector<uint32_t> res_h_begin, ring_attr, ring_chain_key, ring_res_ordinal;
   std::vector<uint32_t> res_chain_key, res_res_ordinal;  // per residue (compact form of chain_key / res_ordinal)
   std::vector<uint32_t> res_atom_begin;                  // CSR of the residues' atoms (compact form of res_id)
   std::vector<int32_t> res_cb, res_sg;
-  std::vector<int32_t> x_milli, y_milli, z_milli;        // on-lattice form of x / y / z (empty when a coordinate is off the lattice)
+  RawVec<int32_t> x_milli, y_milli, z_milli;        // on-lattice form of x / y / z (empty when a coordinate is off the lattice)
   std::vector<uint32_t> res_tag;                         // per residue: |tag difference| <= 1 <=> same chain, ordinals <= 1 apart
   std::vector<uint32_t> atom_gid, ring_gid;              // ids in a larger structure (arph_packed_set_global_ids); empty = none
   std::vector<std::string> chain_by_rank;                // chain ids in byte order = the low 24 bits of chain_key
@@ -29,10 +31,10 @@ struct Packed {
     bool has_sc;
     Plane sc;  // build_sc_plane_positions, complex.rs:486-514
   };
-  std::vector<ResConf> resconfs;
-  std::vector<uint32_t> atom_rc;     // per atom -> resconfs
-  std::vector<int32_t> atom_name;    // per atom -> strings
-  std::vector<int64_t> atom_serial;  // per atom
+  RawVec<ResConf> resconfs;
+  RawVec<uint32_t> atom_rc;     // per atom -> resconfs
+  RawVec<int32_t> atom_name;    // per atom -> strings
+  RawVec<int64_t> atom_serial;  // per atom
   std::vector<uint32_t> ring_rc;     // per ring -> resconfs
   int32_t ring_name = -1;            // id of "Ring"
 

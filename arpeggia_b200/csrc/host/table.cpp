@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <numeric>
 #include <vector>
@@ -99,6 +100,7 @@ void label_ranks(int32_t* lrank) {  // the interaction column is a string: sort 
 // reference leaves open by entity order -- build_table below uses the same order, so both paths give the same frame.
 void build_frame_tables(const Packed& P, FrameTables& T) {
   NvtxRange nvtx_("arph:frame_tables");
+  PhaseClock clk;
   const std::vector<int32_t> srank = string_ranks(P);
   const size_t n_sides = P.resconfs.size(), n_atoms = P.x.size(), n_rings = P.ring_rc.size(), E = n_atoms + n_rings;
   T.sides.assign(n_sides, arp_frame_side{});
@@ -106,11 +108,17 @@ void build_frame_tables(const Packed& P, FrameTables& T) {
   std::vector<uint8_t> side_bad(n_sides, 0);
   {  // chain_rank: dense rank of (model serial, chain id bytes)
     std::vector<std::pair<int64_t, int32_t>> keys(n_sides);
+#pragma omp parallel for schedule(static) if (n_sides > 16384)
     for (size_t k = 0; k < n_sides; ++k) keys[k] = {P.resconfs[k].model_serial, srank[P.resconfs[k].chain]};
-    std::vector<std::pair<int64_t, int32_t>> uniq(keys);
+    // the distinct (model, chain) pairs: residues of a chain follow one another, so the list of pairs that differ from
+    // their predecessor is short; sorted and made unique it is the rank table
+    std::vector<std::pair<int64_t, int32_t>> uniq;
+    for (size_t k = 0; k < n_sides; ++k)
+      if (k == 0 || keys[k] != keys[k - 1]) uniq.push_back(keys[k]);
     std::sort(uniq.begin(), uniq.end());
     uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
     T.t.n_chain_ranks = (uint32_t)std::max<size_t>(uniq.size(), 1);
+#pragma omp parallel for schedule(static) if (n_sides > 16384)
     for (size_t k = 0; k < n_sides; ++k) {
       const Packed::ResConf& r = P.resconfs[k];
       arp_frame_side& s = T.sides[k];
@@ -124,6 +132,7 @@ void build_frame_tables(const Packed& P, FrameTables& T) {
         for (int a = 0; a < 3; ++a) T.side_sc[6 * k + a] = r.sc.c[a], T.side_sc[6 * k + 3 + a] = r.sc.n[a];
     }
   }
+  clk.mark("t1 sides");
   T.ent_side.resize(E);
   T.ent_atomn.resize(E);
   T.ent_atomi.resize(E);
@@ -137,7 +146,8 @@ void build_frame_tables(const Packed& P, FrameTables& T) {
     int32_t alt;
     uint32_t id;
   };
-  std::vector<Key> keys(E);
+  std::unique_ptr<Key[]> keys_store(new Key[std::max<size_t>(E, 1)]);  // (no zero fill: every element is written below)
+  Key* keys = keys_store.get();
 #pragma omp parallel for schedule(static) if (E > 65536)
   for (size_t e = 0; e < E; ++e) {
     const bool ring = e >= n_atoms;
@@ -150,6 +160,7 @@ void build_frame_tables(const Packed& P, FrameTables& T) {
     T.ent_tie[e] = bad ? ARP_ENT_NARROW : 0u;
     keys[e] = Key{P.resconfs[rc].resi, serial, T.sides[rc].chain_rank, srank[P.resconfs[rc].altloc], (uint32_t)e};
   }
+  clk.mark("t2 entity keys");
   const auto key_less = [](const Key& a, const Key& b) {  // a total order (id breaks every tie): one result on any number of threads
     if (a.chain != b.chain) return a.chain < b.chain;
     if (a.resi != b.resi) return a.resi < b.resi;
@@ -157,12 +168,68 @@ void build_frame_tables(const Packed& P, FrameTables& T) {
     if (a.atomi != b.atomi) return a.atomi < b.atomi;
     return a.id < b.id;
   };
-  // The chain rank leads the key: entities are bucketed by chain first (a stable counting sort, O(E)), then every chain
-  // is put in order on its own, chains in parallel.  Within a chain the atoms come first, in file order -- residue by
-  // residue, serials rising, i.e. usually in key order already -- and its few rings after them: each part is sorted only
-  // if it is not sorted yet, then the two are merged.
+  const auto sort_range = [&](Key* b, Key* e) {
+    if (!std::is_sorted(b, e, key_less)) std::sort(b, e, key_less);
+  };
+  const size_t n_chains = T.t.n_chain_ranks;
+  uint32_t max_tie = 0, max_rank = 0;
+  // ranks of one chain from its atoms [ab, ae) and its rings [rb, re), each in key order: a merge walk, nothing is moved
+  const auto rank_chain = [&](const Key* ab, const Key* ae, const Key* rb, const Key* re, uint32_t& top_rank, uint32_t& top_tie) {
+    uint32_t rank = 0, tie = 0;
+    const Key* prev = nullptr;
+    while (ab != ae || rb != re) {
+      const Key* k = (rb == re || (ab != ae && !key_less(*rb, *ab))) ? ab++ : rb++;
+      if (prev) {
+        if (k->resi == prev->resi && k->alt == prev->alt && k->atomi == prev->atomi) {
+          tie += 1;
+        } else {
+          rank += 1;
+          tie = 0;
+        }
+      }
+      T.ent_rank[k->id] = rank;
+      T.ent_tie[k->id] |= tie;
+      top_rank = std::max(top_rank, rank);
+      top_tie = std::max(top_tie, tie);
+      prev = k;
+    }
+  };
+  // The packer lays the atoms out chain by chain (atoms_with_hierarchy() order) and the rings likewise: a chain is one run
+  // of atoms and at most one run of rings.  Each chain is then ranked where it lies -- its runs put in key order if they
+  // are not yet (within a chain the atoms come residue by residue, serials rising: usually sorted already) -- chains in
+  // parallel.  Anything else (a chain in several runs) goes through a counting sort by chain first.
+  struct Run {
+    size_t begin, end;
+  };
+  std::vector<Run> atom_run(n_chains, Run{0, 0}), ring_run(n_chains, Run{0, 0});
+  bool one_run_each = true;
   {
-    const size_t n_chains = T.t.n_chain_ranks;
+    const auto find_runs = [&](size_t lo, size_t hi, std::vector<Run>& out) {
+      for (size_t e = lo; e < hi && one_run_each;) {
+        size_t f = e + 1;
+        const uint32_t c = keys[e].chain;
+        while (f < hi && keys[f].chain == c) ++f;
+        if (out[c].end != out[c].begin) one_run_each = false;  // the chain has appeared before
+        out[c] = Run{e, f};
+        e = f;
+      }
+    };
+    find_runs(0, n_atoms, atom_run);
+    find_runs(n_atoms, E, ring_run);
+    if (std::getenv("ARPH_TABLES_BUCKET")) one_run_each = false;  // tests: the general path on any input
+  }
+  clk.mark("t3 chain runs");
+  if (one_run_each) {
+#pragma omp parallel for schedule(dynamic, 1) reduction(max : max_rank, max_tie) if (E > 65536 && n_chains > 1)
+    for (size_t c = 0; c < n_chains; ++c) {
+      sort_range(keys + atom_run[c].begin, keys + atom_run[c].end);
+      sort_range(keys + ring_run[c].begin, keys + ring_run[c].end);
+      uint32_t top_rank = 0, top_tie = 0;
+      rank_chain(keys + atom_run[c].begin, keys + atom_run[c].end, keys + ring_run[c].begin, keys + ring_run[c].end, top_rank, top_tie);
+      max_rank = std::max(max_rank, top_rank);
+      max_tie = std::max(max_tie, top_tie);
+    }
+  } else {
     std::vector<size_t> begin(n_chains + 1, 0);
     for (size_t e = 0; e < E; ++e) begin[keys[e].chain + 1] += 1;
     for (size_t c = 0; c < n_chains; ++c) begin[c + 1] += begin[c];
@@ -171,37 +238,19 @@ void build_frame_tables(const Packed& P, FrameTables& T) {
       std::vector<size_t> at(begin.begin(), begin.end() - 1);
       for (size_t e = 0; e < E; ++e) by_chain[at[keys[e].chain]++] = keys[e];
     }
-    keys.swap(by_chain);
-    const auto sort_range = [&](Key* b, Key* e) {
-      if (!std::is_sorted(b, e, key_less)) std::sort(b, e, key_less);
-    };
-#pragma omp parallel for schedule(dynamic, 1) if (E > 65536 && n_chains > 1)
+#pragma omp parallel for schedule(dynamic, 1) reduction(max : max_rank, max_tie) if (E > 65536 && n_chains > 1)
     for (size_t c = 0; c < n_chains; ++c) {
-      Key *b = keys.data() + begin[c], *e = keys.data() + begin[c + 1];
-      Key* mid = std::find_if(b, e, [&](const Key& k) { return k.id >= n_atoms; });  // first ring of the chain
+      Key *b = by_chain.data() + begin[c], *e = by_chain.data() + begin[c + 1];
+      Key* mid = std::find_if(b, e, [&](const Key& k) { return k.id >= n_atoms; });  // first ring of the chain (the sort is stable)
       sort_range(b, mid);
       sort_range(mid, e);
-      if (mid != b && mid != e && key_less(*mid, *(mid - 1))) std::inplace_merge(b, mid, e, key_less);
+      uint32_t top_rank = 0, top_tie = 0;
+      rank_chain(b, mid, mid, e, top_rank, top_tie);
+      max_rank = std::max(max_rank, top_rank);
+      max_tie = std::max(max_tie, top_tie);
     }
   }
-  uint32_t rank = 0, tie = 0, max_tie = 0, max_rank = 0;
-  for (size_t k = 0; k < E; ++k) {
-    if (k > 0 && keys[k].chain == keys[k - 1].chain) {
-      const bool same = keys[k].resi == keys[k - 1].resi && keys[k].alt == keys[k - 1].alt && keys[k].atomi == keys[k - 1].atomi;
-      if (same) {
-        tie += 1;
-      } else {
-        rank += 1;
-        tie = 0;
-      }
-    } else {
-      rank = tie = 0;
-    }
-    T.ent_rank[keys[k].id] = rank;
-    T.ent_tie[keys[k].id] |= tie;
-    max_tie = std::max(max_tie, tie);
-    max_rank = std::max(max_rank, rank);
-  }
+  clk.mark("t5 ranks");
   int32_t lrank[ARP_N_LABELS];
   label_ranks(lrank);
   std::memset(T.t.label_rank, 0, sizeof T.t.label_rank);

@@ -359,3 +359,57 @@ def test_mmcif_reader_pieces_on_all_threads(bft, tmp_path, monkeypatch):
     monkeypatch.setenv("ARPH_CIF_PIECE_BYTES", "700")
     with pytest.raises(A.ArpeggiaError, match="row 5001"):
         A.parse_cif(bad)
+
+
+def _packed_fingerprint(atoms, flags=0, izo=False):
+    """Everything the packer and the side-table builder produce for these records, as comparable arrays."""
+    import ctypes as C
+
+    from arpeggia_b200 import _lib
+
+    p = A.Packed(atoms, "/", ignore_zero_occupancy=izo, flags=flags)
+    out = {k: v for k, v in p.arrays().items() if v is not None}
+    tp = C.POINTER(_lib.FrameTables)()
+    _lib.check(_lib.lib().arph_packed_frame_tables(p._h, C.byref(tp)))
+    t = tp.contents
+    E = t.n_atoms + t.n_rings
+    out["sides"] = np.frombuffer((C.c_char * (32 * t.n_sides)).from_address(C.addressof(t.sides.contents)), dtype=np.uint32).copy() if t.n_sides else np.zeros(0, np.uint32)
+    out["side_sc"] = np.ctypeslib.as_array(t.side_sc, shape=(6 * t.n_sides,)).copy() if t.n_sides else np.zeros(0)
+    for k in ("ent_side", "ent_atomn", "ent_atomi", "ent_rank", "ent_tie"):
+        out[k] = np.ctypeslib.as_array(getattr(t, k), shape=(E,)).copy()
+    out["bounds"] = np.array([t.n_chain_ranks, t.n_ent_ranks, t.max_tie])
+    out["warnings"] = np.array(list(p.warnings), dtype=object)
+    # the string dictionary, through an (empty) table
+    out["strings"] = np.array(p.build_table(np.zeros(0, dtype=A.ROW_DTYPE))["strings"], dtype=object)
+    return out, p
+
+
+@pytest.mark.parametrize("blocks", [2, 7, 64])
+def test_packer_blocks_and_table_paths_give_one_result(ubq, bft, blocks, monkeypatch):
+    """The packer groups the records block by block on the host's threads and joins the blocks; the side tables rank every
+    chain where it lies, or after a counting sort by chain.  Whatever the cut and the path: the same arrays, bit for bit --
+    also for records whose chains, residues and conformers are scattered over the file."""
+    from tests import fixtures as F
+
+    cases = {"1ubq": ubq, "6bft": bft}
+    cases.update({k: v.view(A.ATOM_DTYPE) for k, v in F.all_cases(ubq.view(O.ATOM_DTYPE)).items()})
+    rng = np.random.default_rng(11)
+    scattered = bft[rng.permutation(len(bft))]  # every chain, residue and conformer continues in later blocks
+    cases["scattered"] = scattered
+    by_residue = bft[np.argsort(rng.permutation(bft["resi"].max() + 1)[bft["resi"]], kind="stable")]  # whole residues moved about
+    cases["residues_moved"] = by_residue
+    for name, atoms in cases.items():
+        izo = name == "zero_occupancy"
+        monkeypatch.setenv("ARPH_PACK_BLOCKS", "1")
+        monkeypatch.delenv("ARPH_TABLES_BUCKET", raising=False)
+        want, _ = _packed_fingerprint(atoms, izo=izo)
+        monkeypatch.setenv("ARPH_PACK_BLOCKS", str(blocks))
+        got, _ = _packed_fingerprint(atoms, izo=izo)
+        monkeypatch.setenv("ARPH_TABLES_BUCKET", "1")
+        got2, _ = _packed_fingerprint(atoms, izo=izo)
+        assert set(got) == set(want) == set(got2)
+        for k in want:
+            for g in (got, got2):
+                w = want[k]
+                same = (g[k] == w) if np.isscalar(w) else (np.array_equal(g[k].view(np.uint64), w.view(np.uint64)) if getattr(w, "dtype", None) == np.float64 else np.array_equal(g[k], w))
+                assert same, (name, k, blocks)
