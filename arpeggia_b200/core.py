@@ -243,8 +243,7 @@ def table_to_arrow(tp, strings: str = "string"):
     def text(idx, d):
         if n == 0:
             return pa.array([], type=pa.large_string()) if strings != "dictionary" else pa.DictionaryArray.from_arrays(pa.array([], type=pa.int32()), d)
-        a = pa.DictionaryArray.from_arrays(idx, d, safe=False)  # the library only ever writes ids of its own dictionary
-        return a if strings == "dictionary" else a.dictionary_decode()
+        return pa.DictionaryArray.from_arrays(idx, d, safe=False)  # the library only ever writes ids of its own dictionary
 
     bitmap, n_null = None, 0
     if n:  # the library hands the validity of the sc_* columns over in Arrow's own layout
@@ -265,6 +264,19 @@ def table_to_arrow(tp, strings: str = "string"):
         else:
             a = wrap(getattr(t, name), pa.int32(), 4)
         cols.append(a)
+    if strings != "dictionary" and n:
+        # String columns (the reference's dtype): the eleven decodes are independent and Arrow's C++ releases the GIL, so
+        # on a large frame they run side by side
+        todo = [k for k, a in enumerate(cols) if pa.types.is_dictionary(a.type)]
+        if n >= 100_000:
+            from concurrent.futures import ThreadPoolExecutor
+
+            with ThreadPoolExecutor(max_workers=len(todo)) as ex:
+                done = list(ex.map(lambda k: cols[k].dictionary_decode(), todo))
+        else:
+            done = [cols[k].dictionary_decode() for k in todo]
+        for k, a in zip(todo, done):
+            cols[k] = a
     return pa.table(cols, names=list(COLUMNS))
 
 

@@ -8,6 +8,11 @@
 // chains A..F) then give different chain / resi columns than their PDB-format file: that is the reference's behaviour
 // too.  arph_parse_cif_ids(path, 1, ...) selects the author identifiers instead (what the PDB-format file carries).
 // One pass over a whole-file buffer; tokens are string views into it; numbers via std::from_chars.
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
 #include <charconv>
 #include <cstdio>
 #include <cstdlib>
@@ -21,6 +26,43 @@
 #endif
 
 namespace {
+
+// the text of a file: mapped read-only when it is a regular file, else read into a string
+struct FileText {
+  std::string owned;
+  void* map = nullptr;
+  size_t map_len = 0;
+  std::string_view view;
+  bool open(const char* path) {
+    const int fd = ::open(path, O_RDONLY);
+    if (fd < 0) return false;
+    struct stat st;
+    if (::fstat(fd, &st) == 0 && S_ISREG(st.st_mode) && st.st_size > 0) {
+      void* m = ::mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+      if (m != MAP_FAILED) {
+        map = m;
+        map_len = (size_t)st.st_size;
+        ::madvise(m, map_len, MADV_WILLNEED);
+        view = std::string_view(static_cast<const char*>(m), map_len);
+        ::close(fd);
+        return true;
+      }
+    }
+    char chunk[1 << 16];
+    ssize_t got;
+    while ((got = ::read(fd, chunk, sizeof chunk)) > 0) owned.append(chunk, (size_t)got);
+    ::close(fd);
+    if (got < 0) return false;
+    view = owned;
+    return true;
+  }
+  ~FileText() {
+    if (map) ::munmap(map, map_len);
+  }
+  FileText() = default;
+  FileText(const FileText&) = delete;
+  FileText& operator=(const FileText&) = delete;
+};
 
 struct Tokenizer {
   std::string_view text;
@@ -160,15 +202,30 @@ bool row_to_record(const std::string_view* row, const int* where, bool auth_ids,
 // first value on is cut at line ends, every piece tokenises its lines on its own.  A line that is not exactly one row
 // (values wrapped over lines, two rows on a line, a text field) makes the piece give up, and the caller reads the loop
 // with the serial tokenizer instead; the first line that starts with a keyword or tag ends the loop.
+// The records go straight into the caller's array: a piece of L lines holds at most L rows, so piece t writes from the
+// sum of the line counts before it (the few pieces with blank or comment lines are closed up afterwards).
 struct CifPiece {
-  std::vector<arp_atom_record> recs;
+  size_t lines = 0;  // line count of the piece = capacity of its part of the array
+  size_t count = 0;  // records written
   bool irregular = false, ended = false;
   int64_t bad_row = -1;  // piece-local index of a row with an unreadable coordinate
 };
 
-void parse_piece(std::string_view text, size_t width, const int* where, bool auth_ids, CifPiece& P) {
+size_t count_lines(std::string_view text) {
+  size_t n = 0;
+  const char* p = text.data();
+  const char* end = p + text.size();
+  while (p < end) {
+    const void* q = std::memchr(p, '\n', (size_t)(end - p));
+    if (!q) break;
+    ++n;
+    p = static_cast<const char*>(q) + 1;
+  }
+  return n + (p < end ? 1 : 0);  // a last line without a line end
+}
+
+void parse_piece(std::string_view text, size_t width, const int* where, bool auth_ids, arp_atom_record* dst, CifPiece& P) {
   std::vector<std::string_view> row(width);
-  P.recs.reserve(text.size() / 80 + 1);
   size_t pos = 0;
   while (pos < text.size()) {
     size_t eol = text.find('\n', pos);
@@ -198,12 +255,11 @@ void parse_piece(std::string_view text, size_t width, const int* where, bool aut
       P.irregular = true;
       return;
     }
-    arp_atom_record r;
-    if (!row_to_record(row.data(), where, auth_ids, r)) {
-      P.bad_row = (int64_t)P.recs.size();
+    if (!row_to_record(row.data(), where, auth_ids, dst[P.count])) {
+      P.bad_row = (int64_t)P.count;
       return;
     }
-    P.recs.push_back(r);
+    P.count += 1;
   }
 }
 
@@ -214,28 +270,18 @@ extern "C" {
 int arph_parse_cif_ids(const char* path, int use_auth_ids, arp_atom_record** out, int64_t* n) {
   arp::NvtxRange nvtx_("arph:parse_cif");
   const bool auth_ids = use_auth_ids != 0;
+  arp::PhaseClock clk;
   *out = nullptr;
   *n = 0;
-  FILE* f = std::fopen(path, "rb");
-  if (!f) {
+  // a regular file is mapped, not copied: its pages come in under the threads that tokenize them; anything else (a pipe)
+  // is read in 64 KB pieces
+  FileText file;
+  if (!file.open(path)) {
     arp::last_error() = std::string("cannot open ") + path;
     return ARP_ERR_IO;
   }
-  std::string text;
-  {
-    // one read of the whole file when its size is known (regular files), 64 KB pieces otherwise (pipes)
-    long size = -1;
-    if (std::fseek(f, 0, SEEK_END) == 0) size = std::ftell(f);
-    std::rewind(f);
-    if (size > 0) {
-      text.resize((size_t)size);
-      text.resize(std::fread(text.data(), 1, (size_t)size, f));
-    }
-    char chunk[1 << 16];
-    size_t got;
-    while ((got = std::fread(chunk, 1, sizeof chunk, f)) > 0) text.append(chunk, got);
-  }
-  std::fclose(f);
+  const std::string_view text = file.view;
+  clk.mark("cif read");
 
   std::vector<arp_atom_record> recs;
   Tokenizer T{text};
@@ -272,7 +318,7 @@ int arph_parse_cif_ids(const char* path, int use_auth_ids, arp_atom_record** out
     const size_t width = col_of.size();
     if (have) {  // one row per line? then on all host threads
       const size_t data_begin = (size_t)(tok.data() - text.data()) - (T.quoted ? 1 : 0);
-      const std::string_view body = std::string_view(text).substr(data_begin);
+      const std::string_view body = text.substr(data_begin);
       int NT = 1;
 #ifdef _OPENMP
       NT = std::max(1, std::min(omp_get_max_threads(), (int)(body.size() / piece_bytes()) + 1));
@@ -284,41 +330,45 @@ int arph_parse_cif_ids(const char* path, int use_auth_ids, arp_atom_record** out
         cut[(size_t)t] = p == std::string_view::npos ? body.size() : p + 1;
       }
       std::vector<CifPiece> pieces((size_t)NT);
+      const auto piece_text = [&](int t) { return body.substr(cut[(size_t)t], cut[(size_t)t + 1] - cut[(size_t)t]); };
 #pragma omp parallel for schedule(static, 1) num_threads(NT)
-      for (int t = 0; t < NT; ++t) parse_piece(body.substr(cut[(size_t)t], cut[(size_t)t + 1] - cut[(size_t)t]), width, where, auth_ids, pieces[(size_t)t]);
+      for (int t = 0; t < NT; ++t) pieces[(size_t)t].lines = count_lines(piece_text(t));
+      std::vector<size_t> first((size_t)NT + 1, 0);
+      for (int t = 0; t < NT; ++t) first[(size_t)t + 1] = first[(size_t)t] + pieces[(size_t)t].lines;
+      arp_atom_record* arr = (arp_atom_record*)std::malloc(std::max<size_t>(1, first[(size_t)NT]) * sizeof(arp_atom_record));
+      if (!arr) {
+        arp::last_error() = "out of host memory";
+        return ARP_ERR_OOM;
+      }
+      clk.mark("cif header, cuts, lines");
+#pragma omp parallel for schedule(static, 1) num_threads(NT)
+      for (int t = 0; t < NT; ++t) parse_piece(piece_text(t), width, where, auth_ids, arr + first[(size_t)t], pieces[(size_t)t]);
+      clk.mark("cif parse pieces");
       bool regular = true;
       size_t total = 0;
-      int last = NT - 1;
       for (int t = 0; t < NT; ++t) {
-        if (pieces[(size_t)t].irregular) {
+        const CifPiece& pc = pieces[(size_t)t];
+        if (pc.irregular) {
           regular = false;
           break;
         }
-        if (pieces[(size_t)t].bad_row >= 0) {
-          arp::last_error() = "mmCIF _atom_site row " + std::to_string(total + (size_t)pieces[(size_t)t].bad_row + 1) + ": unreadable coordinate";
+        if (pc.bad_row >= 0) {
+          std::free(arr);
+          arp::last_error() = "mmCIF _atom_site row " + std::to_string(total + (size_t)pc.bad_row + 1) + ": unreadable coordinate";
           return ARP_ERR_IO;
         }
-        total += pieces[(size_t)t].recs.size();
-        if (pieces[(size_t)t].ended) {
-          last = t;
-          break;
-        }
+        if (pc.count && total != first[(size_t)t]) std::memmove(arr + total, arr + first[(size_t)t], pc.count * sizeof(arp_atom_record));  // close a gap
+        total += pc.count;
+        if (pc.ended) break;
       }
-      if (regular) {  // the first _atom_site loop is the structure: the pieces go straight into the caller's array
+      if (regular) {  // the first _atom_site loop is the structure
         *n = (int64_t)total;
-        *out = (arp_atom_record*)std::malloc(std::max<size_t>(1, total) * sizeof(arp_atom_record));
-        if (!*out) {
-          arp::last_error() = "out of host memory";
-          return ARP_ERR_OOM;
-        }
-        std::vector<size_t> first((size_t)last + 1, 0);
-        for (int t = 1; t <= last; ++t) first[(size_t)t] = first[(size_t)t - 1] + pieces[(size_t)t - 1].recs.size();
-#pragma omp parallel for schedule(static, 1) num_threads(last + 1)
-        for (int t = 0; t <= last; ++t)
-          if (!pieces[(size_t)t].recs.empty())
-            std::memcpy(*out + first[(size_t)t], pieces[(size_t)t].recs.data(), pieces[(size_t)t].recs.size() * sizeof(arp_atom_record));
+        arp_atom_record* fit = (arp_atom_record*)std::realloc(arr, std::max<size_t>(1, total) * sizeof(arp_atom_record));
+        *out = fit ? fit : arr;
+        clk.mark("cif close up");
         return ARP_OK;
       }
+      std::free(arr);
     }
     std::vector<std::string_view> row(width);
     while (have) {

@@ -351,6 +351,26 @@ def test_mmcif_reader_pieces_on_all_threads(bft, tmp_path, monkeypatch):
     for piece in ("500", "1048576"):
         monkeypatch.setenv("ARPH_CIF_PIECE_BYTES", piece)
         assert np.array_equal(A.parse_cif(q), whole), piece
+    # comment and blank lines between rows, every row on its own line: the pieces stay on the parallel path, the gaps
+    # they leave in the record array are closed up
+    gaps = lines[:first + 3000] + ["# one", "", "# two"] + lines[first + 3000:first + 7000] + ["# a comment", ""] + lines[first + 7000:]
+    g = tmp_path / "g.cif"
+    g.write_text("\n".join(gaps))
+    for piece in ("300", "5000", "1048576"):
+        monkeypatch.setenv("ARPH_CIF_PIECE_BYTES", piece)
+        assert np.array_equal(A.parse_cif(g), whole), piece
+    # not a regular file (a FIFO): read in pieces instead of mapped
+    import os
+    import threading
+
+    fifo = tmp_path / "pipe.cif"
+    os.mkfifo(fifo)
+    feeder = threading.Thread(target=lambda: fifo.write_bytes(p.read_bytes()))
+    feeder.start()
+    try:
+        assert np.array_equal(A.parse_cif(fifo), whole)
+    finally:
+        feeder.join()
     # unreadable coordinate in row 5001
     toks = lines[first + 5000].split(" ")
     toks[10] = "abc"
