@@ -813,6 +813,9 @@ __global__ void __launch_bounds__(PAIR_THREADS, PAIR_MIN_BLOCKS) k_screen(const 
 // store and add: no vote, no atomic in the loop).  Every SA_ROUND trips the warp looks at the lists; a flush runs stage
 // B1 on them -- per-pair label limit, both orientations of the pair filter (one 16-byte gather per hit) -- and sends the
 // survivors, with the input indices the rows will carry, to the queue of k_exact 32 at a time (one atomicAdd per 32).
+// r2c: the flush reads the 32 lists as ONE list, 32 consecutive hits per row (SA_DENSE_FLUSH): lists are 0-5 entries long,
+// so "entry j of every lane" kept under half of a row's lanes busy through the ~60 instructions of stage B1; now every
+// lane of every row but the last works (k_screen_atoms 0.138 -> 0.121 ms on config 3, 0.116 with rounds of two trips).
 constexpr int SA_THREADS = 256;
 constexpr int SA_WARPS = SA_THREADS / 32;
 constexpr uint32_t SA_WINDOW = 512;
@@ -820,7 +823,7 @@ constexpr uint32_t SA_WINDOW = 512;
 #define SA_BUF_N 12
 #endif
 #ifndef SA_ROUND_N
-#define SA_ROUND_N 4
+#define SA_ROUND_N 2  // r2c: with the dense flush, fewer and fuller flushes win over longer straight-line rounds (4: 0.121 ms, 2: 0.116 ms)
 #endif
 constexpr int SA_BUF = SA_BUF_N;      // entries of a lane's hit list
 constexpr int SA_ROUND = SA_ROUND_N;  // trips between two looks at the lists (a trip appends at most 2)
@@ -888,6 +891,72 @@ __device__ __forceinline__ void sa_emit(const PairArgs& G, SaSmem& S, int wid, i
 // Stage B1 on the hit lists of a warp, entry j of every lane at a time (SA_FLUSH_DEPTH gathers in flight): per-pair label
 // limit (no label of complex.rs:217-296 fires beyond it), both orientations of should_compare_entities
 // (complex.rs:76-131); the survivors of a row are ranked by a ballot into the warp's stash.  `mine` = the lane's own RecK.
+#ifndef SA_DENSE_FLUSH
+#define SA_DENSE_FLUSH 1  // 1: the lanes' lists are read as ONE list, 32 consecutive hits per row (every lane busy);
+#endif                    // 0: entry j of every lane per row (lanes with shorter lists idle: ~45 % of a row works)
+#if SA_DENSE_FLUSH
+// Hit g of the warp (lists concatenated in lane order) belongs to the last lane whose list starts at or before g; a lane
+// finds it by a 5-step search over the lanes' start offsets, reads the entry from that lane's column of the hit lists
+// and fetches the from-atom's record from that lane's registers.
+__device__ __forceinline__ void sa_flush(const PairArgs& G, const DevParams& P, SaSmem& S, const unsigned long long* __restrict__ pos2, int tid,
+                                         int lane, uint32_t slot, const RecK mine, uint32_t tf1, uint32_t cnt, SaCarry& K) {
+  (void)pos2, (void)tf1;
+  static_assert(SA_TAG_IN_TRIP, "the dense flush reads lists that already passed the in-chain rule");
+  const uint32_t lt = (1u << lane) - 1u;
+  const int wid = tid >> 5, t0 = tid & ~31;
+  uint4* s2 = S.stash2[wid];
+  uint32_t inc = cnt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += v;
+  }
+  const uint32_t total = __shfl_sync(0xffffffffu, inc, 31), off = inc - cnt;
+  K.n_q += cnt;
+  int n2 = K.n2;
+  for (uint32_t g0 = 0; g0 < total; g0 += 32u) {
+    const uint32_t g = g0 + lane;
+    const bool have = g < total;
+    uint32_t src = 0;
+#pragma unroll
+    for (int st = 16; st > 0; st >>= 1) {
+      const uint32_t probe = src + st;  // <= 31
+      const uint32_t v = __shfl_sync(0xffffffffu, off, probe);
+      if (v <= g) src = probe;
+    }
+    // (lanes past the end of the list land on some lane as well: their entry is not read)
+    const uint32_t o_src = __shfl_sync(0xffffffffu, off, src);
+    const uint32_t a_attr = __shfl_sync(0xffffffffu, mine.attr, src), a_ck = __shfl_sync(0xffffffffu, mine.chain_key, src);
+    const uint32_t a_ro = __shfl_sync(0xffffffffu, mine.res_ordinal, src), a_perm = __shfl_sync(0xffffffffu, mine.perm, src);
+    const uint32_t a_slot = slot - (uint32_t)lane + src;
+    uint2 h = make_uint2(0u, 0x7f800000u);  // no hit: d2 = +inf fails every limit
+    uint4 kb = make_uint4(0u, 0u, 0u, 0u);
+    if (have) {
+      const uint32_t j = g - o_src;
+      ARP_CHK(G.ctr, j < (uint32_t)SA_BUF, 2);  // a lane's list never outgrows its SA_BUF entries
+      h = S.hits[j][t0 + (int)src];
+      ARP_CHK(G.ctr, h.x < G.n_atoms && h.x != a_slot, 3);  // a hit is another atom's sorted slot
+      kb = *reinterpret_cast<const uint4*>(G.recK + h.x);
+    }
+    const float d2 = __uint_as_float(h.y);
+    const bool pot = d2 <= label_limit2(P, S.lim2, a_attr, kb.x);
+    const int dir = pot ? pair_direction(a_attr, a_ck, a_ro, kb.x, kb.y, kb.z) : 0;
+    const bool go = dir != 0;
+    const uint32_t m = __ballot_sync(0xffffffffu, go);
+    ARP_CHK(G.ctr, n2 + __popc(m) <= 64, 4);
+    if (go) s2[n2 + __popc(m & lt)] = make_uint4(a_slot | QF_B, h.x | (dir == 2 ? QF_A : 0u) | QF_B, a_perm, kb.w);
+    n2 += __popc(m);
+    __syncwarp();
+    if (n2 >= 32) {  // the stash holds 64: never more than 31 + 32 before this point
+      K.n2 = n2;
+      sa_emit(G, S, wid, lane, K, false);
+      n2 = K.n2;
+    }
+  }
+  K.n2 = n2;
+  __syncwarp();  // the lists are rewritten by their own lanes next: every lane has read what it needed
+}
+#else
 __device__ __forceinline__ void sa_flush(const PairArgs& G, const DevParams& P, SaSmem& S, const unsigned long long* __restrict__ pos2, int tid,
                                          int lane, uint32_t slot, const RecK mine, uint32_t tf1, uint32_t cnt, SaCarry& K) {
   const uint32_t maxc = __reduce_max_sync(0xffffffffu, cnt);
@@ -938,6 +1007,8 @@ __device__ __forceinline__ void sa_flush(const PairArgs& G, const DevParams& P, 
     K.n2 = n2;
   }
 }
+
+#endif
 
 // The trips of one tile.  A lane is active while s < re.  The trips are branch-free (a lane that has finished keeps
 // computing on slot pair 0 and appends nothing), so a round of SA_ROUND trips is straight-line code; the candidates of
@@ -1034,7 +1105,9 @@ __device__ __forceinline__ void sa_trips(const PairArgs& G, const DevParams& P, 
 
 __global__ void __launch_bounds__(SA_THREADS, SA_MIN_BLOCKS) k_screen_atoms(const PairArgs G, const DevParams P,
                                                                             const unsigned long long* __restrict__ pos2, uint32_t n_atoms) {
-  __shared__ SaSmem S;
+  // dynamic shared memory (sizeof(SaSmem), above the 48 KB a static array may take: api_entry.inc raises the kernel's limit)
+  extern __shared__ __align__(16) unsigned char sa_smem_raw[];
+  SaSmem& S = *reinterpret_cast<SaSmem*>(sa_smem_raw);
   const int lane = threadIdx.x & 31, tid = threadIdx.x, wid = threadIdx.x >> 5;
   if (tid < 16) {
     float m = 0.f;
