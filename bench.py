@@ -209,9 +209,9 @@ def pinned_structure(A, packed, arena=True):
 
 # single-GPU totals of the two multi-GPU configurations (profiles/r1t_big100m.json, r1t_batch.json): what the union of
 # the ranks' results must equal; ms_one_gpu = the same job on ONE B200 with the current kernels
-# (profiles/r2b_bench_1gpu_multi.json: `bench.py --multi on` at N = 1)
-SLAB_EXPECT = {(16, 32, 24): {"rows": 88_915_968, "pairs_in_cutoff": 4_871_872_512, "atoms": 100_515_840, "ms_one_gpu": 21.34}}
-BATCH_EXPECT = {10000: {"rows": 42_379_378, "pairs_in_cutoff": 2_332_010_892, "atoms": 48_780_000, "ms_one_gpu": 9.76}}
+# (profiles/r2c_bench_1gpu_multi.json: `bench.py --multi on` at N = 1)
+SLAB_EXPECT = {(16, 32, 24): {"rows": 88_915_968, "pairs_in_cutoff": 4_871_872_512, "atoms": 100_515_840, "ms_one_gpu": 21.14}}
+BATCH_EXPECT = {10000: {"rows": 42_379_378, "pairs_in_cutoff": 2_332_010_892, "atoms": 48_780_000, "ms_one_gpu": 9.61}}
 
 
 def bench_slab(ctx_device: int, rank: int, world: int, tiling, reps: int = 3):
