@@ -462,7 +462,7 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n, bool one_sh
     } else {
       CK(cudaEventRecord(c->udep[1], c->stream));
       CK(cudaStreamWaitEvent(c->side, c->udep[1], 0));
-      k_expand_res_id<<<(unsigned)((c->n_atoms + 255) / 256), 256, 0, c->side>>>(c->res_atom_begin.p, (uint32_t)c->n_res, (uint32_t)c->n_atoms, c->res_id.p);
+      k_expand_res_id<<<(unsigned)((c->n_res + 255) / 256), 256, 0, c->side>>>(c->res_atom_begin.p, (uint32_t)c->n_res, (uint32_t)c->n_atoms, c->res_id.p);  // a warp per 32 residues
     }
     CK(cudaGetLastError());
     side_used = true;
