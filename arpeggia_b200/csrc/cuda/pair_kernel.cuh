@@ -834,6 +834,9 @@ static_assert(SA_BUF > 2 * SA_ROUND, "a round must fit the list");
 #ifndef SA_TAG_IN_TRIP
 #define SA_TAG_IN_TRIP 1  // 1: the in-chain rule is decided in the trip (tags ride in the position records: 32 bytes per trip);
 #endif                    // 0: in the flush, with one 4-byte gather per hit (24 bytes per trip, three times as many hits)
+#ifndef SA_LD256
+#define SA_LD256 1  // the candidate pair comes in with one 32-byte load
+#endif
 #ifndef SA_FLUSH_DEPTH
 #define SA_FLUSH_DEPTH 2  // hit-list rows (= gathers per lane) in flight in a flush
 #endif
@@ -1023,7 +1026,12 @@ __device__ __forceinline__ void sa_trips(const PairArgs& G, const DevParams& P, 
   constexpr uint32_t HROW = 8u * SA_THREADS;                                      // byte stride of the hit lists
   const uint32_t hp0 = (uint32_t)__cvta_generic_to_shared(&S.hits[0][tid]);
   auto load = [&](uint32_t ld, ulonglong2& XY, ulonglong2& ZT) {
-    // slot pair (ld, ld + 1): 32 bytes as two 16-byte loads: (x0 x1 | y0 y1) and (z0 z1 | t0 t1)
+    // slot pair (ld, ld + 1): 32 bytes, (x0 x1 | y0 y1) and (z0 z1 | t0 t1)
+#if SA_TAG_IN_TRIP && SA_LD256
+    // one 256-bit load (LDG.E.256, sm_100): half the load instructions and L1 requests of two 16-byte loads
+    asm("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];" : "=l"(XY.x), "=l"(XY.y), "=l"(ZT.x), "=l"(ZT.y) : "l"(pos2 + 2u * ld));
+    return;
+#endif
     XY = *reinterpret_cast<const ulonglong2*>(pos2 + 2u * ld);
 #if SA_TAG_IN_TRIP
     ZT = *reinterpret_cast<const ulonglong2*>(pos2 + 2u * ld + 2u);
