@@ -65,6 +65,8 @@ class Structure(C.Structure):
         ("res_chain_key", _U32P), ("res_res_ordinal", _U32P), ("res_atom_begin", _U32P),
         ("x_milli", _I32P), ("y_milli", _I32P), ("z_milli", _I32P),
         ("atom_gid", _U32P), ("ring_gid", _U32P), ("res_tag", _U32P),
+        ("xyz_milli21", C.POINTER(C.c_uint64)), ("xyz_milli21_origin", C.c_int32 * 3), ("reserved2_", C.c_int32),
+        ("attr16", C.POINTER(C.c_uint16)),
     ]
 
 

@@ -100,6 +100,10 @@ class Packed:
         out["res_atom_begin"] = view(s.res_atom_begin, s.n_residues + 1, np.uint32) if s.res_atom_begin else None
         for k in ("x_milli", "y_milli", "z_milli"):  # on-lattice form of the coordinates, None when a coordinate is off it
             out[k] = view(getattr(s, k), s.n_atoms, np.int32) if getattr(s, k) else None
+        # the most compact forms: 21-bit lattice words relative to xyz_milli21_origin, 16-bit attribute words
+        out["xyz_milli21"] = view(s.xyz_milli21, s.n_atoms, np.uint64) if s.xyz_milli21 else None
+        out["xyz_milli21_origin"] = np.array(list(s.xyz_milli21_origin), dtype=np.int32)
+        out["attr16"] = view(s.attr16, s.n_atoms, np.uint16) if s.attr16 else None
         for k in ("ring_center", "ring_normal"):
             out[k] = view(getattr(s, k), 3 * s.n_rings, np.float64).reshape(-1, 3)
         for k in ("ring_attr", "ring_chain_key", "ring_res_ordinal"):

@@ -102,6 +102,9 @@ struct arp_ctx {
   bool per_residue_keys = false;                  // every structure of the job came with it
   DBuf<int32_t> res_cb, res_sg;
   DBuf<int32_t> xm, ym, zm;                       // on-lattice coordinates as uploaded (arp_structure.x_milli)
+  DBuf<uint64_t> xyz21;                           // ... or as 21-bit words (arp_structure.xyz_milli21)
+  DBuf<uint16_t> attr16;                    // 16-bit attribute words as uploaded (arp_structure.attr16)
+  int xyz21_origin[3] = {0, 0, 0};
   DBuf<uint32_t> atom_struct, ring_struct;
   DBuf<StructDesc> descs;
   std::vector<StructDesc> h_descs;
@@ -313,7 +316,9 @@ void flush_uploads_impl(arp_ctx* c, After&& after) {
   };
   std::vector<Run> runs;
   size_t arena = 0;
-  const auto words = [](const UpItem& u) { return (reinterpret_cast<uintptr_t>(u.h) & 3u) == 0 && (u.bytes & 3u) == 0; };  // k_scatter_segments moves 4-byte words
+  // k_scatter_segments moves 4-byte words: a 16-bit array of odd length is moved with its last word completed by whatever
+  // follows it in the landing area (the device buffers have room for it)
+  const auto words = [](const UpItem& u) { return (reinterpret_cast<uintptr_t>(u.h) & 3u) == 0; };
   for (size_t k = 0; k < it.size();) {
     size_t j = k;
     HostSpan run_span;
@@ -354,7 +359,7 @@ void flush_uploads_impl(arp_ctx* c, After&& after) {
         const UpItem& u = it[k];
         S.src[S.n] = land + (u.h - it[r.first].h);
         S.dst[S.n] = u.d;
-        S.bytes[S.n] = u.bytes;
+        S.bytes[S.n] = (u.bytes + 3u) & ~(size_t)3u;
         most = std::max(most, u.bytes);
         S.n += 1;
       }
@@ -449,7 +454,7 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n, bool one_sh
 
   CK(cudaEventRecord(c->ev[0], c->stream));
   c->h_words.need(32);
-  bool side_used = false;
+  bool side_used = false, use_21 = false, use_attr16 = false, milli = false;
   c->up_items.clear();
   c->up_copies = 0;
   c->h2d_pending = false;
@@ -458,7 +463,12 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n, bool one_sh
     if (which == 1) {
       CK(cudaEventRecord(c->udep[0], c->stream));
       CK(cudaStreamWaitEvent(c->side, c->udep[0], 0));
-      k_expand_milli<<<(unsigned)((c->n_atoms + 255) / 256), 256, 0, c->side>>>(c->xm.p, c->ym.p, c->zm.p, (uint32_t)c->n_atoms, c->x.p, c->y.p, c->z.p);
+      if (use_21 || use_attr16)
+        k_expand_milli21<<<(unsigned)((c->n_atoms + 255) / 256), 256, 0, c->side>>>(use_21 ? reinterpret_cast<const unsigned long long*>(c->xyz21.p) : nullptr, c->xyz21_origin[0], c->xyz21_origin[1],
+                                                                                  c->xyz21_origin[2], use_attr16 ? c->attr16.p : nullptr,
+                                                                                  (uint32_t)c->n_atoms, c->x.p, c->y.p, c->z.p, c->attr.p);
+      if (!use_21 && milli)
+        k_expand_milli<<<(unsigned)((c->n_atoms + 255) / 256), 256, 0, c->side>>>(c->xm.p, c->ym.p, c->zm.p, (uint32_t)c->n_atoms, c->x.p, c->y.p, c->z.p);
     } else {
       CK(cudaEventRecord(c->udep[1], c->stream));
       CK(cudaStreamWaitEvent(c->side, c->udep[1], 0));
@@ -480,26 +490,41 @@ void do_upload(arp_ctx* c, const arp_structure* const* s, int64_t n, bool one_sh
   auto nrg3 = [](const arp_structure* t) { return 3 * t->n_rings; };
   auto nh = [](const arp_structure* t) { return t->n_h; };
 #define UP(buf, field, lenf) upload_concat(c, c->buf, s, n, [](const arp_structure* t) { return t->field; }, lenf, 0, nullptr, false)
-  bool milli = c->n_atoms > 0;
+  // the most compact forms (single-structure jobs): 21-bit lattice words and 16-bit attribute words
+  use_21 = n == 1 && c->n_atoms > 0 && s[0]->xyz_milli21 != nullptr;
+  use_attr16 = n == 1 && c->n_atoms > 0 && s[0]->attr16 != nullptr;
+  milli = c->n_atoms > 0;
   for (int64_t k = 0; k < n; ++k)
     if (!s[k]->x_milli || !s[k]->y_milli || !s[k]->z_milli) milli = false;
-  if (milli) {  // on-lattice coordinates: half the bytes over PCIe, f64 rebuilt here
+  if (use_21 || use_attr16 || milli) {  // on-lattice coordinates: a half or a third of the bytes over PCIe, f64 rebuilt here
     c->x.need(c->n_atoms);
     c->y.need(c->n_atoms);
     c->z.need(c->n_atoms);
+    c->attr.need(std::max<int64_t>(c->n_atoms, 1));
     const size_t q = c->up_items.size();
-    UP(xm, x_milli, nat);
-    UP(ym, y_milli, nat);
-    UP(zm, z_milli, nat);
+    if (use_21) {
+      for (int a3 = 0; a3 < 3; ++a3) c->xyz21_origin[a3] = s[0]->xyz_milli21_origin[a3];
+      UP(xyz21, xyz_milli21, nat);
+    } else if (milli) {
+      UP(xm, x_milli, nat);
+      UP(ym, y_milli, nat);
+      UP(zm, z_milli, nat);
+    }
+    if (use_attr16) UP(attr16, attr16, nat);
     then_kernel(q, 1);  // on the side stream: the next copies do not wait for the kernel
-  } else {
+  }
+  if (!use_21 && !milli) {
     for (int64_t k = 0; k < n; ++k)
       if (s[k]->n_atoms > 0 && (!s[k]->x || !s[k]->y || !s[k]->z)) throw arp::Error{ARP_ERR_ARG, "structure has neither x / y / z nor x_milli / y_milli / z_milli"};
     UP(x, x, nat);
     UP(y, y, nat);
     UP(z, z, nat);
   }
-  UP(attr, attr, nat);
+  if (!use_attr16) {
+    for (int64_t k = 0; k < n; ++k)
+      if (s[k]->n_atoms > 0 && !s[k]->attr) throw arp::Error{ARP_ERR_ARG, "structure has neither attr nor attr16"};
+    UP(attr, attr, nat);
+  }
   c->per_residue_keys = true;
   for (int64_t k = 0; k < n; ++k)
     if (!s[k]->res_chain_key || !s[k]->res_res_ordinal) c->per_residue_keys = false;

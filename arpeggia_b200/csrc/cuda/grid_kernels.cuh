@@ -324,6 +324,23 @@ __global__ void __launch_bounds__(256) k_expand_milli(const int32_t* __restrict_
   z[a] = __ddiv_rn((double)zm[a], 1000.0);
 }
 
+// ... and from the 21-bit form (arp_structure.xyz_milli21: dx | dy << 21 | dz << 42 relative to an integer origin), with
+// the 16-bit attribute words widened in the same pass (attr16 may be NULL: attr then came as 32-bit words)
+__global__ void __launch_bounds__(256) k_expand_milli21(const unsigned long long* __restrict__ w, int ox, int oy, int oz,
+                                                        const unsigned short* __restrict__ attr16, uint32_t n_atoms,
+                                                        double* __restrict__ x, double* __restrict__ y, double* __restrict__ z,
+                                                        uint32_t* __restrict__ attr) {
+  const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= n_atoms) return;
+  if (w) {
+    const unsigned long long v = w[a];
+    x[a] = __ddiv_rn((double)(ox + (int)(v & 0x1fffffull)), 1000.0);
+    y[a] = __ddiv_rn((double)(oy + (int)((v >> 21) & 0x1fffffull)), 1000.0);
+    z[a] = __ddiv_rn((double)(oz + (int)((v >> 42) & 0x1fffffull)), 1000.0);
+  }
+  if (attr16) attr[a] = attr16[a];
+}
+
 // Pass 2 of the counting sort: write the cell-sorted records.  The atom that arrived first in a cell also
 // publishes the cell as a work item of the pair kernel.
 __global__ void __launch_bounds__(256)

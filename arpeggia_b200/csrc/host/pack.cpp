@@ -844,6 +844,50 @@ void Packed::finish() {
       x_milli.clear(), y_milli.clear(), z_milli.clear();
     }
   }
+  // the most compact forms (arp_structure.xyz_milli21 / attr16): lattice coordinates relative to the box corner in 21 bits
+  // each -- structures up to 2 097 A across -- and the attribute words in 16 bits
+  t.xyz_milli21 = nullptr;
+  t.attr16 = nullptr;
+  t.xyz_milli21_origin[0] = t.xyz_milli21_origin[1] = t.xyz_milli21_origin[2] = 0;
+  xyz21.clear();
+  attr16.clear();
+  if (t.x_milli && t.has_bbox) {
+    int64_t o[3];
+    bool fits = true;
+    for (int axis = 0; axis < 3; ++axis) {
+      o[axis] = std::llrint(t.bbox_min[axis] * 1000.0);  // the smallest lattice value of the axis (the map is monotone)
+      if (std::llrint(t.bbox_max[axis] * 1000.0) - o[axis] >= ((int64_t)1 << 21)) fits = false;
+    }
+    if (fits) {
+      xyz21.resize((size_t)na);
+      int ok = 1;
+#pragma omp parallel for schedule(static) reduction(& : ok) if (big)
+      for (int64_t k = 0; k < na; ++k) {
+        const int64_t dx = x_milli[k] - o[0], dy = y_milli[k] - o[1], dz = z_milli[k] - o[2];
+        if ((dx | dy | dz) < 0 || ((dx | dy | dz) >> 21)) ok = 0;
+        xyz21[k] = (uint64_t)dx | ((uint64_t)dy << 21) | ((uint64_t)dz << 42);
+      }
+      if (ok) {
+        t.xyz_milli21 = xyz21.data();
+        for (int axis = 0; axis < 3; ++axis) t.xyz_milli21_origin[axis] = (int32_t)o[axis];
+      } else {
+        xyz21.clear();
+      }
+    }
+  }
+  if (na > 0) {
+    attr16.resize((size_t)na);
+    int ok = 1;
+#pragma omp parallel for schedule(static) reduction(& : ok) if (big)
+    for (int64_t k = 0; k < na; ++k) {
+      if (attr[k] >> 16) ok = 0;
+      attr16[k] = (uint16_t)attr[k];
+    }
+    if (ok)
+      t.attr16 = attr16.data();
+    else
+      attr16.clear();
+  }
 }
 
 }  // namespace arp

@@ -18,6 +18,8 @@ struct Packed {
   std::vector<uint32_t> res_chain_key, res_res_ordinal;  // per residue (compact form of chain_key / res_ordinal)
   std::vector<uint32_t> res_atom_begin;                  // CSR of the residues' atoms (compact form of res_id)
   std::vector<int32_t> res_cb, res_sg;
+  RawVec<uint64_t> xyz21;                                // 21-bit lattice words (arp_structure.xyz_milli21; empty when they do not apply)
+  RawVec<uint16_t> attr16;                               // attr as 16-bit words
   RawVec<int32_t> x_milli, y_milli, z_milli;        // on-lattice form of x / y / z (empty when a coordinate is off the lattice)
   std::vector<uint32_t> res_tag;                         // per residue: |tag difference| <= 1 <=> same chain, ordinals <= 1 apart
   std::vector<uint32_t> atom_gid, ring_gid;              // ids in a larger structure (arph_packed_set_global_ids); empty = none

@@ -180,7 +180,13 @@ def pinned_structure(A, packed, arena=True):
     # arrays stay NULL and are neither copied here nor uploaded
     # ... and res_id as the residues' atom ranges (res_atom_begin)
     # ... and the coordinates on the 0.001 A lattice (x_milli) when the packer offers that form: 12 instead of 24 B / atom
-    sizes = {"x_milli": 4, "y_milli": 4, "z_milli": 4, "attr": 4} if src.x_milli else {"x": 8, "y": 8, "z": 8, "attr": 4}
+    # ... or as 21-bit lattice words with 16-bit attribute words (xyz_milli21 / attr16): 10 instead of 16 B / atom
+    if src.xyz_milli21 and src.attr16:
+        sizes = {"xyz_milli21": 8, "attr16": 2}
+        for k in range(3):
+            dst.xyz_milli21_origin[k] = src.xyz_milli21_origin[k]
+    else:
+        sizes = {"x_milli": 4, "y_milli": 4, "z_milli": 4, "attr": 4} if src.x_milli else {"x": 8, "y": 8, "z": 8, "attr": 4}
     n, nr, ng, nh = src.n_atoms, src.n_residues, src.n_rings, src.n_h
     lens = {**{k: n * s for k, s in sizes.items()}, "res_chain_key": 4 * nr, "res_res_ordinal": 4 * nr, "res_atom_begin": 4 * (nr + 1), "res_h_begin": 4 * (nr + 1), "h_x": 8 * nh, "h_y": 8 * nh, "h_z": 8 * nh,
             "res_cb": 4 * nr, "res_sg": 4 * nr, "ring_center": 24 * ng, "ring_normal": 24 * ng, "ring_attr": 4 * ng,

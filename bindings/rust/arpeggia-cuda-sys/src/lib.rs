@@ -77,6 +77,10 @@ pub struct arp_structure {
     pub atom_gid: *const u32,
     pub ring_gid: *const u32,
     pub res_tag: *const u32,
+    pub xyz_milli21: *const u64,
+    pub xyz_milli21_origin: [i32; 3],
+    pub reserved2_: i32,
+    pub attr16: *const u16,
 }
 
 #[repr(C)]

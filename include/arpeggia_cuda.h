@@ -145,6 +145,18 @@ typedef struct arp_structure {
    * and in ordinal order (violations that are visible between neighbouring residues fail the job with ARP_ERR_ARG).
    * Slab jobs (arp_slab_exchange) need tags that are valid across ranks, so there the caller must supply them. */
   const uint32_t* res_tag;
+  /* Optional most compact form of the two per-atom arrays that are left (single-structure jobs; what a host keeps when
+   * the PCIe copy is the cost of a call):
+   *   xyz_milli21  one 64-bit word per atom:  dx | dy << 21 | dz << 42,  d* = *_milli - xyz_milli21_origin[*] in [0, 2^21)
+   *                -- the on-lattice coordinates of a structure up to 2 097 A across, 8 instead of 12 bytes per atom;
+   *                when given, x_milli / y_milli / z_milli and x / y / z are not read (may be NULL);
+   *   attr16       attr as 16-bit words (every ARP_ATTR_* bit a caller sets lies below bit 15), 2 instead of 4 bytes;
+   *                when given, attr is not read (may be NULL).
+   * The device rebuilds x / y / z (one IEEE division per coordinate, as for x_milli) and attr itself. */
+  const uint64_t* xyz_milli21;
+  int32_t xyz_milli21_origin[3];
+  int32_t reserved2_;
+  const uint16_t* attr16;
 } arp_structure;
 
 #define ARP_FLAG_EMIT_RADIUS_SCREEN 0x1u /* screen atom pairs at min(dist_cutoff, largest distance at which any

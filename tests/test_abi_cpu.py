@@ -33,7 +33,7 @@ def test_every_declared_symbol_is_exported_and_bound():
 
 def test_struct_sizes_match_the_headers():
     assert C.sizeof(_lib.Params) == 24 and _lib.ROW_DTYPE.itemsize == 16 and _lib.ATOM_DTYPE.itemsize == 96
-    assert C.sizeof(_lib.Structure) == 4 * 8 + 18 * 8 + 6 * 8 + 2 * 4 + 3 * 8 + 3 * 8 + 3 * 8  # counts, pointers, bbox hint, compact forms, lattice form, ids + tags
+    assert C.sizeof(_lib.Structure) == 4 * 8 + 18 * 8 + 6 * 8 + 2 * 4 + 3 * 8 + 3 * 8 + 3 * 8 + (8 + 4 * 4 + 8)  # counts, pointers, bbox hint, compact forms, lattice form, ids + tags, 21-bit lattice words + 16-bit attr
     assert C.sizeof(_lib.SlabInfo) == 12 * 8 + 2 * 4 + 4 * 4 and C.sizeof(_lib.CommId) == 128
     assert C.sizeof(_lib.Result) == 8 * 8
 

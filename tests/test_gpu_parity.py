@@ -338,15 +338,26 @@ def test_lattice_coordinates_same_rows(ctx, bft):
     a = p.arrays()
     for k in "xyz":
         assert np.array_equal(a[k + "_milli"] / 1000.0, a[k])  # one IEEE division gives back the parsed double
+    assert p.structure.xyz_milli21 and p.structure.attr16
     s = _lib.Structure.from_buffer_copy(p.structure)
-    s.x = s.y = s.z = None  # only the lattice form
+    s.x = s.y = s.z = None  # only the lattice forms: the 21-bit words win
+    s.x_milli = s.y_milli = s.z_milli = None
+    s.attr = None  # ... and only the 16-bit attribute words
+    lat21 = ctx.contacts_rows([ctypes.pointer(s)], 0.1, 6.5)
+    s = _lib.Structure.from_buffer_copy(p.structure)
+    s.x = s.y = s.z = None  # only the 32-bit lattice form
+    s.xyz_milli21 = None
+    s.attr16 = None
     lat = ctx.contacts_rows([ctypes.pointer(s)], 0.1, 6.5)
     s = _lib.Structure.from_buffer_copy(p.structure)
     s.x_milli = s.y_milli = s.z_milli = None  # only f64
+    s.xyz_milli21 = None
+    s.attr16 = None
     f64 = ctx.contacts_rows([ctypes.pointer(s)], 0.1, 6.5)
     key = ["from", "to", "label", "distance"]
     assert np.array_equal(np.sort(lat["rows"], order=key), np.sort(f64["rows"], order=key))
-    assert lat["pairs_in_cutoff"] == f64["pairs_in_cutoff"] == 396474
+    assert np.array_equal(np.sort(lat21["rows"], order=key), np.sort(f64["rows"], order=key))
+    assert lat["pairs_in_cutoff"] == f64["pairs_in_cutoff"] == lat21["pairs_in_cutoff"] == 396474
     s.x = None
     with pytest.raises(A.ArpeggiaError) as e:
         ctx.contacts_rows([ctypes.pointer(s)], 0.1, 6.5)
@@ -544,7 +555,7 @@ def test_arrays_of_one_host_arena_travel_as_one_copy(ctx, bft, ubq):
         L.arp_result_free(ctx._h, rp)
         return np.sort(v, order=key), ctx.stats()["upload_copies"]
 
-    for atoms, milli in ((bft, True), (ubq, True), (bft, False)):
+    for atoms, milli in ((bft, True), (ubq, True), (bft, False), (ubq, "21")):
         p = A.Packed(atoms)
         src = p.structure
         n, nr, ng, nh = src.n_atoms, src.n_residues, src.n_rings, src.n_h
@@ -552,7 +563,11 @@ def test_arrays_of_one_host_arena_travel_as_one_copy(ctx, bft, ubq):
         lens = {"attr": 4 * n, "res_chain_key": 4 * nr, "res_res_ordinal": 4 * nr, "res_atom_begin": 4 * (nr + 1), "res_h_begin": 4 * (nr + 1),
                 "h_x": 8 * nh, "h_y": 8 * nh, "h_z": 8 * nh, "res_cb": 4 * nr, "res_sg": 4 * nr, "ring_center": 24 * ng, "ring_normal": 24 * ng,
                 "ring_attr": 4 * ng, "ring_chain_key": 4 * ng, "ring_res_ordinal": 4 * ng, "res_tag": 4 * nr}
-        lens.update({"x_milli": 4 * n, "y_milli": 4 * n, "z_milli": 4 * n} if milli else {"x": 8 * n, "y": 8 * n, "z": 8 * n})
+        if milli == "21":  # the most compact forms: 8-byte lattice words, 16-bit attributes
+            del lens["attr"]
+            lens.update({"xyz_milli21": 8 * n, "attr16": 2 * n})
+        else:
+            lens.update({"x_milli": 4 * n, "y_milli": 4 * n, "z_milli": 4 * n} if milli else {"x": 8 * n, "y": 8 * n, "z": 8 * n})
         assert bool(src.x_milli) and bool(src.res_tag)
         names = list(lens)
         np.random.default_rng(5).shuffle(names)  # the arena's order is not the library's upload order
@@ -562,7 +577,7 @@ def test_arrays_of_one_host_arena_travel_as_one_copy(ctx, bft, ubq):
         try:
             dst = AL.Structure()
             for name, _ in AL.Structure._fields_:
-                if name.startswith("n_") or name.startswith("bbox_") or name == "has_bbox":
+                if name.startswith("n_") or name.startswith("bbox_") or name == "has_bbox" or name == "xyz_milli21_origin":
                     setattr(dst, name, getattr(src, name))
             at = 0
             for k, name in enumerate(names):

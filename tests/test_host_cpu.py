@@ -191,10 +191,25 @@ def test_lattice_form_of_the_coordinates(ubq, bft):
             m = a[k + "_milli"]
             assert m is not None and m.dtype == np.int32
             assert np.array_equal((m.astype(np.float64) / 1000.0).view(np.uint64), a[k].view(np.uint64))
+        # the 21-bit words (arp_structure.xyz_milli21) hold the same lattice values relative to the box corner, the 16-bit
+        # attribute words the same attributes
+        w, o = a["xyz_milli21"], a["xyz_milli21_origin"].astype(np.int64)
+        assert w is not None and w.dtype == np.uint64
+        for j, k in enumerate("xyz"):
+            assert np.array_equal(((w >> np.uint64(21 * j)) & np.uint64(0x1FFFFF)).astype(np.int64) + o[j], a[k + "_milli"].astype(np.int64))
+            assert o[j] == a[k + "_milli"].min()
+        assert (w >> np.uint64(63)).max() == 0
+        assert a["attr16"] is not None and np.array_equal(a["attr16"].astype(np.uint32), a["attr"])
+    wide = np.concatenate([ubq, ubq])  # 2 200 A across: the 21-bit form does not apply, the 32-bit one does
+    wide["x"][len(ubq):] += 2200.0
+    wide["serial"][len(ubq):] += 5000
+    wide["chain"][len(ubq):] = b"B"
+    a = A.Packed(wide).arrays()
+    assert a["xyz_milli21"] is None and a["x_milli"] is not None and a["attr16"] is not None
     off = ubq.copy()
     off["x"][17] += 1e-7  # one coordinate off the lattice: the form is withdrawn for the whole structure
     a = A.Packed(off).arrays()
-    assert a["x_milli"] is None and a["y_milli"] is None and a["z_milli"] is None
+    assert a["x_milli"] is None and a["y_milli"] is None and a["z_milli"] is None and a["xyz_milli21"] is None
     neg0 = ubq.copy()
     neg0["z"][3] = -0.0  # "-0.000" parses to -0.0, which 0 / 1000.0 does not give back
     assert A.Packed(neg0).arrays()["z_milli"] is None
