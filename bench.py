@@ -780,6 +780,9 @@ def main():
                     "ms_host_other_rank0": e2e_ms - st["ms_h2d"] - st["ms_run"] - st["ms_d2h"], "calls": e2e_steps, "cpu_binding": binding,
                     "last_call_per_rank": {k: [round(float(v), 4) for v in e2e_ranks[k]] for k in e2e_keys},
                     "host_layout": "one page-locked arena, arrays 256-byte aligned one after the other", "upload_copies": st["upload_copies"],
+                    "host_forms": ("xyz_milli21 (8 B/atom) + attr16 (2 B/atom)" if packed.structure.xyz_milli21 and packed.structure.attr16 else
+                                   "x_milli, y_milli, z_milli (12 B/atom) + attr (4 B/atom)" if packed.structure.x_milli else "x, y, z f64 + attr")
+                                  + " + the packer's per-residue arrays (chain key, ordinal, atom range, H range, CB, SG, tag)",
                     "separate_allocations": e2e_sep,
                     "api": "arp_contacts (C ABI, pinned host SoA in, host rows out)"},
             "e2e_concurrent": e2e_conc,
