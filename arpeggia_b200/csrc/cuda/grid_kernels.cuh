@@ -99,28 +99,44 @@ __device__ __forceinline__ int cell_coord(double p, double origin, double inv_ed
 // Pass 1 of the counting sort: cell id of every point and its arrival rank inside the cell.
 // `ring_grid` selects which of the two grids of StructDesc is addressed; points are read with a stride so that
 // both the SoA atom arrays (stride 1) and the interleaved ring centres (stride 3) fit.
+#ifndef CA_PER_THREAD
+#define CA_PER_THREAD 1  // points per thread.  The kernel waits for the atomics' return values (79 % of its stall samples), but
+#endif                   // two or four points per thread -- loads, then atomics, in flight together -- measured SLOWER on config 3
+                         // (grid stage 0.081 -> 0.085 / 0.086 ms, r2c): with one point per thread the SMs already hold 64 warps
 __global__ void __launch_bounds__(256)
 k_cell_assign(const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz, int stride, uint32_t n,
               const uint32_t* __restrict__ point_struct, const StructDesc* __restrict__ descs, double inv_edge, int ring_grid,
               uint32_t* __restrict__ cell_of, uint32_t* __restrict__ rank_of, uint32_t* __restrict__ cell_count,
               unsigned int* __restrict__ box_error) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const StructDesc& d = descs[point_struct ? point_struct[i] : 0u];
-  const int nx = ring_grid ? d.rnx : d.nx, ny = ring_grid ? d.rny : d.ny, nz = ring_grid ? d.rnz : d.nz;
-  const double x = px[(size_t)i * stride], y = py[(size_t)i * stride], z = pz[(size_t)i * stride];
-  if (box_error) {
-    // the grid was laid out from the caller's bounding-box hint: an atom outside it (or a NaN) voids the layout
-    const double tx = (x - d.ox) * inv_edge, ty = (y - d.oy) * inv_edge, tz = (z - d.oz) * inv_edge;
-    const double eps = 1e-6;
-    if (!(tx > -eps && tx < nx + eps && ty > -eps && ty < ny + eps && tz > -eps && tz < nz + eps)) atomicOr(box_error, 2u);
+  const uint32_t i0 = blockIdx.x * (blockDim.x * CA_PER_THREAD) + threadIdx.x;
+  uint32_t c[CA_PER_THREAD];
+#pragma unroll
+  for (int u = 0; u < CA_PER_THREAD; ++u) {
+    const uint32_t i = i0 + u * blockDim.x;
+    if (i >= n) continue;
+    const StructDesc& d = descs[point_struct ? point_struct[i] : 0u];
+    const int nx = ring_grid ? d.rnx : d.nx, ny = ring_grid ? d.rny : d.ny, nz = ring_grid ? d.rnz : d.nz;
+    const double x = px[(size_t)i * stride], y = py[(size_t)i * stride], z = pz[(size_t)i * stride];
+    if (box_error) {
+      // the grid was laid out from the caller's bounding-box hint: an atom outside it (or a NaN) voids the layout
+      const double tx = (x - d.ox) * inv_edge, ty = (y - d.oy) * inv_edge, tz = (z - d.oz) * inv_edge;
+      const double eps = 1e-6;
+      if (!(tx > -eps && tx < nx + eps && ty > -eps && ty < ny + eps && tz > -eps && tz < nz + eps)) atomicOr(box_error, 2u);
+    }
+    const int ix = cell_coord(x, d.ox, inv_edge, nx);
+    const int iy = cell_coord(y, d.oy, inv_edge, ny);
+    const int iz = cell_coord(z, d.oz, inv_edge, nz);
+    c[u] = (ring_grid ? d.rcell_base : d.cell_base) + (uint32_t)((iz * ny + iy) * nx + ix);
   }
-  const int ix = cell_coord(x, d.ox, inv_edge, nx);
-  const int iy = cell_coord(y, d.oy, inv_edge, ny);
-  const int iz = cell_coord(z, d.oz, inv_edge, nz);
-  const uint32_t c = (ring_grid ? d.rcell_base : d.cell_base) + (uint32_t)((iz * ny + iy) * nx + ix);
-  cell_of[i] = c;
-  rank_of[i] = atomicAdd(&cell_count[c], 1u);
+  uint32_t r[CA_PER_THREAD];
+#pragma unroll
+  for (int u = 0; u < CA_PER_THREAD; ++u)
+    if (i0 + u * blockDim.x < n) r[u] = atomicAdd(&cell_count[c[u]], 1u);
+#pragma unroll
+  for (int u = 0; u < CA_PER_THREAD; ++u) {
+    const uint32_t i = i0 + u * blockDim.x;
+    if (i < n) cell_of[i] = c[u], rank_of[i] = r[u];
+  }
 }
 
 // ---- exclusive scan of the cell counts (in place) ------------------------------------------------------------
