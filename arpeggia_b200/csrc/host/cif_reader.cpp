@@ -8,11 +8,6 @@
 // chains A..F) then give different chain / resi columns than their PDB-format file: that is the reference's behaviour
 // too.  arph_parse_cif_ids(path, 1, ...) selects the author identifiers instead (what the PDB-format file carries).
 // One pass over a whole-file buffer; tokens are string views into it; numbers via std::from_chars.
-#include <fcntl.h>
-#include <sys/mman.h>
-#include <sys/stat.h>
-#include <unistd.h>
-
 #include <charconv>
 #include <cstdio>
 #include <cstdlib>
@@ -26,43 +21,6 @@
 #endif
 
 namespace {
-
-// the text of a file: mapped read-only when it is a regular file, else read into a string
-struct FileText {
-  std::string owned;
-  void* map = nullptr;
-  size_t map_len = 0;
-  std::string_view view;
-  bool open(const char* path) {
-    const int fd = ::open(path, O_RDONLY);
-    if (fd < 0) return false;
-    struct stat st;
-    if (::fstat(fd, &st) == 0 && S_ISREG(st.st_mode) && st.st_size > 0) {
-      void* m = ::mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
-      if (m != MAP_FAILED) {
-        map = m;
-        map_len = (size_t)st.st_size;
-        ::madvise(m, map_len, MADV_WILLNEED);
-        view = std::string_view(static_cast<const char*>(m), map_len);
-        ::close(fd);
-        return true;
-      }
-    }
-    char chunk[1 << 16];
-    ssize_t got;
-    while ((got = ::read(fd, chunk, sizeof chunk)) > 0) owned.append(chunk, (size_t)got);
-    ::close(fd);
-    if (got < 0) return false;
-    view = owned;
-    return true;
-  }
-  ~FileText() {
-    if (map) ::munmap(map, map_len);
-  }
-  FileText() = default;
-  FileText(const FileText&) = delete;
-  FileText& operator=(const FileText&) = delete;
-};
 
 struct Tokenizer {
   std::string_view text;
@@ -275,7 +233,7 @@ int arph_parse_cif_ids(const char* path, int use_auth_ids, arp_atom_record** out
   *n = 0;
   // a regular file is mapped, not copied: its pages come in under the threads that tokenize them; anything else (a pipe)
   // is read in 64 KB pieces
-  FileText file;
+  arp::FileText file;
   if (!file.open(path)) {
     arp::last_error() = std::string("cannot open ") + path;
     return ARP_ERR_IO;

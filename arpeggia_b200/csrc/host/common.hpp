@@ -1,5 +1,10 @@
 // Shared internals of the host side (not part of the ABI).
 #pragma once
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -7,6 +12,7 @@
 #include <cstring>
 #include <memory>
 #include <string>
+#include <string_view>
 #include <utility>
 #include <vector>
 
@@ -97,6 +103,43 @@ struct NoInitAlloc : std::allocator<T> {
 };
 template <class T>
 using RawVec = std::vector<T, NoInitAlloc<T>>;
+
+// the text of a file: mapped read-only when it is a regular file, else read into a string
+struct FileText {
+  std::string owned;
+  void* map = nullptr;
+  size_t map_len = 0;
+  std::string_view view;
+  bool open(const char* path) {
+    const int fd = ::open(path, O_RDONLY);
+    if (fd < 0) return false;
+    struct stat st;
+    if (::fstat(fd, &st) == 0 && S_ISREG(st.st_mode) && st.st_size > 0) {
+      void* m = ::mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+      if (m != MAP_FAILED) {
+        map = m;
+        map_len = (size_t)st.st_size;
+        ::madvise(m, map_len, MADV_WILLNEED);
+        view = std::string_view(static_cast<const char*>(m), map_len);
+        ::close(fd);
+        return true;
+      }
+    }
+    char chunk[1 << 16];
+    ssize_t got;
+    while ((got = ::read(fd, chunk, sizeof chunk)) > 0) owned.append(chunk, (size_t)got);
+    ::close(fd);
+    if (got < 0) return false;
+    view = owned;
+    return true;
+  }
+  ~FileText() {
+    if (map) ::munmap(map, map_len);
+  }
+  FileText() = default;
+  FileText(const FileText&) = delete;
+  FileText& operator=(const FileText&) = delete;
+};
 
 // ARPH_TIMING=1: the phases of the packer and of the side-table builder on stderr (a development aid)
 struct PhaseClock {

@@ -61,27 +61,13 @@ int arph_parse_pdb(const char* path, arp_atom_record** out, int64_t* n) {
   arp::NvtxRange nvtx_("arph:parse_pdb");
   *out = nullptr;
   *n = 0;
-  FILE* f = std::fopen(path, "rb");
-  if (!f) {
+  // a regular file is mapped, not copied (its pages come in under the threads that parse them); a pipe is read in pieces
+  arp::FileText file;
+  if (!file.open(path)) {
     arp::last_error() = std::string("cannot open ") + path;
     return ARP_ERR_IO;
   }
-  std::string text;
-  {
-    // one read of the whole file when its size is known (regular files), 64 KB pieces otherwise (pipes)
-    long size = -1;
-    if (std::fseek(f, 0, SEEK_END) == 0) size = std::ftell(f);
-    std::rewind(f);
-    if (size > 0) {
-      text.resize((size_t)size);
-      const size_t got = std::fread(text.data(), 1, (size_t)size, f);
-      text.resize(got);
-    }
-    char chunk[1 << 16];
-    size_t got;
-    while ((got = std::fread(chunk, 1, sizeof chunk, f)) > 0) text.append(chunk, got);
-  }
-  std::fclose(f);
+  const std::string_view text = file.view;
 
   // Lines are independent except for the MODEL serial they inherit: the text is cut into one chunk per host thread at line
   // boundaries, every chunk is parsed on its own (records + the MODEL lines it saw), then the serials are carried across
