@@ -448,3 +448,29 @@ def test_packer_blocks_and_table_paths_give_one_result(ubq, bft, blocks, monkeyp
                 w = want[k]
                 same = (g[k] == w) if np.isscalar(w) else (np.array_equal(g[k].view(np.uint64), w.view(np.uint64)) if getattr(w, "dtype", None) == np.float64 else np.array_equal(g[k], w))
                 assert same, (name, k, blocks)
+
+
+def test_mmcif_reals_are_correctly_rounded(tmp_path):
+    """The reader's fast path for reals ([-]digits[.digits], <= 15 digits: one division of two exact doubles) and its
+    from_chars path give the correctly rounded double for every spelling: checked against Python's float()."""
+    rng = np.random.default_rng(3)
+    texts = ["0", "-0", "-0.000", "+1.5", "5.", ".5", "-.25", "000012.3400", "1e3", "-2.5E-3", "123456789012345", "0.123456789012345",
+             "1234567.89012345", "12345678901234567890", "0.1234567890123456789", "9007199254740993", "1.7976931348623157e308", "4.9e-324"]
+    for _ in range(3000):
+        digits = int(rng.integers(1, 19))
+        frac = int(rng.integers(0, digits + 1))
+        body = "".join(str(int(d)) for d in rng.integers(0, 10, size=digits))
+        t = body[: digits - frac] + ("." + body[digits - frac:] if frac or rng.random() < 0.2 else "")
+        if t in ("", "."):
+            t = "0"
+        texts.append(("-" if rng.random() < 0.5 else "") + t)
+    head = "data_X\nloop_\n_atom_site.group_PDB\n_atom_site.id\n_atom_site.type_symbol\n_atom_site.label_atom_id\n_atom_site.label_comp_id\n" \
+           "_atom_site.label_asym_id\n_atom_site.label_seq_id\n_atom_site.Cartn_x\n_atom_site.Cartn_y\n_atom_site.Cartn_z\n_atom_site.occupancy\n"
+    rows = [f"ATOM {k + 1} C CA ALA A {k + 1} {t} 1.0 -2.0 1.00" for k, t in enumerate(texts)]
+    p = tmp_path / "reals.cif"
+    p.write_text(head + "\n".join(rows) + "\n")
+    got = A.parse_cif(p)
+    assert len(got) == len(texts)
+    want = np.array([float(t) for t in texts])
+    assert np.array_equal(got["x"].view(np.uint64), want.view(np.uint64))
+    assert (got["y"] == 1.0).all() and (got["z"] == -2.0).all() and (got["occupancy"] == 1.0).all()
