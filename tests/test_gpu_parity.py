@@ -1,5 +1,6 @@
 """GPU parity: the CUDA path (through the C ABI) against the CPU oracle on the same inputs.  Needs a B200."""
 import ctypes
+import os
 import numpy as np
 import pytest
 
@@ -149,6 +150,30 @@ def test_config3_1m_atoms_bit_exact(ctx, bft):
     want = O.contacts(atoms.view(O.ATOM_DTYPE), "/", 0.1, 6.5, flags=O.FLAG_SKIP_LOAD_FILTER, num_threads=0)
     assert_tables_equal(got, want, "1M")
     assert got["pairs_in_cutoff"] == want["pairs_in_cutoff"] and got["pairs_classified"] == want["pairs_classified"]
+
+
+@pytest.mark.skipif(not os.environ.get("ARP_BIG_TESTS"), reason="8 M atoms against the oracle: a minute of host time; run with ARP_BIG_TESTS=1 "
+                    "(last run: profiles/r2c_big_oracle_diff.txt)")
+def test_8m_atoms_touching_copies_bit_exact(ctx, bft):
+    """The largest inputs diffed against the ORACLE, both screen modes: 6bft tiled 10x10x10 at config
+    3's pitch (8.18 M atoms; at that pitch the copies do not reach each other: every total is 1000 x the single structure)
+    and 8x8x8 at the dense pitch (4.19 M atoms, neighbouring copies interpenetrate: inter-copy contacts and clashes in
+    every direction).  Beyond these sizes the checks are properties (totals of config 5 = multiples of the single
+    structure, slab unions = the one-GPU rows)."""
+    from arpeggia_b200 import synth
+
+    for name, atoms in (("8.18M, config-3 pitch", synth.tile(bft, 10, 10, 10, synth.PITCH_6BFT)),
+                        ("4.19M, dense pitch", synth.tile(bft, 8, 8, 8, synth.PITCH_6BFT_DENSE))):
+        want = O.contacts(atoms.view(O.ATOM_DTYPE), "/", 0.1, 6.5, flags=O.FLAG_SKIP_LOAD_FILTER, num_threads=0)
+        got = ctx.contacts_table(atoms, "/", 0.1, 6.5, flags=2)
+        assert_tables_equal(got, want, name)
+        assert got["pairs_in_cutoff"] == want["pairs_in_cutoff"] and got["pairs_classified"] == want["pairs_classified"]
+        emit = ctx.contacts_table(atoms, "/", 0.1, 6.5, flags=2 | A.FLAG_NO_COUNTERS)
+        assert_tables_equal(emit, want, name + ", emit-radius screen")
+        per_copy = got["n_rows"] / (len(atoms) / len(bft))
+        print(f"{name}: {len(atoms)} atoms, {got['n_rows']} rows ({per_copy:.1f} per copy; 7236 for a lone copy), "
+              f"{got['pairs_in_cutoff']} pairs in cutoff: both screen modes equal to the oracle")
+        del want, got, emit
 
 
 def test_dense_overlapping_copies_clashes(ctx, bft):
