@@ -153,6 +153,7 @@ struct arp_ctx {
   DBuf<uint32_t> rcell_of, rrank_of, rcell_start, rperm, cations;
   DBuf<float> pos2;          // sorted positions + residue tags interleaved per slot pair (k_screen_atoms)
   DBuf<SlotCell> slot_cell;  // cell and boundary bits per sorted slot (k_screen_atoms)
+  DBuf<uint32_t> slot_atom;  // BUILD_BY_SLOT: the atom of every sorted slot (k_scatter_atoms -> k_build_records)
   DBuf<RecA> recA;           // counting mode
   DBuf<RecB> recB;
   DBuf<RecK> recK;

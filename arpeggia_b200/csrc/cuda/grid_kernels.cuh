@@ -357,6 +357,10 @@ __global__ void __launch_bounds__(256) k_expand_milli21(const unsigned long long
   if (attr16) attr[a] = attr16[a];
 }
 
+#ifndef BUILD_BY_SLOT
+#define BUILD_BY_SLOT 0  // 1: emit-radius mode builds its records in two kernels (k_scatter_atoms: slot -> atom; k_build_records)
+#endif
+
 // Pass 2 of the counting sort: write the cell-sorted records.  The atom that arrived first in a cell also
 // publishes the cell as a work item of the pair kernel.
 __global__ void __launch_bounds__(256)
@@ -366,7 +370,7 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
                 const uint32_t* __restrict__ atom_struct, const StructDesc* __restrict__ descs, const uint32_t* __restrict__ cell_of, const uint32_t* __restrict__ rank_of, const uint32_t* __restrict__ cell_start,
                 uint32_t n, double edge, double inv_edge, RecA* __restrict__ recA, RecB* __restrict__ recB, Item* __restrict__ items,
                 uint32_t* __restrict__ cations, Counters* __restrict__ ctr, RecK* __restrict__ recK, float* __restrict__ pos2,
-                SlotCell* __restrict__ slot_cell, const uint32_t* __restrict__ res_tag) {
+                SlotCell* __restrict__ slot_cell, const uint32_t* __restrict__ res_tag, uint32_t* __restrict__ slot_atom) {
   // slots in `items` / `cations` are reserved per BLOCK (shared-memory counters, one global atomicAdd each): the 110 000
   // same-address atomics of a one-per-cell reservation were 40 % of this kernel's stall samples
   __shared__ uint32_t s_items, s_cat, s_items_base, s_cat_base;
@@ -387,6 +391,10 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
   c = cell_of[a], r = rank_of[a];
   slot = cell_start[c] + r;
   ARP_CHK(ctr, slot < n && slot < cell_start[c + 1], 10);  // the atom's place lies inside its cell's slot range
+  if (slot_atom) {  // two-kernel build (BUILD_BY_SLOT): this pass only says which atom sits in which slot
+    slot_atom[slot] = a;
+    w = attr[a] & 0x7fffffffu;
+  } else {
   px = x[a], py = y[a], pz = z[a];
   RecA ra;
   ra.x = (float)(px - d.ox);
@@ -418,6 +426,7 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
     slot_cell[slot] = SlotCell{c, (ix > 0 ? 1u : 0u) | (ix + 1 < d.nx ? 2u : 0u) | (iy > 0 ? 4u : 0u) | (iy + 1 < d.ny ? 8u : 0u) | (iz + 1 < d.nz ? 16u : 0u)};
   } else {
     recA[slot] = ra;
+  }
   }
   }
   // the few atoms that can make a cation-pi contact (aromatic.rs:18) are listed for the ring kernel; the first arrival
@@ -480,6 +489,39 @@ k_scatter_atoms(const double* __restrict__ x, const double* __restrict__ y, cons
     // a compact list: k_screen hands the items out to warps
     items[s_items_base + i] = it;
   }
+}
+
+// Second pass of the two-kernel build of the emit-radius mode (BUILD_BY_SLOT): one thread per sorted SLOT gathers its atom's
+// inputs and writes the records -- RecB, RecK, pos2, SlotCell -- so that a warp's stores are contiguous (the one-kernel
+// build writes the same 72 bytes per atom from the atom's side: eight scattered stores per lane).
+__global__ void __launch_bounds__(256)
+k_build_records(const uint32_t* __restrict__ slot_atom, const double* __restrict__ x, const double* __restrict__ y, const double* __restrict__ z,
+                const uint32_t* __restrict__ attr, const uint32_t* __restrict__ chain_key, const uint32_t* __restrict__ res_ordinal,
+                const uint32_t* __restrict__ res_id, const uint32_t* __restrict__ res_chain_key, const uint32_t* __restrict__ res_res_ordinal,
+                const uint32_t* __restrict__ atom_struct, const StructDesc* __restrict__ descs, const uint32_t* __restrict__ cell_of,
+                uint32_t n, double inv_edge, RecB* __restrict__ recB, RecK* __restrict__ recK, float* __restrict__ pos2,
+                SlotCell* __restrict__ slot_cell, const uint32_t* __restrict__ res_tag) {
+  const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot >= n) return;
+  const uint32_t a = slot_atom[slot];
+  const StructDesc& d = descs[atom_struct ? atom_struct[a] : 0u];
+  const double px = x[a], py = y[a], pz = z[a];
+  const uint32_t w = attr[a] & 0x7fffffffu;
+  const uint32_t wa = w | (((w & ARP_ATTR_LIGAND) && (w & ARP_ATTR_ELEM_MASK) && !(w & ARP_ATTR_GHOST)) ? 0x80000000u : 0u);
+  const uint32_t rid = res_id[a];
+  const uint32_t ck = res_chain_key ? res_chain_key[rid] : chain_key[a];
+  const uint32_t ro = res_chain_key ? res_res_ordinal[rid] : res_ordinal[a];
+  RecB rb;
+  rb.x = px, rb.y = py, rb.z = pz;
+  rb.attr = wa;
+  rb.res_id = rid;
+  recB[slot] = rb;
+  recK[slot] = RecK{wa, ck, ro, a};
+  float* q = pos2 + 8u * (size_t)(slot >> 1) + (slot & 1u);
+  q[0] = (float)(px - d.ox), q[2] = (float)(py - d.oy), q[4] = (float)(pz - d.oz);
+  q[6] = __uint_as_float(res_tag[rid]);
+  const int ix = cell_coord(px, d.ox, inv_edge, d.nx), iy = cell_coord(py, d.oy, inv_edge, d.ny), iz = cell_coord(pz, d.oz, inv_edge, d.nz);
+  slot_cell[slot] = SlotCell{cell_of[a], (ix > 0 ? 1u : 0u) | (ix + 1 < d.nx ? 2u : 0u) | (iy > 0 ? 4u : 0u) | (iy + 1 < d.ny ? 8u : 0u) | (iz + 1 < d.nz ? 16u : 0u)};
 }
 
 __global__ void __launch_bounds__(256)
