@@ -617,3 +617,49 @@ def test_arrays_of_one_host_arena_travel_as_one_copy(ctx, bft, ubq):
             assert copies == 1 and copies_plain >= 1, (copies, copies_plain)  # (the packer's own vectors may happen to be neighbours too)
         finally:
             L.arp_host_free(block)
+
+
+def test_device_resident_and_mixed_inputs(ctx, bft):
+    """arp_structure arrays may live in device memory (a caller that produced them on the GPU), or some on the host and
+    some on the device: never merged into a host copy, same rows."""
+    import ctypes as C
+
+    import torch
+
+    from arpeggia_b200 import _lib as AL
+
+    L = AL.lib()
+    prm = AL.Params(0.1, 6.5, 0, 0)
+    key = ["from", "to", "label", "distance"]
+    p = A.Packed(bft)
+    src = p.structure
+
+    def rows_of(sp):
+        rp = C.POINTER(AL.Result)()
+        AL.check(L.arp_contacts(ctx._h, sp, C.byref(prm), C.byref(rp)), ctx._h)
+        v = np.frombuffer((C.c_char * (rp.contents.n_rows * 16)).from_address(rp.contents.rows), dtype=A.ROW_DTYPE).copy()
+        L.arp_result_free(ctx._h, rp)
+        return np.sort(v, order=key)
+
+    want = rows_of(p.structure_ptr)
+    n, nr, ng, nh = src.n_atoms, src.n_residues, src.n_rings, src.n_h
+    lens = {"x": 8 * n, "y": 8 * n, "z": 8 * n, "attr": 4 * n, "res_chain_key": 4 * nr, "res_res_ordinal": 4 * nr, "res_atom_begin": 4 * (nr + 1),
+            "res_h_begin": 4 * (nr + 1), "h_x": 8 * nh, "h_y": 8 * nh, "h_z": 8 * nh, "res_cb": 4 * nr, "res_sg": 4 * nr, "ring_center": 24 * ng,
+            "ring_normal": 24 * ng, "ring_attr": 4 * ng, "ring_chain_key": 4 * ng, "ring_res_ordinal": 4 * ng, "res_tag": 4 * nr}
+    for on_device in (set(lens), {"x", "z", "attr", "res_tag", "ring_center"}):
+        dst = AL.Structure()
+        for name, _ in AL.Structure._fields_:
+            if name.startswith("n_") or name.startswith("bbox_") or name == "has_bbox":
+                setattr(dst, name, getattr(src, name))
+        keep = []
+        for name, nbytes in lens.items():
+            ptr = C.cast(getattr(src, name), C.c_void_p)
+            if name in on_device and nbytes:
+                host = np.frombuffer((C.c_char * nbytes).from_address(ptr.value), dtype=np.uint8)
+                t = torch.from_numpy(host.copy()).to("cuda:0")
+                keep.append(t)
+                ptr = C.c_void_p(t.data_ptr())
+            setattr(dst, name, C.cast(ptr, dict(AL.Structure._fields_)[name]))
+        torch.cuda.synchronize()
+        got = rows_of(C.pointer(dst))
+        assert np.array_equal(got, want), sorted(on_device)[:3]
