@@ -617,6 +617,27 @@ def test_arrays_of_one_host_arena_travel_as_one_copy(ctx, bft, ubq):
             assert copies == 1 and copies_plain >= 1, (copies, copies_plain)  # (the packer's own vectors may happen to be neighbours too)
         finally:
             L.arp_host_free(block)
+        # every array in a page-locked allocation of its own: such allocations often lie back to back in the address space,
+        # but one copy must not run from one into the next (cudaMemcpyAsync refuses it) -- the upload asks for the extent of
+        # the allocation before it merges
+        blocks = []
+        try:
+            dst = AL.Structure()
+            for name, _ in AL.Structure._fields_:
+                if name.startswith("n_") or name.startswith("bbox_") or name == "has_bbox" or name == "xyz_milli21_origin":
+                    setattr(dst, name, getattr(src, name))
+            for name in names:
+                b = C.c_void_p()
+                AL.check(L.arp_host_alloc(C.byref(b), max(lens[name], 1)))
+                blocks.append(b)
+                if lens[name]:
+                    C.memmove(b, C.cast(getattr(src, name), C.c_void_p), lens[name])
+                setattr(dst, name, C.cast(b, dict(AL.Structure._fields_)[name]))
+            got, copies = rows_of(C.pointer(dst))
+            assert np.array_equal(got, want) and copies >= 2, (milli, copies)
+        finally:
+            for b in blocks:
+                L.arp_host_free(b)
 
 
 def test_device_resident_and_mixed_inputs(ctx, bft):
