@@ -684,3 +684,34 @@ def test_device_resident_and_mixed_inputs(ctx, bft):
         torch.cuda.synchronize()
         got = rows_of(C.pointer(dst))
         assert np.array_equal(got, want), sorted(on_device)[:3]
+
+
+def test_cli_contacts_writes_the_table(ubq_path, tmp_path, caplog):
+    """`python -m arpeggia_b200 contacts` (the flag surface of src/cli/contacts.rs:9-52): the four output formats hold the
+    532 rows of 1ubq; an extension in --filename is replaced like Path::with_extension; a missing input is logged, not raised."""
+    import json
+
+    import pyarrow.csv as pacsv
+    import pyarrow.parquet as pq
+
+    from arpeggia_b200.__main__ import main
+
+    want = O.contacts(A.parse_pdb(ubq_path).view(O.ATOM_DTYPE))
+    out = tmp_path / "out"
+    assert main(["contacts", "-i", str(ubq_path), "-o", str(out)]) == 0
+    t = pacsv.read_csv(out / "contacts.csv")
+    assert t.column_names == A.COLUMNS and t.num_rows == want["n_rows"] == 532
+    assert t["from_atomi"].to_pylist() == want["from_atomi"].tolist() and t["interaction"].to_pylist() == want["interaction"].tolist()
+    assert main(["contacts", "-i", str(ubq_path), "-o", str(out), "-t", "parquet", "-f", "table.old", "-g", "/", "-d", "6.5", "-c", "0.1", "-j", "2"]) == 0
+    t = pq.read_table(out / "table.parquet")  # "table.old" -> "table.parquet"
+    assert t.num_rows == 532 and t["sc_dihedral"].null_count == int((~want["sc_valid"]).sum())
+    assert np.array_equal(t["distance"].to_numpy().view(np.uint32), want["distance"].view(np.uint32))
+    assert main(["contacts", "-i", str(ubq_path), "-o", str(out), "-t", "json", "--ignore-zero-occupancy"]) == 0
+    rows = json.loads((out / "contacts.json").read_text())
+    assert len(rows) == 532 and rows[0]["from_resn"] == want["from_resn"][0] and list(rows[0]) == A.COLUMNS
+    assert main(["contacts", "-i", str(ubq_path), "-o", str(out), "-t", "ndjson"]) == 0
+    lines = (out / "contacts.ndjson").read_text().splitlines()
+    assert len(lines) == 532 and json.loads(lines[-1])["to_atomi"] == int(want["to_atomi"][-1])
+    with caplog.at_level("ERROR"):
+        assert main(["contacts", "-i", str(tmp_path / "nope.pdb"), "-o", str(out)]) == 0  # cli/contacts.rs:58-64: logged, no panic
+    assert not (out / "nope.csv").exists()
