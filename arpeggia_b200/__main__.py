@@ -38,8 +38,13 @@ def main(argv=None) -> int:
         log.warning("No hydrogen atoms found in the structure. This may affect the accuracy of the results.")
     df = contacts(inp, a.groups, a.vdw_comp, a.dist_cutoff, a.ignore_zero_occupancy, a.num_threads, device=a.device)
     os.makedirs(out_dir, exist_ok=True)
-    inter = df["interaction"].to_pylist() if hasattr(df["interaction"], "to_pylist") else list(df["interaction"])
-    n_clash = sum(1 for v in inter if v == "StericClash")
+    col = df["interaction"]
+    if hasattr(col, "to_pylist"):  # pyarrow: counted in Arrow's C++, no Python list of a million strings
+        import pyarrow.compute as pc
+
+        n_clash = int(pc.sum(pc.equal(col, "StericClash")).as_py() or 0)
+    else:  # polars
+        n_clash = int((col == "StericClash").sum())
     if n_clash:  # cli/contacts.rs:116-132
         log.warning("Found %d steric %s", n_clash, "clash" if n_clash == 1 else "clashes")
     # Path::with_extension (cli/contacts.rs:111-113): an extension already in the name is REPLACED, not appended to
