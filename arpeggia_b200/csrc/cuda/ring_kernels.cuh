@@ -58,7 +58,10 @@ __device__ __forceinline__ uint32_t runs9_slot(const Runs9& r, uint32_t j, uint3
 // atoms that are positively ionizable by residue name can give a row (aromatic.rs:18) and a row needs
 // dist <= 4.5 < ring-grid edge, so walking the few cations and looking for rings around them visits exactly the pairs
 // that can produce a row -- about 20x fewer tests than sweeping all atoms around all rings.
-__global__ void __launch_bounds__(256) k_rings(const RingArgs R, const DevParams P) {
+#ifndef RINGS_MIN_BLOCKS
+#define RINGS_MIN_BLOCKS 4
+#endif
+__global__ void __launch_bounds__(256, RINGS_MIN_BLOCKS) k_rings(const RingArgs R, const DevParams P) {
   const int lane = threadIdx.x & 15;
   const uint32_t hm = (threadIdx.x & 16) ? 0xffff0000u : 0x0000ffffu;  // the half warps of a warp run independently
   const uint32_t groups = (gridDim.x * blockDim.x) >> 4;
