@@ -8,6 +8,8 @@ import arpeggia_b200 as A
 from oracle import oracle as O
 from tests.util import assert_tables_equal
 
+ROOT = __import__("pathlib").Path(__file__).resolve().parents[1]
+
 pytestmark = pytest.mark.gpu
 
 
@@ -701,6 +703,10 @@ def test_cli_contacts_writes_the_table(ubq_path, tmp_path, caplog):
     assert main(["contacts", "-i", str(ubq_path), "-o", str(out)]) == 0
     t = pacsv.read_csv(out / "contacts.csv")
     assert t.column_names == A.COLUMNS and t.num_rows == want["n_rows"] == 532
+    try:
+        import polars  # noqa: F401  (with polars the file is polars' own; the golden pins this repository's writer)
+    except ImportError:
+        assert (out / "contacts.csv").read_text() == (ROOT / "tests" / "golden" / "1ubq_contacts.csv").read_text()
     assert t["from_atomi"].to_pylist() == want["from_atomi"].tolist() and t["interaction"].to_pylist() == want["interaction"].tolist()
     assert main(["contacts", "-i", str(ubq_path), "-o", str(out), "-t", "parquet", "-f", "table.old", "-g", "/", "-d", "6.5", "-c", "0.1", "-j", "2"]) == 0
     t = pq.read_table(out / "table.parquet")  # "table.old" -> "table.parquet"

@@ -10,6 +10,8 @@ from arpeggia_b200 import _lib
 from oracle import oracle as O
 from tests.util import assert_tables_equal
 
+ROOT = __import__("pathlib").Path(__file__).resolve().parents[1]
+
 
 @pytest.fixture(scope="module")
 def ubq(ubq_path):
@@ -474,3 +476,19 @@ def test_mmcif_reals_are_correctly_rounded(tmp_path):
     want = np.array([float(t) for t in texts])
     assert np.array_equal(got["x"].view(np.uint64), want.view(np.uint64))
     assert (got["y"] == 1.0).all() and (got["z"] == -2.0).all() and (got["occupancy"] == 1.0).all()
+
+
+def test_golden_csv_of_1ubq(ubq):
+    """tests/golden/1ubq_contacts.csv = the oracle's table of 1ubq (pinned by the reference's golden values) through the CLI's
+    CSV writer, in the layout of polars' CsvWriter: bare header, quotes only where needed, "2.0" not "2", nulls empty."""
+    from arpeggia_b200.frame import csv_text, to_arrow
+
+    golden = (ROOT / "tests" / "golden" / "1ubq_contacts.csv").read_text()
+    assert csv_text(to_arrow(O.contacts(ubq.view(O.ATOM_DTYPE)))) == golden
+    lines = golden.splitlines()
+    assert len(lines) == 533 and lines[0].split(",") == A.COLUMNS and '"' not in golden
+    import pyarrow as pa
+
+    t = pa.table({"s": pa.array(["x", "y,z", None, 'q"t'], type=pa.large_string()), "f": pa.array([1.5, None, 2.0, 1e-7], type=pa.float32()),
+                  "i": pa.array([1, 2, None, 4], type=pa.int32())})
+    assert csv_text(t) == 's,f,i\nx,1.5,1\n"y,z",,2\n,2.0,\n"q""t",1e-7,4\n'
